@@ -1,0 +1,51 @@
+"""Shared mesh/query generators for the tests (the BASELINE.json configs, scaled down)."""
+import numpy as np
+
+
+def cobb_douglas(x):
+    """f = prod x_i^alpha_i, alpha = (0.3, 0.6, 0.2, 0.1)[:d]  (src/delaunay_2_test.cpp:32-50)."""
+    x = np.asarray(x, dtype=np.float64)
+    a = np.array([0.3, 0.6, 0.2, 0.1, 0.05, 0.05])[: x.shape[-1]]
+    return np.prod(np.power(x, a), axis=-1)
+
+
+def linspace_ref(first, last, n):
+    """the reference's linspace: first + i*step (README.md:37-42)."""
+    step = (last - first) / (n - 1)
+    return np.array([first + i * step for i in range(n)])
+
+
+def grid_mesh(lo=0.0, hi=5.0, n=10):
+    """config 1: n x n grid, inserted i-outer/j-inner (README.md:55-60); every cell split by the
+    diagonal (x1,y0)-(x0,y1), the tie-break CGAL's perturbed in-circle test produces
+    (SURVEY.md appendix B.2 / C.1).  Returns coords, f, triangles (ccw)."""
+    g = linspace_ref(lo, hi, n)
+    coords = np.array([[g[i], g[j]] for i in range(n) for j in range(n)])
+    vid = lambda i, j: i * n + j
+    tris = []
+    for i in range(n - 1):
+        for j in range(n - 1):
+            a, b, c, d = vid(i, j), vid(i + 1, j), vid(i, j + 1), vid(i + 1, j + 1)
+            tris.append([a, b, c])   # A(x0,y0) B(x1,y0) C(x0,y1)
+            tris.append([b, d, c])   # B D(x1,y1) C      -> diagonal B-C
+    return coords, cobb_douglas(coords), np.array(tris, dtype=np.int32)
+
+
+def grid_queries(lo=0.0, hi=5.0, n=20):
+    q = linspace_ref(lo, hi, n)
+    return np.array([[q[i], q[j]] for i in range(n) for j in range(n)])
+
+
+def scipy_mesh(points):
+    """Delaunay triangulation of `points` through Qhull: (simplices int32, neighbors int32).
+    scipy's convention matches the C ABI: neighbour k is opposite vertex k, -1 = hull."""
+    from scipy.spatial import Delaunay
+    tri = Delaunay(points)
+    return tri.simplices.astype(np.int32), tri.neighbors.astype(np.int32)
+
+
+def random_mesh(dim, nv, seed):
+    rng = np.random.default_rng(seed)
+    pts = rng.random((nv, dim))
+    sv, sn = scipy_mesh(pts)
+    return pts, cobb_douglas(pts), sv, sn
