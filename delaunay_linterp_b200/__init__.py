@@ -1,0 +1,11 @@
+"""delaunay_linterp_b200 -- B200-native batched evaluation of Delaunay piecewise-linear interpolants.
+
+Drop-in for the interp hot path of rncarpio/delaunay_linterp (locate -> barycentric -> gather),
+behind a C ABI (include/dli.h).  The CUDA library is required; there is no CPU fallback.
+"""
+from ._capi import (DliError, LIB_PATH, STATUS_NO_MESH, STATUS_OK, STATUS_OUTSIDE_NAN, STATUS_OUTSIDE_PROJECTED,
+                    STATUS_STEP_LIMIT, lib)
+from .mesh import Mesh, debug_orient
+
+__all__ = ["Mesh", "debug_orient", "DliError", "lib", "LIB_PATH", "STATUS_OK", "STATUS_OUTSIDE_PROJECTED",
+           "STATUS_OUTSIDE_NAN", "STATUS_STEP_LIMIT", "STATUS_NO_MESH"]

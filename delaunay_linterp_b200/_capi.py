@@ -1,0 +1,106 @@
+"""ctypes binding of the C ABI in include/dli.h (libdli.so).
+
+There is no CPU fallback: if the library is missing, or no CUDA device is present when a mesh is
+created, an error is raised.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdli.so")
+
+DLI_MAX_DIM = 6
+DLI_MESH_HEADER_WORDS = 16
+
+STATUS_OK, STATUS_OUTSIDE_PROJECTED, STATUS_OUTSIDE_NAN, STATUS_STEP_LIMIT, STATUS_NO_MESH = 0, 1, 2, 3, 4
+
+
+class DliError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("dli error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Options(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_int32),
+        ("device", C.c_int32),
+        ("hint_cells_per_simplex", C.c_float),
+        ("max_walk_steps", C.c_int32),
+        ("sort_queries", C.c_int32),
+        ("epilogue", C.c_int32),
+        ("threads_per_block", C.c_int32),
+        ("reserved", C.c_int32 * 9),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("queries", C.c_int64),
+        ("walk_steps", C.c_int64),
+        ("max_walk_steps", C.c_int64),
+        ("exact_fallbacks", C.c_int64),
+        ("outside", C.c_int64),
+        ("kernel_launches", C.c_int64),
+    ]
+
+
+# every symbol include/dli.h declares: (name, restype, argtypes)
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_bp = C.POINTER(C.c_uint8)
+_vp = C.c_void_p
+SYMBOLS = [
+    ("dli_options_init", None, [C.POINTER(Options)]),
+    ("dli_mesh_create", C.c_int, [C.c_int, C.c_int64, _vp, _vp, C.c_int64, _vp, _vp, C.POINTER(Options), C.POINTER(_vp)]),
+    ("dli_mesh_set_values", C.c_int, [_vp, _vp]),
+    ("dli_mesh_destroy", None, [_vp]),
+    ("dli_mesh_dim", C.c_int, [_vp]),
+    ("dli_mesh_num_vertices", C.c_int64, [_vp]),
+    ("dli_mesh_num_simplices", C.c_int64, [_vp]),
+    ("dli_mesh_device_bytes", C.c_int64, [_vp]),
+    ("dli_mesh_get_simplices", C.c_int, [_vp, _vp, _vp]),
+    ("dli_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_locate", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp]),
+    ("dli_simplex_error_count", C.c_int64, [_vp]),
+    ("dli_simplex_error_prepare", C.c_int, [_vp, _vp, _vp, _vp]),
+    ("dli_simplex_error_finish", C.c_int, [_vp, C.c_int64, _vp, _vp]),
+    ("dli_mesh_header", C.c_int, [_vp, C.POINTER(C.c_int64)]),
+    ("dli_mesh_create_from_header", C.c_int, [C.POINTER(C.c_int64), C.POINTER(Options), C.POINTER(_vp)]),
+    ("dli_mesh_num_buffers", C.c_int, [_vp]),
+    ("dli_mesh_buffer", C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_int64)]),
+    ("dli_mesh_get_grid_params", C.c_int, [_vp, _vp]),
+    ("dli_mesh_set_grid_params", C.c_int, [_vp, _vp]),
+    ("dli_mesh_collect_stats", C.c_int, [_vp, C.c_int]),
+    ("dli_mesh_get_stats", C.c_int, [_vp, C.POINTER(Stats)]),
+    ("dli_debug_orient", C.c_int, [C.c_int, C.c_int64, _vp, _vp, _vp]),
+    ("dli_debug_orient_host", C.c_int, [C.c_int, C.c_int64, _vp, _vp]),
+    ("dli_last_error", C.c_char_p, []),
+    ("dli_device_count", C.c_int, []),
+]
+
+_lib = None
+
+
+def lib():
+    """Loads libdli.so (building it first if the sources are newer and nvcc is available)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "delaunay_linterp_b200: %s is missing. Build it with `python -m delaunay_linterp_b200.build` "
+            "(needs nvcc); there is no CPU fallback." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    for name, res, args in SYMBOLS:
+        fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc < 0:
+        raise DliError(rc, lib().dli_last_error().decode("utf-8", "replace"))
+    return rc

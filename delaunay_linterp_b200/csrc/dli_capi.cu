@@ -1,0 +1,821 @@
+// dli_capi.cu -- the C ABI (include/dli.h): flattener, hint-grid build, batched interp / locate
+// dispatch (device-pointer and host-pointer paths), error evaluator, replication support.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "dli_kernels.cuh"
+
+using namespace dli;
+
+// ---------------------------------------------------------------------------------------------
+// error handling
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                      \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess) {                                                                          \
+      char b_[512];                                                                                   \
+      snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return fail(DLI_ERR_CUDA, b_);                                                                  \
+    }                                                                                                 \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (dev >= 0 && dev != prev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// mesh object
+// ---------------------------------------------------------------------------------------------
+struct dli_mesh {
+  int dim = 0;
+  int device = 0;
+  int64_t nv = 0, ns = 0;
+  int32_t nh = 0;
+  dli_options opt{};
+  int vs = 0, ss = 0;  // record strides (doubles / ints)
+  // host copies of the canonical connectivity (error items, get_simplices)
+  std::vector<int32_t> h_sv, h_sn;
+  // device buffers
+  double *d_vrec = nullptr;
+  int32_t *d_srec = nullptr;
+  int4 *d_hull = nullptr;
+  int32_t *d_hint = nullptr;
+  GridView grid{};
+  int max_steps = 0, fast_steps = 0;
+  // error items (lazy)
+  std::mutex mu;
+  bool items_ready = false;
+  int64_t n_items = 0;
+  std::vector<int32_t> h_item_simplex, h_item_verts;
+  int32_t *d_item_verts = nullptr;
+  // stats
+  bool collect_stats = false;
+  unsigned long long *d_stats = nullptr;
+  mutable dli_stats last{};
+};
+
+static void mesh_free(dli_mesh *m) {
+  if (!m) return;
+  DeviceGuard g(m->device);
+  cudaFree(m->d_vrec);
+  cudaFree(m->d_srec);
+  cudaFree(m->d_hull);
+  cudaFree(m->d_hint);
+  cudaFree(m->d_item_verts);
+  cudaFree(m->d_stats);
+  delete m;
+}
+
+extern "C" void dli_options_init(dli_options *o) {
+  if (!o) return;
+  memset(o, 0, sizeof(*o));
+  o->struct_size = (int32_t)sizeof(dli_options);
+  o->device = -1;
+  o->hint_cells_per_simplex = 0.f;
+  o->max_walk_steps = 0;
+  o->sort_queries = 0;
+  o->epilogue = 0;
+  o->threads_per_block = 0;
+}
+
+extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
+
+extern "C" int dli_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+// ---------------------------------------------------------------------------------------------
+// flattener (host part)
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct FacetRec {
+  int32_t key[DLI_MAX_DIM];
+  int32_t s, slot;
+};
+
+int derive_neighbors(int d, int64_t ns, const int32_t *sv, int32_t *sn) {
+  const int k = d + 1;
+  std::vector<FacetRec> fr((size_t)ns * k);
+  for (int64_t s = 0; s < ns; s++)
+    for (int slot = 0; slot < k; slot++) {
+      FacetRec &r = fr[(size_t)s * k + slot];
+      int c = 0;
+      for (int j = 0; j < k; j++)
+        if (j != slot) r.key[c++] = sv[s * k + j];
+      std::sort(r.key, r.key + d);
+      r.s = (int32_t)s;
+      r.slot = slot;
+    }
+  auto less = [d](const FacetRec &a, const FacetRec &b) {
+    for (int i = 0; i < d; i++)
+      if (a.key[i] != b.key[i]) return a.key[i] < b.key[i];
+    return false;
+  };
+  auto same = [d](const FacetRec &a, const FacetRec &b) {
+    for (int i = 0; i < d; i++)
+      if (a.key[i] != b.key[i]) return false;
+    return true;
+  };
+  std::sort(fr.begin(), fr.end(), less);
+  for (size_t i = 0; i < fr.size(); i++) sn[(size_t)fr[i].s * k + fr[i].slot] = -1;
+  for (size_t i = 0; i + 1 < fr.size();) {
+    if (same(fr[i], fr[i + 1])) {
+      if (i + 2 < fr.size() && same(fr[i], fr[i + 2])) return -1;  // facet shared by 3 simplices
+      sn[(size_t)fr[i].s * k + fr[i].slot] = fr[i + 1].s;
+      sn[(size_t)fr[i + 1].s * k + fr[i + 1].slot] = fr[i].s;
+      i += 2;
+    } else {
+      i += 1;
+    }
+  }
+  return 0;
+}
+
+template <int D>
+void launch_hint_build(dli_mesh *m, cudaStream_t st) {
+  int threads = 128;
+  k_hint_raster<D><<<(unsigned)((m->ns + threads - 1) / threads), threads, 0, st>>>(
+      m->grid, (int)m->ns, m->d_vrec, m->vs, m->d_srec, m->ss, m->d_hint);
+}
+template <int D>
+void launch_hint_dilate(dli_mesh *m, unsigned int *d_rem, cudaStream_t st) {
+  int threads = 256;
+  k_hint_dilate<D><<<(unsigned)((m->grid.cells + threads - 1) / threads), threads, 0, st>>>(m->grid, m->d_hint, d_rem);
+}
+
+int build_hint_grid(dli_mesh *m, const double *coords) {
+  const int d = m->dim;
+  // bounding box of the vertices
+  double lo[DLI_MAX_DIM], hi[DLI_MAX_DIM];
+  for (int k = 0; k < d; k++) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+  for (int64_t v = 0; v < m->nv; v++)
+    for (int k = 0; k < d; k++) {
+      double x = coords[v * d + k];
+      if (x < lo[k]) lo[k] = x;
+      if (x > hi[k]) hi[k] = x;
+    }
+  float cps = m->opt.hint_cells_per_simplex;
+  if (!(cps > 0.f)) cps = (d == 2) ? 2.0f : 1.0f;
+  double target = std::max(1.0, (double)m->ns * cps);
+  int g = (int)std::ceil(std::pow(target, 1.0 / d));
+  g = std::max(1, std::min(g, d == 2 ? 16384 : (d == 3 ? 1024 : 128)));
+  m->grid.cells = 1;
+  for (int k = 0; k < d; k++) {
+    double ext = hi[k] - lo[k];
+    if (!(ext > 0.0) || !std::isfinite(ext)) ext = 1.0;
+    m->grid.g[k] = g;
+    m->grid.o[k] = lo[k];
+    m->grid.cell[k] = ext / g;
+    m->grid.ic[k] = g / ext;
+    m->grid.cells *= g;
+  }
+  CU(cudaMalloc(&m->d_hint, sizeof(int32_t) * (size_t)m->grid.cells));
+  CU(cudaMemset(m->d_hint, 0xff, sizeof(int32_t) * (size_t)m->grid.cells));
+  unsigned int *d_rem = nullptr;
+  CU(cudaMalloc(&d_rem, sizeof(unsigned int)));
+  cudaStream_t st = 0;
+  switch (d) {
+    case 2: launch_hint_build<2>(m, st); break;
+    case 3: launch_hint_build<3>(m, st); break;
+    case 4: launch_hint_build<4>(m, st); break;
+  }
+  CU(cudaGetLastError());
+  // dilation rounds until no empty cell is left (or no progress)
+  unsigned int prev = 0xffffffffu;
+  for (int round = 0; round < 4 * g + 8; round++) {
+    CU(cudaMemsetAsync(d_rem, 0, sizeof(unsigned int), st));
+    switch (d) {
+      case 2: launch_hint_dilate<2>(m, d_rem, st); break;
+      case 3: launch_hint_dilate<3>(m, d_rem, st); break;
+      case 4: launch_hint_dilate<4>(m, d_rem, st); break;
+    }
+    unsigned int rem = 0;
+    CU(cudaMemcpy(&rem, d_rem, sizeof rem, cudaMemcpyDeviceToHost));
+    if (rem == 0) break;
+    if (rem == prev && round > 2) {  // nothing rasterised at all (tiny mesh): start everywhere from simplex 0
+      break;
+    }
+    prev = rem;
+  }
+  k_hint_fill_rest<<<(unsigned)((m->grid.cells + 255) / 256), 256, 0, st>>>(m->grid.cells, m->d_hint, 0);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(st));
+  cudaFree(d_rem);
+  return DLI_OK;
+}
+
+}  // namespace
+
+static int mesh_alloc_common(dli_mesh *m) {
+  const int d = m->dim;
+  if (d == 2) { m->vs = 4; m->ss = 8; }
+  else if (d == 3) { m->vs = RecD<3>::VS; m->ss = RecD<3>::SS; }
+  else { m->vs = RecD<4>::VS; m->ss = RecD<4>::SS; }
+  m->max_steps = m->opt.max_walk_steps > 0 ? m->opt.max_walk_steps : (int)std::min<int64_t>(m->ns + 16, 0x7fffffff);
+  m->fast_steps = std::min(m->max_steps, d == 2 ? 24 : 32);
+  CU(cudaMalloc(&m->d_vrec, sizeof(double) * (size_t)std::max<int64_t>(m->nv, 1) * m->vs));
+  CU(cudaMalloc(&m->d_srec, sizeof(int32_t) * (size_t)std::max<int64_t>(m->ns, 1) * m->ss));
+  if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
+  CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
+  CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
+  // keep stream-ordered allocations cached between calls
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, m->device) == cudaSuccess) {
+    unsigned long long thr = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  return DLI_OK;
+}
+
+static int resolve_options(const dli_options *opt, dli_options *out) {
+  dli_options_init(out);
+  if (opt) {
+    size_t sz = opt->struct_size > 0 ? std::min<size_t>(opt->struct_size, sizeof(dli_options)) : sizeof(dli_options);
+    memcpy(out, opt, sz);
+    out->struct_size = (int32_t)sizeof(dli_options);
+  }
+  return DLI_OK;
+}
+
+extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const double *f, int64_t ns,
+                               const int32_t *sv_in, const int32_t *sn_in, const dli_options *opt, dli_mesh **out) {
+  if (!out) return fail(DLI_ERR_ARG, "dli_mesh_create: out is NULL");
+  *out = nullptr;
+  if (dim < 2 || dim > 4) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_create: dim must be 2, 3 or 4");
+  if (nv < 0 || ns < 0 || nv > 0x7fffffff || ns > 0x7ffffff0) return fail(DLI_ERR_ARG, "dli_mesh_create: bad sizes");
+  if ((nv > 0 && (!coords || !f)) || (ns > 0 && !sv_in)) return fail(DLI_ERR_ARG, "dli_mesh_create: NULL array");
+  const int d = dim, k = dim + 1;
+  dli_mesh *m = new dli_mesh;
+  m->dim = d; m->nv = nv; m->ns = ns;
+  resolve_options(opt, &m->opt);
+  int ndev = dli_device_count();
+  if (ndev <= 0) { delete m; return fail(DLI_ERR_CUDA, "dli_mesh_create: no CUDA device available (this library has no CPU fallback)"); }
+  if (m->opt.device >= 0) m->device = m->opt.device;
+  else if (cudaGetDevice(&m->device) != cudaSuccess) { delete m; return fail(DLI_ERR_CUDA, "cudaGetDevice failed"); }
+  DeviceGuard guard(m->device);
+  if (!guard.ok) { delete m; return fail(DLI_ERR_CUDA, "dli_mesh_create: cannot select device"); }
+
+  // ---- connectivity: copy, derive neighbours, canonical orientation
+  m->h_sv.assign(sv_in, sv_in + (size_t)ns * k);
+  m->h_sn.resize((size_t)ns * k);
+  for (size_t i = 0; i < m->h_sv.size(); i++)
+    if (m->h_sv[i] < 0 || m->h_sv[i] >= nv) { delete m; return fail(DLI_ERR_MESH, "dli_mesh_create: vertex index out of range"); }
+  if (sn_in) {
+    memcpy(m->h_sn.data(), sn_in, sizeof(int32_t) * (size_t)ns * k);
+    for (size_t i = 0; i < m->h_sn.size(); i++)
+      if (m->h_sn[i] >= ns) { delete m; return fail(DLI_ERR_MESH, "dli_mesh_create: neighbour index out of range"); }
+      else if (m->h_sn[i] < 0) m->h_sn[i] = -1;
+  } else if (derive_neighbors(d, ns, m->h_sv.data(), m->h_sn.data()) != 0) {
+    delete m;
+    return fail(DLI_ERR_MESH, "dli_mesh_create: a facet is shared by more than two simplices");
+  }
+  for (int64_t s = 0; s < ns; s++) {
+    double pts[(DLI_MAX_DIM + 1) * DLI_MAX_DIM];
+    for (int j = 0; j < k; j++)
+      for (int c = 0; c < d; c++) pts[j * d + c] = coords[(size_t)m->h_sv[s * k + j] * d + c];
+    int o = orient_host(d, pts);
+    if (o == 0) {
+      char b[160];
+      snprintf(b, sizeof b, "dli_mesh_create: simplex %lld is degenerate (zero volume)", (long long)s);
+      delete m;
+      return fail(DLI_ERR_MESH, b);
+    }
+    if (o < 0) {  // exchange slots 0 and 1 (vertices and the neighbours opposite them)
+      std::swap(m->h_sv[s * k], m->h_sv[s * k + 1]);
+      std::swap(m->h_sn[s * k], m->h_sn[s * k + 1]);
+    }
+  }
+
+  // ---- 2D hull edge table
+  std::vector<int4> hull;
+  std::vector<int32_t> enc_sn(m->h_sn);  // device encoding of neighbours
+  if (d == 2) {
+    std::vector<int32_t> from((size_t)nv, -1), to((size_t)nv, -1);
+    for (int64_t s = 0; s < ns; s++)
+      for (int j = 0; j < 3; j++)
+        if (m->h_sn[s * 3 + j] < 0) {
+          int32_t h = (int32_t)hull.size();
+          hull.push_back(make_int4((int)s, j, -1, -1));
+          from[m->h_sv[s * 3 + (j + 1) % 3]] = h;
+          to[m->h_sv[s * 3 + (j + 2) % 3]] = h;
+          enc_sn[s * 3 + j] = ~h;
+        }
+    for (auto &h : hull) {
+      int32_t P = m->h_sv[(size_t)h.x * 3 + (h.y + 1) % 3], Q = m->h_sv[(size_t)h.x * 3 + (h.y + 2) % 3];
+      h.z = from[Q];
+      h.w = to[P];
+    }
+    m->nh = (int32_t)hull.size();
+  }
+
+  int rc = mesh_alloc_common(m);
+  if (rc != DLI_OK) { mesh_free(m); return rc; }
+
+  // ---- pack records
+  {
+    std::vector<double> vrec((size_t)std::max<int64_t>(nv, 1) * m->vs, 0.0);
+    for (int64_t v = 0; v < nv; v++) {
+      for (int c = 0; c < d; c++) vrec[(size_t)v * m->vs + c] = coords[v * d + c];
+      vrec[(size_t)v * m->vs + d] = f[v];
+    }
+    std::vector<int32_t> srec((size_t)std::max<int64_t>(ns, 1) * m->ss, 0);
+    for (int64_t s = 0; s < ns; s++)
+      for (int j = 0; j < k; j++) {
+        srec[(size_t)s * m->ss + j] = m->h_sv[s * k + j];
+        srec[(size_t)s * m->ss + k + j] = enc_sn[s * k + j];
+      }
+    cudaError_t e = cudaMemcpy(m->d_vrec, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(m->d_srec, srec.data(), sizeof(int32_t) * srec.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && d == 2 && !hull.empty())
+      e = cudaMemcpy(m->d_hull, hull.data(), sizeof(int4) * hull.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { mesh_free(m); return fail(DLI_ERR_CUDA, std::string("mesh upload failed: ") + cudaGetErrorString(e)); }
+  }
+  if (ns > 0) {
+    rc = build_hint_grid(m, coords);
+    if (rc != DLI_OK) { mesh_free(m); return rc; }
+  }
+  *out = m;
+  return DLI_OK;
+}
+
+extern "C" int dli_mesh_set_values(dli_mesh *m, const double *f) {
+  if (!m || !f) return fail(DLI_ERR_ARG, "dli_mesh_set_values: NULL argument");
+  DeviceGuard guard(m->device);
+  // strided copy into the f slot of every vertex record
+  CU(cudaMemcpy2D(m->d_vrec + m->dim, sizeof(double) * m->vs, f, sizeof(double), sizeof(double), (size_t)m->nv,
+                  cudaMemcpyHostToDevice));
+  return DLI_OK;
+}
+
+extern "C" void dli_mesh_destroy(dli_mesh *m) { mesh_free(m); }
+extern "C" int dli_mesh_dim(const dli_mesh *m) { return m ? m->dim : 0; }
+extern "C" int64_t dli_mesh_num_vertices(const dli_mesh *m) { return m ? m->nv : 0; }
+extern "C" int64_t dli_mesh_num_simplices(const dli_mesh *m) { return m ? m->ns : 0; }
+extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
+  if (!m) return 0;
+  return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
+                   sizeof(int32_t) * m->grid.cells);
+}
+extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
+  if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
+  if (m->h_sv.empty() && m->ns > 0) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_get_simplices: mesh was created from a header (no host copy)");
+  if (sv) memcpy(sv, m->h_sv.data(), sizeof(int32_t) * m->h_sv.size());
+  if (sn) memcpy(sn, m->h_sn.data(), sizeof(int32_t) * m->h_sn.size());
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// interp / locate dispatch
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+Mesh2View view2(const dli_mesh *m) {
+  Mesh2View v;
+  v.vrec = reinterpret_cast<const double4 *>(m->d_vrec);
+  v.frec = reinterpret_cast<const int4 *>(m->d_srec);
+  v.hull = m->d_hull;
+  v.hint = m->d_hint;
+  v.ox = m->grid.o[0]; v.oy = m->grid.o[1];
+  v.icx = m->grid.ic[0]; v.icy = m->grid.ic[1];
+  v.gx = m->grid.g[0]; v.gy = m->grid.g[1];
+  v.ns = (int)m->ns; v.nh = m->nh;
+  v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
+  return v;
+}
+MeshDView viewD(const dli_mesh *m) {
+  MeshDView v;
+  v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint;
+  for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
+  v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
+  return v;
+}
+
+constexpr int64_t kChunk = 1ll << 24;  // queries per launch pair; bounds the straggler queue (64 MiB)
+
+struct Launch {
+  const dli_mesh *m;
+  cudaStream_t st;
+  int32_t *queue;
+  unsigned int *qcount;
+  unsigned long long *stats;
+  int launches = 0;
+};
+
+template <bool STATS, int EPI>
+void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
+  Mesh2View v = view2(L.m);
+  int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : 256;
+  tpb = std::min(256, std::max(32, tpb / 32 * 32));
+  k_interp2_fast<STATS, EPI><<<(unsigned)((n + tpb - 1) / tpb), tpb, 0, L.st>>>(
+      v, n, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.stats);
+  k_interp2_full<STATS, EPI><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
+                                                         L.qcount, -1, L.stats);
+  L.launches += 2;
+}
+template <int D, bool STATS, int EPI>
+void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
+  MeshDView v = viewD(L.m);
+  int tpb = 128;
+  k_interpD_fast<D, STATS, EPI><<<(unsigned)((n + tpb - 1) / tpb), tpb, 0, L.st>>>(v, n, xs, ys, so, sto, L.queue,
+                                                                                    L.qcount, L.stats);
+  k_interpD_full<D, STATS, EPI><<<148 * 2, 64, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, -1, L.stats);
+  L.launches += 2;
+}
+
+template <bool STATS, int EPI>
+void launch_any(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
+  switch (L.m->dim) {
+    case 2: launch2<STATS, EPI>(L, n, xs, ys, so, sto); break;
+    case 3: launchD<3, STATS, EPI>(L, n, xs, ys, so, sto); break;
+    case 4: launchD<4, STATS, EPI>(L, n, xs, ys, so, sto); break;
+  }
+}
+
+// all pointers are device pointers; enqueues on `st`
+int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto,
+               cudaStream_t st, int *launches) {
+  if (n == 0) return DLI_OK;
+  if (m->ns == 0) {
+    k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, ys, so, sto);
+    CU(cudaGetLastError());
+    if (launches) *launches += 1;
+    return DLI_OK;
+  }
+  int64_t cap = std::min(n, kChunk);
+  int32_t *queue = nullptr;
+  CU(cudaMallocAsync(&queue, sizeof(int32_t) * (size_t)cap + 16, st));
+  unsigned int *qcount = reinterpret_cast<unsigned int *>(queue + cap);
+  // (queue + cap) is 4-byte aligned, which is all an unsigned int needs
+  Launch L{m, st, queue, qcount, m->d_stats};
+  if (m->collect_stats) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, st));
+  const int d = m->dim;
+  for (int64_t off = 0; off < n; off += kChunk) {
+    int64_t cn = std::min(kChunk, n - off);
+    CU(cudaMemsetAsync(qcount, 0, sizeof(unsigned int), st));
+    const double *cx = xs + off * d;
+    double *cy = ys ? ys + off : nullptr;
+    int32_t *cs = so ? so + off : nullptr;
+    uint8_t *ct = sto ? sto + off : nullptr;
+    if (m->collect_stats) {
+      if (m->opt.epilogue == 0) launch_any<true, 0>(L, cn, cx, cy, cs, ct);
+      else launch_any<true, 1>(L, cn, cx, cy, cs, ct);
+    } else {
+      if (m->opt.epilogue == 0) launch_any<false, 0>(L, cn, cx, cy, cs, ct);
+      else launch_any<false, 1>(L, cn, cx, cy, cs, ct);
+    }
+    CU(cudaGetLastError());
+  }
+  CU(cudaFreeAsync(queue, st));
+  if (launches) *launches += L.launches;
+  return DLI_OK;
+}
+
+bool is_device_ptr(const void *p, bool *known) {
+  cudaPointerAttributes a;
+  *known = true;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); *known = false; return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// host-pointer path: chunked H2D / compute / D2H pipeline over a ring of device slots
+int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, int *launches) {
+  if (n == 0) return DLI_OK;
+  const int d = m->dim;
+  const int kSlots = 3;
+  const int64_t chunk = std::min<int64_t>(n, 1ll << 22);
+  struct Slot {
+    cudaStream_t st = nullptr;
+    double *x = nullptr, *y = nullptr;
+    int32_t *s = nullptr;
+    uint8_t *t = nullptr;
+  } slot[kSlots];
+  int rc = DLI_OK;
+  auto cleanup = [&]() {
+    for (auto &s : slot) {
+      if (s.st) cudaStreamSynchronize(s.st);
+      cudaFree(s.x); cudaFree(s.y); cudaFree(s.s); cudaFree(s.t);
+      if (s.st) cudaStreamDestroy(s.st);
+    }
+  };
+  int nslots = (int)std::min<int64_t>(kSlots, (n + chunk - 1) / chunk);
+  for (int i = 0; i < nslots && rc == DLI_OK; i++) {
+    cudaError_t e = cudaStreamCreateWithFlags(&slot[i].st, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&slot[i].x, sizeof(double) * (size_t)chunk * d);
+    if (e == cudaSuccess && ys) e = cudaMalloc(&slot[i].y, sizeof(double) * (size_t)chunk);
+    if (e == cudaSuccess && so) e = cudaMalloc(&slot[i].s, sizeof(int32_t) * (size_t)chunk);
+    if (e == cudaSuccess && sto) e = cudaMalloc(&slot[i].t, (size_t)chunk);
+    if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("dli_interp: staging allocation failed: ") + cudaGetErrorString(e));
+  }
+  int64_t c = 0;
+  for (int64_t off = 0; off < n && rc == DLI_OK; off += chunk, c++) {
+    Slot &s = slot[c % nslots];
+    int64_t cn = std::min(chunk, n - off);
+    cudaError_t e = cudaMemcpyAsync(s.x, xs + off * d, sizeof(double) * (size_t)cn * d, cudaMemcpyHostToDevice, s.st);
+    if (e != cudaSuccess) { rc = fail(DLI_ERR_CUDA, std::string("H2D copy failed: ") + cudaGetErrorString(e)); break; }
+    rc = run_device(m, cn, s.x, s.y, s.s, s.t, s.st, launches);
+    if (rc != DLI_OK) break;
+    if (ys) e = cudaMemcpyAsync(ys + off, s.y, sizeof(double) * (size_t)cn, cudaMemcpyDeviceToHost, s.st);
+    if (e == cudaSuccess && so) e = cudaMemcpyAsync(so + off, s.s, sizeof(int32_t) * (size_t)cn, cudaMemcpyDeviceToHost, s.st);
+    if (e == cudaSuccess && sto) e = cudaMemcpyAsync(sto + off, s.t, (size_t)cn, cudaMemcpyDeviceToHost, s.st);
+    if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(e));
+  }
+  for (int i = 0; i < nslots; i++)
+    if (slot[i].st) {
+      cudaError_t e = cudaStreamSynchronize(slot[i].st);
+      if (e != cudaSuccess && rc == DLI_OK) rc = fail(DLI_ERR_CUDA, std::string("dli_interp: ") + cudaGetErrorString(e));
+    }
+  cleanup();
+  return rc;
+}
+
+int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, void *stream,
+                  const char *who) {
+  if (!m) return fail(DLI_ERR_ARG, std::string(who) + ": NULL mesh");
+  if (n < 0) return fail(DLI_ERR_ARG, std::string(who) + ": negative n");
+  if (n == 0) return DLI_OK;
+  if (!xs) return fail(DLI_ERR_ARG, std::string(who) + ": xs is NULL");
+  DeviceGuard guard(m->device);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, std::string(who) + ": cannot select device");
+  bool known;
+  bool dev = is_device_ptr(xs, &known);
+  const void *outs[3] = {ys, so, sto};
+  for (const void *p : outs)
+    if (p) {
+      bool k2;
+      if (is_device_ptr(p, &k2) != dev) return fail(DLI_ERR_ARG, std::string(who) + ": xs and outputs must all be host or all be device pointers");
+    }
+  int launches = 0;
+  int rc;
+  if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches);
+  else rc = run_host(m, n, xs, ys, so, sto, &launches);
+  m->last.kernel_launches = launches;
+  m->last.queries = n;
+  return rc;
+}
+
+}  // namespace
+
+extern "C" int dli_interp(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto,
+                          void *stream) {
+  if (n > 0 && !ys) return fail(DLI_ERR_ARG, "dli_interp: ys is NULL");
+  return interp_common(m, n, xs, ys, so, sto, stream, "dli_interp");
+}
+extern "C" int dli_locate(const dli_mesh *m, int64_t n, const double *xs, int32_t *so, uint8_t *sto, void *stream) {
+  if (n > 0 && !so) return fail(DLI_ERR_ARG, "dli_locate: simplex_out is NULL");
+  return interp_common(m, n, xs, nullptr, so, sto, stream, "dli_locate");
+}
+
+extern "C" int dli_mesh_collect_stats(dli_mesh *m, int enable) {
+  if (!m) return fail(DLI_ERR_ARG, "NULL mesh");
+  m->collect_stats = enable != 0;
+  return DLI_OK;
+}
+extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
+  if (!m || !out) return fail(DLI_ERR_ARG, "NULL argument");
+  DeviceGuard guard(m->device);
+  unsigned long long w[ST_WORDS];
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(w, m->d_stats, sizeof w, cudaMemcpyDeviceToHost));
+  out->queries = m->last.queries;
+  out->walk_steps = (int64_t)w[ST_STEPS];
+  out->max_walk_steps = (int64_t)w[ST_MAXSTEPS];
+  out->exact_fallbacks = (int64_t)w[ST_EXACT];
+  out->outside = (int64_t)w[ST_OUTSIDE];
+  out->kernel_launches = m->last.kernel_launches;
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// error evaluator
+// ---------------------------------------------------------------------------------------------
+static int ensure_items(dli_mesh *m) {
+  std::lock_guard<std::mutex> lk(m->mu);
+  if (m->items_ready) return DLI_OK;
+  if (m->h_sv.empty() && m->ns > 0) return fail(DLI_ERR_UNSUPPORTED, "error evaluator needs a mesh created with dli_mesh_create");
+  const int d = m->dim, k = d + 1;
+  m->h_item_simplex.clear();
+  m->h_item_verts.clear();
+  for (int64_t s = 0; s < m->ns; s++) {
+    for (int item = -1; item < k; item++) {
+      int32_t fv[DLI_MAX_DIM + 1];
+      int nf = 0;
+      if (item == -1) {
+        for (int j = 0; j < k; j++) fv[nf++] = m->h_sv[s * k + j];
+      } else {
+        if (m->h_sn[s * k + item] >= 0) continue;
+        for (int j = 0; j < k; j++)
+          if (j != item) fv[nf++] = m->h_sv[s * k + j];
+      }
+      int lo = (item == -1) ? (1 << nf) - 1 : 0;
+      for (int mask = lo; mask < (1 << nf); mask++) {
+        if (__builtin_popcount((unsigned)mask) < 2) continue;
+        int c = 0;
+        for (int b = 0; b < nf; b++)
+          if (mask >> b & 1) { m->h_item_verts.push_back(fv[b]); c++; }
+        for (; c < k; c++) m->h_item_verts.push_back(-1);
+        m->h_item_simplex.push_back((int32_t)s);
+      }
+    }
+  }
+  m->n_items = (int64_t)m->h_item_simplex.size();
+  DeviceGuard guard(m->device);
+  CU(cudaMalloc(&m->d_item_verts, sizeof(int32_t) * std::max<size_t>(m->h_item_verts.size(), 1)));
+  CU(cudaMemcpy(m->d_item_verts, m->h_item_verts.data(), sizeof(int32_t) * m->h_item_verts.size(), cudaMemcpyHostToDevice));
+  m->items_ready = true;
+  return DLI_OK;
+}
+
+extern "C" int64_t dli_simplex_error_count(const dli_mesh *m) {
+  if (!m) return fail(DLI_ERR_ARG, "NULL mesh");
+  int rc = ensure_items(const_cast<dli_mesh *>(m));
+  return rc != DLI_OK ? rc : m->n_items;
+}
+
+extern "C" int dli_simplex_error_prepare(const dli_mesh *mc, double *centroids, int32_t *item_simplex,
+                                         int32_t *item_vertices) {
+  dli_mesh *m = const_cast<dli_mesh *>(mc);
+  if (!m || !centroids) return fail(DLI_ERR_ARG, "dli_simplex_error_prepare: NULL argument");
+  int rc = ensure_items(m);
+  if (rc != DLI_OK) return rc;
+  const int64_t n = m->n_items;
+  if (item_simplex) memcpy(item_simplex, m->h_item_simplex.data(), sizeof(int32_t) * (size_t)n);
+  if (item_vertices) memcpy(item_vertices, m->h_item_verts.data(), sizeof(int32_t) * m->h_item_verts.size());
+  if (n == 0) return DLI_OK;
+  DeviceGuard guard(m->device);
+  double *d_c = nullptr;
+  CU(cudaMalloc(&d_c, sizeof(double) * (size_t)n * m->dim));
+  unsigned blocks = (unsigned)((n + 255) / 256);
+  switch (m->dim) {
+    case 2: k_error_prepare<2><<<blocks, 256>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_c); break;
+    case 3: k_error_prepare<3><<<blocks, 256>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_c); break;
+    case 4: k_error_prepare<4><<<blocks, 256>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_c); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpy(centroids, d_c, sizeof(double) * (size_t)n * m->dim, cudaMemcpyDeviceToHost);
+  cudaFree(d_c);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_simplex_error_prepare: ") + cudaGetErrorString(e));
+  return DLI_OK;
+}
+
+extern "C" int dli_simplex_error_finish(const dli_mesh *mc, int64_t n, const double *phi, double *err) {
+  dli_mesh *m = const_cast<dli_mesh *>(mc);
+  if (!m || (n > 0 && (!phi || !err))) return fail(DLI_ERR_ARG, "dli_simplex_error_finish: NULL argument");
+  int rc = ensure_items(m);
+  if (rc != DLI_OK) return rc;
+  if (n != m->n_items) return fail(DLI_ERR_ARG, "dli_simplex_error_finish: n does not match dli_simplex_error_count");
+  if (n == 0) return DLI_OK;
+  DeviceGuard guard(m->device);
+  double *d_phi = nullptr, *d_err = nullptr;
+  CU(cudaMalloc(&d_phi, sizeof(double) * (size_t)n));
+  cudaError_t e = cudaMalloc(&d_err, sizeof(double) * (size_t)n);
+  if (e == cudaSuccess) e = cudaMemcpy(d_phi, phi, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    unsigned blocks = (unsigned)((n + 127) / 128);
+    switch (m->dim) {
+      case 2: k_error_finish<2><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_phi, d_err); break;
+      case 3: k_error_finish<3><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_phi, d_err); break;
+      case 4: k_error_finish<4><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_phi, d_err); break;
+    }
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(err, d_err, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost);
+  cudaFree(d_phi);
+  cudaFree(d_err);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_simplex_error_finish: ") + cudaGetErrorString(e));
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// replication support
+// ---------------------------------------------------------------------------------------------
+// header words: 0 version, 1 dim, 2 nv, 3 ns, 4 nh, 5 cells, 6..9 grid g[k], 10 max_steps, 11 fast_steps,
+// 12..15 reserved.  The floating-point grid parameters travel in buffer 0 (a small device block).
+extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORDS]) {
+  if (!m || !h) return fail(DLI_ERR_ARG, "NULL argument");
+  memset(h, 0, sizeof(int64_t) * DLI_MESH_HEADER_WORDS);
+  h[0] = DLI_VERSION; h[1] = m->dim; h[2] = m->nv; h[3] = m->ns; h[4] = m->nh; h[5] = m->grid.cells;
+  for (int k = 0; k < 4; k++) h[6 + k] = m->grid.g[k];
+  h[10] = m->max_steps; h[11] = m->fast_steps;
+  // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
+  // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
+  // (see dli_mesh_buffer): index 0 = 96-byte parameter block.
+  return DLI_OK;
+}
+
+struct GridParams {
+  double o[DLI_MAX_DIM], cell[DLI_MAX_DIM], ic[DLI_MAX_DIM];
+};
+
+extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS], const dli_options *opt,
+                                           dli_mesh **out) {
+  if (!h || !out) return fail(DLI_ERR_ARG, "NULL argument");
+  *out = nullptr;
+  if (h[0] != DLI_VERSION) return fail(DLI_ERR_ARG, "dli_mesh_create_from_header: version mismatch");
+  if (dli_device_count() <= 0) return fail(DLI_ERR_CUDA, "no CUDA device available");
+  dli_mesh *m = new dli_mesh;
+  m->dim = (int)h[1]; m->nv = h[2]; m->ns = h[3]; m->nh = (int32_t)h[4];
+  if (m->dim < 2 || m->dim > 4) { delete m; return fail(DLI_ERR_UNSUPPORTED, "bad dim in header"); }
+  resolve_options(opt, &m->opt);
+  if (m->opt.device >= 0) m->device = m->opt.device;
+  else cudaGetDevice(&m->device);
+  DeviceGuard guard(m->device);
+  m->grid.cells = h[5];
+  for (int k = 0; k < 4; k++) m->grid.g[k] = (int)h[6 + k];
+  int rc = mesh_alloc_common(m);
+  m->max_steps = (int)h[10];
+  m->fast_steps = (int)h[11];
+  if (rc != DLI_OK) { mesh_free(m); return rc; }
+  cudaError_t e = cudaMalloc(&m->d_hint, sizeof(int32_t) * (size_t)std::max<int64_t>(m->grid.cells, 1));
+  if (e != cudaSuccess) { mesh_free(m); return fail(DLI_ERR_CUDA, "hint allocation failed"); }
+  *out = m;
+  return DLI_OK;
+}
+
+extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 4 : 0; }
+
+// buffers 0..3: vertex records, simplex records, hull table, hint grid
+extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t *bytes) {
+  if (!m || !ptr || !bytes) return fail(DLI_ERR_ARG, "NULL argument");
+  switch (index) {
+    case 0: *ptr = m->d_vrec; *bytes = (int64_t)sizeof(double) * std::max<int64_t>(m->nv, 1) * m->vs; break;
+    case 1: *ptr = m->d_srec; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1) * m->ss; break;
+    case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
+    case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
+    default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
+  }
+  return DLI_OK;
+}
+
+// grid parameters (doubles) for replication: host-side get/set
+extern "C" int dli_mesh_get_grid_params(const dli_mesh *m, double *out /* [3 * DLI_MAX_DIM] */) {
+  if (!m || !out) return fail(DLI_ERR_ARG, "NULL argument");
+  for (int k = 0; k < DLI_MAX_DIM; k++) { out[k] = m->grid.o[k]; out[DLI_MAX_DIM + k] = m->grid.cell[k]; out[2 * DLI_MAX_DIM + k] = m->grid.ic[k]; }
+  return DLI_OK;
+}
+extern "C" int dli_mesh_set_grid_params(dli_mesh *m, const double *in) {
+  if (!m || !in) return fail(DLI_ERR_ARG, "NULL argument");
+  for (int k = 0; k < DLI_MAX_DIM; k++) { m->grid.o[k] = in[k]; m->grid.cell[k] = in[DLI_MAX_DIM + k]; m->grid.ic[k] = in[2 * DLI_MAX_DIM + k]; }
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// predicate test hook
+// ---------------------------------------------------------------------------------------------
+extern "C" int dli_debug_orient(int dim, int64_t n, const double *pts, int8_t *sign_out, uint8_t *exact_used) {
+  if (dim < 2 || dim > 4) return fail(DLI_ERR_UNSUPPORTED, "dli_debug_orient: dim must be 2..4");
+  if (n < 0 || (n > 0 && (!pts || !sign_out))) return fail(DLI_ERR_ARG, "dli_debug_orient: bad argument");
+  if (n == 0) return DLI_OK;
+  if (dli_device_count() <= 0) return fail(DLI_ERR_CUDA, "no CUDA device available");
+  size_t per = (size_t)(dim + 1) * dim;
+  double *d_p = nullptr;
+  int8_t *d_s = nullptr;
+  uint8_t *d_e = nullptr;
+  CU(cudaMalloc(&d_p, sizeof(double) * per * (size_t)n));
+  cudaError_t e = cudaMalloc(&d_s, (size_t)n);
+  if (e == cudaSuccess) e = cudaMalloc(&d_e, (size_t)n);
+  if (e == cudaSuccess) e = cudaMemcpy(d_p, pts, sizeof(double) * per * (size_t)n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    unsigned blocks = (unsigned)((n + 63) / 64);
+    switch (dim) {
+      case 2: k_debug_orient<2><<<blocks, 64>>>(n, d_p, d_s, d_e); break;
+      case 3: k_debug_orient<3><<<blocks, 64>>>(n, d_p, d_s, d_e); break;
+      case 4: k_debug_orient<4><<<blocks, 64>>>(n, d_p, d_s, d_e); break;
+    }
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(sign_out, d_s, (size_t)n, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && exact_used) e = cudaMemcpy(exact_used, d_e, (size_t)n, cudaMemcpyDeviceToHost);
+  cudaFree(d_p); cudaFree(d_s); cudaFree(d_e);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_debug_orient: ") + cudaGetErrorString(e));
+  return DLI_OK;
+}
+
+extern "C" int dli_debug_orient_host(int dim, int64_t n, const double *pts, int8_t *sign_out) {
+  if (dim < 2 || dim > 4) return fail(DLI_ERR_UNSUPPORTED, "dli_debug_orient_host: dim must be 2..4");
+  if (n < 0 || (n > 0 && (!pts || !sign_out))) return fail(DLI_ERR_ARG, "dli_debug_orient_host: bad argument");
+  size_t per = (size_t)(dim + 1) * dim;
+  for (int64_t i = 0; i < n; i++) sign_out[i] = (int8_t)orient_host(dim, pts + per * (size_t)i);
+  return DLI_OK;
+}

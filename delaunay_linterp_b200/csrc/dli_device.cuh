@@ -1,0 +1,547 @@
+// dli_device.cuh -- device-side mesh views and the per-query device functions
+// (jump-and-walk locate, outside-hull handling, barycentric + gather epilogue).
+//
+// Reference behaviour restated (paths relative to the reference tree):
+//   2D driver   src/delaunay_2_interp.h:515-572      dD driver  src/delaunay_d_interp.h:988-1010
+//   2D epilogue src/delaunay_2_interp.h:195-239, 563-569 (Eigen dynamic determinant = partial-pivot LU)
+//   dD epilogue src/delaunay_d_interp.h:601-650, 998-1004 (exact differences truncated, exact sum truncated)
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "dli_exact.cuh"
+#include "../../include/dli.h"
+
+namespace dli {
+
+constexpr int kMaxProjections = 16;  // 2D outside-hull project/re-locate rounds before accepting the hull face
+
+// ---------------------------------------------------------------------------------------------
+// Device mesh views (plain structs passed by value to kernels)
+// ---------------------------------------------------------------------------------------------
+
+// 2D: vertex record double4 {x, y, f, 0} (32 B = one DRAM sector);
+//     face record 2 x int4 {v0, v1, v2, n0 | n1, n2, 0, 0} (32 B); neighbour >= 0 = face id,
+//     < 0 = ~(hull edge index); hull record int4 {face, slot, next, prev}.
+struct Mesh2View {
+  const double4 *vrec;
+  const int4 *frec;
+  const int4 *hull;
+  const int32_t *hint;
+  double ox, oy, icx, icy;  // hint grid origin and 1/cell size
+  int gx, gy;
+  int ns, nh;
+  int max_steps;   // hard cap on simplices visited per query
+  int fast_steps;  // fast-path cap; longer walks are re-run by the straggler/exact pass
+};
+
+// dD (D = 3, 4): vertex record VS doubles {x_0..x_{D-1}, f, pad}; simplex record SS ints
+// {v_0..v_D, n_0..n_D, pad}; neighbour < 0 = hull.
+template <int D>
+struct RecD {
+  static constexpr int VS = (D + 1 <= 4) ? 4 : 8;        // doubles per vertex record (32 B / 64 B)
+  static constexpr int SS = (2 * (D + 1) <= 8) ? 8 : 16;  // ints per simplex record (32 B / 64 B)
+};
+struct MeshDView {
+  const double *vrec;
+  const int32_t *srec;
+  const int32_t *hint;
+  double o[DLI_MAX_DIM], ic[DLI_MAX_DIM];
+  int g[DLI_MAX_DIM];
+  int ns;
+  int max_steps;
+  int fast_steps;
+};
+
+struct StatsAcc {  // per-thread accumulators, flushed by the kernels when stats are enabled
+  unsigned long long steps = 0, exact = 0, outside = 0;
+  unsigned int max_steps = 0;
+};
+
+// ---------------------------------------------------------------------------------------------
+// 2D epilogue (reference operation order)
+// ---------------------------------------------------------------------------------------------
+
+// Eigen partial-pivot LU determinant of [[a, b], [c, d]]
+__device__ __forceinline__ double lu_det2(double a, double b, double c, double d) {
+  double s = 1.0;
+  if (fabs(c) > fabs(a)) {
+    double t = a; a = c; c = t;
+    t = b; b = d; d = t;
+    s = -1.0;
+  }
+  double l = (a != 0.0) ? c / a : 0.0;
+  double u = d - l * b;
+  return s * (a * u);
+}
+// signed area: column j = P_{j+1} - P_0 (src/delaunay_2_interp.h:202-207), det / 2!
+__device__ __forceinline__ double vol2(double ax, double ay, double bx, double by, double cx, double cy) {
+  return lu_det2(bx - ax, cx - ax, by - ay, cy - ay) * 0.5;
+}
+__device__ __forceinline__ double epilogue2_ref(double px, double py, const double4 &A, const double4 &B,
+                                                 const double4 &C) {
+  double whole = vol2(A.x, A.y, B.x, B.y, C.x, C.y);
+  double b0 = vol2(px, py, B.x, B.y, C.x, C.y) / whole;
+  double b1 = vol2(A.x, A.y, px, py, C.x, C.y) / whole;
+  double b2 = vol2(A.x, A.y, B.x, B.y, px, py) / whole;
+  double sum = 0.0;
+  sum = sum + b0 * A.z;
+  sum = sum + b1 * B.z;
+  sum = sum + b2 * C.z;
+  return sum;
+}
+// closed form (option epilogue = 1): one reciprocal, cross products
+__device__ __forceinline__ double epilogue2_fast(double px, double py, const double4 &A, const double4 &B,
+                                                  const double4 &C) {
+  double w = (B.x - A.x) * (C.y - A.y) - (C.x - A.x) * (B.y - A.y);
+  double w0 = (B.x - px) * (C.y - py) - (C.x - px) * (B.y - py);
+  double w1 = (C.x - px) * (A.y - py) - (A.x - px) * (C.y - py);
+  double w2 = (A.x - px) * (B.y - py) - (B.x - px) * (A.y - py);
+  double r = 1.0 / w;
+  return (w0 * A.z + w1 * B.z + w2 * C.z) * r;
+}
+
+// CGAL Cartesian Line_2(P,Q) + projection in plain doubles
+__device__ inline void project_on_line(double Px, double Py, double Qx, double Qy, double &px, double &py) {
+  double a, b, c;
+  if (Py == Qy) {
+    a = 0.0;
+    if (Qx > Px) { b = 1.0; c = -Py; }
+    else if (Qx == Px) { b = 0.0; c = 0.0; }
+    else { b = -1.0; c = Py; }
+  } else if (Qx == Px) {
+    b = 0.0;
+    if (Qy > Py) { a = -1.0; c = Px; }
+    else { a = 1.0; c = -Px; }
+  } else {
+    a = Py - Qy;
+    b = Qx - Px;
+    c = -Px * a - Py * b;
+  }
+  double x, y;
+  if (a == 0.0) { x = px; y = -c / b; }
+  else if (b == 0.0) { x = -c / a; y = py; }
+  else {
+    double a2 = a * a, b2 = b * b, d = a2 + b2;
+    x = (b2 * px - a * b * py - a * c) / d;
+    y = (-a * b * px + a2 * py - b * c) / d;
+  }
+  px = x; py = y;
+}
+
+__device__ __forceinline__ int hint2(const Mesh2View &m, double x, double y) {
+  int i = (int)((x - m.ox) * m.icx);
+  int j = (int)((y - m.oy) * m.icy);
+  i = max(0, min(m.gx - 1, i));
+  j = max(0, min(m.gy - 1, j));
+  return __ldg(m.hint + (size_t)j * m.gx + i);
+}
+
+struct Face2 {
+  int v0, v1, v2, n0, n1, n2;
+};
+__device__ __forceinline__ Face2 load_face(const Mesh2View &m, int f) {
+  int4 a = __ldg(m.frec + 2 * (size_t)f), b = __ldg(m.frec + 2 * (size_t)f + 1);
+  Face2 r;
+  r.v0 = a.x; r.v1 = a.y; r.v2 = a.z; r.n0 = a.w; r.n1 = b.x; r.n2 = b.y;
+  return r;
+}
+__device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
+  // one 32-byte record = one sector
+  const double2 *p = reinterpret_cast<const double2 *>(m.vrec + v);
+  double2 lo = __ldg(p), hi = __ldg(p + 1);
+  return make_double4(lo.x, lo.y, hi.x, hi.y);
+}
+
+// Fast path: static filter only.  Returns true with the containing face's vertices loaded when every
+// decision was certain, the point stayed inside the hull and the walk was short; false = hand the
+// query to the full path.
+__device__ __forceinline__ bool locate2_fast(const Mesh2View &m, double px, double py, int &f, double4 &A,
+                                             double4 &B, double4 &C, unsigned int &steps) {
+  int from = -1;
+  const double fc = filter_const(2);
+  for (int it = 0; it < m.fast_steps; it++) {
+    steps++;
+    Face2 F = load_face(m, f);
+    A = load_vert(m, F.v0);
+    B = load_vert(m, F.v1);
+    C = load_vert(m, F.v2);
+    double ax = A.x - px, ay = A.y - py, bx = B.x - px, by = B.y - py, cx = C.x - px, cy = C.y - py;
+    // edge opposite v0 = (B, C); opposite v1 = (C, A); opposite v2 = (A, B); orient(X, Y, p) with
+    // differences taken against p
+    double l0 = bx * cy, r0 = by * cx, d0 = l0 - r0, e0 = fc * (fabs(l0) + fabs(r0));
+    double l1 = cx * ay, r1 = cy * ax, d1 = l1 - r1, e1 = fc * (fabs(l1) + fabs(r1));
+    double l2 = ax * by, r2 = ay * bx, d2 = l2 - r2, e2 = fc * (fabs(l2) + fabs(r2));
+    bool neg0 = (-d0 > e0) && !(F.n0 >= 0 && F.n0 == from);
+    bool neg1 = (-d1 > e1) && !(F.n1 >= 0 && F.n1 == from);
+    bool neg2 = (-d2 > e2) && !(F.n2 >= 0 && F.n2 == from);
+    if (neg0 | neg1 | neg2) {
+      int nb = neg0 ? F.n0 : (neg1 ? F.n1 : F.n2);
+      if (nb < 0) return false;  // leaving the hull: full path
+      from = f;
+      f = nb;
+      continue;
+    }
+    // no certainly-negative edge: inside iff the others are certainly positive (the edge we came
+    // through is known positive)
+    bool pos0 = (d0 > e0) || (F.n0 >= 0 && F.n0 == from);
+    bool pos1 = (d1 > e1) || (F.n1 >= 0 && F.n1 == from);
+    bool pos2 = (d2 > e2) || (F.n2 >= 0 && F.n2 == from);
+    return pos0 & pos1 & pos2;
+  }
+  return false;
+}
+
+// among the hull edges strictly visible from p (a contiguous chain containing h0) the one with the
+// smallest index; canonical stand-in for "whichever infinite face CGAL's walk ended in"
+__device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px, double py, int h0,
+                                                  StatsAcc &st) {
+  int best = h0;
+  for (int dir = 0; dir < 2; dir++) {
+    int h = h0;
+    for (int it = 0; it < m.nh; it++) {
+      int4 hr = __ldg(m.hull + h);
+      h = dir ? hr.w : hr.z;
+      if (h < 0 || h == h0) break;
+      int4 r = __ldg(m.hull + h);
+      Face2 F = load_face(m, r.x);
+      int vs[3] = {F.v0, F.v1, F.v2};
+      double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
+      int s = orient2d_filtered(P.x, P.y, Q.x, Q.y, px, py);
+      if (s == 2) { st.exact++; s = orient2d_exact(P.x, P.y, Q.x, Q.y, px, py); }
+      if (s >= 0) break;
+      if (h < best) best = h;
+    }
+  }
+  return best;
+}
+
+// Full path: exact-sign walk over closed faces, outside-hull projection loop, status codes.
+// Returns the face in f with its vertices loaded; p is updated to the projected point.
+__device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &py, int &f, double4 &A, double4 &B,
+                                       double4 &C, StatsAcc &st) {
+  uint8_t status = DLI_STATUS_OK;
+  int from = -1;
+  unsigned int steps = 0;
+  for (int proj = 0;; proj++) {
+    int exit_h = -1;
+    bool found = false;
+    for (;;) {
+      if ((int)steps >= m.max_steps) { st.steps += steps; return DLI_STATUS_STEP_LIMIT; }
+      steps++;
+      Face2 F = load_face(m, f);
+      A = load_vert(m, F.v0);
+      B = load_vert(m, F.v1);
+      C = load_vert(m, F.v2);
+      int nbs[3] = {F.n0, F.n1, F.n2};
+      int mv = -1;
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        if (nbs[j] >= 0 && nbs[j] == from) continue;
+        const double4 &X = (j == 0) ? B : (j == 1 ? C : A);
+        const double4 &Y = (j == 0) ? C : (j == 1 ? A : B);
+        int s = orient2d_filtered(X.x, X.y, Y.x, Y.y, px, py);
+        if (s == 2) { st.exact++; s = orient2d_exact(X.x, X.y, Y.x, Y.y, px, py); }
+        if (s < 0) { mv = j; break; }
+      }
+      if (mv < 0) { found = true; break; }
+      int nb = nbs[mv];
+      if (nb < 0) { exit_h = ~nb; break; }
+      from = f;
+      f = nb;
+    }
+    if (found) break;
+    if (status == DLI_STATUS_OK) st.outside++;
+    status = DLI_STATUS_OUTSIDE_PROJECTED;
+    if (proj >= kMaxProjections) break;  // accept the hull face (ulp-level extrapolation)
+    int h = canonical_visible_hull_edge(m, px, py, exit_h, st);
+    int4 r = __ldg(m.hull + h);
+    Face2 F = load_face(m, r.x);
+    int vs[3] = {F.v0, F.v1, F.v2};
+    double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
+    project_on_line(P.x, P.y, Q.x, Q.y, px, py);
+    f = r.x;
+    from = -1;
+  }
+  st.steps += steps;
+  if (steps > st.max_steps) st.max_steps = steps;
+  return status;
+}
+
+// ---------------------------------------------------------------------------------------------
+// dD
+// ---------------------------------------------------------------------------------------------
+
+template <int D>
+__device__ __forceinline__ int hintD(const MeshDView &m, const double *p) {
+  size_t idx = 0;
+#pragma unroll
+  for (int a = D - 1; a >= 0; a--) {
+    int i = (int)((p[a] - m.o[a]) * m.ic[a]);
+    i = max(0, min(m.g[a] - 1, i));
+    idx = idx * m.g[a] + i;
+  }
+  return __ldg(m.hint + idx);
+}
+
+template <int D>
+struct SimplexD {
+  int v[D + 1], n[D + 1];
+  double x[(D + 1) * D];
+  double f[D + 1];
+};
+
+template <int D>
+__device__ __forceinline__ void load_simplex_ids(const MeshDView &m, int s, SimplexD<D> &S) {
+  constexpr int SS = RecD<D>::SS;
+  const int4 *r = reinterpret_cast<const int4 *>(m.srec + (size_t)s * SS);
+  int tmp[SS];
+#pragma unroll
+  for (int i = 0; i < SS / 4; i++) {
+    if (i * 4 < 2 * (D + 1)) {
+      int4 t = __ldg(r + i);
+      tmp[4 * i] = t.x; tmp[4 * i + 1] = t.y; tmp[4 * i + 2] = t.z; tmp[4 * i + 3] = t.w;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i <= D; i++) { S.v[i] = tmp[i]; S.n[i] = tmp[D + 1 + i]; }
+}
+template <int D>
+__device__ __forceinline__ void load_simplex_verts(const MeshDView &m, SimplexD<D> &S) {
+  constexpr int VS = RecD<D>::VS;
+#pragma unroll
+  for (int i = 0; i <= D; i++) {
+    const double2 *r = reinterpret_cast<const double2 *>(m.vrec + (size_t)S.v[i] * VS);
+    double tmp[VS];
+#pragma unroll
+    for (int k = 0; k < VS / 2; k++) {
+      if (2 * k < D + 1) {
+        double2 t = __ldg(r + k);
+        tmp[2 * k] = t.x; tmp[2 * k + 1] = t.y;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < D; k++) S.x[i * D + k] = tmp[k];
+    S.f[i] = tmp[D];
+  }
+}
+
+// sign of the orientation of the simplex with vertex j replaced by p; EXACT selects the fallback
+template <int D, bool EXACT>
+__device__ __forceinline__ int orient_replaced(const SimplexD<D> &S, int j, const double *p, StatsAcc &st) {
+  double pts[(D + 1) * D];
+#pragma unroll
+  for (int i = 0; i <= D; i++)
+#pragma unroll
+    for (int k = 0; k < D; k++) pts[i * D + k] = (i == j) ? p[k] : S.x[i * D + k];
+  int s = orient_filtered<D>(pts);
+  if (EXACT && s == 2) { st.exact++; s = orient_exact<D>(pts); }
+  return s;
+}
+
+// fast path (filter only).  true = located with certainty inside the hull.
+template <int D>
+__device__ __forceinline__ bool locateD_fast(const MeshDView &m, const double *p, int &s, SimplexD<D> &S,
+                                             unsigned int &steps) {
+  int from = -1;
+  StatsAcc dummy;
+  for (int it = 0; it < m.fast_steps; it++) {
+    steps++;
+    load_simplex_ids<D>(m, s, S);
+    load_simplex_verts<D>(m, S);
+    int mv = -1;
+    bool uncertain = false;
+#pragma unroll
+    for (int j = 0; j <= D; j++) {
+      if (mv >= 0) continue;
+      if (S.n[j] >= 0 && S.n[j] == from) continue;
+      int sg = orient_replaced<D, false>(S, j, p, dummy);
+      if (sg == -1) mv = j;
+      else if (sg != 1) uncertain = true;
+    }
+    if (mv < 0) return !uncertain;
+    int nb = S.n[mv];
+    if (nb < 0) return false;
+    from = s;
+    s = nb;
+  }
+  return false;
+}
+
+// full path: exact signs; outside the hull -> DLI_STATUS_OUTSIDE_NAN (src/delaunay_d_interp.h:1005-1008)
+template <int D>
+__device__ inline uint8_t locateD_full(const MeshDView &m, const double *p, int &s, SimplexD<D> &S, StatsAcc &st) {
+  int from = -1;
+  unsigned int steps = 0;
+  for (;;) {
+    if ((int)steps >= m.max_steps) { st.steps += steps; return DLI_STATUS_STEP_LIMIT; }
+    steps++;
+    load_simplex_ids<D>(m, s, S);
+    load_simplex_verts<D>(m, S);
+    int mv = -1;
+    for (int j = 0; j <= D; j++) {
+      if (S.n[j] >= 0 && S.n[j] == from) continue;
+      if (orient_replaced<D, true>(S, j, p, st) < 0) { mv = j; break; }
+    }
+    if (mv < 0) break;
+    int nb = S.n[mv];
+    if (nb < 0) {
+      st.steps += steps; st.outside++;
+      if (steps > st.max_steps) st.max_steps = steps;
+      return DLI_STATUS_OUTSIDE_NAN;
+    }
+    from = s;
+    s = nb;
+  }
+  st.steps += steps;
+  if (steps > st.max_steps) st.max_steps = steps;
+  return DLI_STATUS_OK;
+}
+
+// Eigen PartialPivLU determinant (unblocked), n = D, matrix row-major in registers (destroyed)
+template <int D>
+__device__ __forceinline__ double lu_det(double *a) {
+  double sgn = 1.0;
+#pragma unroll
+  for (int c = 0; c < D; c++) {
+    int piv = c;
+    double best = fabs(a[c * D + c]);
+#pragma unroll
+    for (int r = c + 1; r < D; r++) {
+      double v = fabs(a[r * D + c]);
+      if (v > best) { best = v; piv = r; }
+    }
+    // swap rows c and piv (piv is dynamic: select-based swap keeps everything in registers)
+#pragma unroll
+    for (int r = c + 1; r < D; r++) {
+      if (r == piv) {
+#pragma unroll
+        for (int j = 0; j < D; j++) { double t = a[c * D + j]; a[c * D + j] = a[r * D + j]; a[r * D + j] = t; }
+      }
+    }
+    if (piv != c) sgn = -sgn;
+    double pv = a[c * D + c];
+#pragma unroll
+    for (int r = c + 1; r < D; r++) {
+      double l = (pv != 0.0) ? a[r * D + c] / pv : a[r * D + c];
+      a[r * D + c] = l;
+#pragma unroll
+      for (int j = c + 1; j < D; j++) a[r * D + j] = a[r * D + j] - l * a[c * D + j];
+    }
+  }
+  double prod = a[0];
+#pragma unroll
+  for (int i = 1; i < D; i++) prod = prod * a[i * D + i];
+  return sgn * prod;
+}
+
+// signed volume; column j = pts[j+1] - pts[0]; exact difference rounded toward zero (Gmpq
+// subtraction + mpq_get_d, src/delaunay_d_interp.h:608-613), det / D!
+template <int D>
+__device__ __forceinline__ double volD(const double *const *pts) {
+  double a[D * D];
+#pragma unroll
+  for (int j = 0; j < D; j++)
+#pragma unroll
+    for (int i = 0; i < D; i++) a[i * D + j] = __dsub_rz(pts[j + 1][i], pts[0][i]);
+  constexpr double fact = (D == 2 ? 2.0 : D == 3 ? 6.0 : D == 4 ? 24.0 : 120.0);
+  return lu_det<D>(a) / fact;
+}
+
+// exact sum of products truncated toward zero (Gmpq accumulation + mpq_get_d, :998-1004)
+template <int K>
+__device__ inline double dot_exact_trunc(const double *b, const double *f) {
+  double e[2 * K + 1], t[2 * K + 2];
+  int n = 0;
+  for (int i = 0; i < K; i++) {
+    double p, q;
+    two_prod(b[i], f[i], p, q);
+    grow_ze(e, n, q);
+    grow_ze(e, n, p);
+  }
+  double A = 0.0;
+  for (int i = n - 1; i >= 0; i--) A += e[i];
+  if (!isfinite(A)) return A;
+  for (int it = 0; it < 8; it++) {
+    int tn = n;
+    for (int i = 0; i < n; i++) t[i] = e[i];
+    grow_ze(t, tn, -A);
+    int sd = expansion_sign(t, tn);
+    int sa = (A > 0.0) - (A < 0.0);
+    if (sd == 0) break;
+    if (sa != 0 && sd == -sa) { A = nextafter(A, 0.0); continue; }
+    double up = nextafter(A, sd > 0 ? (double)INFINITY : -(double)INFINITY);
+    tn = n;
+    for (int i = 0; i < n; i++) t[i] = e[i];
+    grow_ze(t, tn, -up);
+    int su = expansion_sign(t, tn);
+    if (su == 0 || su == sd) { A = up; if (su == 0) break; continue; }
+    break;
+  }
+  return A;
+}
+
+template <int D>
+__device__ __forceinline__ double epilogueD_ref(const double *p, const SimplexD<D> &S) {
+  const double *pts[D + 1];
+#pragma unroll
+  for (int i = 0; i <= D; i++) pts[i] = &S.x[i * D];
+  double whole = volD<D>(pts);
+  double b[D + 1];
+#pragma unroll
+  for (int i = 0; i <= D; i++) {
+    const double *q[D + 1];
+#pragma unroll
+    for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
+    b[i] = volD<D>(q) / whole;
+  }
+  return dot_exact_trunc<D + 1>(b, S.f);
+}
+
+// closed form (option epilogue = 1): one LU solve of [P1-P0 .. PD-P0] lam = p - P0
+template <int D>
+__device__ __forceinline__ double epilogueD_fast(const double *p, const SimplexD<D> &S) {
+  double a[D * (D + 1)];
+#pragma unroll
+  for (int i = 0; i < D; i++) {
+#pragma unroll
+    for (int j = 0; j < D; j++) a[i * (D + 1) + j] = S.x[(j + 1) * D + i] - S.x[i];
+    a[i * (D + 1) + D] = p[i] - S.x[i];
+  }
+#pragma unroll
+  for (int c = 0; c < D; c++) {
+    int piv = c;
+    double best = fabs(a[c * (D + 1) + c]);
+#pragma unroll
+    for (int r = c + 1; r < D; r++) {
+      double v = fabs(a[r * (D + 1) + c]);
+      if (v > best) { best = v; piv = r; }
+    }
+#pragma unroll
+    for (int r = c + 1; r < D; r++)
+      if (r == piv) {
+#pragma unroll
+        for (int j = 0; j <= D; j++) { double t = a[c * (D + 1) + j]; a[c * (D + 1) + j] = a[r * (D + 1) + j]; a[r * (D + 1) + j] = t; }
+      }
+    double inv = 1.0 / a[c * (D + 1) + c];
+#pragma unroll
+    for (int r = c + 1; r < D; r++) {
+      double l = a[r * (D + 1) + c] * inv;
+#pragma unroll
+      for (int j = c + 1; j <= D; j++) a[r * (D + 1) + j] -= l * a[c * (D + 1) + j];
+    }
+  }
+  double lam[D];
+#pragma unroll
+  for (int i = D - 1; i >= 0; i--) {
+    double s = a[i * (D + 1) + D];
+#pragma unroll
+    for (int j = i + 1; j < D; j++) s -= a[i * (D + 1) + j] * lam[j];
+    lam[i] = s / a[i * (D + 1) + i];
+  }
+  double l0 = 1.0, y = 0.0;
+#pragma unroll
+  for (int i = 0; i < D; i++) { l0 -= lam[i]; y += lam[i] * S.f[i + 1]; }
+  return y + l0 * S.f[0];
+}
+
+}  // namespace dli

@@ -1,0 +1,262 @@
+// dli_exact.cuh -- orientation predicates with a static floating-point filter and an exact
+// fallback in floating-point expansion arithmetic (Shewchuk-style), usable on host and device.
+//
+// Replaces what CGAL's Exact_predicates_inexact_constructions_kernel (2D,
+// src/delaunay_2_interp.h:66) and Cartesian_d<Gmpq> (dD, src/delaunay_d_interp.h:43-50) give the
+// reference's locate: the exact sign of the orientation determinant.
+//
+// Must be compiled with FMA contraction off (-fmad=false / -ffp-contract=off): the error-free
+// transformations below rely on individually rounded operations; the one fused operation that is
+// wanted (two_prod) is written as an explicit fma().
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDACC__)
+#define DLI_HD __host__ __device__
+#define DLI_HDI __host__ __device__ __forceinline__
+#else
+#define DLI_HD
+#define DLI_HDI inline
+#endif
+
+namespace dli {
+
+constexpr double kEps = 1.1102230246251565e-16;  // 2^-53
+// |computed det - true det| <= kFilter[d] * permanent for the cofactor expansion over rounded
+// differences used below.  d=2: Shewchuk's (3 + 16 eps) eps.  d=3,4: (number of roundings on the
+// longest path: d entry roundings + (d-1) products + 1+2+..+(d-1) accumulations = 8 resp. 13),
+// tripled for slack against the (1+eps)^k - 1 higher-order terms and the rounding of the
+// permanent itself.
+DLI_HDI double filter_const(int d) {
+  return d == 2 ? (3.0 + 16.0 * kEps) * kEps : (d == 3 ? 24.0 * kEps : 64.0 * kEps);
+}
+
+DLI_HDI void two_sum(double a, double b, double &x, double &y) {
+  double s = a + b;
+  double bv = s - a;
+  double av = s - bv;
+  x = s;
+  y = (a - av) + (b - bv);
+}
+DLI_HDI void two_prod(double a, double b, double &x, double &y) {
+  double p = a * b;
+  x = p;
+  y = fma(a, b, -p);
+}
+
+// e[0..n) += b, e grows to n+1 components (zeros are kept; the expansion stays nonoverlapping)
+DLI_HDI void grow(double *e, int &n, double b) {
+  double Q = b;
+  for (int i = 0; i < n; i++) {
+    double Qn, q;
+    two_sum(Q, e[i], Qn, q);
+    e[i] = q;
+    Q = Qn;
+  }
+  e[n++] = Q;
+}
+// same with zero elimination (keeps long expansions short)
+DLI_HDI void grow_ze(double *e, int &n, double b) {
+  double Q = b;
+  int h = 0;
+  for (int i = 0; i < n; i++) {
+    double Qn, q;
+    two_sum(Q, e[i], Qn, q);
+    Q = Qn;
+    if (q != 0.0) e[h++] = q;
+  }
+  if (Q != 0.0 || h == 0) e[h++] = Q;
+  n = h;
+}
+DLI_HDI int expansion_sign(const double *e, int n) {
+  for (int i = n - 1; i >= 0; i--) {
+    if (e[i] > 0.0) return 1;
+    if (e[i] < 0.0) return -1;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 2D
+// ---------------------------------------------------------------------------------------------
+
+// exact sign of (ax-cx)(by-cy) - (ay-cy)(bx-cx): the six surviving products of raw coordinates,
+// each split exactly with two_prod, summed exactly.
+DLI_HD inline int orient2d_exact(double ax, double ay, double bx, double by, double cx, double cy) {
+  double e[12];
+  int n = 0;
+  const double pa[6] = {ax, -ax, -cx, -ay, ay, cy};
+  const double pb[6] = {by, cy, by, bx, cx, bx};
+  for (int i = 0; i < 6; i++) {
+    double p, q;
+    two_prod(pa[i], pb[i], p, q);
+    grow(e, n, q);
+    grow(e, n, p);
+  }
+  return expansion_sign(e, n);
+}
+
+// filtered evaluation.  Returns the sign if certain, otherwise 2.
+DLI_HDI int orient2d_filtered(double ax, double ay, double bx, double by, double cx, double cy) {
+  double l = (ax - cx) * (by - cy);
+  double r = (ay - cy) * (bx - cx);
+  double det = l - r;
+  double bound = filter_const(2) * (fabs(l) + fabs(r));
+  if (det > bound) return 1;
+  if (-det > bound) return -1;
+  return 2;
+}
+DLI_HDI int orient2d(double ax, double ay, double bx, double by, double cx, double cy) {
+  int s = orient2d_filtered(ax, ay, bx, by, cx, cy);
+  return s == 2 ? orient2d_exact(ax, ay, bx, by, cx, cy) : s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// d dimensions (d = 3, 4): sign of det[p_i 1], i = 0..d  (positive = our canonical orientation)
+// ---------------------------------------------------------------------------------------------
+
+// determinant and permanent of a K x K matrix held in registers (row-major), cofactor expansion
+// along column 0.
+template <int K>
+struct DetPerm {
+  DLI_HDI static double eval(const double *m, double &perm) {
+    double det = 0.0, pm = 0.0;
+#pragma unroll
+    for (int r = 0; r < K; r++) {
+      double sub[(K - 1) * (K - 1)];
+      int rr = 0;
+#pragma unroll
+      for (int i = 0; i < K; i++) {
+        if (i == r) continue;
+#pragma unroll
+        for (int j = 1; j < K; j++) sub[rr * (K - 1) + (j - 1)] = m[i * K + j];
+        rr++;
+      }
+      double sp;
+      double sd = DetPerm<K - 1>::eval(sub, sp);
+      double t = m[r * K] * sd;
+      det = (r & 1) ? det - t : det + t;
+      pm += fabs(m[r * K]) * sp;
+    }
+    perm = pm;
+    return det;
+  }
+};
+template <>
+struct DetPerm<2> {
+  DLI_HDI static double eval(const double *m, double &perm) {
+    double a = m[0] * m[3], b = m[1] * m[2];
+    perm = fabs(a) + fabs(b);
+    return a - b;
+  }
+};
+template <>
+struct DetPerm<1> {
+  DLI_HDI static double eval(const double *m, double &perm) {
+    perm = fabs(m[0]);
+    return m[0];
+  }
+};
+
+// filtered orientation of D+1 points; q replaces vertex `slot` when slot >= 0.
+// pts: (D+1) x D row-major.  Returns sign if certain else 2.
+template <int D>
+DLI_HDI int orient_filtered(const double *pts) {
+  double m[D * D];
+#pragma unroll
+  for (int i = 0; i < D; i++)
+#pragma unroll
+    for (int j = 0; j < D; j++) m[i * D + j] = pts[i * D + j] - pts[D * D + j];
+  double perm;
+  double det = DetPerm<D>::eval(m, perm);
+  double bound = filter_const(D) * perm;
+  if (det > bound) return 1;
+  if (-det > bound) return -1;
+  return 2;
+}
+
+// Exact product of k doubles accumulated into an expansion: the running product is itself an
+// expansion (at most 2^(k-1) components) scaled exactly term by term.
+// Exact determinant sign of the (D+1)x(D+1) homogeneous matrix [1 p]: sum over permutations is
+// organised as a Laplace expansion along the ones column; every minor is a D x D determinant of
+// raw coordinates expanded into its D! signed products.
+template <int D>
+struct ExactCap {  // components of the full expansion (before zero elimination)
+  static constexpr int fact = (D == 1 ? 1 : D == 2 ? 2 : D == 3 ? 6 : D == 4 ? 24 : 120);
+  static constexpr int value = (D + 1) * fact * (1 << (D - 1));
+};
+
+// merge-free exact accumulation: products are generated one at a time and added with grow_ze.
+// Cost O(n^2) two_sums in the worst case; n <= 96 (D=3) / 960 (D=4); it only runs when the filter fails.
+template <int D>
+DLI_HD inline int orient_exact(const double *pts) {
+  double e[ExactCap<D>::value];
+  int n = 0;
+  // iterate over the rows r left out (the Laplace expansion along the ones column) and over all
+  // permutations of the D columns for the remaining D rows.
+  int rows[D];
+  for (int r = 0; r <= D; r++) {
+    int c = 0;
+    for (int i = 0; i <= D; i++)
+      if (i != r) rows[c++] = i;
+    // sign of the cofactor of entry (r, D) (ones as the LAST column): (-1)^(r + D)
+    int base_sign = ((r + D) & 1) ? -1 : 1;
+    // Heap-free permutation enumeration via factorial number system
+    constexpr int F = ExactCap<D>::fact;
+    for (int code = 0; code < F; code++) {
+      int perm[D], avail[D];
+      for (int i = 0; i < D; i++) avail[i] = i;
+      int cc = code, parity = 0, left = D;
+      for (int i = 0; i < D; i++) {
+        int radix = left;
+        int idx = cc % radix;
+        cc /= radix;
+        perm[i] = avail[idx];
+        parity += idx;  // number of smaller remaining elements skipped = inversions contributed
+        for (int j = idx; j < left - 1; j++) avail[j] = avail[j + 1];
+        left--;
+      }
+      double sgn = ((parity & 1) ? -1.0 : 1.0) * (double)base_sign;
+      // exact product of D factors as an expansion t[0..tn)
+      double t[1 << (D - 1)];
+      int tn = 1;
+      t[0] = sgn * pts[rows[0] * D + perm[0]];
+      for (int i = 1; i < D; i++) {
+        double b = pts[rows[i] * D + perm[i]];
+        double u[1 << (D - 1)];
+        int un = 0;
+        for (int j = 0; j < tn; j++) {
+          double p, q;
+          two_prod(t[j], b, p, q);
+          u[un++] = q;
+          u[un++] = p;
+        }
+        for (int j = 0; j < un; j++) t[j] = u[j];
+        tn = un;
+      }
+      // the components of t are exact partial products; add them one by one (any order is exact)
+      for (int j = 0; j < tn; j++)
+        if (t[j] != 0.0) grow_ze(e, n, t[j]);
+    }
+  }
+  return expansion_sign(e, n);
+}
+
+template <int D>
+DLI_HDI int orient(const double *pts) {
+  int s = orient_filtered<D>(pts);
+  return s == 2 ? orient_exact<D>(pts) : s;
+}
+
+// run-time dimension front end for host code (flattener)
+inline int orient_host(int d, const double *pts) {
+  switch (d) {
+    case 2: return orient2d(pts[0], pts[1], pts[2], pts[3], pts[4], pts[5]);
+    case 3: return orient<3>(pts);
+    case 4: return orient<4>(pts);
+    default: return 0;
+  }
+}
+
+}  // namespace dli

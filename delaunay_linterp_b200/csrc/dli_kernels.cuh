@@ -1,0 +1,378 @@
+// dli_kernels.cuh -- __global__ kernels (sm_100a): batched interp (fast + straggler/exact pass),
+// hint-grid construction, per-simplex error evaluator, predicate test hook.
+#pragma once
+#include "dli_device.cuh"
+
+namespace dli {
+
+// stats words in device memory
+enum { ST_STEPS = 0, ST_MAXSTEPS = 1, ST_EXACT = 2, ST_OUTSIDE = 3, ST_HARD = 4, ST_WORDS = 8 };
+
+__device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAcc &st) {
+  // warp-aggregate, one atomic per warp per counter
+  unsigned long long s = st.steps, e = st.exact, o = st.outside;
+  unsigned int mx = st.max_steps;
+  unsigned mask = __activemask();
+  for (int off = 16; off > 0; off >>= 1) {
+    s += __shfl_down_sync(mask, s, off);
+    e += __shfl_down_sync(mask, e, off);
+    o += __shfl_down_sync(mask, o, off);
+    mx = max(mx, __shfl_down_sync(mask, mx, off));
+  }
+  // with a partial mask shfl_down from an inactive lane returns the caller's own value: only use the
+  // aggregated value when the whole warp is here, otherwise fall back to per-thread atomics
+  if (mask == 0xffffffffu) {
+    if ((threadIdx.x & 31) == 0) {
+      if (s) atomicAdd(g + ST_STEPS, s);
+      if (e) atomicAdd(g + ST_EXACT, e);
+      if (o) atomicAdd(g + ST_OUTSIDE, o);
+      atomicMax(g + ST_MAXSTEPS, (unsigned long long)mx);
+    }
+  } else {
+    if (st.steps) atomicAdd(g + ST_STEPS, st.steps);
+    if (st.exact) atomicAdd(g + ST_EXACT, st.exact);
+    if (st.outside) atomicAdd(g + ST_OUTSIDE, st.outside);
+    atomicMax(g + ST_MAXSTEPS, (unsigned long long)st.max_steps);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 2D interp
+// ---------------------------------------------------------------------------------------------
+
+// Fast pass: one thread per query, filter-only predicates, fused epilogue.  Queries it cannot
+// certify (filter failure, hull exit, long walk) are appended to `queue` for k_interp2_full.
+template <bool STATS, int EPI>
+__global__ void __launch_bounds__(256)
+k_interp2_fast(Mesh2View m, int64_t n, const double2 *__restrict__ xs, double *__restrict__ ys,
+               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
+               unsigned int *__restrict__ queue_count, unsigned long long *__restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  StatsAcc st;
+  if (i < n) {
+    double2 q = __ldcs(xs + i);  // streamed once: keep it out of the way of the mesh in L2
+    int f = hint2(m, q.x, q.y);
+    double4 A, B, C;
+    unsigned int steps = 0;
+    bool ok = locate2_fast(m, q.x, q.y, f, A, B, C, steps);
+    if (ok) {
+      if (ys) {
+        double y = (EPI == 0) ? epilogue2_ref(q.x, q.y, A, B, C) : epilogue2_fast(q.x, q.y, A, B, C);
+        __stcs(ys + i, y);
+      }
+      if (simplex_out) __stcs(simplex_out + i, f);
+      if (status_out) status_out[i] = DLI_STATUS_OK;
+      if (STATS) { st.steps = steps; st.max_steps = steps; }
+    } else {
+      unsigned int slot = atomicAdd(queue_count, 1u);
+      queue[slot] = (int32_t)i;
+    }
+  }
+  if (STATS) flush_stats(stats, st);
+}
+
+// Straggler / exact pass over the queue written by the fast pass (count read on the device: no
+// host synchronisation between the two launches).
+template <bool STATS, int EPI>
+__global__ void __launch_bounds__(128)
+k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__ ys,
+               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
+               const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
+               int64_t n_direct /* >= 0: ignore the queue, process queries [0, n_direct) */,
+               unsigned long long *__restrict__ stats) {
+  int64_t cnt = n_direct >= 0 ? n_direct : (int64_t)*queue_count;
+  StatsAcc st;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
+    int64_t i = n_direct >= 0 ? k : (int64_t)queue[k];
+    double2 q = xs[i];
+    double px = q.x, py = q.y;
+    int f = hint2(m, px, py);
+    double4 A, B, C;
+    uint8_t status = locate2_full(m, px, py, f, A, B, C, st);
+    double y;
+    if (status == DLI_STATUS_STEP_LIMIT) {
+      y = __longlong_as_double(0x7ff8000000000000LL);
+    } else {
+      y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
+    }
+    if (ys) ys[i] = y;
+    if (simplex_out) simplex_out[i] = f;
+    if (status_out) status_out[i] = status;
+  }
+  if (STATS) {
+    flush_stats(stats, st);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_direct < 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// dD interp
+// ---------------------------------------------------------------------------------------------
+
+template <int D, bool STATS, int EPI>
+__global__ void __launch_bounds__(128)
+k_interpD_fast(MeshDView m, int64_t n, const double *__restrict__ xs, double *__restrict__ ys,
+               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
+               unsigned int *__restrict__ queue_count, unsigned long long *__restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  StatsAcc st;
+  if (i < n) {
+    double p[D];
+#pragma unroll
+    for (int k = 0; k < D; k++) p[k] = __ldcs(xs + i * D + k);
+    int s = hintD<D>(m, p);
+    SimplexD<D> S;
+    unsigned int steps = 0;
+    bool ok = locateD_fast<D>(m, p, s, S, steps);
+    if (ok) {
+      if (ys) {
+        double y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
+        __stcs(ys + i, y);
+      }
+      if (simplex_out) __stcs(simplex_out + i, s);
+      if (status_out) status_out[i] = DLI_STATUS_OK;
+      if (STATS) { st.steps = steps; st.max_steps = steps; }
+    } else {
+      unsigned int slot = atomicAdd(queue_count, 1u);
+      queue[slot] = (int32_t)i;
+    }
+  }
+  if (STATS) flush_stats(stats, st);
+}
+
+template <int D, bool STATS, int EPI>
+__global__ void __launch_bounds__(64)
+k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ ys,
+               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
+               const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count, int64_t n_direct,
+               unsigned long long *__restrict__ stats) {
+  int64_t cnt = n_direct >= 0 ? n_direct : (int64_t)*queue_count;
+  StatsAcc st;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
+    int64_t i = n_direct >= 0 ? k : (int64_t)queue[k];
+    double p[D];
+#pragma unroll
+    for (int a = 0; a < D; a++) p[a] = xs[i * D + a];
+    int s = hintD<D>(m, p);
+    SimplexD<D> S;
+    uint8_t status = locateD_full<D>(m, p, s, S, st);
+    double y;
+    if (status != DLI_STATUS_OK) {
+      y = __longlong_as_double(0x7ff8000000000000LL);
+      if (status == DLI_STATUS_OUTSIDE_NAN) s = -1;
+    } else {
+      y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
+    }
+    if (ys) ys[i] = y;
+    if (simplex_out) simplex_out[i] = s;
+    if (status_out) status_out[i] = status;
+  }
+  if (STATS) {
+    flush_stats(stats, st);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_direct < 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+  }
+}
+
+__global__ void k_fill_nomesh(int64_t n, double *ys, int32_t *simplex_out, uint8_t *status_out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (ys) ys[i] = __longlong_as_double(0x7ff8000000000000LL);
+  if (simplex_out) simplex_out[i] = -1;
+  if (status_out) status_out[i] = DLI_STATUS_NO_MESH;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Hint grid: cell -> a simplex containing (or near) the cell centre.  Hints need not be exact:
+// any simplex is a valid walk start, so plain floating-point tests are used here.
+// ---------------------------------------------------------------------------------------------
+
+struct GridView {
+  double o[DLI_MAX_DIM], cell[DLI_MAX_DIM], ic[DLI_MAX_DIM];
+  int g[DLI_MAX_DIM];
+  int64_t cells;
+};
+
+// one thread per simplex: visit the cells of its bounding box whose centre lies inside it
+template <int D>
+__global__ void k_hint_raster(GridView gv, int ns, const double *__restrict__ vrec, int vs, const int32_t *__restrict__ srec,
+                              int ss, int32_t *__restrict__ hint) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  double x[(D + 1) * D];
+  int lo[D], hi[D];
+  for (int i = 0; i <= D; i++) {
+    int v = srec[(size_t)s * ss + i];
+    for (int k = 0; k < D; k++) x[i * D + k] = vrec[(size_t)v * vs + k];
+  }
+  int64_t total = 1;
+  for (int k = 0; k < D; k++) {
+    double mn = x[k], mx = x[k];
+    for (int i = 1; i <= D; i++) { mn = fmin(mn, x[i * D + k]); mx = fmax(mx, x[i * D + k]); }
+    // cells whose centre o + (c + 0.5) * cell lies in [mn, mx]
+    int a = (int)ceil((mn - gv.o[k]) * gv.ic[k] - 0.5);
+    int b = (int)floor((mx - gv.o[k]) * gv.ic[k] - 0.5);
+    lo[k] = max(a, 0);
+    hi[k] = min(b, gv.g[k] - 1);
+    if (hi[k] < lo[k]) return;
+    total *= (hi[k] - lo[k] + 1);
+  }
+  // whole-simplex orientation (positive by construction); tolerance relative to it
+  double m0[D * D];
+  for (int i = 0; i < D; i++)
+    for (int k = 0; k < D; k++) m0[i * D + k] = x[i * D + k] - x[D * D + k];
+  double perm;
+  double whole = DetPerm<D>::eval(m0, perm);
+  double tol = -1e-9 * fabs(whole);
+  int c[D];
+  for (int k = 0; k < D; k++) c[k] = lo[k];
+  for (int64_t it = 0; it < total; it++) {
+    double p[D];
+    for (int k = 0; k < D; k++) p[k] = gv.o[k] + (c[k] + 0.5) * gv.cell[k];
+    bool inside = true;
+    for (int j = 0; j <= D && inside; j++) {
+      double pts[(D + 1) * D];
+      for (int i = 0; i <= D; i++)
+        for (int k = 0; k < D; k++) pts[i * D + k] = (i == j) ? p[k] : x[i * D + k];
+      double mm[D * D];
+      for (int i = 0; i < D; i++)
+        for (int k = 0; k < D; k++) mm[i * D + k] = pts[i * D + k] - pts[D * D + k];
+      double pm;
+      if (DetPerm<D>::eval(mm, pm) < tol) inside = false;
+    }
+    if (inside) {
+      size_t idx = 0;
+      for (int k = D - 1; k >= 0; k--) idx = idx * gv.g[k] + c[k];
+      hint[idx] = s;
+    }
+    for (int k = 0; k < D; k++) {  // odometer
+      if (++c[k] <= hi[k]) break;
+      c[k] = lo[k];
+    }
+  }
+}
+
+// empty cells (-1) adopt a neighbour's hint; in place (any neighbour's value is a valid hint)
+template <int D>
+__global__ void k_hint_dilate(GridView gv, int32_t *hint, unsigned int *remaining) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= gv.cells) return;
+  if (hint[idx] >= 0) return;
+  int64_t stride = 1, rem = idx;
+  int found = -1;
+  for (int k = 0; k < D; k++) {
+    int ck = (int)(rem % gv.g[k]);
+    rem /= gv.g[k];
+    if (found < 0 && ck > 0) { int v = ((volatile int32_t *)hint)[idx - stride]; if (v >= 0) found = v; }
+    if (found < 0 && ck < gv.g[k] - 1) { int v = ((volatile int32_t *)hint)[idx + stride]; if (v >= 0) found = v; }
+    stride *= gv.g[k];
+  }
+  if (found >= 0) hint[idx] = found;
+  else atomicAdd(remaining, 1u);
+}
+__global__ void k_hint_fill_rest(int64_t cells, int32_t *hint, int32_t value) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < cells && hint[idx] < 0) hint[idx] = value;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-simplex error evaluator (src/delaunay_2_interp.h:725-741 and helpers; closed form of the
+// reference's SVD: err = (phi - mean f)^2 * |e_z - proj_span(e_z)|^2, span = span{w_i - w_0},
+// w_i = (v_i, f_i) the lifted vertices of the (sub-)simplex).
+// ---------------------------------------------------------------------------------------------
+
+// items: item_verts [n][D+1] padded with -1 (device); centroid accumulated in slot order then divided
+template <int D>
+__global__ void k_error_prepare(int64_t n, const int32_t *__restrict__ item_verts, const double *__restrict__ vrec,
+                                int vs, double *__restrict__ centroids) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double c[D];
+  for (int k = 0; k < D; k++) c[k] = 0.0;
+  int cnt = 0;
+  for (int a = 0; a <= D; a++) {
+    int v = item_verts[i * (D + 1) + a];
+    if (v < 0) break;
+    for (int k = 0; k < D; k++) c[k] += vrec[(size_t)v * vs + k];
+    cnt++;
+  }
+  for (int k = 0; k < D; k++) centroids[i * D + k] = c[k] / cnt;
+}
+
+template <int D>
+__global__ void k_error_finish(int64_t n, const int32_t *__restrict__ item_verts, const double *__restrict__ vrec,
+                               int vs, const double *__restrict__ phi, double *__restrict__ err) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  constexpr int N = D + 1;  // lifted dimension
+  double w[(D + 1) * N];
+  int np = 0;
+  double fbar = 0.0;
+  for (int a = 0; a <= D; a++) {
+    int v = item_verts[i * (D + 1) + a];
+    if (v < 0) break;
+    for (int k = 0; k < D; k++) w[a * N + k] = vrec[(size_t)v * vs + k];
+    w[a * N + D] = vrec[(size_t)v * vs + D];
+    fbar += w[a * N + D];
+    np++;
+  }
+  fbar /= np;
+  // modified Gram-Schmidt on u_j = w_j - w_0 (j = 1..np-1), then orthogonalise e_z against them
+  double q[D * N];
+  int nq = 0;
+  for (int j = 1; j < np; j++) {
+    double u[N];
+    for (int k = 0; k < N; k++) u[k] = w[j * N + k] - w[k];
+    for (int pass = 0; pass < 2; pass++)  // re-orthogonalise once
+      for (int t = 0; t < nq; t++) {
+        double d = 0.0;
+        for (int k = 0; k < N; k++) d += u[k] * q[t * N + k];
+        for (int k = 0; k < N; k++) u[k] -= d * q[t * N + k];
+      }
+    double nn = 0.0;
+    for (int k = 0; k < N; k++) nn += u[k] * u[k];
+    if (nn > 0.0) {
+      double inv = 1.0 / sqrt(nn);
+      for (int k = 0; k < N; k++) q[nq * N + k] = u[k] * inv;
+      nq++;
+    }
+  }
+  double r[N];
+  for (int k = 0; k < N; k++) r[k] = (k == D) ? 1.0 : 0.0;
+  for (int pass = 0; pass < 2; pass++)
+    for (int t = 0; t < nq; t++) {
+      double d = 0.0;
+      for (int k = 0; k < N; k++) d += r[k] * q[t * N + k];
+      for (int k = 0; k < N; k++) r[k] -= d * q[t * N + k];
+    }
+  double fac = 0.0;
+  for (int k = 0; k < N; k++) fac += r[k] * r[k];
+  double delta = phi[i] - fbar;
+  err[i] = delta * delta * fac;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Test hook: the device predicate on explicit point sets
+// ---------------------------------------------------------------------------------------------
+template <int D>
+__global__ void k_debug_orient(int64_t n, const double *__restrict__ pts, int8_t *__restrict__ sign_out,
+                               uint8_t *__restrict__ exact_used) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double p[(D + 1) * D];
+  for (int k = 0; k < (D + 1) * D; k++) p[k] = pts[i * (D + 1) * D + k];
+  int s;
+  bool ex;
+  if constexpr (D == 2) {
+    s = orient2d_filtered(p[0], p[1], p[2], p[3], p[4], p[5]);
+    ex = (s == 2);
+    if (ex) s = orient2d_exact(p[0], p[1], p[2], p[3], p[4], p[5]);
+  } else {
+    s = orient_filtered<D>(p);
+    ex = (s == 2);
+    if (ex) s = orient_exact<D>(p);
+  }
+  sign_out[i] = (int8_t)s;
+  if (exact_used) exact_used[i] = ex;
+}
+
+}  // namespace dli

@@ -1,0 +1,185 @@
+/*
+ * dli.h -- C ABI of the B200 batched Delaunay linear-interpolation engine.
+ *
+ * This is the drop-in boundary for the reference's interp hot path.  The reference
+ * (rncarpio/delaunay_linterp) has no FFI layer: the path is a header-only C++ member function
+ * called once per query.  Each entry point below names the reference interface it replaces
+ * (paths relative to the reference tree).  All pointers are plain C arrays, row-major; no C++
+ * or torch types cross this boundary.  See INTEGRATION.md for the reference-side bindings.
+ *
+ * Conventions
+ *   - return value: 0 = success, negative = error (dli_last_error() has the message).  No
+ *     exception ever crosses the ABI.
+ *   - query / result pointers may be HOST or DEVICE pointers (detected with
+ *     cudaPointerGetAttributes).  With device pointers the call only enqueues work on `stream`
+ *     and returns; with host pointers it runs a chunked H2D / compute / D2H pipeline and returns
+ *     when the results are in the host buffers.
+ *   - per-query conditions are reported in status_out, never as an error return.
+ *   - a mesh handle is immutable apart from dli_mesh_set_values(); interp/locate calls on the
+ *     same mesh may be issued concurrently from several host threads / streams.
+ *   - the library needs a CUDA device (sm_100a).  There is no CPU fallback: without a device
+ *     every call that touches the GPU fails with DLI_ERR_CUDA.
+ */
+#ifndef DLI_H_
+#define DLI_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLI_VERSION 1
+#define DLI_MAX_DIM 6
+
+/* error returns */
+#define DLI_OK 0
+#define DLI_ERR_ARG (-1)     /* bad argument */
+#define DLI_ERR_MESH (-2)    /* invalid mesh: degenerate simplex, bad index, non-manifold facet */
+#define DLI_ERR_CUDA (-3)    /* CUDA runtime error or no device */
+#define DLI_ERR_NOMEM (-4)
+#define DLI_ERR_UNSUPPORTED (-5)
+
+/* per-query status (status_out) */
+#define DLI_STATUS_OK 0                /* located in a closed simplex (FACE / EDGE / VERTEX in CGAL terms) */
+#define DLI_STATUS_OUTSIDE_PROJECTED 1 /* 2D: outside the hull; projected on the hull edge line and re-located
+                                          (src/delaunay_2_interp.h:530-545) */
+#define DLI_STATUS_OUTSIDE_NAN 2       /* dD: outside the hull; value is quiet NaN, simplex -1
+                                          (src/delaunay_d_interp.h:1005-1008) */
+#define DLI_STATUS_STEP_LIMIT 3        /* walk exceeded max_walk_steps (invalid / non-Delaunay mesh); value NaN.
+                                          The 2D header wrapper turns this into std::invalid_argument
+                                          (src/delaunay_2_interp.h:546-551) */
+#define DLI_STATUS_NO_MESH 4           /* mesh has no simplex (fewer than dim+1 affinely independent points) */
+
+typedef struct dli_mesh dli_mesh; /* opaque: owns the device structure-of-arrays buffers and the hint grid */
+
+typedef struct dli_options {
+  int32_t struct_size;            /* sizeof(dli_options); lets the struct grow compatibly */
+  int32_t device;                 /* CUDA device ordinal, -1 = current device */
+  float hint_cells_per_simplex;   /* start-hint grid resolution; <= 0 = default (2D: 2.0, dD: 1.0) */
+  int32_t max_walk_steps;         /* <= 0 = default (n_simplices + 16) */
+  int32_t sort_queries;           /* 0 = evaluate in input order (default), 1 = bin queries by hint cell first */
+  int32_t epilogue;               /* 0 = reference operation order (partial-pivot LU determinants, default),
+                                     1 = closed-form solve (faster, differs in the last ulps on slivers) */
+  int32_t threads_per_block;      /* <= 0 = default */
+  int32_t reserved[9];
+} dli_options;
+
+/* fills *opt with the defaults */
+void dli_options_init(dli_options *opt);
+
+/*
+ * Flattener.  Replaces the pointer-based CGAL containers the path reads:
+ *   2D  Delaunay_2 / Triangulation_data_structure_2 (src/delaunay_2_interp.h:66-95, member m_pTriang :405;
+ *       accessors face->vertex(i), face->neighbor(i), vertex->point(), vertex->info())
+ *   dD  Delaunay_d + m_pointMap (src/delaunay_d_interp.h:303,757; modified_cgal/Delaunay_d.h:389-396,
+ *       426-439, 1015-1028)
+ * coords            [n_vertices][dim]
+ * f                 [n_vertices]
+ * simplex_vertices  [n_simplices][dim+1]   finite simplices only, any orientation
+ * simplex_neighbors [n_simplices][dim+1]   k-th entry is the simplex opposite vertex k, -1 across the hull;
+ *                                          NULL = derive from shared facets
+ * The arrays are copied; the caller keeps ownership.  n_simplices == 0 is allowed (every query then
+ * reports DLI_STATUS_NO_MESH).
+ */
+int dli_mesh_create(int dim, int64_t n_vertices, const double *coords, const double *f, int64_t n_simplices,
+                    const int32_t *simplex_vertices, const int32_t *simplex_neighbors, const dli_options *opt,
+                    dli_mesh **out);
+
+/* same geometry, new vertex values (vertex->info() = f, src/delaunay_2_interp.h:446) */
+int dli_mesh_set_values(dli_mesh *mesh, const double *f /* [n_vertices], host */);
+
+void dli_mesh_destroy(dli_mesh *mesh);
+
+int dli_mesh_dim(const dli_mesh *mesh);
+int64_t dli_mesh_num_vertices(const dli_mesh *mesh);
+int64_t dli_mesh_num_simplices(const dli_mesh *mesh);
+/* bytes of device memory held by the mesh (records + hint grid) */
+int64_t dli_mesh_device_bytes(const dli_mesh *mesh);
+/* canonical (positively oriented) simplices as the engine stores them, in the caller's numbering; host arrays,
+   either may be NULL.  Vertex order inside a simplex is the order the barycentric epilogue uses. */
+int dli_mesh_get_simplices(const dli_mesh *mesh, int32_t *simplex_vertices, int32_t *simplex_neighbors);
+
+/*
+ * Batched interp.  Replaces, for n queries at once,
+ *   Delaunay_incremental_interp_2::interp / interp_point   (src/delaunay_2_interp.h:510-513, 515-572)
+ *   Delaunay_incremental_interp_d::interp / interp_point   (src/delaunay_d_interp.h:982-986, 988-1010)
+ * i.e. locate (CGAL Triangulation_2::locate / Delaunay_d::locate, modified_cgal/Delaunay_d.h:811-850)
+ * + compute_barycentric_coords (:223-239 / :628-650) + weighted gather (:563-569 / :998-1004).
+ * xs          [n][dim]  host or device
+ * ys          [n]       same memory space as xs
+ * simplex_out [n] or NULL: id (caller's numbering) of the simplex used, -1 if none
+ * status_out  [n] or NULL: DLI_STATUS_*
+ * stream      cudaStream_t (as void*), NULL = default stream
+ */
+int dli_interp(const dli_mesh *mesh, int64_t n, const double *xs, double *ys, int32_t *simplex_out,
+               uint8_t *status_out, void *stream);
+
+/* Point location only (CGAL locate as used at src/delaunay_2_interp.h:525, src/delaunay_d_interp.h:990).
+   2D queries outside the hull report the hull face behind the canonical visible hull edge. */
+int dli_locate(const dli_mesh *mesh, int64_t n, const double *xs, int32_t *simplex_out, uint8_t *status_out,
+               void *stream);
+
+/*
+ * Batched per-simplex error evaluator.  Replaces compute_simplex_error + add_error_of_boundary_subsimplices
+ * (src/delaunay_2_interp.h:725-741, 683-699, 657-680, 331-342; dD src/delaunay_d_interp.h:1078-1093, 810-848)
+ * for every simplex of the mesh at once.  The host callback m_fn (src/delaunay_2_interp.h:408, 421-431)
+ * stays on the host, between the two calls:
+ *     n = dli_simplex_error_count(mesh);
+ *     dli_simplex_error_prepare(mesh, centroids, item_simplex, item_vertices);   // device kernel
+ *     phi[i] = fn(centroids[i]);                                                 // caller
+ *     dli_simplex_error_finish(mesh, n, phi, err);                               // device kernel
+ * Items: every simplex, then for each hull facet of it every vertex subset of size >= 2 (duplicates across
+ * simplices kept, as in the reference).  Order: simplices ascending; inside a simplex the simplex itself,
+ * then hull facets by ascending slot, subsets by ascending bitmask.
+ * Host pointers.  item_vertices is [n][dim+1], padded with -1.
+ */
+int64_t dli_simplex_error_count(const dli_mesh *mesh);
+int dli_simplex_error_prepare(const dli_mesh *mesh, double *centroids /* [n][dim] */,
+                              int32_t *item_simplex /* [n] or NULL */, int32_t *item_vertices /* [n][dim+1] or NULL */);
+int dli_simplex_error_finish(const dli_mesh *mesh, int64_t n, const double *f_at_centroids /* [n] */,
+                             double *err /* [n] */);
+
+/*
+ * Multi-GPU replication support: the mesh is a set of device buffers.  Rank 0 flattens; the other ranks
+ * allocate an empty mesh of the same shape from the 16-word header and receive the buffers through any
+ * broadcast (NCCL / torch.distributed) on the raw device pointers.
+ */
+#define DLI_MESH_HEADER_WORDS 16
+int dli_mesh_header(const dli_mesh *mesh, int64_t header[DLI_MESH_HEADER_WORDS]);
+int dli_mesh_create_from_header(const int64_t header[DLI_MESH_HEADER_WORDS], const dli_options *opt, dli_mesh **out);
+int dli_mesh_num_buffers(const dli_mesh *mesh);
+int dli_mesh_buffer(const dli_mesh *mesh, int index, void **device_ptr, int64_t *bytes);
+/* hint-grid geometry (origin, cell size, 1/cell size; 3 x DLI_MAX_DIM doubles), host side of the replication */
+int dli_mesh_get_grid_params(const dli_mesh *mesh, double *out /* [3 * DLI_MAX_DIM] */);
+int dli_mesh_set_grid_params(dli_mesh *mesh, const double *in /* [3 * DLI_MAX_DIM] */);
+
+/* instrumentation: counters of the most recent interp/locate on this mesh that had `collect_stats` enabled */
+typedef struct dli_stats {
+  int64_t queries;
+  int64_t walk_steps;       /* simplices visited, all queries */
+  int64_t max_walk_steps;   /* longest single walk */
+  int64_t exact_fallbacks;  /* orientation tests that fell through the static filter */
+  int64_t outside;          /* queries that left the hull */
+  int64_t kernel_launches;  /* launches issued by the most recent call */
+} dli_stats;
+int dli_mesh_collect_stats(dli_mesh *mesh, int enable);
+int dli_mesh_get_stats(const dli_mesh *mesh, dli_stats *out);
+
+/* test hook: sign of the orientation determinant of n simplices given as [n][dim+1][dim] device-side
+   filtered-exact predicate (the one the walk uses); host pointers; sign_out [n] in {-1,0,1};
+   exact_used_out [n] or NULL tells whether the exact fallback ran. */
+int dli_debug_orient(int dim, int64_t n, const double *pts, int8_t *sign_out, uint8_t *exact_used_out);
+
+/* the same predicate evaluated on the host (the flattener uses it to orient simplices); needs no GPU */
+int dli_debug_orient_host(int dim, int64_t n, const double *pts, int8_t *sign_out);
+
+/* thread-local message for the last non-zero return on this thread */
+const char *dli_last_error(void);
+/* number of CUDA devices visible (0 if none / no driver) */
+int dli_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLI_H_ */

@@ -1,0 +1,151 @@
+"""GPU parity: CUDA path (through the C ABI) vs the CPU oracle, 2D."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle.oracle import OracleMesh
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-12  # north_star: values within 1e-12 relative in fp64
+
+
+def _check_parity(mesh, om, q, ys, simplex, status, allow_outside=True):
+    yo, so, sto = om.interp(q, mode=1, nthreads=8)
+    assert np.array_equal(status, sto), "status codes differ"
+    inside = sto == 0
+    # located simplex: identical for strictly interior queries, any incident simplex otherwise
+    contains, strict_o = om.classify(q, so)
+    contains_g, _ = om.classify(q, simplex)
+    assert contains_g[inside].all(), "GPU returned a simplex that does not contain the query"
+    same = simplex == so
+    assert same[inside & strict_o].all(), "interior query located in a different simplex"
+    # values
+    scale = np.maximum(np.abs(yo), 1e-300)
+    rel = np.abs(ys - yo) / scale
+    assert np.all(rel[np.isfinite(yo)] <= REL_TOL), "max rel diff %g" % rel[np.isfinite(yo)].max()
+    # where the simplex is identical the arithmetic is the same operation order: bit-exact
+    bit = same & np.isfinite(yo)
+    assert np.array_equal(ys[bit], yo[bit])
+    return yo, so, sto
+
+
+def test_config1_readme_grid(gpu):
+    import delaunay_linterp_b200 as dl
+    for lo, want in ((0.0, 5.800002), (0.01, 1.909975)):
+        c, f, t = helpers.grid_mesh(lo)
+        q = helpers.grid_queries(lo)
+        m = dl.Mesh(c, f, t)
+        ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+        sse = float(np.sum((helpers.cobb_douglas(q) - ys) ** 2))
+        assert abs(sse - want) < 5e-7, sse   # README.md:130 prints 5.800002
+        om = OracleMesh(c, f, t)
+        _check_parity(m, om, q, ys, s, st)
+
+
+@pytest.mark.parametrize("nv,nq,seed", [(1000, 20000, 11), (100000, 400000, 12)])
+def test_random_mesh_inside_and_outside(gpu, nv, nq, seed):
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, nv, seed)
+    rng = np.random.default_rng(seed + 100)
+    q = rng.random((nq, 2)) * 1.1 - 0.05          # ~17% outside the hull
+    # add exact vertices, edge midpoints and far-away points
+    q[:200] = pts[:200]
+    q[200:400] = 0.5 * (pts[sv[:200, 0]] + pts[sv[:200, 1]])
+    q[400:410] = [[-3.0, 0.5], [4.0, 0.5], [0.5, -7.0], [0.5, 9.0], [-2, -2], [3, 3], [-2, 3], [3, -2], [0.5, 1e6], [-1e6, 0.5]]
+    m = dl.Mesh(pts, f, sv, sn)
+    m.collect_stats(True)
+    ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+    stats = m.stats()
+    om = OracleMesh(pts, f, sv, sn)
+    _check_parity(m, om, q, ys, s, st)
+    assert stats["outside"] == int((st == 1).sum())
+    assert stats["walk_steps"] >= nq
+    # neighbours derived by the library give the same answers
+    m2 = dl.Mesh(pts, f, sv, None)
+    ys2 = m2.interp(q)
+    assert np.array_equal(ys, ys2, equal_nan=True)
+    # locate-only agrees with interp's simplex
+    s2 = m.locate(q)
+    assert np.array_equal(s, s2)
+
+
+def test_device_pointer_path_matches_host_path(gpu):
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 5000, 21)
+    q = np.random.default_rng(22).random((100000, 2))
+    m = dl.Mesh(pts, f, sv, sn)
+    ys_h = m.interp(q)
+    xq = torch.from_numpy(q).cuda()
+    ys_d, s_d, st_d = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(ys_h, ys_d.cpu().numpy(), equal_nan=True)
+
+
+def test_closed_form_epilogue_within_tolerance(gpu):
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 20000, 31)
+    q = np.random.default_rng(32).random((200000, 2)) * 0.96 + 0.02
+    y0 = dl.Mesh(pts, f, sv, sn).interp(q)
+    y1 = dl.Mesh(pts, f, sv, sn, epilogue="closed_form").interp(q)
+    rel = np.abs(y1 - y0) / np.maximum(np.abs(y0), 1e-300)
+    assert rel.max() < 1e-10, rel.max()     # slivers: see SURVEY appendix A.2
+    assert np.median(rel) < 1e-15
+
+
+def test_affine_reproduction_and_set_values(gpu):
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 3000, 41)
+    m = dl.Mesh(pts, f, sv, sn)
+    g = 2.0 + 3.0 * pts[:, 0] - 1.5 * pts[:, 1]
+    m.set_values(g)
+    q = np.random.default_rng(42).random((50000, 2)) * 0.9 + 0.05
+    ys = m.interp(q)
+    want = 2.0 + 3.0 * q[:, 0] - 1.5 * q[:, 1]
+    assert np.max(np.abs(ys - want)) < 1e-12
+    # vertex queries return the vertex value
+    yv = m.interp(pts[:500])
+    assert np.max(np.abs(yv - g[:500])) < 1e-13
+
+
+def test_empty_and_tiny_inputs(gpu):
+    import delaunay_linterp_b200 as dl
+    pts = np.array([[0.0, 0.0], [1.0, 0.0], [0.0, 1.0]])
+    m = dl.Mesh(pts, np.array([1.0, 2.0, 3.0]), np.array([[0, 1, 2]], dtype=np.int32))
+    assert m.interp(np.zeros((0, 2))).shape == (0,)
+    ys, st = m.interp(np.array([[0.25, 0.25], [2.0, 2.0], [0.0, 0.0]]), return_status=True)
+    assert ys[0] == 1.0 + 0.25 * 1 + 0.25 * 2 and st[0] == 0
+    assert st[1] == dl.STATUS_OUTSIDE_PROJECTED and abs(ys[1] - 2.5) < 1e-15   # projected on the hypotenuse midpoint
+    assert ys[2] == 1.0
+    # a mesh without simplices: every query reports NO_MESH and NaN
+    m0 = dl.Mesh(pts[:2], np.array([1.0, 2.0]), np.zeros((0, 3), np.int32))
+    y0, s0, st0 = m0.interp(np.array([[0.1, 0.1]]), return_simplex=True, return_status=True)
+    assert np.isnan(y0[0]) and s0[0] == -1 and st0[0] == dl.STATUS_NO_MESH
+    # degenerate simplex rejected
+    with pytest.raises(dl.DliError):
+        dl.Mesh(np.array([[0.0, 0.0], [1.0, 1.0], [2.0, 2.0]]), np.zeros(3), np.array([[0, 1, 2]], dtype=np.int32))
+
+
+def test_device_predicate_adversarial(gpu):
+    """orientation signs of near-degenerate triples vs exact rationals"""
+    import delaunay_linterp_b200 as dl
+    from oracle import pyoracle
+    rng = np.random.default_rng(51)
+    n = 3000
+    a = rng.random((n, 2))
+    b = rng.random((n, 2))
+    t = rng.random(n)
+    c = a + (b - a) * t[:, None]                    # nearly collinear (rounded)
+    k = rng.integers(-2, 3, size=n)
+    for i in range(n):                              # nudge by a few ulps
+        for _ in range(abs(int(k[i]))):
+            c[i, 1] = np.nextafter(c[i, 1], 2.0 if k[i] > 0 else -1.0)
+    c[:50] = a[:50]                                 # exact duplicates -> 0
+    pts = np.stack([a, b, c], axis=1)
+    sign, used = dl.debug_orient(pts)
+    want = np.array([pyoracle.orient(p.tolist()) for p in pts], dtype=np.int8)
+    assert np.array_equal(sign, want)
+    assert used.mean() > 0.1                        # these inputs do exercise the exact fallback
+    sign_h = dl.debug_orient(pts, on_device=False)
+    assert np.array_equal(sign_h, want)
