@@ -30,7 +30,8 @@ class Options(C.Structure):
         ("sort_queries", C.c_int32),
         ("epilogue", C.c_int32),
         ("threads_per_block", C.c_int32),
-        ("reserved", C.c_int32 * 9),
+        ("queries_per_warp", C.c_int32),
+        ("reserved", C.c_int32 * 8),
     ]
 
 
@@ -42,6 +43,9 @@ class Stats(C.Structure):
         ("exact_fallbacks", C.c_int64),
         ("outside", C.c_int64),
         ("kernel_launches", C.c_int64),
+        ("fast_kernel_launches", C.c_int64),
+        ("fast_kernel_ms", C.c_double),
+        ("full_kernel_ms", C.c_double),
     ]
 
 
@@ -69,6 +73,8 @@ SYMBOLS = [
     ("dli_mesh_create_from_header", C.c_int, [C.POINTER(C.c_int64), C.POINTER(Options), C.POINTER(_vp)]),
     ("dli_mesh_num_buffers", C.c_int, [_vp]),
     ("dli_mesh_buffer", C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_int64)]),
+    ("dli_mesh_buffer_read", C.c_int, [_vp, C.c_int, _vp]),
+    ("dli_mesh_buffer_write", C.c_int, [_vp, C.c_int, _vp]),
     ("dli_mesh_get_grid_params", C.c_int, [_vp, _vp]),
     ("dli_mesh_set_grid_params", C.c_int, [_vp, _vp]),
     ("dli_mesh_collect_stats", C.c_int, [_vp, C.c_int]),

@@ -68,9 +68,12 @@ struct dli_mesh {
   std::vector<int32_t> h_item_simplex, h_item_verts;
   int32_t *d_item_verts = nullptr;
   // stats
-  bool collect_stats = false;
+  bool collect_stats = false;   // counters (atomics in the kernels)
+  bool collect_timing = false;  // CUDA events around the interp kernels
   unsigned long long *d_stats = nullptr;
   mutable dli_stats last{};
+  mutable std::mutex ev_mu;
+  mutable std::vector<cudaEvent_t> ev;  // triples (before fast, after fast, after full)
 };
 
 static void mesh_free(dli_mesh *m) {
@@ -82,6 +85,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_hint);
   cudaFree(m->d_item_verts);
   cudaFree(m->d_stats);
+  for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
   delete m;
 }
 
@@ -95,6 +99,7 @@ extern "C" void dli_options_init(dli_options *o) {
   o->sort_queries = 0;
   o->epilogue = 0;
   o->threads_per_block = 0;
+  o->queries_per_warp = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -412,15 +417,26 @@ MeshDView viewD(const dli_mesh *m) {
   return v;
 }
 
-constexpr int64_t kChunk = 1ll << 24;  // queries per launch pair; bounds the straggler queue (64 MiB)
+constexpr int64_t kChunk = 1ll << 30;      // queries per launch pair (int32 indices in the straggler queue)
+constexpr int64_t kQueueCap = 1ll << 22;   // straggler queue entries (16 MiB); overflow = the full pass re-runs the batch
 
 struct Launch {
   const dli_mesh *m;
   cudaStream_t st;
   int32_t *queue;
   unsigned int *qcount;
+  unsigned int qcap = 0;
   unsigned long long *stats;
   int launches = 0;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  void mark(int i) {
+    if (!m->collect_timing) return;
+    if (cudaEventCreate(&ev[i]) == cudaSuccess) cudaEventRecord(ev[i], st);
+    if (i == 2) {
+      std::lock_guard<std::mutex> lk(m->ev_mu);
+      for (int k = 0; k < 3; k++) m->ev.push_back(ev[k]);
+    }
+  }
 };
 
 template <bool STATS, int EPI>
@@ -428,19 +444,31 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   Mesh2View v = view2(L.m);
   int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : 256;
   tpb = std::min(256, std::max(32, tpb / 32 * 32));
-  k_interp2_fast<STATS, EPI><<<(unsigned)((n + tpb - 1) / tpb), tpb, 0, L.st>>>(
-      v, n, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.stats);
+  // queries per warp: large enough to amortise the drain at the end of a warp's range, small enough to
+  // give every SM many CTAs
+  int per_warp = L.m->opt.queries_per_warp > 0 ? L.m->opt.queries_per_warp : 1024;
+  while (per_warp > 32 && n / per_warp < 148 * 64) per_warp >>= 1;
+  int64_t warps = (n + per_warp - 1) / per_warp;
+  int wpb = tpb / 32;
+  L.mark(0);
+  k_interp2_fast<STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
+      v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  L.mark(1);
   k_interp2_full<STATS, EPI><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
-                                                         L.qcount, -1, L.stats);
+                                                         L.qcount, L.qcap, n, L.stats);
+  L.mark(2);
   L.launches += 2;
 }
 template <int D, bool STATS, int EPI>
 void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
   MeshDView v = viewD(L.m);
   int tpb = 128;
+  L.mark(0);
   k_interpD_fast<D, STATS, EPI><<<(unsigned)((n + tpb - 1) / tpb), tpb, 0, L.st>>>(v, n, xs, ys, so, sto, L.queue,
-                                                                                    L.qcount, L.stats);
-  k_interpD_full<D, STATS, EPI><<<148 * 2, 64, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, -1, L.stats);
+                                                                                    L.qcount, L.qcap, L.stats);
+  L.mark(1);
+  k_interpD_full<D, STATS, EPI><<<148 * 2, 64, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
+  L.mark(2);
   L.launches += 2;
 }
 
@@ -463,12 +491,13 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     if (launches) *launches += 1;
     return DLI_OK;
   }
-  int64_t cap = std::min(n, kChunk);
+  int64_t cap = std::min(n, kQueueCap);
   int32_t *queue = nullptr;
   CU(cudaMallocAsync(&queue, sizeof(int32_t) * (size_t)cap + 16, st));
   unsigned int *qcount = reinterpret_cast<unsigned int *>(queue + cap);
   // (queue + cap) is 4-byte aligned, which is all an unsigned int needs
-  Launch L{m, st, queue, qcount, m->d_stats};
+  Launch L;
+  L.m = m; L.st = st; L.queue = queue; L.qcount = qcount; L.qcap = (unsigned int)cap; L.stats = m->d_stats;
   if (m->collect_stats) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, st));
   const int d = m->dim;
   for (int64_t off = 0; off < n; off += kChunk) {
@@ -589,7 +618,13 @@ extern "C" int dli_locate(const dli_mesh *m, int64_t n, const double *xs, int32_
 
 extern "C" int dli_mesh_collect_stats(dli_mesh *m, int enable) {
   if (!m) return fail(DLI_ERR_ARG, "NULL mesh");
-  m->collect_stats = enable != 0;
+  m->collect_stats = (enable & 1) != 0;
+  m->collect_timing = (enable & 2) != 0;
+  {
+    std::lock_guard<std::mutex> lk(m->ev_mu);
+    for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
+    m->ev.clear();
+  }
   return DLI_OK;
 }
 extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
@@ -604,6 +639,20 @@ extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
   out->exact_fallbacks = (int64_t)w[ST_EXACT];
   out->outside = (int64_t)w[ST_OUTSIDE];
   out->kernel_launches = m->last.kernel_launches;
+  out->fast_kernel_launches = 0;
+  out->fast_kernel_ms = out->full_kernel_ms = 0.0;
+  {
+    std::lock_guard<std::mutex> lk(m->ev_mu);
+    for (size_t i = 0; i + 2 < m->ev.size(); i += 3) {
+      float a = 0.f, b = 0.f;
+      if (cudaEventElapsedTime(&a, m->ev[i], m->ev[i + 1]) == cudaSuccess &&
+          cudaEventElapsedTime(&b, m->ev[i + 1], m->ev[i + 2]) == cudaSuccess) {
+        out->fast_kernel_ms += a;
+        out->full_kernel_ms += b;
+        out->fast_kernel_launches++;
+      }
+    }
+  }
   return DLI_OK;
 }
 
@@ -765,6 +814,28 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }
+  return DLI_OK;
+}
+
+// copy a whole mesh buffer out of / into the mesh; `ptr` may be a host or a device pointer
+extern "C" int dli_mesh_buffer_read(const dli_mesh *m, int index, void *dst) {
+  void *p; int64_t b;
+  int rc = dli_mesh_buffer(m, index, &p, &b);
+  if (rc != DLI_OK) return rc;
+  if (b == 0) return DLI_OK;
+  if (!dst) return fail(DLI_ERR_ARG, "dli_mesh_buffer_read: NULL dst");
+  DeviceGuard guard(m->device);
+  CU(cudaMemcpy(dst, p, (size_t)b, cudaMemcpyDefault));
+  return DLI_OK;
+}
+extern "C" int dli_mesh_buffer_write(dli_mesh *m, int index, const void *src) {
+  void *p; int64_t b;
+  int rc = dli_mesh_buffer(m, index, &p, &b);
+  if (rc != DLI_OK) return rc;
+  if (b == 0) return DLI_OK;
+  if (!src) return fail(DLI_ERR_ARG, "dli_mesh_buffer_write: NULL src");
+  DeviceGuard guard(m->device);
+  CU(cudaMemcpy(p, src, (size_t)b, cudaMemcpyDefault));
   return DLI_OK;
 }
 

@@ -139,17 +139,19 @@ __device__ __forceinline__ int hint2(const Mesh2View &m, double x, double y) {
 struct Face2 {
   int v0, v1, v2, n0, n1, n2;
 };
+// one 32-byte record = one sector = one 256-bit load (LDG.E.256, sm_100+)
 __device__ __forceinline__ Face2 load_face(const Mesh2View &m, int f) {
-  int4 a = __ldg(m.frec + 2 * (size_t)f), b = __ldg(m.frec + 2 * (size_t)f + 1);
   Face2 r;
-  r.v0 = a.x; r.v1 = a.y; r.v2 = a.z; r.n0 = a.w; r.n1 = b.x; r.n2 = b.y;
+  int p0, p1;
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.v0), "=r"(r.v1), "=r"(r.v2), "=r"(r.n0), "=r"(r.n1), "=r"(r.n2), "=r"(p0), "=r"(p1)
+               : "l"(m.frec + 2 * (size_t)f));
   return r;
 }
 __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
-  // one 32-byte record = one sector
-  const double2 *p = reinterpret_cast<const double2 *>(m.vrec + v);
-  double2 lo = __ldg(p), hi = __ldg(p + 1);
-  return make_double4(lo.x, lo.y, hi.x, hi.y);
+  double4 r;
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(m.vrec + v));
+  return r;
 }
 
 // Fast path: static filter only.  Returns true with the containing face's vertices loaded when every

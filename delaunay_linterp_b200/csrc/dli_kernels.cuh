@@ -40,32 +40,85 @@ __device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAc
 // 2D interp
 // ---------------------------------------------------------------------------------------------
 
-// Fast pass: one thread per query, filter-only predicates, fused epilogue.  Queries it cannot
-// certify (filter failure, hull exit, long walk) are appended to `queue` for k_interp2_full.
+// Fast pass.  Each warp owns a contiguous range of `per_warp` queries and runs a lane-level state
+// machine: every loop iteration performs exactly ONE walk step for every lane; a lane whose query
+// finished (epilogue done, or handed to the straggler queue) is refilled with the next unclaimed
+// query of the warp's range at the top of the next iteration (ballot/popc rank, no atomics, no
+// shared memory).  Walk-length variance therefore costs no SIMT efficiency in the step body.
+// Predicates are filter-only here; queries it cannot certify (filter failure, hull exit, long walk)
+// are appended to `queue` for k_interp2_full.  If the queue overflows (`queue_cap`), the counter
+// keeps growing and k_interp2_full re-runs the whole batch (degenerate inputs only).
 template <bool STATS, int EPI>
-__global__ void __launch_bounds__(256)
-k_interp2_fast(Mesh2View m, int64_t n, const double2 *__restrict__ xs, double *__restrict__ ys,
+__global__ void __launch_bounds__(256, 4)
+k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
-               unsigned int *__restrict__ queue_count, unsigned long long *__restrict__ stats) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * per_warp;
+  if (base >= n) return;  // warp-uniform
+  const int64_t end = min(n, base + (int64_t)per_warp);
+  int64_t next = base;
+  bool active = false;
+  double px = 0.0, py = 0.0;
+  int f = 0, from = -1;
+  int64_t qi = 0;
+  unsigned int steps = 0;
+  const double fc = filter_const(2);
   StatsAcc st;
-  if (i < n) {
-    double2 q = __ldcs(xs + i);  // streamed once: keep it out of the way of the mesh in L2
-    int f = hint2(m, q.x, q.y);
-    double4 A, B, C;
-    unsigned int steps = 0;
-    bool ok = locate2_fast(m, q.x, q.y, f, A, B, C, steps);
-    if (ok) {
-      if (ys) {
-        double y = (EPI == 0) ? epilogue2_ref(q.x, q.y, A, B, C) : epilogue2_fast(q.x, q.y, A, B, C);
-        __stcs(ys + i, y);
+  for (;;) {
+    unsigned need = __ballot_sync(FULL, !active);
+    if (need) {
+      int64_t idx = next + __popc(need & ((1u << lane) - 1u));
+      if (!active && idx < end) {
+        double2 q = __ldcs(xs + idx);
+        px = q.x; py = q.y;
+        qi = idx;
+        f = hint2(m, px, py);
+        from = -1;
+        steps = 0;
+        active = true;
       }
-      if (simplex_out) __stcs(simplex_out + i, f);
-      if (status_out) status_out[i] = DLI_STATUS_OK;
-      if (STATS) { st.steps = steps; st.max_steps = steps; }
-    } else {
-      unsigned int slot = atomicAdd(queue_count, 1u);
-      queue[slot] = (int32_t)i;
+      next += __popc(need);
+    }
+    if (!__any_sync(FULL, active)) break;
+    if (active) {
+      steps++;
+      Face2 F = load_face(m, f);
+      double4 A = load_vert(m, F.v0), B = load_vert(m, F.v1), C = load_vert(m, F.v2);
+      double ax = A.x - px, ay = A.y - py, bx = B.x - px, by = B.y - py, cx = C.x - px, cy = C.y - py;
+      // edge opposite v0 = (B, C); opposite v1 = (C, A); opposite v2 = (A, B)
+      double l0 = bx * cy, r0 = by * cx, d0 = l0 - r0, e0 = fc * (fabs(l0) + fabs(r0));
+      double l1 = cx * ay, r1 = cy * ax, d1 = l1 - r1, e1 = fc * (fabs(l1) + fabs(r1));
+      double l2 = ax * by, r2 = ay * bx, d2 = l2 - r2, e2 = fc * (fabs(l2) + fabs(r2));
+      bool c0 = (F.n0 >= 0) & (F.n0 == from), c1 = (F.n1 >= 0) & (F.n1 == from), c2 = (F.n2 >= 0) & (F.n2 == from);
+      bool neg0 = (-d0 > e0) & !c0, neg1 = (-d1 > e1) & !c1, neg2 = (-d2 > e2) & !c2;
+      bool give_up = false;
+      if (neg0 | neg1 | neg2) {
+        int nb = neg0 ? F.n0 : (neg1 ? F.n1 : F.n2);
+        if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
+        else { from = f; f = nb; }
+      } else {
+        bool pos = ((d0 > e0) | c0) & ((d1 > e1) | c1) & ((d2 > e2) | c2);
+        if (pos) {
+          if (ys) {
+            double y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
+            __stcs(ys + qi, y);
+          }
+          if (simplex_out) __stcs(simplex_out + qi, f);
+          if (status_out) status_out[qi] = DLI_STATUS_OK;
+          if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
+          active = false;
+        } else {
+          give_up = true;  // a decision the static filter cannot certify
+        }
+      }
+      if (give_up) {
+        unsigned int slot = atomicAdd(queue_count, 1u);
+        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        active = false;
+      }
     }
   }
   if (STATS) flush_stats(stats, st);
@@ -78,12 +131,14 @@ __global__ void __launch_bounds__(128)
 k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
-               int64_t n_direct /* >= 0: ignore the queue, process queries [0, n_direct) */,
+               unsigned int queue_cap, int64_t n /* batch size: processed directly if the queue overflowed */,
                unsigned long long *__restrict__ stats) {
-  int64_t cnt = n_direct >= 0 ? n_direct : (int64_t)*queue_count;
+  int64_t cnt = (int64_t)*queue_count;
+  const bool direct = cnt > (int64_t)queue_cap;
+  if (direct) cnt = n;
   StatsAcc st;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
-    int64_t i = n_direct >= 0 ? k : (int64_t)queue[k];
+    int64_t i = direct ? k : (int64_t)queue[k];
     double2 q = xs[i];
     double px = q.x, py = q.y;
     int f = hint2(m, px, py);
@@ -101,7 +156,7 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
   }
   if (STATS) {
     flush_stats(stats, st);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n_direct < 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
   }
 }
 
@@ -113,7 +168,7 @@ template <int D, bool STATS, int EPI>
 __global__ void __launch_bounds__(128)
 k_interpD_fast(MeshDView m, int64_t n, const double *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
-               unsigned int *__restrict__ queue_count, unsigned long long *__restrict__ stats) {
+               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   StatsAcc st;
   if (i < n) {
@@ -134,7 +189,7 @@ k_interpD_fast(MeshDView m, int64_t n, const double *__restrict__ xs, double *__
       if (STATS) { st.steps = steps; st.max_steps = steps; }
     } else {
       unsigned int slot = atomicAdd(queue_count, 1u);
-      queue[slot] = (int32_t)i;
+      if (slot < queue_cap) queue[slot] = (int32_t)i;
     }
   }
   if (STATS) flush_stats(stats, st);
@@ -144,12 +199,14 @@ template <int D, bool STATS, int EPI>
 __global__ void __launch_bounds__(64)
 k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
-               const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count, int64_t n_direct,
-               unsigned long long *__restrict__ stats) {
-  int64_t cnt = n_direct >= 0 ? n_direct : (int64_t)*queue_count;
+               const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
+               unsigned int queue_cap, int64_t n, unsigned long long *__restrict__ stats) {
+  int64_t cnt = (int64_t)*queue_count;
+  const bool direct = cnt > (int64_t)queue_cap;
+  if (direct) cnt = n;
   StatsAcc st;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
-    int64_t i = n_direct >= 0 ? k : (int64_t)queue[k];
+    int64_t i = direct ? k : (int64_t)queue[k];
     double p[D];
 #pragma unroll
     for (int a = 0; a < D; a++) p[a] = xs[i * D + a];
@@ -169,7 +226,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
   }
   if (STATS) {
     flush_stats(stats, st);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n_direct < 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
   }
 }
 

@@ -17,7 +17,7 @@ def _is_torch_tensor(x):
 
 
 def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, sort_queries=0, epilogue=0,
-                  threads_per_block=0):
+                  threads_per_block=0, queries_per_warp=0):
     o = Options()
     lib().dli_options_init(C.byref(o))
     o.device = int(device)
@@ -26,6 +26,7 @@ def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, sort_
     o.sort_queries = int(sort_queries)
     o.epilogue = {"reference": 0, "closed_form": 1}.get(epilogue, epilogue)
     o.threads_per_block = int(threads_per_block)
+    o.queries_per_warp = int(queries_per_warp)
     return o
 
 
@@ -182,8 +183,9 @@ class Mesh:
         return err
 
     # ---- instrumentation
-    def collect_stats(self, enable=True):
-        check(lib().dli_mesh_collect_stats(self._h, 1 if enable else 0))
+    def collect_stats(self, enable=True, timing=False):
+        """counters add atomics to the kernels; timing records CUDA events around every interp launch."""
+        check(lib().dli_mesh_collect_stats(self._h, (1 if enable else 0) | (2 if timing else 0)))
 
     def stats(self):
         s = Stats()
@@ -217,6 +219,12 @@ class Mesh:
             check(lib().dli_mesh_buffer(self._h, i, C.byref(p), C.byref(b)))
             out.append((p.value or 0, b.value))
         return out
+
+    def buffer_read(self, index, dst_ptr):
+        check(lib().dli_mesh_buffer_read(self._h, index, dst_ptr))
+
+    def buffer_write(self, index, src_ptr):
+        check(lib().dli_mesh_buffer_write(self._h, index, src_ptr))
 
 
 def debug_orient(pts, on_device=True):

@@ -62,7 +62,8 @@ typedef struct dli_options {
   int32_t epilogue;               /* 0 = reference operation order (partial-pivot LU determinants, default),
                                      1 = closed-form solve (faster, differs in the last ulps on slivers) */
   int32_t threads_per_block;      /* <= 0 = default */
-  int32_t reserved[9];
+  int32_t queries_per_warp;       /* 2D fast pass: contiguous queries owned by one warp; <= 0 = default (1024) */
+  int32_t reserved[8];
 } dli_options;
 
 /* fills *opt with the defaults */
@@ -150,6 +151,9 @@ int dli_mesh_header(const dli_mesh *mesh, int64_t header[DLI_MESH_HEADER_WORDS])
 int dli_mesh_create_from_header(const int64_t header[DLI_MESH_HEADER_WORDS], const dli_options *opt, dli_mesh **out);
 int dli_mesh_num_buffers(const dli_mesh *mesh);
 int dli_mesh_buffer(const dli_mesh *mesh, int index, void **device_ptr, int64_t *bytes);
+/* whole-buffer copies out of / into the mesh; the other side may be a host or a device pointer */
+int dli_mesh_buffer_read(const dli_mesh *mesh, int index, void *dst);
+int dli_mesh_buffer_write(dli_mesh *mesh, int index, const void *src);
 /* hint-grid geometry (origin, cell size, 1/cell size; 3 x DLI_MAX_DIM doubles), host side of the replication */
 int dli_mesh_get_grid_params(const dli_mesh *mesh, double *out /* [3 * DLI_MAX_DIM] */);
 int dli_mesh_set_grid_params(dli_mesh *mesh, const double *in /* [3 * DLI_MAX_DIM] */);
@@ -162,7 +166,13 @@ typedef struct dli_stats {
   int64_t exact_fallbacks;  /* orientation tests that fell through the static filter */
   int64_t outside;          /* queries that left the hull */
   int64_t kernel_launches;  /* launches issued by the most recent call */
+  /* timing mode (enable & 2): CUDA-event durations accumulated over every call since timing was enabled */
+  int64_t fast_kernel_launches;
+  double fast_kernel_ms;    /* sum of the fast-pass kernel durations */
+  double full_kernel_ms;    /* sum of the straggler/exact-pass kernel durations */
 } dli_stats;
+/* enable: 0 = off, bit 0 = counters (adds atomics to the kernels), bit 1 = per-launch CUDA-event timing of the
+   two interp kernels on the launching stream.  Enabling resets the accumulated timing. */
 int dli_mesh_collect_stats(dli_mesh *mesh, int enable);
 int dli_mesh_get_stats(const dli_mesh *mesh, dli_stats *out);
 

@@ -23,6 +23,8 @@ VAR = {
  "cps4": dict(hint_cells_per_simplex=4.0), "cps8": dict(hint_cells_per_simplex=8.0),
  "cf2": dict(hint_cells_per_simplex=2.0, epilogue="closed_form"), "cf4": dict(hint_cells_per_simplex=4.0, epilogue="closed_form"),
  "t128": dict(hint_cells_per_simplex=2.0, threads_per_block=128),
+ "qpw256": dict(hint_cells_per_simplex=2.0, queries_per_warp=256), "qpw512": dict(hint_cells_per_simplex=2.0, queries_per_warp=512),
+ "qpw2048": dict(hint_cells_per_simplex=2.0, queries_per_warp=2048), "qpw4096": dict(hint_cells_per_simplex=2.0, queries_per_warp=4096),
 }
 for name in a.variants.split(","):
     t = time.time()
