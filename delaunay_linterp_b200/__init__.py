@@ -6,6 +6,7 @@ behind a C ABI (include/dli.h).  The CUDA library is required; there is no CPU f
 from ._capi import (DliError, LIB_PATH, STATUS_NO_MESH, STATUS_OK, STATUS_OUTSIDE_NAN, STATUS_OUTSIDE_PROJECTED,
                     STATUS_STEP_LIMIT, lib)
 from .mesh import Mesh, debug_orient
+from .interp2 import DelaunayInterp2
 
-__all__ = ["Mesh", "debug_orient", "DliError", "lib", "LIB_PATH", "STATUS_OK", "STATUS_OUTSIDE_PROJECTED",
+__all__ = ["Mesh", "DelaunayInterp2", "debug_orient", "DliError", "lib", "LIB_PATH", "STATUS_OK", "STATUS_OUTSIDE_PROJECTED",
            "STATUS_OUTSIDE_NAN", "STATUS_STEP_LIMIT", "STATUS_NO_MESH"]

@@ -85,6 +85,29 @@ SYMBOLS = [
     ("dli_device_count", C.c_int, []),
 ]
 
+DLI_FN = C.CFUNCTYPE(C.c_double, C.c_int, C.POINTER(C.c_double), C.c_void_p)
+
+# include/dli_host.h
+HOST_SYMBOLS = [
+    ("dli_di2_create", _vp, [DLI_FN, _vp]),
+    ("dli_di2_destroy", None, [_vp]),
+    ("dli_di2_insert", C.c_int32, [_vp, C.c_double, C.c_double, C.c_double]),
+    ("dli_di2_insert_many", C.c_int, [_vp, C.c_int64, _vp, _vp, C.c_int, C.c_int]),
+    ("dli_di2_insert_largest_error_point", C.c_int, [_vp, _dp, _dp, _dp]),
+    ("dli_di2_get_largest_error_tuple", C.c_int, [_vp, _dp, _dp, _dp]),
+    ("dli_di2_error_queue_size", C.c_int64, [_vp]),
+    ("dli_di2_get_error_queue", C.c_int, [_vp, _vp, _vp, _vp]),
+    ("dli_di2_num_vertices", C.c_int64, [_vp]),
+    ("dli_di2_num_faces", C.c_int64, [_vp]),
+    ("dli_di2_dimension", C.c_int, [_vp]),
+    ("dli_di2_export", C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    ("dli_di2_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_di2_device_mesh", _vp, [_vp]),
+    ("dli_di2_set_options", C.c_int, [_vp, C.POINTER(Options)]),
+    ("dli_di2_get_all_vertices", C.c_int64, [_vp, _vp]),
+    ("dli_di2_get_line_segments", C.c_int64, [_vp, _vp]),
+]
+
 _lib = None
 
 
@@ -98,7 +121,7 @@ def lib():
             "delaunay_linterp_b200: %s is missing. Build it with `python -m delaunay_linterp_b200.build` "
             "(needs nvcc); there is no CPU fallback." % LIB_PATH)
     L = C.CDLL(LIB_PATH)
-    for name, res, args in SYMBOLS:
+    for name, res, args in SYMBOLS + HOST_SYMBOLS:
         fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args

@@ -13,8 +13,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdli.so")
 SOURCES = ["dli_capi.cu", "dli_hostmesh.cpp"]
-HEADERS = ["dli_exact.cuh", "dli_device.cuh", "dli_kernels.cuh", "dli_hostmesh.h", "../../include/dli.h",
-           "../../include/dli_hostmesh_c.h"]
+HEADERS = ["dli_exact.cuh", "dli_device.cuh", "dli_kernels.cuh", "../../include/dli.h", "../../include/dli_host.h",
+           "../../include/dli_error_math.h"]
 
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-shared", "-Xcompiler", "-fPIC",

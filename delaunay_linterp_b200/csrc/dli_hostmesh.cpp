@@ -1,0 +1,619 @@
+// dli_hostmesh.cpp -- host-side incremental 2D Delaunay triangulation (Bowyer-Watson with an
+// infinite vertex, exact predicates, CGAL-compatible symbolic perturbation) and the adaptive
+// insertion queue of Delaunay_incremental_interp_2; C ABI in include/dli_host.h.
+//
+// This is where the reference keeps CGAL::Delaunay_triangulation_2 (src/delaunay_2_interp.h:66-95,
+// insert :434-448) and its boost skew_heap queue (:397-400, :455-508).  Construction is host work by
+// design (north_star); the GPU engine consumes the flattened result (dli_di2_export -> dli_mesh_create).
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <queue>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/dli_error_math.h"
+#include "../../include/dli_host.h"
+#include "dli_exact.cuh"
+
+namespace {
+
+using dli::grow_ze;
+using dli::two_prod;
+
+// ---------------------------------------------------------------------------------------------
+// exact in-circle
+// ---------------------------------------------------------------------------------------------
+typedef std::vector<double> Exp;
+
+void exp_add(Exp &e, double b) {
+  if (b == 0.0 && !e.empty()) return;
+  e.push_back(0.0);
+  int n = (int)e.size() - 1;
+  grow_ze(e.data(), n, b);
+  e.resize(n);
+}
+// exact orient2d determinant of raw coordinates as an expansion
+Exp orient_exp(double ax, double ay, double bx, double by, double cx, double cy) {
+  Exp e;
+  const double pa[6] = {ax, -ax, -cx, -ay, ay, cy};
+  const double pb[6] = {by, cy, by, bx, cx, bx};
+  for (int i = 0; i < 6; i++) {
+    double p, q;
+    two_prod(pa[i], pb[i], p, q);
+    exp_add(e, q);
+    exp_add(e, p);
+  }
+  return e;
+}
+// acc += sgn * (x*x + y*y) * m   (all exact)
+void add_lift_times(Exp &acc, double x, double y, const Exp &m, double sgn) {
+  double l[4];
+  two_prod(x, x, l[1], l[0]);
+  two_prod(y, y, l[3], l[2]);
+  for (int i = 0; i < 4; i++) {
+    if (l[i] == 0.0) continue;
+    for (double mj : m) {
+      double p, q;
+      two_prod(sgn * l[i], mj, p, q);
+      exp_add(acc, q);
+      exp_add(acc, p);
+    }
+  }
+}
+int incircle_exact(double ax, double ay, double bx, double by, double cx, double cy, double dx, double dy) {
+  // det4 = +lift_a o(b,c,d) - lift_b o(a,c,d) + lift_c o(a,b,d) - lift_d o(a,b,c)
+  Exp acc;
+  add_lift_times(acc, ax, ay, orient_exp(bx, by, cx, cy, dx, dy), 1.0);
+  add_lift_times(acc, bx, by, orient_exp(ax, ay, cx, cy, dx, dy), -1.0);
+  add_lift_times(acc, cx, cy, orient_exp(ax, ay, bx, by, dx, dy), 1.0);
+  add_lift_times(acc, dx, dy, orient_exp(ax, ay, bx, by, cx, cy), -1.0);
+  return dli::expansion_sign(acc.data(), (int)acc.size());
+}
+// > 0: d strictly inside the circle through a, b, c (ccw); Shewchuk's static filter then exact
+int incircle(double ax, double ay, double bx, double by, double cx, double cy, double dx, double dy) {
+  double adx = ax - dx, ady = ay - dy, bdx = bx - dx, bdy = by - dy, cdx = cx - dx, cdy = cy - dy;
+  double bdxcdy = bdx * cdy, cdxbdy = cdx * bdy, alift = adx * adx + ady * ady;
+  double cdxady = cdx * ady, adxcdy = adx * cdy, blift = bdx * bdx + bdy * bdy;
+  double adxbdy = adx * bdy, bdxady = bdx * ady, clift = cdx * cdx + cdy * cdy;
+  double det = alift * (bdxcdy - cdxbdy) + blift * (cdxady - adxcdy) + clift * (adxbdy - bdxady);
+  double perm = (std::fabs(bdxcdy) + std::fabs(cdxbdy)) * alift + (std::fabs(cdxady) + std::fabs(adxcdy)) * blift +
+                (std::fabs(adxbdy) + std::fabs(bdxady)) * clift;
+  double bound = (10.0 + 96.0 * dli::kEps) * dli::kEps * perm;
+  if (det > bound) return 1;
+  if (-det > bound) return -1;
+  return incircle_exact(ax, ay, bx, by, cx, cy, dx, dy);
+}
+
+inline int orient(double ax, double ay, double bx, double by, double cx, double cy) {
+  return dli::orient2d(ax, ay, bx, by, cx, cy);
+}
+
+// ---------------------------------------------------------------------------------------------
+// triangulation
+// ---------------------------------------------------------------------------------------------
+constexpr int INF = -1;  // the infinite vertex
+
+struct Face {
+  int v[3];
+  int n[3];
+};
+
+struct HostMesh2 {
+  std::vector<double> X, Y, F;
+  std::vector<Face> fc;
+  std::vector<uint8_t> alive;
+  std::vector<uint32_t> gen;
+  std::vector<int> freelist;
+  int dim = -1;
+  int last = -1;  // some alive finite face
+  int64_t n_finite = 0;
+  std::vector<int> new_faces, removed_faces;  // finite faces touched by the last insertion
+  // scratch
+  std::vector<int> cavity, stack;
+  std::vector<uint8_t> mark;
+
+  bool is_inf(int f) const { return fc[f].v[0] == INF || fc[f].v[1] == INF || fc[f].v[2] == INF; }
+  int new_face() {
+    int id;
+    if (!freelist.empty()) { id = freelist.back(); freelist.pop_back(); }
+    else { id = (int)fc.size(); fc.push_back(Face()); alive.push_back(0); gen.push_back(0); mark.push_back(0); }
+    alive[id] = 1;
+    return id;
+  }
+  int o3(int a, int b, double px, double py) const { return orient(X[a], Y[a], X[b], Y[b], px, py); }
+  bool lex_less(int a, int b) const { return X[a] < X[b] || (X[a] == X[b] && Y[a] < Y[b]); }
+
+  // CGAL Delaunay_triangulation_2::side_of_oriented_circle(p0,p1,p2,p,perturb = true)
+  int side_of_circle_perturbed(int p0, int p1, int p2, int p) const {
+    int s = incircle(X[p0], Y[p0], X[p1], Y[p1], X[p2], Y[p2], X[p], Y[p]);
+    if (s != 0) return s;
+    int pts[4] = {p0, p1, p2, p};
+    std::sort(pts, pts + 4, [this](int a, int b) { return lex_less(a, b); });
+    for (int i = 3; i > 0; --i) {
+      if (pts[i] == p) return -1;
+      int o;
+      if (pts[i] == p2 && (o = orient(X[p0], Y[p0], X[p1], Y[p1], X[p], Y[p])) != 0) return o;
+      if (pts[i] == p1 && (o = orient(X[p0], Y[p0], X[p], Y[p], X[p2], Y[p2])) != 0) return o;
+      if (pts[i] == p0 && (o = orient(X[p], Y[p], X[p1], Y[p1], X[p2], Y[p2])) != 0) return o;
+    }
+    return -1;
+  }
+
+  // is vertex p (already appended to X/Y) in conflict with face f?
+  bool conflict(int f, int p) const {
+    const Face &t = fc[f];
+    for (int i = 0; i < 3; i++)
+      if (t.v[i] == INF) {
+        int a = t.v[(i + 1) % 3], b = t.v[(i + 2) % 3];
+        int o = o3(a, b, X[p], Y[p]);
+        if (o > 0) return true;
+        if (o < 0) return false;
+        // collinear with the hull edge: in conflict iff strictly between its end points
+        double ax = X[a], ay = Y[a], bx = X[b], by = Y[b], px = X[p], py = Y[p];
+        if (ax != bx) return (ax < px && px < bx) || (bx < px && px < ax);
+        return (ay < py && py < by) || (by < py && py < ay);
+      }
+    return side_of_circle_perturbed(t.v[0], t.v[1], t.v[2], p) > 0;
+  }
+
+  // exact visibility walk from `last`; returns a finite face whose closed hull contains p, or the
+  // infinite face p is strictly visible from
+  int locate(double px, double py) const {
+    int f = last, from = -1;
+    for (;;) {
+      const Face &t = fc[f];
+      int moved = -1;
+      for (int j = 0; j < 3; j++) {
+        if (t.n[j] == from) continue;
+        int a = t.v[(j + 1) % 3], b = t.v[(j + 2) % 3];
+        if (o3(a, b, px, py) < 0) { moved = j; break; }
+      }
+      if (moved < 0) return f;
+      int nb = t.n[moved];
+      if (is_inf(nb)) return nb;
+      from = f;
+      f = nb;
+    }
+  }
+
+  void link_all() {  // (re)build every neighbour link from directed edges; creates the infinite faces
+    std::unordered_map<uint64_t, std::pair<int, int>> emap;
+    auto key = [](int u, int v) { return ((uint64_t)(uint32_t)(u + 1) << 32) | (uint32_t)(v + 1); };
+    int nf = (int)fc.size();
+    for (int f = 0; f < nf; f++)
+      if (alive[f])
+        for (int j = 0; j < 3; j++) emap[key(fc[f].v[(j + 1) % 3], fc[f].v[(j + 2) % 3])] = {f, j};
+    std::vector<std::pair<int, int>> hull;
+    for (int f = 0; f < nf; f++)
+      if (alive[f])
+        for (int j = 0; j < 3; j++) {
+          int u = fc[f].v[(j + 1) % 3], v = fc[f].v[(j + 2) % 3];
+          if (!emap.count(key(v, u))) hull.push_back({v, u});
+        }
+    for (auto &e : hull) {
+      int id = new_face();
+      fc[id].v[0] = INF; fc[id].v[1] = e.first; fc[id].v[2] = e.second;
+      for (int j = 0; j < 3; j++) emap[key(fc[id].v[(j + 1) % 3], fc[id].v[(j + 2) % 3])] = {id, j};
+    }
+    for (int f = 0; f < (int)fc.size(); f++)
+      if (alive[f])
+        for (int j = 0; j < 3; j++) {
+          auto it = emap.find(key(fc[f].v[(j + 2) % 3], fc[f].v[(j + 1) % 3]));
+          fc[f].n[j] = it == emap.end() ? -1 : it->second.first;
+        }
+  }
+
+  // returns vertex id; *is_new = false when the point already exists (value overwritten)
+  int insert(double px, double py, double fv, bool *is_new) {
+    new_faces.clear();
+    removed_faces.clear();
+    *is_new = true;
+    int nv = (int)X.size();
+    if (dim < 2) {
+      for (int v = 0; v < nv; v++)
+        if (X[v] == px && Y[v] == py) { F[v] = fv; *is_new = false; return v; }
+      X.push_back(px); Y.push_back(py); F.push_back(fv);
+      int p = nv;
+      if (dim == -1) { dim = 0; return p; }
+      if (dim == 0) { dim = 1; return p; }
+      // dim == 1: still collinear?
+      int a = 0, b = 1;
+      if (orient(X[a], Y[a], X[b], Y[b], px, py) == 0) return p;
+      // first non-collinear point: fan over the sorted collinear points
+      std::vector<int> s(nv);
+      for (int i = 0; i < nv; i++) s[i] = i;
+      std::sort(s.begin(), s.end(), [this](int u, int v) { return lex_less(u, v); });
+      for (int i = 0; i + 1 < nv; i++) {
+        int id = new_face();
+        bool ccw = orient(X[s[i]], Y[s[i]], X[s[i + 1]], Y[s[i + 1]], px, py) > 0;
+        fc[id].v[0] = ccw ? s[i] : s[i + 1];
+        fc[id].v[1] = ccw ? s[i + 1] : s[i];
+        fc[id].v[2] = p;
+        new_faces.push_back(id);
+        n_finite++;
+      }
+      link_all();
+      last = new_faces[0];
+      dim = 2;
+      return p;
+    }
+    int loc = locate(px, py);
+    if (!is_inf(loc)) {
+      for (int i = 0; i < 3; i++) {
+        int v = fc[loc].v[i];
+        if (X[v] == px && Y[v] == py) { F[v] = fv; *is_new = false; return v; }
+      }
+    }
+    X.push_back(px); Y.push_back(py); F.push_back(fv);
+    int p = nv;
+    // cavity = connected set of faces in conflict with p
+    cavity.clear();
+    stack.clear();
+    stack.push_back(loc);
+    mark[loc] = 1;
+    while (!stack.empty()) {
+      int f = stack.back();
+      stack.pop_back();
+      cavity.push_back(f);
+      for (int j = 0; j < 3; j++) {
+        int nb = fc[f].n[j];
+        if (!mark[nb] && conflict(nb, p)) { mark[nb] = 1; stack.push_back(nb); }
+      }
+    }
+    // boundary edges -> new faces (p, a, b)
+    struct BEdge { int a, b, out; };
+    std::vector<BEdge> be;
+    for (int f : cavity)
+      for (int j = 0; j < 3; j++) {
+        int nb = fc[f].n[j];
+        if (!mark[nb]) be.push_back({fc[f].v[(j + 1) % 3], fc[f].v[(j + 2) % 3], nb});
+      }
+    std::vector<int> created(be.size());
+    std::unordered_map<int, int> start_at;
+    start_at.reserve(be.size() * 2);
+    std::vector<int> fresh;  // allocate without reusing the cavity's own slots yet
+    for (size_t i = 0; i < be.size(); i++) {
+      int id = new_face();
+      created[i] = id;
+      fc[id].v[0] = p; fc[id].v[1] = be[i].a; fc[id].v[2] = be[i].b;
+      fc[id].n[0] = be[i].out;
+      Face &o = fc[be[i].out];
+      for (int k = 0; k < 3; k++)
+        if (o.v[(k + 1) % 3] == be[i].b && o.v[(k + 2) % 3] == be[i].a) o.n[k] = id;
+      start_at[be[i].a] = id;
+    }
+    for (size_t i = 0; i < be.size(); i++) {
+      int id = created[i];
+      int nxt = start_at[be[i].b];  // the new face whose edge starts where this one ends
+      fc[id].n[1] = nxt;            // slot 1 = edge b -> p
+      fc[nxt].n[2] = id;            // slot 2 of (p, b, c) = edge p -> b
+    }
+    for (int f : cavity) {
+      mark[f] = 0;
+      alive[f] = 0;
+      gen[f]++;
+      if (!is_inf(f)) { removed_faces.push_back(f); n_finite--; }
+      freelist.push_back(f);
+    }
+    for (int id : created)
+      if (!is_inf(id)) { new_faces.push_back(id); n_finite++; }
+    last = new_faces.empty() ? last : new_faces[0];
+    return p;
+  }
+};
+
+// Hilbert index of a point in the unit square (16 bits per axis)
+uint32_t hilbert16(uint32_t x, uint32_t y) {
+  uint32_t d = 0;
+  for (uint32_t s = 1u << 15; s > 0; s >>= 1) {
+    uint32_t rx = (x & s) ? 1 : 0, ry = (y & s) ? 1 : 0;
+    d += s * s * ((3 * rx) ^ ry);
+    if (ry == 0) {
+      if (rx == 1) { x = 65535 - x; y = 65535 - y; }
+      uint32_t t = x; x = y; y = t;
+    }
+  }
+  return d;
+}
+
+struct QEntry {
+  double err, f, x, y;
+  uint64_t seq;
+  int face;
+  uint32_t gen;
+};
+struct QLess {
+  bool operator()(const QEntry &a, const QEntry &b) const {
+    if (a.err != b.err) return a.err < b.err;  // max-heap on err (ErrorTuple::operator<, :392-394)
+    return a.seq > b.seq;                      // ties: earliest pushed first (the reference leaves ties unspecified)
+  }
+};
+
+}  // namespace
+
+struct dli_di2 {
+  HostMesh2 hm;
+  dli_fn fn = nullptr;
+  void *user = nullptr;
+  std::priority_queue<QEntry, std::vector<QEntry>, QLess> pq;
+  std::vector<int> nent;  // live queue entries per face handle
+  int64_t live = 0;
+  uint64_t seq = 0;
+  // device side
+  dli_mesh *mesh = nullptr;
+  bool dirty = true;
+  dli_options opt;
+  bool have_opt = false;
+
+  bool entry_live(const QEntry &e) const { return hm.alive[e.face] && hm.gen[e.face] == e.gen; }
+  void push(double err, double f, double x, double y, int face) {
+    pq.push(QEntry{err, f, x, y, seq++, face, hm.gen[face]});
+    if ((int)nent.size() <= face) nent.resize(hm.fc.size(), 0);
+    nent[face]++;
+    live++;
+  }
+  void drop_face_entries(int face) {
+    if (face < (int)nent.size()) { live -= nent[face]; nent[face] = 0; }
+  }
+  void prune() {
+    while (!pq.empty() && !entry_live(pq.top())) pq.pop();
+  }
+  // compute_simplex_error for the face and its hull edges (src/delaunay_2_interp.h:476-491)
+  void add_face_errors(int face) {
+    const Face &t = hm.fc[face];
+    double w[9];
+    for (int i = 0; i < 3; i++) { w[i * 3] = hm.X[t.v[i]]; w[i * 3 + 1] = hm.Y[t.v[i]]; w[i * 3 + 2] = hm.F[t.v[i]]; }
+    double c[2] = {(w[0] + w[3] + w[6]) / 3, (w[1] + w[4] + w[7]) / 3};
+    double phi = fn(2, c, user);
+    push(dli_simplex_error<2>(3, w, phi), phi, c[0], c[1], face);
+    for (int j = 0; j < 3; j++)
+      if (hm.is_inf(t.n[j])) {  // hull edge = the two vertices other than j, in slot order
+        double e[6];
+        int k = 0;
+        for (int i = 0; i < 3; i++)
+          if (i != j) { e[k * 3] = w[i * 3]; e[k * 3 + 1] = w[i * 3 + 1]; e[k * 3 + 2] = w[i * 3 + 2]; k++; }
+        double ce[2] = {(e[0] + e[3]) / 2, (e[1] + e[4]) / 2};
+        double ph = fn(2, ce, user);
+        push(dli_simplex_error<2>(2, e, ph), ph, ce[0], ce[1], face);
+      }
+  }
+  int insert(double x, double y, double f) {
+    bool is_new;
+    int v = hm.insert(x, y, f, &is_new);
+    dirty = true;
+    if (fn) {
+      for (int r : hm.removed_faces) drop_face_entries(r);
+      if (nent.size() < hm.fc.size()) nent.resize(hm.fc.size(), 0);
+      if (!is_new && hm.dim == 2) {
+        // value change of an existing vertex: its star is "modified" (:438-446): refresh those entries
+        for (int fi = 0; fi < (int)hm.fc.size(); fi++)
+          if (hm.alive[fi] && !hm.is_inf(fi) && (hm.fc[fi].v[0] == v || hm.fc[fi].v[1] == v || hm.fc[fi].v[2] == v)) {
+            drop_face_entries(fi);
+            hm.gen[fi]++;
+            add_face_errors(fi);
+          }
+      }
+      for (int nf : hm.new_faces) add_face_errors(nf);
+    }
+    return v;
+  }
+};
+
+extern "C" {
+
+dli_di2 *dli_di2_create(dli_fn fn, void *user) {
+  dli_di2 *d = new dli_di2;
+  d->fn = fn;
+  d->user = user;
+  return d;
+}
+void dli_di2_destroy(dli_di2 *d) {
+  if (!d) return;
+  if (d->mesh) dli_mesh_destroy(d->mesh);
+  delete d;
+}
+int32_t dli_di2_insert(dli_di2 *d, double x, double y, double f) {
+  if (!d) return DLI_ERR_ARG;
+  if (!(std::isfinite(x) && std::isfinite(y))) return DLI_ERR_ARG;
+  return d->insert(x, y, f);
+}
+
+int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f, int spatial_sort, int use_gpu) {
+  if (!d || n < 0 || (n > 0 && (!xy || !f))) return DLI_ERR_ARG;
+  std::vector<int64_t> order((size_t)n);
+  for (int64_t i = 0; i < n; i++) order[i] = i;
+  if (spatial_sort && n > 1) {
+    double lo[2] = {INFINITY, INFINITY}, hi[2] = {-INFINITY, -INFINITY};
+    for (int64_t i = 0; i < n; i++)
+      for (int k = 0; k < 2; k++) { lo[k] = std::min(lo[k], xy[2 * i + k]); hi[k] = std::max(hi[k], xy[2 * i + k]); }
+    double sx = hi[0] > lo[0] ? 65535.0 / (hi[0] - lo[0]) : 0.0, sy = hi[1] > lo[1] ? 65535.0 / (hi[1] - lo[1]) : 0.0;
+    std::vector<uint32_t> key((size_t)n);
+    for (int64_t i = 0; i < n; i++)
+      key[i] = hilbert16((uint32_t)((xy[2 * i] - lo[0]) * sx), (uint32_t)((xy[2 * i + 1] - lo[1]) * sy));
+    std::sort(order.begin(), order.end(), [&key](int64_t a, int64_t b) { return key[a] < key[b]; });
+  }
+  dli_fn fn = d->fn;
+  d->fn = nullptr;  // build the triangulation first, then the queue in one batch
+  for (int64_t k = 0; k < n; k++) {
+    int64_t i = order[k];
+    if (!(std::isfinite(xy[2 * i]) && std::isfinite(xy[2 * i + 1]))) { d->fn = fn; return DLI_ERR_ARG; }
+    d->insert(xy[2 * i], xy[2 * i + 1], f[i]);
+  }
+  d->fn = fn;
+  if (!fn || d->hm.dim < 2) return DLI_OK;
+  // rebuild the whole queue
+  while (!d->pq.empty()) d->pq.pop();
+  d->nent.assign(d->hm.fc.size(), 0);
+  d->live = 0;
+  HostMesh2 &hm = d->hm;
+  if (!use_gpu) {
+    for (int fi = 0; fi < (int)hm.fc.size(); fi++)
+      if (hm.alive[fi] && !hm.is_inf(fi)) d->add_face_errors(fi);
+    return DLI_OK;
+  }
+  // batched: flatten -> GPU centroids -> host callback -> GPU error kernel
+  int64_t nv = (int64_t)hm.X.size(), nf = hm.n_finite;
+  std::vector<double> coords((size_t)nv * 2);
+  std::vector<int32_t> tri((size_t)nf * 3), nbr((size_t)nf * 3), handle((size_t)nf);
+  {
+    std::vector<int> compact(hm.fc.size(), -1);
+    int c = 0;
+    for (int fi = 0; fi < (int)hm.fc.size(); fi++)
+      if (hm.alive[fi] && !hm.is_inf(fi)) { compact[fi] = c; handle[c] = fi; c++; }
+    for (int64_t v = 0; v < nv; v++) { coords[2 * v] = hm.X[v]; coords[2 * v + 1] = hm.Y[v]; }
+    for (int64_t t = 0; t < nf; t++)
+      for (int j = 0; j < 3; j++) {
+        tri[3 * t + j] = hm.fc[handle[t]].v[j];
+        int nb = hm.fc[handle[t]].n[j];
+        nbr[3 * t + j] = hm.is_inf(nb) ? -1 : compact[nb];
+      }
+  }
+  if (d->mesh) { dli_mesh_destroy(d->mesh); d->mesh = nullptr; }
+  int rc = dli_mesh_create(2, nv, coords.data(), hm.F.data(), nf, tri.data(), nbr.data(), d->have_opt ? &d->opt : nullptr,
+                           &d->mesh);
+  if (rc != DLI_OK) return rc;
+  d->dirty = false;
+  int64_t ni = dli_simplex_error_count(d->mesh);
+  if (ni < 0) return (int)ni;
+  std::vector<double> cent((size_t)ni * 2), phi((size_t)ni), err((size_t)ni);
+  std::vector<int32_t> item_simplex((size_t)ni);
+  rc = dli_simplex_error_prepare(d->mesh, cent.data(), item_simplex.data(), nullptr);
+  if (rc != DLI_OK) return rc;
+  for (int64_t i = 0; i < ni; i++) phi[i] = fn(2, &cent[2 * i], d->user);
+  rc = dli_simplex_error_finish(d->mesh, ni, phi.data(), err.data());
+  if (rc != DLI_OK) return rc;
+  for (int64_t i = 0; i < ni; i++) d->push(err[i], phi[i], cent[2 * i], cent[2 * i + 1], handle[item_simplex[i]]);
+  return DLI_OK;
+}
+
+int dli_di2_get_largest_error_tuple(dli_di2 *d, double *err, double *f, double *xy) {
+  if (!d || !d->fn) return DLI_ERR_ARG;
+  d->prune();
+  if (d->pq.empty()) return DLI_ERR_ARG;
+  const QEntry &e = d->pq.top();
+  if (err) *err = e.err;
+  if (f) *f = e.f;
+  if (xy) { xy[0] = e.x; xy[1] = e.y; }
+  return DLI_OK;
+}
+int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, double *xy) {
+  if (!d || !d->fn) return DLI_ERR_ARG;
+  d->prune();
+  if (d->pq.empty()) return DLI_ERR_ARG;
+  QEntry e = d->pq.top();
+  if (err) *err = e.err;
+  if (f) *f = e.f;
+  if (xy) { xy[0] = e.x; xy[1] = e.y; }
+  d->insert(e.x, e.y, e.f);
+  return DLI_OK;
+}
+int64_t dli_di2_error_queue_size(dli_di2 *d) { return d ? d->live : 0; }
+int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy) {
+  if (!d) return DLI_ERR_ARG;
+  std::vector<QEntry> all;
+  auto copy = d->pq;
+  while (!copy.empty()) {
+    if (d->entry_live(copy.top())) all.push_back(copy.top());
+    copy.pop();
+  }
+  for (size_t i = 0; i < all.size(); i++) {
+    if (err) err[i] = all[i].err;
+    if (f) f[i] = all[i].f;
+    if (xy) { xy[2 * i] = all[i].x; xy[2 * i + 1] = all[i].y; }
+  }
+  return DLI_OK;
+}
+
+int64_t dli_di2_num_vertices(const dli_di2 *d) { return d ? (int64_t)d->hm.X.size() : 0; }
+int64_t dli_di2_num_faces(const dli_di2 *d) { return d ? d->hm.n_finite : 0; }
+int dli_di2_dimension(const dli_di2 *d) { return d ? d->hm.dim : -1; }
+
+int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, int32_t *nbr) {
+  if (!d) return DLI_ERR_ARG;
+  const HostMesh2 &hm = d->hm;
+  int64_t nv = (int64_t)hm.X.size();
+  if (coords) for (int64_t v = 0; v < nv; v++) { coords[2 * v] = hm.X[v]; coords[2 * v + 1] = hm.Y[v]; }
+  if (f) memcpy(f, hm.F.data(), sizeof(double) * (size_t)nv);
+  if (tri || nbr) {
+    std::vector<int> compact(hm.fc.size(), -1);
+    int c = 0;
+    for (int fi = 0; fi < (int)hm.fc.size(); fi++)
+      if (hm.alive[fi] && !hm.is_inf(fi)) compact[fi] = c++;
+    for (int fi = 0; fi < (int)hm.fc.size(); fi++) {
+      int t = compact[fi];
+      if (t < 0) continue;
+      for (int j = 0; j < 3; j++) {
+        if (tri) tri[3 * t + j] = hm.fc[fi].v[j];
+        if (nbr) { int nb = hm.fc[fi].n[j]; nbr[3 * t + j] = hm.is_inf(nb) ? -1 : compact[nb]; }
+      }
+    }
+  }
+  return DLI_OK;
+}
+
+int dli_di2_set_options(dli_di2 *d, const dli_options *opt) {
+  if (!d) return DLI_ERR_ARG;
+  d->have_opt = opt != nullptr;
+  if (opt) d->opt = *opt;
+  d->dirty = true;
+  return DLI_OK;
+}
+
+static int di2_refresh(dli_di2 *d) {
+  if (!d->dirty && d->mesh) return DLI_OK;
+  if (d->mesh) { dli_mesh_destroy(d->mesh); d->mesh = nullptr; }
+  int64_t nv = (int64_t)d->hm.X.size(), nf = d->hm.dim == 2 ? d->hm.n_finite : 0;
+  std::vector<double> coords((size_t)nv * 2 + 2);
+  std::vector<int32_t> tri((size_t)nf * 3 + 3), nbr((size_t)nf * 3 + 3);
+  dli_di2_export(d, coords.data(), nullptr, nf ? tri.data() : nullptr, nf ? nbr.data() : nullptr);
+  std::vector<double> fv(d->hm.F);
+  fv.push_back(0.0);
+  int rc = dli_mesh_create(2, nv, coords.data(), fv.data(), nf, tri.data(), nbr.data(), d->have_opt ? &d->opt : nullptr,
+                           &d->mesh);
+  if (rc == DLI_OK) d->dirty = false;
+  return rc;
+}
+
+int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
+                   void *stream) {
+  if (!d) return DLI_ERR_ARG;
+  int rc = di2_refresh(d);
+  if (rc != DLI_OK) return rc;
+  return dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);
+}
+const dli_mesh *dli_di2_device_mesh(dli_di2 *d) {
+  if (!d) return nullptr;
+  if (di2_refresh(d) != DLI_OK) return nullptr;
+  return d->mesh;
+}
+
+int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz) {
+  if (!d) return 0;
+  int64_t nv = (int64_t)d->hm.X.size();
+  if (xyz) for (int64_t v = 0; v < nv; v++) { xyz[3 * v] = d->hm.X[v]; xyz[3 * v + 1] = d->hm.Y[v]; xyz[3 * v + 2] = d->hm.F[v]; }
+  return nv;
+}
+int64_t dli_di2_get_line_segments(const dli_di2 *d, double *seg) {
+  if (!d) return 0;
+  const HostMesh2 &hm = d->hm;
+  int64_t ne = 0;
+  for (int fi = 0; fi < (int)hm.fc.size(); fi++) {
+    if (!hm.alive[fi] || hm.is_inf(fi)) continue;
+    for (int j = 0; j < 3; j++) {
+      int nb = hm.fc[fi].n[j];
+      if (!hm.is_inf(nb) && nb < fi) continue;  // interior edges once
+      int a = hm.fc[fi].v[(j + 1) % 3], b = hm.fc[fi].v[(j + 2) % 3];
+      if (seg) {
+        double *s = seg + 6 * ne;
+        s[0] = hm.X[a]; s[1] = hm.Y[a]; s[2] = hm.F[a];
+        s[3] = hm.X[b]; s[4] = hm.Y[b]; s[5] = hm.F[b];
+      }
+      ne++;
+    }
+  }
+  return ne;
+}
+
+}  // extern "C"

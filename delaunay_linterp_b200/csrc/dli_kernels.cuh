@@ -2,6 +2,7 @@
 // hint-grid construction, per-simplex error evaluator, predicate test hook.
 #pragma once
 #include "dli_device.cuh"
+#include "../../include/dli_error_math.h"
 
 namespace dli {
 
@@ -363,48 +364,14 @@ __global__ void k_error_finish(int64_t n, const int32_t *__restrict__ item_verts
   constexpr int N = D + 1;  // lifted dimension
   double w[(D + 1) * N];
   int np = 0;
-  double fbar = 0.0;
   for (int a = 0; a <= D; a++) {
     int v = item_verts[i * (D + 1) + a];
     if (v < 0) break;
     for (int k = 0; k < D; k++) w[a * N + k] = vrec[(size_t)v * vs + k];
     w[a * N + D] = vrec[(size_t)v * vs + D];
-    fbar += w[a * N + D];
     np++;
   }
-  fbar /= np;
-  // modified Gram-Schmidt on u_j = w_j - w_0 (j = 1..np-1), then orthogonalise e_z against them
-  double q[D * N];
-  int nq = 0;
-  for (int j = 1; j < np; j++) {
-    double u[N];
-    for (int k = 0; k < N; k++) u[k] = w[j * N + k] - w[k];
-    for (int pass = 0; pass < 2; pass++)  // re-orthogonalise once
-      for (int t = 0; t < nq; t++) {
-        double d = 0.0;
-        for (int k = 0; k < N; k++) d += u[k] * q[t * N + k];
-        for (int k = 0; k < N; k++) u[k] -= d * q[t * N + k];
-      }
-    double nn = 0.0;
-    for (int k = 0; k < N; k++) nn += u[k] * u[k];
-    if (nn > 0.0) {
-      double inv = 1.0 / sqrt(nn);
-      for (int k = 0; k < N; k++) q[nq * N + k] = u[k] * inv;
-      nq++;
-    }
-  }
-  double r[N];
-  for (int k = 0; k < N; k++) r[k] = (k == D) ? 1.0 : 0.0;
-  for (int pass = 0; pass < 2; pass++)
-    for (int t = 0; t < nq; t++) {
-      double d = 0.0;
-      for (int k = 0; k < N; k++) d += r[k] * q[t * N + k];
-      for (int k = 0; k < N; k++) r[k] -= d * q[t * N + k];
-    }
-  double fac = 0.0;
-  for (int k = 0; k < N; k++) fac += r[k] * r[k];
-  double delta = phi[i] - fbar;
-  err[i] = delta * delta * fac;
+  err[i] = dli_simplex_error<D>(np, w, phi[i]);
 }
 
 // ---------------------------------------------------------------------------------------------

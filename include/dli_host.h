@@ -1,0 +1,80 @@
+/*
+ * dli_host.h -- C ABI of the host-side objects that stand where the reference keeps CGAL:
+ * an incremental 2D Delaunay triangulation with vertex values and the adaptive-insertion
+ * error queue, feeding the GPU engine (include/dli.h) through the flattener.
+ *
+ * The reference builds on CGAL::Delaunay_triangulation_2 (src/delaunay_2_interp.h:66-95), which is
+ * not available here (no CGAL in the image), so construction is native: Bowyer-Watson insertion with
+ * exact orientation / in-circle predicates and CGAL's symbolic perturbation for cocircular points
+ * (Delaunay_triangulation_2::side_of_oriented_circle(p0,p1,p2,p,perturb)), which makes the
+ * triangulation independent of insertion order and reproduces the README known answer.
+ *
+ * dli_di2 mirrors class Delaunay_incremental_interp_2 (src/delaunay_2_interp.h:402-864):
+ *   insert                         :450-493   -> dli_di2_insert
+ *   insert_largest_error_point     :498-504   -> dli_di2_insert_largest_error_point
+ *   get_largest_error_tuple        :506-508   -> dli_di2_get_largest_error_tuple
+ *   interp / interp_point          :510-572   -> dli_di2_interp (batched, on the GPU)
+ *   get_error_queue                :743-746   -> dli_di2_get_error_queue
+ *   get_all_vertices               :806-840   -> dli_di2_get_all_vertices
+ *   get_line_segments              :842-862   -> dli_di2_get_line_segments
+ *   compute_simplex_error + add_error_of_boundary_subsimplices :725-741, :683-699 (host, per inserted star;
+ *   the whole-mesh batched form is dli_simplex_error_* in dli.h)
+ */
+#ifndef DLI_HOST_H_
+#define DLI_HOST_H_
+
+#include <stdint.h>
+#include "dli.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* host callback: f(x), the reference's std::function<double(int, double*)> m_fn (src/delaunay_2_interp.h:408) */
+typedef double (*dli_fn)(int n_dims, const double *x, void *user);
+
+typedef struct dli_di2 dli_di2;
+
+/* fn may be NULL: no error queue is kept (ctor without callback, src/delaunay_2_interp.h:410-412) */
+dli_di2 *dli_di2_create(dli_fn fn, void *user);
+void dli_di2_destroy(dli_di2 *d);
+
+/* insert(x, f): a duplicate point only overwrites its value (CGAL insert returns the existing vertex).
+   Returns the vertex id (>= 0) or a negative error. */
+int32_t dli_di2_insert(dli_di2 *d, double x, double y, double f);
+/* bulk insertion; spatial_sort != 0 inserts along a Hilbert curve (same triangulation, faster).
+   With a callback the error queue is rebuilt afterwards (batched on the GPU when use_gpu != 0). */
+int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f, int spatial_sort, int use_gpu);
+
+/* pops the largest-error tuple, inserts its point with the stored f (no re-evaluation), returns it.
+   DLI_ERR_ARG if the queue is empty or there is no callback (the reference asserts, :499-500). */
+int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, double *xy);
+int dli_di2_get_largest_error_tuple(dli_di2 *d, double *err, double *f, double *xy);
+int64_t dli_di2_error_queue_size(dli_di2 *d);
+/* all live tuples ordered by decreasing error; arrays of dli_di2_error_queue_size() entries */
+int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy);
+
+int64_t dli_di2_num_vertices(const dli_di2 *d);
+int64_t dli_di2_num_faces(const dli_di2 *d); /* finite faces */
+/* triangulation dimension: -1 empty, 0 one point, 1 all collinear, 2 triangulated */
+int dli_di2_dimension(const dli_di2 *d);
+
+/* flattened triangulation: coords [nv][2], f [nv], tri [nf][3] (ccw), nbr [nf][3] (-1 = hull); any may be NULL */
+int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, int32_t *nbr);
+
+/* batched interp on the GPU; (re)flattens lazily after insertions.  Host or device pointers as dli_interp.
+   With dimension < 2 every query reports DLI_STATUS_NO_MESH (the reference throws, :546-551). */
+int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
+                   void *stream);
+/* the device mesh currently backing dli_di2_interp (NULL before the first interp); owned by d */
+const dli_mesh *dli_di2_device_mesh(dli_di2 *d);
+int dli_di2_set_options(dli_di2 *d, const dli_options *opt);
+
+/* plot data: vertices as (x, y, f) triples [nv][3]; finite edges as segments [ne][2][3]; count query with NULL */
+int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz);
+int64_t dli_di2_get_line_segments(const dli_di2 *d, double *segments);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLI_HOST_H_ */

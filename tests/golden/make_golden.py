@@ -23,7 +23,8 @@ known = {
     "source": "/root/reference/README.md:126-131 (transcript of src/delaunay_2_test2.cpp-style program)",
     "regular_grid_sse": {"value": "5.800002", "line": "README.md:130", "status": "reproduced by the oracle"},
     "adaptive_grid_sse": {"value": "0.044019", "line": "README.md:131",
-                          "status": "NOT reproducible from the current header (SURVEY.md F7); historical"},
+                          "status": "reproduced by the native host triangulation + adaptive queue (dli_di2) with the "
+                                    "oracle's interp (tests/test_hostmesh.py); SURVEY.md F7's restatement did not"},
     "test2_variant_regular_grid_sse": {"value": "1.909975", "status": "unpublished; predicted by the restatement"},
 }
 with open(os.path.join(HERE, "readme_known_answers.json"), "w") as fh:

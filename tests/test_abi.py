@@ -9,9 +9,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _declared_symbols():
-    src = open(os.path.join(ROOT, "include", "dli.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(dli_[a-z0-9_]+)\s*\(", src)))
+    names = set()
+    for hdr in ("dli.h", "dli_host.h"):
+        src = open(os.path.join(ROOT, "include", hdr)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names |= set(re.findall(r"\b(dli_[a-z0-9_]+)\s*\(", src))
+    names.discard("dli_fn")
+    return sorted(names)
 
 
 def test_library_exports_every_declared_symbol():
@@ -23,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 20
     for n in names:
         assert hasattr(L, n), "libdli.so does not export %s" % n
-    bound = {s[0] for s in _capi.SYMBOLS}
+    bound = {s[0] for s in _capi.SYMBOLS + _capi.HOST_SYMBOLS}
     assert set(names) == bound, set(names) ^ bound
 
 

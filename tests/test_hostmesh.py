@@ -1,0 +1,124 @@
+"""CPU: the native host triangulation + adaptive queue (include/dli_host.h) that stand where the reference keeps
+CGAL, pinned by BOTH README known answers (README.md:130 and :131)."""
+import numpy as np
+
+import helpers
+from oracle.oracle import OracleMesh
+
+
+def _fn(x):
+    return x[0] ** 0.3 * x[1] ** 0.6
+
+
+def _tri_key(tri, coords):
+    return sorted(tuple(sorted(map(tuple, coords[t].tolist()))) for t in tri)
+
+
+def test_regular_grid_via_insert_matches_readme():
+    """README.md:55-60 + :130: 100 insert() calls on the 10x10 grid, SSE 5.800002; the cocircular tie-break
+    (CGAL's symbolic perturbation) yields the (x1,y0)-(x0,y1) diagonals."""
+    import delaunay_linterp_b200 as dl
+    for lo, want in ((0.0, "5.800002"), (0.01, "1.909975")):
+        g = helpers.linspace_ref(lo, 5.0, 10)
+        t = dl.DelaunayInterp2()
+        for i in range(10):
+            for j in range(10):
+                t.insert([g[i], g[j]], _fn([g[i], g[j]]))
+        c, f, tri, nb = t.export()
+        assert t.n_vertices == 100 and t.n_faces == 162
+        c2, f2, t2 = helpers.grid_mesh(lo)
+        assert _tri_key(tri, c) == _tri_key(t2, c2)
+        q = helpers.grid_queries(lo)
+        ys, _, st = OracleMesh(c, f, tri, nb).interp(q)
+        assert "%.6f" % float(np.sum((helpers.cobb_douglas(q) - ys) ** 2)) == want
+
+
+def test_insertion_order_independence_on_cocircular_grid():
+    import delaunay_linterp_b200 as dl
+    g = helpers.linspace_ref(0.0, 5.0, 7)
+    pts = [[g[i], g[j]] for i in range(7) for j in range(7)]
+    keys = []
+    for seed in (0, 1, 2):
+        order = np.random.default_rng(seed).permutation(len(pts))
+        t = dl.DelaunayInterp2()
+        for k in order:
+            t.insert(pts[k], 0.0)
+        c, f, tri, nb = t.export()
+        keys.append(_tri_key(tri, c))
+    assert keys[0] == keys[1] == keys[2]
+
+
+def test_adaptive_insertion_matches_readme():
+    """README.md:62-75 + :131: 4 corners + 96 x insert_largest_error_point, 'adaptive grid: sum of squared
+    errors: 0.044019'."""
+    import delaunay_linterp_b200 as dl
+    a = dl.DelaunayInterp2(_fn)
+    for p in ([0.0, 0.0], [0.0, 5.0], [5.0, 0.0], [5.0, 5.0]):
+        a.insert(p, _fn(p))
+    # 2 faces + 4 hull edges + 1 stale entry: the 4th corner is inserted OUTSIDE the hull of the first three, and
+    # the face behind the formerly-hull hypotenuse is not in the new vertex's star, so its edge entry survives --
+    # exactly what the reference does (src/delaunay_2_interp.h:459-474 erases star faces only); the README's
+    # 0.044019 depends on it (its first adaptive point is that stale midpoint (2.5, 2.5)).
+    q0 = a.get_error_queue()
+    assert len(q0) == 2 + 4 + 1 and q0[0][2] == [2.5, 2.5]
+    top = a.get_largest_error_tuple()
+    got = a.insert_largest_error_point()
+    assert got == top
+    for _ in range(95):
+        a.insert_largest_error_point()
+    assert a.n_vertices == 100
+    c, f, tri, nb = a.export()
+    q = helpers.grid_queries(0.0)
+    ys, _, _ = OracleMesh(c, f, tri, nb).interp(q)
+    assert "%.6f" % float(np.sum((helpers.cobb_douglas(q) - ys) ** 2)) == "0.044019"
+    # queue order is non-increasing and its entries belong to the current triangulation
+    errs = [e[0] for e in a.get_error_queue()]
+    assert all(errs[i] >= errs[i + 1] for i in range(len(errs) - 1))
+    n_hull = int((nb < 0).sum())
+    assert len(errs) == a.n_faces + n_hull
+
+
+def test_random_points_match_qhull():
+    import delaunay_linterp_b200 as dl
+    from scipy.spatial import Delaunay
+    pts = np.random.default_rng(5).random((5000, 2))
+    for sort in (True, False):
+        t = dl.DelaunayInterp2()
+        t.insert_many(pts, np.zeros(len(pts)), spatial_sort=sort)
+        c, f, tri, nb = t.export()
+        idx = {tuple(p): i for i, p in enumerate(pts.tolist())}
+        mine = sorted(tuple(sorted(idx[tuple(c[v])] for v in tr)) for tr in tri.tolist())
+        ref = sorted(tuple(sorted(tr)) for tr in Delaunay(pts).simplices.tolist())
+        assert mine == ref
+        OracleMesh(c, f, tri, nb)            # valid orientation / manifold
+        # neighbour table is symmetric
+        for s in range(0, len(tri), 97):
+            for k in range(3):
+                o = nb[s, k]
+                if o >= 0:
+                    assert s in nb[o]
+
+
+def test_degenerate_sequences():
+    import delaunay_linterp_b200 as dl
+    t = dl.DelaunayInterp2()
+    assert t.dimension == -1
+    t.insert([0.0, 0.0], 1.0)
+    t.insert([1.0, 1.0], 2.0)
+    t.insert([2.0, 2.0], 3.0)            # collinear
+    t.insert([1.0, 1.0], 5.0)            # duplicate: value overwritten
+    assert t.dimension == 1 and t.n_vertices == 3 and t.n_faces == 0
+    t.insert([0.5, 0.5], 4.0)            # still collinear
+    t.insert([0.0, 1.0], 0.0)            # first non-collinear point -> fan of 3 triangles
+    assert t.dimension == 2 and t.n_faces == 3
+    t.insert([1.5, 1.5], 9.0)            # on a hull edge
+    t.insert([3.0, 3.0], 7.0)            # collinear with the hull line, outside
+    t.insert([-1.0, -5.0], 7.0)          # far outside
+    c, f, tri, nb = t.export()
+    assert f[1] == 5.0
+    OracleMesh(c, f, tri, nb)
+    area = 0.0
+    for a, b, cc in tri:
+        area += 0.5 * ((c[b, 0] - c[a, 0]) * (c[cc, 1] - c[a, 1]) - (c[cc, 0] - c[a, 0]) * (c[b, 1] - c[a, 1]))
+    from scipy.spatial import ConvexHull
+    assert abs(area - ConvexHull(c).volume) < 1e-12
