@@ -5,7 +5,7 @@
 
 A "step" is one pass of the hot path over one batch of synthetic queries.  Workload at every N:
 BASELINE.json configs[1] per GPU ("2D scattered: 1M uniform-random vertices, 100M uniform queries in the
-convex hull, fp64"): mesh seed 1001, U[0,1)^2, Qhull-triangulated on the host; per-rank query seed 2001+rank,
+convex hull, fp64"): mesh seed 1001, U[0,1)^2, triangulated on the host by the native incremental Delaunay; per-rank query seed 2001+rank,
 U[0.02,0.98)^2, unsorted.  For N > 1 the mesh is flattened on rank 0 and replicated with one NCCL broadcast;
 every rank evaluates its own 100M-query shard (weak scaling, no data-path collective).
 
@@ -41,7 +41,7 @@ QUERY_SEED = 2001
 
 
 def workload_name(nq):
-    return ("cfg2: 2D scattered, 1M uniform-random vertices (seed 1001, Qhull), %dM uniform queries in "
+    return ("cfg2: 2D scattered, 1M uniform-random vertices (seed 1001), %dM uniform queries in "
             "U[0.02,0.98)^2 per GPU (seed 2001+rank), unsorted, fp64" % (nq // 1_000_000))
 
 
@@ -50,10 +50,13 @@ def f_cobb_douglas(x):
 
 
 def build_mesh_host(nv):
-    from scipy.spatial import Delaunay
+    """host-side construction (stays on the host by design): the native incremental Delaunay behind the
+    reference's insert() API (include/dli_host.h), bulk mode.  Same triangulation as Qhull for these points."""
+    import delaunay_linterp_b200 as dl
     pts = np.random.default_rng(MESH_SEED).random((nv, 2))
-    tri = Delaunay(pts)
-    return pts, f_cobb_douglas(pts), tri.simplices.astype(np.int32), tri.neighbors.astype(np.int32)
+    t = dl.DelaunayInterp2()
+    t.insert_many(pts, f_cobb_douglas(pts), spatial_sort=True, use_gpu=False)
+    return t.export()
 
 
 def host_queries(n, seed):

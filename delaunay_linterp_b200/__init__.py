@@ -7,6 +7,7 @@ from ._capi import (DliError, LIB_PATH, STATUS_NO_MESH, STATUS_OK, STATUS_OUTSID
                     STATUS_STEP_LIMIT, lib)
 from .mesh import Mesh, debug_orient
 from .interp2 import DelaunayInterp2
+from .interpd import Delaunay_incremental_interp_d, get_lifted_point
 
-__all__ = ["Mesh", "DelaunayInterp2", "debug_orient", "DliError", "lib", "LIB_PATH", "STATUS_OK", "STATUS_OUTSIDE_PROJECTED",
+__all__ = ["Mesh", "DelaunayInterp2", "Delaunay_incremental_interp_d", "get_lifted_point", "debug_orient", "DliError", "lib", "LIB_PATH", "STATUS_OK", "STATUS_OUTSIDE_PROJECTED",
            "STATUS_OUTSIDE_NAN", "STATUS_STEP_LIMIT", "STATUS_NO_MESH"]

@@ -1,0 +1,100 @@
+// C++ port of the reference's demo driver src/delaunay_2_test2.cpp (README.md:29-110), with the assertions the
+// reference never had.  Uses the drop-in header include/delaunay_2_interp.h; link with libdli.so.
+//   ./test_delaunay_2            full run (needs a GPU: interp goes through the CUDA engine)
+//   ./test_delaunay_2 --host     host-side part only (insert / adaptive queue / flatten)
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "delaunay_2_interp.h"
+
+using std::array;
+using std::vector;
+
+static vector<double> linspace(double first, double last, int len) {
+  vector<double> result(len);
+  double step = (last - first) / (len - 1);
+  for (int i = 0; i < len; i++) result[i] = first + i * step;
+  return result;
+}
+static double fn(int, double *x) { return pow(x[0], 0.3) * pow(x[1], 0.6); }
+
+#define CHECK(cond)                                                        \
+  do {                                                                     \
+    if (!(cond)) { printf("CHECK FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); return 1; } \
+  } while (0)
+
+static int run(double lo, const char *want_regular, const char *want_adaptive, bool host_only) {
+  int n_points = 10;
+  Delaunay_incremental_interp_2 triang;
+  vector<double> grid = linspace(lo, 5., n_points);
+  for (int i = 0; i < n_points; i++)
+    for (int j = 0; j < n_points; j++) {
+      array<double, 2> args = {grid[i], grid[j]};
+      triang.insert(args.begin(), args.end(), fn(2, &args[0]));
+    }
+  CHECK(triang.number_of_vertices() == 100 && triang.number_of_faces() == 162);
+
+  std::function<double(int, double *)> fn_obj(fn);
+  Delaunay_incremental_interp_2 adaptive_triang(fn_obj);
+  array<double, 2> args;
+  args[0] = grid.front(); args[1] = grid.front(); adaptive_triang.insert(args.begin(), args.end(), fn(2, &args[0]));
+  args[0] = grid.front(); args[1] = grid.back();  adaptive_triang.insert(args.begin(), args.end(), fn(2, &args[0]));
+  args[0] = grid.back();  args[1] = grid.front(); adaptive_triang.insert(args.begin(), args.end(), fn(2, &args[0]));
+  args[0] = grid.back();  args[1] = grid.back();  adaptive_triang.insert(args.begin(), args.end(), fn(2, &args[0]));
+  ErrorTuple top = adaptive_triang.get_largest_error_tuple();
+  ErrorTuple got = adaptive_triang.insert_largest_error_point();
+  CHECK(top.m_err == got.m_err && top.m_x == got.m_x);
+  for (int i = 0; i < n_points * n_points - 5; i++) adaptive_triang.insert_largest_error_point();
+  CHECK(adaptive_triang.number_of_vertices() == 100);
+  vector<ErrorTuple> q = adaptive_triang.get_error_queue();
+  for (size_t i = 0; i + 1 < q.size(); i++) CHECK(!(q[i] < q[i + 1]));
+  CHECK(adaptive_triang.get_all_vertices().size() == 100);
+  CHECK(adaptive_triang.get_line_segments().size() == 100 + adaptive_triang.number_of_faces() - 1);  // Euler: E = V + F - 1
+  if (host_only) { printf("host-only checks ok (lo=%g)\n", lo); return 0; }
+
+  vector<double> interp_grid = linspace(lo, 5., 2 * n_points), true_f, reg, ada, xs;
+  for (size_t i = 0; i < interp_grid.size(); i++)
+    for (size_t j = 0; j < interp_grid.size(); j++) {
+      array<double, 2> a = {interp_grid[i], interp_grid[j]};
+      true_f.push_back(fn(2, &a[0]));
+      reg.push_back(triang.interp(a.begin(), a.end()));            // scalar API, one query per call
+      ada.push_back(adaptive_triang.interp(a.begin(), a.end()));
+      xs.push_back(a[0]); xs.push_back(a[1]);
+    }
+  // batched API gives the same values
+  vector<double> reg_b(true_f.size()), ada_b(true_f.size());
+  vector<unsigned char> st(true_f.size());
+  triang.interp_batch(xs.data(), true_f.size(), reg_b.data(), st.data());
+  adaptive_triang.interp_batch(xs.data(), true_f.size(), ada_b.data());
+  double sse1 = 0, sse2 = 0;
+  for (size_t i = 0; i < true_f.size(); i++) {
+    CHECK(reg[i] == reg_b[i] && ada[i] == ada_b[i] && st[i] == DLI_STATUS_OK);
+    sse1 += (true_f[i] - reg[i]) * (true_f[i] - reg[i]);
+    sse2 += (true_f[i] - ada[i]) * (true_f[i] - ada[i]);
+  }
+  char b1[64], b2[64];
+  snprintf(b1, sizeof b1, "%f", sse1);
+  snprintf(b2, sizeof b2, "%f", sse2);
+  printf("regular grid: sum of squared errors: %s\nadaptive grid: sum of squared errors: %s\n", b1, b2);
+  CHECK(strcmp(b1, want_regular) == 0);
+  if (want_adaptive) CHECK(strcmp(b2, want_adaptive) == 0);
+  // outside the hull: projected, not an error (:530-545)
+  CHECK(std::fabs(triang.interp_point(Point(-1.0, 2.5)) - triang.interp_point(Point(lo, 2.5))) < 1e-14);
+  // no triangulation yet: std::invalid_argument (:546-551)
+  Delaunay_incremental_interp_2 empty;
+  bool threw = false;
+  try { empty.interp_point(Point(0.5, 0.5)); } catch (std::invalid_argument const &) { threw = true; }
+  CHECK(threw);
+  return 0;
+}
+
+int main(int argc, char **argv) {
+  bool host_only = argc > 1 && strcmp(argv[1], "--host") == 0;
+  // README.md:130-131 (grid on [0,5]) and the src/delaunay_2_test2.cpp variant (grid on [0.01,5])
+  if (run(0.0, "5.800002", "0.044019", host_only)) return 1;
+  if (run(0.01, "1.909975", nullptr, host_only)) return 1;
+  printf("ok\n");
+  return 0;
+}

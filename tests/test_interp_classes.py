@@ -1,0 +1,94 @@
+"""The reference-facing classes (DelaunayInterp2, Delaunay_incremental_interp_d): host logic on CPU, interp on GPU."""
+import math
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle.oracle import OracleMesh
+
+
+def _fn3(x):
+    return x[0] ** 0.3 * x[1] ** 0.6 * x[2] ** 0.2
+
+
+def test_dd_class_host_side_queue():
+    """src/delaunay_d_test2.cpp-style adaptive loop in 3D: corners of the cube, then insert_largest_error_point."""
+    import delaunay_linterp_b200 as dl
+    t = dl.Delaunay_incremental_interp_d(3, _fn3)
+    assert t.get_dimension() == 3
+    corners = [[a, b, c] for a in (0.01, 2.0) for b in (0.01, 2.0) for c in (0.01, 2.0)]
+    for p in corners:
+        t.insert(p, _fn3(p))
+    q = t.get_error_queue()
+    assert len(q) > 0 and all(q[i][0] >= q[i + 1][0] for i in range(len(q) - 1))
+    top = t.get_largest_error_tuple()
+    got = t.insert_largest_error_point()
+    assert got == top and len(got[2]) == 3
+    for _ in range(20):
+        t.insert_largest_error_point()
+    pts, f, sv, sn = t.export()
+    assert len(pts) == 8 + 21
+    # every live entry belongs to a current simplex; the mesh is valid for the oracle
+    OracleMesh(pts, f, sv, sn)
+    # per-insert host tuples == the oracle's SVD-form tuples of the final mesh (as multisets of errors)
+    om = OracleMesh(pts, f, sv, sn)
+    o_simplex, o_nv, o_verts, o_cent = om.error_items()
+    want = np.sort(om.error_eval(o_nv, o_verts, o_cent, np.array([_fn3(c) for c in o_cent])))
+    have = np.sort(np.array([e[0] for e in t.get_error_queue()]))
+    assert len(want) == len(have)
+    assert np.allclose(want, have, rtol=1e-8, atol=1e-18)
+    assert dl.get_lifted_point([1.0, 2.0]) == [1.0, 2.0, 5.0]
+
+
+@pytest.mark.gpu
+def test_interp2_class_on_gpu(gpu):
+    import delaunay_linterp_b200 as dl
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
+    a = dl.DelaunayInterp2(fn)
+    for p in ([0.0, 0.0], [0.0, 5.0], [5.0, 0.0], [5.0, 5.0]):
+        a.insert(p, fn(p))
+    for _ in range(96):
+        a.insert_largest_error_point()
+    q = helpers.grid_queries(0.0)
+    ys = a.interp(q)
+    assert "%.6f" % float(np.sum((helpers.cobb_douglas(q) - ys) ** 2)) == "0.044019"    # README.md:131
+    assert a.interp([2.5, 2.5]) == ys[np.flatnonzero((q == [2.5, 2.5]).all(1))[0]] if ((q == [2.5, 2.5]).all(1)).any() else True
+    assert isinstance(a.interp([1.0, 1.0]), float)
+    # interleaving insert and interp re-flattens lazily
+    y0 = a.interp([1.234, 2.345])
+    a.insert([1.234, 2.345], 7.0)
+    assert a.interp([1.234, 2.345]) == 7.0 and y0 != 7.0
+    # empty triangulation: the scalar form raises like the reference (std::invalid_argument)
+    with pytest.raises(ValueError):
+        dl.DelaunayInterp2().interp([0.5, 0.5])
+    # bulk build + GPU-batched queue rebuild == per-insert host queue
+    pts = np.random.default_rng(3).random((3000, 2)) * 4.9 + 0.05
+    b1, b2 = dl.DelaunayInterp2(fn), dl.DelaunayInterp2(fn)
+    b1.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=True)
+    b2.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False)
+    e1 = np.array([e[0] for e in b1.get_error_queue()])
+    e2 = np.array([e[0] for e in b2.get_error_queue()])
+    assert len(e1) == len(e2) and np.allclose(e1, e2, rtol=1e-10, atol=1e-20)
+    assert b1.get_largest_error_tuple()[2] == b2.get_largest_error_tuple()[2]
+
+
+@pytest.mark.gpu
+def test_dd_class_on_gpu(gpu):
+    import delaunay_linterp_b200 as dl
+    t = dl.Delaunay_incremental_interp_d(3, _fn3)
+    corners = [[a, b, c] for a in (0.01, 2.0) for b in (0.01, 2.0) for c in (0.01, 2.0)]
+    for p in corners:
+        t.insert(p, _fn3(p))
+    for _ in range(40):
+        t.insert_largest_error_point()
+    assert math.isnan(t.interp([3.0, 3.0, 3.0]))                      # outside: NaN (:1005-1008)
+    q = np.random.default_rng(1).random((5000, 3)) * 1.9 + 0.05
+    ys = t.interp(q)
+    pts, f, sv, sn = t.export()
+    yo, _, _ = OracleMesh(pts, f, sv, sn).interp(q)
+    assert np.max(np.abs(ys - yo) / np.maximum(np.abs(yo), 1e-300)) <= 1e-12
+    before = sorted(e[0] for e in t.get_error_queue())
+    t.rebuild_error_queue()                                            # GPU batch == per-insert host tuples
+    after = sorted(e[0] for e in t.get_error_queue())
+    assert len(before) == len(after) and np.allclose(before, after, rtol=1e-8, atol=1e-18)
