@@ -59,6 +59,14 @@ def build_mesh_host(nv):
     return t.export()
 
 
+def build_mesh_host_qhull(nv):
+    """reference arm: mesh from Qhull (scipy), so that nothing of the product is on that arm's path."""
+    from scipy.spatial import Delaunay
+    pts = np.random.default_rng(MESH_SEED).random((nv, 2))
+    tri = Delaunay(pts)
+    return pts, f_cobb_douglas(pts), tri.simplices.astype(np.int32), tri.neighbors.astype(np.int32)
+
+
 def host_queries(n, seed):
     return np.random.default_rng(seed).random((n, 2)) * 0.96 + 0.02
 
@@ -156,7 +164,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return 0
     ncores = os.cpu_count() or 1
-    pts, f, sv, sn = build_mesh_host(NV)
+    pts, f, sv, sn = build_mesh_host_qhull(NV)
     om, q = cpu_baseline_sample(pts, f, sv, sn, ncores, target_s=4.0)
     for _ in range(args.warmup):
         om.interp(q[: max(1000, len(q) // 8)], mode=0, nthreads=ncores)
