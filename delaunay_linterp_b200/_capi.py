@@ -31,7 +31,9 @@ class Options(C.Structure):
         ("epilogue", C.c_int32),
         ("threads_per_block", C.c_int32),
         ("queries_per_warp", C.c_int32),
-        ("reserved", C.c_int32 * 8),
+        ("packed_faces", C.c_int32),
+        ("min_blocks_per_sm", C.c_int32),
+        ("reserved", C.c_int32 * 6),
     ]
 
 

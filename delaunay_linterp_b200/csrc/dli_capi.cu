@@ -59,6 +59,7 @@ struct dli_mesh {
   int32_t *d_srec = nullptr;
   int4 *d_hull = nullptr;
   int32_t *d_hint = nullptr;
+  ulonglong2 *d_fpack = nullptr;  // 2D packed face records (fast pass), NULL when ids do not fit 21 bits
   GridView grid{};
   int max_steps = 0, fast_steps = 0;
   // error items (lazy)
@@ -83,6 +84,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_srec);
   cudaFree(m->d_hull);
   cudaFree(m->d_hint);
+  cudaFree(m->d_fpack);
   cudaFree(m->d_item_verts);
   cudaFree(m->d_stats);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
@@ -100,6 +102,8 @@ extern "C" void dli_options_init(dli_options *o) {
   o->epilogue = 0;
   o->threads_per_block = 0;
   o->queries_per_warp = 0;
+  o->packed_faces = 0;
+  o->min_blocks_per_sm = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -243,6 +247,8 @@ static int mesh_alloc_common(dli_mesh *m) {
   CU(cudaMalloc(&m->d_vrec, sizeof(double) * (size_t)std::max<int64_t>(m->nv, 1) * m->vs));
   CU(cudaMalloc(&m->d_srec, sizeof(int32_t) * (size_t)std::max<int64_t>(m->ns, 1) * m->ss));
   if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
+  if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
+    CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
   // keep stream-ordered allocations cached between calls
@@ -361,6 +367,12 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
     rc = build_hint_grid(m, coords);
     if (rc != DLI_OK) { mesh_free(m); return rc; }
   }
+  if (m->d_fpack) {
+    k_pack_faces<<<(unsigned)((ns + 255) / 256), 256>>>((int)ns, reinterpret_cast<const int4 *>(m->d_srec), m->d_fpack);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { mesh_free(m); return fail(DLI_ERR_CUDA, std::string("face packing failed: ") + cudaGetErrorString(e)); }
+  }
   *out = m;
   return DLI_OK;
 }
@@ -381,7 +393,7 @@ extern "C" int64_t dli_mesh_num_simplices(const dli_mesh *m) { return m ? m->ns 
 extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
-                   sizeof(int32_t) * m->grid.cells);
+                   sizeof(int32_t) * m->grid.cells + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
@@ -400,6 +412,7 @@ Mesh2View view2(const dli_mesh *m) {
   Mesh2View v;
   v.vrec = reinterpret_cast<const double4 *>(m->d_vrec);
   v.frec = reinterpret_cast<const int4 *>(m->d_srec);
+  v.fpack = m->d_fpack;
   v.hull = m->d_hull;
   v.hint = m->d_hint;
   v.ox = m->grid.o[0]; v.oy = m->grid.o[1];
@@ -441,6 +454,9 @@ struct Launch {
 
 template <bool STATS, int EPI>
 void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
+  const int minb = L.m->opt.min_blocks_per_sm;
+  auto fast = L.m->d_fpack ? (minb == 5 ? k_interp2_fast<STATS, EPI, true, 5> : k_interp2_fast<STATS, EPI, true, 4>)
+                           : (minb == 5 ? k_interp2_fast<STATS, EPI, false, 5> : k_interp2_fast<STATS, EPI, false, 4>);
   Mesh2View v = view2(L.m);
   int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : 256;
   tpb = std::min(256, std::max(32, tpb / 32 * 32));
@@ -451,7 +467,7 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int64_t warps = (n + per_warp - 1) / per_warp;
   int wpb = tpb / 32;
   L.mark(0);
-  k_interp2_fast<STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
+  fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
       v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   L.mark(1);
   k_interp2_full<STATS, EPI><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
@@ -463,9 +479,13 @@ template <int D, bool STATS, int EPI>
 void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
   MeshDView v = viewD(L.m);
   int tpb = 128;
+  int per_warp = L.m->opt.queries_per_warp > 0 ? L.m->opt.queries_per_warp : 512;
+  while (per_warp > 32 && n / per_warp < 148 * 64) per_warp >>= 1;
+  int64_t warps = (n + per_warp - 1) / per_warp;
+  int wpb = tpb / 32;
   L.mark(0);
-  k_interpD_fast<D, STATS, EPI><<<(unsigned)((n + tpb - 1) / tpb), tpb, 0, L.st>>>(v, n, xs, ys, so, sto, L.queue,
-                                                                                    L.qcount, L.qcap, L.stats);
+  k_interpD_fast<D, STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(v, n, per_warp, xs, ys, so, sto, L.queue,
+                                                                                      L.qcount, L.qcap, L.stats);
   L.mark(1);
   k_interpD_full<D, STATS, EPI><<<148 * 2, 64, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
   L.mark(2);
@@ -802,9 +822,9 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   return DLI_OK;
 }
 
-extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 4 : 0; }
+extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 5 : 0; }
 
-// buffers 0..3: vertex records, simplex records, hull table, hint grid
+// buffers 0..4: vertex records, simplex records, hull table, hint grid, packed 2D face records (may be empty)
 extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t *bytes) {
   if (!m || !ptr || !bytes) return fail(DLI_ERR_ARG, "NULL argument");
   switch (index) {
@@ -812,6 +832,7 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 1: *ptr = m->d_srec; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1) * m->ss; break;
     case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
+    case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }
   return DLI_OK;

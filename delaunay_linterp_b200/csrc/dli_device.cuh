@@ -25,6 +25,10 @@ constexpr int kMaxProjections = 16;  // 2D outside-hull project/re-locate rounds
 struct Mesh2View {
   const double4 *vrec;
   const int4 *frec;
+  // optional packed face records for the fast pass (meshes with <= 2^21 vertices and < 2^21-1 faces):
+  // 16 B = {v0 | v1 << 21 | v2 << 42, n0 | n1 << 21 | n2 << 42}, neighbour 0x1FFFFF = hull.  Halves the
+  // L2 footprint of the face array (two faces per sector).
+  const ulonglong2 *fpack;
   const int4 *hull;
   const int32_t *hint;
   double ox, oy, icx, icy;  // hint grid origin and 1/cell size
@@ -146,6 +150,18 @@ __device__ __forceinline__ Face2 load_face(const Mesh2View &m, int f) {
   asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r.v0), "=r"(r.v1), "=r"(r.v2), "=r"(r.n0), "=r"(r.n1), "=r"(r.n2), "=r"(p0), "=r"(p1)
                : "l"(m.frec + 2 * (size_t)f));
+  return r;
+}
+constexpr unsigned kPackMask = 0x1FFFFFu;
+__device__ __forceinline__ Face2 load_face_packed(const Mesh2View &m, int f) {
+  unsigned long long w0, w1;
+  asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(m.fpack + f));
+  Face2 r;
+  r.v0 = (int)(w0 & kPackMask); r.v1 = (int)((w0 >> 21) & kPackMask); r.v2 = (int)(w0 >> 42);
+  int n0 = (int)(w1 & kPackMask), n1 = (int)((w1 >> 21) & kPackMask), n2 = (int)(w1 >> 42);
+  r.n0 = n0 == (int)kPackMask ? -1 : n0;
+  r.n1 = n1 == (int)kPackMask ? -1 : n1;
+  r.n2 = n2 == (int)kPackMask ? -1 : n2;
   return r;
 }
 __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
@@ -340,6 +356,74 @@ __device__ __forceinline__ int orient_replaced(const SimplexD<D> &S, int j, cons
   return s;
 }
 
+// All D+1 facet orientations of one walk step at once.  With R_i = v_i - q (rows of a (D+1) x D matrix),
+// the orientation of the simplex with vertex j replaced by q is (-1)^(j+D) * det(R without row j); the D+1
+// determinants share their lower-order minors (cofactor expansion along column 0, minors along their first
+// column), so the rounding structure -- and therefore the filter constant -- is that of DetPerm<D>.
+// Outputs o[j] (signed so that o[j] < 0 means "q is beyond facet j") and the permanent bound scale pm[j].
+template <int D>
+struct OrientAll;
+template <>
+struct OrientAll<3> {
+  __device__ __forceinline__ static void eval(const double *R, double *o, double *pm) {
+    // 2x2 minors over columns (1,2) for the 6 row pairs
+    double M[4][4], P[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = a + 1; b < 4; b++) {
+        double l = R[a * 3 + 1] * R[b * 3 + 2], r = R[a * 3 + 2] * R[b * 3 + 1];
+        M[a][b] = l - r;
+        P[a][b] = fabs(l) + fabs(r);
+      }
+    auto det3 = [&](int a, int b, int c, double &perm) {
+      double t0 = R[a * 3] * M[b][c], t1 = R[b * 3] * M[a][c], t2 = R[c * 3] * M[a][b];
+      perm = fabs(R[a * 3]) * P[b][c] + fabs(R[b * 3]) * P[a][c] + fabs(R[c * 3]) * P[a][b];
+      return (t0 - t1) + t2;
+    };
+    o[0] = -det3(1, 2, 3, pm[0]);
+    o[1] = det3(0, 2, 3, pm[1]);
+    o[2] = -det3(0, 1, 3, pm[2]);
+    o[3] = det3(0, 1, 2, pm[3]);
+  }
+};
+template <>
+struct OrientAll<4> {
+  __device__ __forceinline__ static void eval(const double *R, double *o, double *pm) {
+    double M2[5][5], P2[5][5];
+#pragma unroll
+    for (int a = 0; a < 5; a++)
+#pragma unroll
+      for (int b = a + 1; b < 5; b++) {
+        double l = R[a * 4 + 2] * R[b * 4 + 3], r = R[a * 4 + 3] * R[b * 4 + 2];
+        M2[a][b] = l - r;
+        P2[a][b] = fabs(l) + fabs(r);
+      }
+    double M3[5][5][5], P3[5][5][5];
+#pragma unroll
+    for (int a = 0; a < 5; a++)
+#pragma unroll
+      for (int b = a + 1; b < 5; b++)
+#pragma unroll
+        for (int c = b + 1; c < 5; c++) {
+          double t0 = R[a * 4 + 1] * M2[b][c], t1 = R[b * 4 + 1] * M2[a][c], t2 = R[c * 4 + 1] * M2[a][b];
+          M3[a][b][c] = (t0 - t1) + t2;
+          P3[a][b][c] = fabs(R[a * 4 + 1]) * P2[b][c] + fabs(R[b * 4 + 1]) * P2[a][c] + fabs(R[c * 4 + 1]) * P2[a][b];
+        }
+    auto det4 = [&](int a, int b, int c, int d, double &perm) {
+      double t0 = R[a * 4] * M3[b][c][d], t1 = R[b * 4] * M3[a][c][d], t2 = R[c * 4] * M3[a][b][d], t3 = R[d * 4] * M3[a][b][c];
+      perm = fabs(R[a * 4]) * P3[b][c][d] + fabs(R[b * 4]) * P3[a][c][d] + fabs(R[c * 4]) * P3[a][b][d] +
+             fabs(R[d * 4]) * P3[a][b][c];
+      return ((t0 - t1) + t2) - t3;
+    };
+    o[0] = det4(1, 2, 3, 4, pm[0]);
+    o[1] = -det4(0, 2, 3, 4, pm[1]);
+    o[2] = det4(0, 1, 3, 4, pm[2]);
+    o[3] = -det4(0, 1, 2, 4, pm[3]);
+    o[4] = det4(0, 1, 2, 3, pm[4]);
+  }
+};
+
 // fast path (filter only).  true = located with certainty inside the hull.
 template <int D>
 __device__ __forceinline__ bool locateD_fast(const MeshDView &m, const double *p, int &s, SimplexD<D> &S,
@@ -449,9 +533,9 @@ __device__ __forceinline__ double volD(const double *const *pts) {
   return lu_det<D>(a) / fact;
 }
 
-// exact sum of products truncated toward zero (Gmpq accumulation + mpq_get_d, :998-1004)
+// exact sum of products truncated toward zero (Gmpq accumulation + mpq_get_d, :998-1004): slow, exact path
 template <int K>
-__device__ inline double dot_exact_trunc(const double *b, const double *f) {
+__device__ __noinline__ double dot_exact_trunc_slow(const double *b, const double *f) {
   double e[2 * K + 1], t[2 * K + 2];
   int n = 0;
   for (int i = 0; i < K; i++) {
@@ -480,6 +564,37 @@ __device__ inline double dot_exact_trunc(const double *b, const double *f) {
     break;
   }
   return A;
+}
+
+// Same value, register-only fast path: compensated (double-double) accumulation gives the total as h + l
+// with |l| <= ulp(h)/2 up to an error far below |l|; the truncation toward zero is then h when l has the
+// sign of h (or is an exact zero), else the neighbour of h towards zero.  When l is too small to trust its
+// sign (relative to the accumulated rounding bound) the exact path decides.
+template <int K>
+__device__ __forceinline__ double dot_exact_trunc(const double *b, const double *f) {
+  double s, lo = 0.0, pabs, q;
+  two_prod(b[0], f[0], s, q);
+  lo = q;
+  pabs = fabs(s);
+  bool all_exact = (q == 0.0);
+#pragma unroll
+  for (int i = 1; i < K; i++) {
+    double p, qq, sn, e;
+    two_prod(b[i], f[i], p, qq);
+    two_sum(s, p, sn, e);
+    s = sn;
+    lo += e + qq;
+    pabs += fabs(p);
+    all_exact = all_exact && (e == 0.0) && (qq == 0.0);
+  }
+  if (all_exact) return s;  // every operation was exact: s is the exact total
+  double h, l;
+  two_sum(s, lo, h, l);  // (|lo| <= |s| is not guaranteed under cancellation, so not fast_two_sum)
+  if (!isfinite(h)) return h;
+  // rounding of `lo` itself is bounded by ~K^2 2^-106 sum|p_i|; demand a wide margin
+  if (!(fabs(l) > 8.673617379884035e-19 * 1.1102230246251565e-16 * 1048576.0 * pabs)) return dot_exact_trunc_slow<K>(b, f);
+  bool same = (l > 0.0) == (h > 0.0);
+  return same ? h : nextafter(h, 0.0);
 }
 
 template <int D>

@@ -49,8 +49,8 @@ __device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAc
 // Predicates are filter-only here; queries it cannot certify (filter failure, hull exit, long walk)
 // are appended to `queue` for k_interp2_full.  If the queue overflows (`queue_cap`), the counter
 // keeps growing and k_interp2_full re-runs the whole batch (degenerate inputs only).
-template <bool STATS, int EPI>
-__global__ void __launch_bounds__(256, 4)
+template <bool STATS, int EPI, bool PACKED, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
                unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
@@ -86,7 +86,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
     if (!__any_sync(FULL, active)) break;
     if (active) {
       steps++;
-      Face2 F = load_face(m, f);
+      Face2 F = PACKED ? load_face_packed(m, f) : load_face(m, f);
       double4 A = load_vert(m, F.v0), B = load_vert(m, F.v1), C = load_vert(m, F.v2);
       double ax = A.x - px, ay = A.y - py, bx = B.x - px, by = B.y - py, cx = C.x - px, cy = C.y - py;
       // edge opposite v0 = (B, C); opposite v1 = (C, A); opposite v2 = (A, B)
@@ -165,32 +165,91 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
 // dD interp
 // ---------------------------------------------------------------------------------------------
 
+// dD fast pass: the same warp-persistent lane state machine as k_interp2_fast (one walk step per lane per
+// iteration, ballot/popc refill), all D+1 facet orientations of a step from shared minors (OrientAll<D>).
 template <int D, bool STATS, int EPI>
 __global__ void __launch_bounds__(128)
-k_interpD_fast(MeshDView m, int64_t n, const double *__restrict__ xs, double *__restrict__ ys,
+k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
                unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  StatsAcc st;
-  if (i < n) {
-    double p[D];
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * per_warp;
+  if (base >= n) return;  // warp-uniform
+  const int64_t end = min(n, base + (int64_t)per_warp);
+  int64_t next = base;
+  bool active = false;
+  double p[D];
 #pragma unroll
-    for (int k = 0; k < D; k++) p[k] = __ldcs(xs + i * D + k);
-    int s = hintD<D>(m, p);
-    SimplexD<D> S;
-    unsigned int steps = 0;
-    bool ok = locateD_fast<D>(m, p, s, S, steps);
-    if (ok) {
-      if (ys) {
-        double y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
-        __stcs(ys + i, y);
+  for (int k = 0; k < D; k++) p[k] = 0.0;
+  int s = 0, from = -1;
+  int64_t qi = 0;
+  unsigned int steps = 0;
+  const double fc = filter_const(D);
+  StatsAcc st;
+  for (;;) {
+    unsigned need = __ballot_sync(FULL, !active);
+    if (need) {
+      int64_t idx = next + __popc(need & ((1u << lane) - 1u));
+      if (!active && idx < end) {
+#pragma unroll
+        for (int k = 0; k < D; k++) p[k] = __ldcs(xs + idx * D + k);
+        qi = idx;
+        s = hintD<D>(m, p);
+        from = -1;
+        steps = 0;
+        active = true;
       }
-      if (simplex_out) __stcs(simplex_out + i, s);
-      if (status_out) status_out[i] = DLI_STATUS_OK;
-      if (STATS) { st.steps = steps; st.max_steps = steps; }
-    } else {
-      unsigned int slot = atomicAdd(queue_count, 1u);
-      if (slot < queue_cap) queue[slot] = (int32_t)i;
+      next += __popc(need);
+    }
+    if (!__any_sync(FULL, active)) break;
+    if (active) {
+      steps++;
+      SimplexD<D> S;
+      load_simplex_ids<D>(m, s, S);
+      load_simplex_verts<D>(m, S);
+      double R[(D + 1) * D], o[D + 1], pm[D + 1];
+#pragma unroll
+      for (int i = 0; i <= D; i++)
+#pragma unroll
+        for (int k = 0; k < D; k++) R[i * D + k] = S.x[i * D + k] - p[k];
+      OrientAll<D>::eval(R, o, pm);
+      int mv = -1;
+      bool all_pos = true;
+#pragma unroll
+      for (int j = D; j >= 0; j--) {
+        bool came = (S.n[j] >= 0) & (S.n[j] == from);
+        double e = fc * pm[j];
+        if (!came) {
+          if (-o[j] > e) mv = j;               // lowest such j wins (loop runs downwards)
+          else if (!(o[j] > e)) all_pos = false;
+        }
+      }
+      bool give_up = false;
+      if (mv >= 0) {
+        int nb = S.n[0];
+#pragma unroll
+        for (int j = 1; j <= D; j++) nb = (mv == j) ? S.n[j] : nb;
+        if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;
+        else { from = s; s = nb; }
+      } else if (all_pos) {
+        if (ys) {
+          double y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
+          __stcs(ys + qi, y);
+        }
+        if (simplex_out) __stcs(simplex_out + qi, s);
+        if (status_out) status_out[qi] = DLI_STATUS_OK;
+        if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
+        active = false;
+      } else {
+        give_up = true;
+      }
+      if (give_up) {
+        unsigned int slot = atomicAdd(queue_count, 1u);
+        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        active = false;
+      }
     }
   }
   if (STATS) flush_stats(stats, st);
@@ -229,6 +288,19 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
     flush_stats(stats, st);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
   }
+}
+
+// 32-byte face records -> 16-byte packed records (see Mesh2View::fpack)
+__global__ void k_pack_faces(int ns, const int4 *__restrict__ frec, ulonglong2 *__restrict__ fpack) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns) return;
+  int4 a = frec[2 * (size_t)f], b = frec[2 * (size_t)f + 1];
+  unsigned long long n0 = a.w < 0 ? kPackMask : (unsigned)a.w, n1 = b.x < 0 ? kPackMask : (unsigned)b.x,
+                     n2 = b.y < 0 ? kPackMask : (unsigned)b.y;
+  ulonglong2 r;
+  r.x = (unsigned long long)(unsigned)a.x | ((unsigned long long)(unsigned)a.y << 21) | ((unsigned long long)(unsigned)a.z << 42);
+  r.y = n0 | (n1 << 21) | (n2 << 42);
+  fpack[f] = r;
 }
 
 __global__ void k_fill_nomesh(int64_t n, double *ys, int32_t *simplex_out, uint8_t *status_out) {
