@@ -32,8 +32,7 @@ class Options(C.Structure):
         ("threads_per_block", C.c_int32),
         ("queries_per_warp", C.c_int32),
         ("packed_faces", C.c_int32),
-        ("min_blocks_per_sm", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("reserved", C.c_int32 * 7),
     ]
 
 

@@ -103,7 +103,6 @@ extern "C" void dli_options_init(dli_options *o) {
   o->threads_per_block = 0;
   o->queries_per_warp = 0;
   o->packed_faces = 0;
-  o->min_blocks_per_sm = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -454,9 +453,7 @@ struct Launch {
 
 template <bool STATS, int EPI>
 void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
-  const int minb = L.m->opt.min_blocks_per_sm;
-  auto fast = L.m->d_fpack ? (minb == 5 ? k_interp2_fast<STATS, EPI, true, 5> : k_interp2_fast<STATS, EPI, true, 4>)
-                           : (minb == 5 ? k_interp2_fast<STATS, EPI, false, 5> : k_interp2_fast<STATS, EPI, false, 4>);
+  auto fast = L.m->d_fpack ? k_interp2_fast<STATS, EPI, true> : k_interp2_fast<STATS, EPI, false>;
   Mesh2View v = view2(L.m);
   int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : 256;
   tpb = std::min(256, std::max(32, tpb / 32 * 32));

@@ -49,8 +49,8 @@ __device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAc
 // Predicates are filter-only here; queries it cannot certify (filter failure, hull exit, long walk)
 // are appended to `queue` for k_interp2_full.  If the queue overflows (`queue_cap`), the counter
 // keeps growing and k_interp2_full re-runs the whole batch (degenerate inputs only).
-template <bool STATS, int EPI, bool PACKED, int MINB>
-__global__ void __launch_bounds__(256, MINB)
+template <bool STATS, int EPI, bool PACKED>
+__global__ void __launch_bounds__(256, 4)
 k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
                unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {

@@ -65,8 +65,7 @@ typedef struct dli_options {
   int32_t queries_per_warp;       /* 2D fast pass: contiguous queries owned by one warp; <= 0 = default (1024) */
   int32_t packed_faces;           /* 2D: 0 = use 16-byte packed face records in the fast pass when ids fit 21 bits
                                      (default), -1 = never */
-  int32_t min_blocks_per_sm;      /* 2D fast pass register budget: 4 (default, 64 registers) or 5 (48 registers, spills; measured slower) CTAs of 256 */
-  int32_t reserved[6];
+  int32_t reserved[7];
 } dli_options;
 
 /* fills *opt with the defaults */

@@ -24,8 +24,6 @@ VAR = {
  "cf2": dict(hint_cells_per_simplex=2.0, epilogue="closed_form"), "cf4": dict(hint_cells_per_simplex=4.0, epilogue="closed_form"),
  "nopack": dict(hint_cells_per_simplex=2.0, packed_faces=-1), "cf2nopack": dict(hint_cells_per_simplex=2.0, packed_faces=-1, epilogue="closed_form"),
  "cps1cf": dict(hint_cells_per_simplex=1.0, epilogue="closed_form"),
- "mb5": dict(hint_cells_per_simplex=2.0, min_blocks_per_sm=5), "mb6": dict(hint_cells_per_simplex=2.0, min_blocks_per_sm=6),
- "mb5cf": dict(hint_cells_per_simplex=2.0, min_blocks_per_sm=5, epilogue="closed_form"), "mb6cf": dict(hint_cells_per_simplex=2.0, min_blocks_per_sm=6, epilogue="closed_form"),
  "t128": dict(hint_cells_per_simplex=2.0, threads_per_block=128),
  "qpw256": dict(hint_cells_per_simplex=2.0, queries_per_warp=256), "qpw512": dict(hint_cells_per_simplex=2.0, queries_per_warp=512),
  "qpw2048": dict(hint_cells_per_simplex=2.0, queries_per_warp=2048), "qpw4096": dict(hint_cells_per_simplex=2.0, queries_per_warp=4096),
