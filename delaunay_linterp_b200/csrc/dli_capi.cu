@@ -60,6 +60,8 @@ struct dli_mesh {
   int4 *d_hull = nullptr;
   int32_t *d_hint = nullptr;
   ulonglong2 *d_fpack = nullptr;  // 2D packed face records (fast pass), NULL when ids do not fit 21 bits
+  uint4 *d_fat = nullptr;         // 2D 64-byte walk records (k_interp2_fat), NULL when unused
+  int64_t n_slow_faces = 0;       // faces carrying the slow flag in d_fat
   GridView grid{};
   int max_steps = 0, fast_steps = 0;
   // error items (lazy)
@@ -85,6 +87,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_hull);
   cudaFree(m->d_hint);
   cudaFree(m->d_fpack);
+  cudaFree(m->d_fat);
   cudaFree(m->d_item_verts);
   cudaFree(m->d_stats);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
@@ -248,6 +251,8 @@ static int mesh_alloc_common(dli_mesh *m) {
   if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
   if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
     CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
+  if (d == 2 && m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0 && m->ns < (1 << 21) - 1)
+    CU(cudaMalloc(&m->d_fat, 64 * (size_t)m->ns));
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
   // keep stream-ordered allocations cached between calls
@@ -256,6 +261,21 @@ static int mesh_alloc_common(dli_mesh *m) {
     unsigned long long thr = ~0ull;
     cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
   }
+  return DLI_OK;
+}
+
+// (re)builds the 64-byte walk records from the canonical records (values and geometry)
+static int build_fat_records(dli_mesh *m) {
+  if (!m->d_fat) return DLI_OK;
+  unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
+  CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
+  k_build_fat2<<<(unsigned)((m->ns + 255) / 256), 256>>>((int)m->ns, reinterpret_cast<const int4 *>(m->d_srec),
+                                                       reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
+  CU(cudaGetLastError());
+  unsigned int cnt = 0;
+  CU(cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost));
+  CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
+  m->n_slow_faces = cnt;
   return DLI_OK;
 }
 
@@ -372,6 +392,8 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { mesh_free(m); return fail(DLI_ERR_CUDA, std::string("face packing failed: ") + cudaGetErrorString(e)); }
   }
+  rc = build_fat_records(m);
+  if (rc != DLI_OK) { mesh_free(m); return rc; }
   *out = m;
   return DLI_OK;
 }
@@ -382,7 +404,7 @@ extern "C" int dli_mesh_set_values(dli_mesh *m, const double *f) {
   // strided copy into the f slot of every vertex record
   CU(cudaMemcpy2D(m->d_vrec + m->dim, sizeof(double) * m->vs, f, sizeof(double), sizeof(double), (size_t)m->nv,
                   cudaMemcpyHostToDevice));
-  return DLI_OK;
+  return build_fat_records(m);
 }
 
 extern "C" void dli_mesh_destroy(dli_mesh *m) { mesh_free(m); }
@@ -392,7 +414,8 @@ extern "C" int64_t dli_mesh_num_simplices(const dli_mesh *m) { return m ? m->ns 
 extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
-                   sizeof(int32_t) * m->grid.cells + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0));
+                   sizeof(int32_t) * m->grid.cells + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
+                   (m->d_fat ? 64 * m->ns : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
@@ -412,6 +435,7 @@ Mesh2View view2(const dli_mesh *m) {
   v.vrec = reinterpret_cast<const double4 *>(m->d_vrec);
   v.frec = reinterpret_cast<const int4 *>(m->d_srec);
   v.fpack = m->d_fpack;
+  v.fat = m->d_fat;
   v.hull = m->d_hull;
   v.hint = m->d_hint;
   v.ox = m->grid.o[0]; v.oy = m->grid.o[1];
@@ -464,8 +488,12 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int64_t warps = (n + per_warp - 1) / per_warp;
   int wpb = tpb / 32;
   L.mark(0);
-  fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
-      v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  if (EPI == 0 && L.m->d_fat)
+    k_interp2_fat<STATS><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
+        v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  else
+    fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
+        v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   L.mark(1);
   k_interp2_full<STATS, EPI><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
                                                          L.qcount, L.qcap, n, L.stats);
@@ -525,10 +553,10 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     int32_t *cs = so ? so + off : nullptr;
     uint8_t *ct = sto ? sto + off : nullptr;
     if (m->collect_stats) {
-      if (m->opt.epilogue == 0) launch_any<true, 0>(L, cn, cx, cy, cs, ct);
+      if (m->opt.epilogue != DLI_EPILOGUE_CLOSED_FORM) launch_any<true, 0>(L, cn, cx, cy, cs, ct);
       else launch_any<true, 1>(L, cn, cx, cy, cs, ct);
     } else {
-      if (m->opt.epilogue == 0) launch_any<false, 0>(L, cn, cx, cy, cs, ct);
+      if (m->opt.epilogue != DLI_EPILOGUE_CLOSED_FORM) launch_any<false, 0>(L, cn, cx, cy, cs, ct);
       else launch_any<false, 1>(L, cn, cx, cy, cs, ct);
     }
     CU(cudaGetLastError());
@@ -777,13 +805,14 @@ extern "C" int dli_simplex_error_finish(const dli_mesh *mc, int64_t n, const dou
 // replication support
 // ---------------------------------------------------------------------------------------------
 // header words: 0 version, 1 dim, 2 nv, 3 ns, 4 nh, 5 cells, 6..9 grid g[k], 10 max_steps, 11 fast_steps,
-// 12..15 reserved.  The floating-point grid parameters travel in buffer 0 (a small device block).
+// 12 has packed faces, 13 has walk records, 14..15 reserved.  The floating-point grid parameters travel in buffer 0 (a small device block).
 extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORDS]) {
   if (!m || !h) return fail(DLI_ERR_ARG, "NULL argument");
   memset(h, 0, sizeof(int64_t) * DLI_MESH_HEADER_WORDS);
   h[0] = DLI_VERSION; h[1] = m->dim; h[2] = m->nv; h[3] = m->ns; h[4] = m->nh; h[5] = m->grid.cells;
   for (int k = 0; k < 4; k++) h[6 + k] = m->grid.g[k];
   h[10] = m->max_steps; h[11] = m->fast_steps;
+  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? 1 : 0;  // optional buffers the replica must mirror
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
   // (see dli_mesh_buffer): index 0 = 96-byte parameter block.
@@ -810,6 +839,13 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   m->grid.cells = h[5];
   for (int k = 0; k < 4; k++) m->grid.g[k] = (int)h[6 + k];
   int rc = mesh_alloc_common(m);
+  // mirror the source's optional buffers exactly (every rank must see the same buffer list)
+  if (rc == DLI_OK && !h[12] && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
+  if (rc == DLI_OK && !h[13] && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
+  if (rc == DLI_OK && h[12] && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
+    rc = fail(DLI_ERR_CUDA, "packed face allocation failed");
+  if (rc == DLI_OK && h[13] && !m->d_fat && cudaMalloc(&m->d_fat, 64 * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
+    rc = fail(DLI_ERR_CUDA, "walk record allocation failed");
   m->max_steps = (int)h[10];
   m->fast_steps = (int)h[11];
   if (rc != DLI_OK) { mesh_free(m); return rc; }
@@ -819,9 +855,10 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   return DLI_OK;
 }
 
-extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 5 : 0; }
+extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 6 : 0; }
 
-// buffers 0..4: vertex records, simplex records, hull table, hint grid, packed 2D face records (may be empty)
+// buffers 0..5: vertex records, simplex records, hull table, hint grid, packed 2D face records (may be empty),
+// 64-byte 2D walk records (may be empty)
 extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t *bytes) {
   if (!m || !ptr || !bytes) return fail(DLI_ERR_ARG, "NULL argument");
   switch (index) {
@@ -830,6 +867,7 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
+    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)64 * m->ns : 0; break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }
   return DLI_OK;

@@ -29,6 +29,8 @@ struct Mesh2View {
   // 16 B = {v0 | v1 << 21 | v2 << 42, n0 | n1 << 21 | n2 << 42}, neighbour 0x1FFFFF = hull.  Halves the
   // L2 footprint of the face array (two faces per sector).
   const ulonglong2 *fpack;
+  // optional 64-byte self-contained walk records (FatFace2) for the pair-transposed fast pass k_interp2_fat
+  const uint4 *fat;
   const int4 *hull;
   const int32_t *hint;
   double ox, oy, icx, icy;  // hint grid origin and 1/cell size
@@ -168,6 +170,28 @@ __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
   double4 r;
   asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(m.vrec + v));
   return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 64-byte self-contained walk record of a 2D face (fast pass k_interp2_fat).  One walk step = ONE
+// 128-byte line instead of a face record plus three vertex records:
+//   half 0 (32 B, geometry): p0 = vertex 0 in fp64; a = fp32(v1 - v0), b = fp32(v2 - v0)
+//   half 1 (32 B, values + topology): f0, grad f (the face's affine interpolant
+//          y = f0 + g . (p - p0)); three 21-bit neighbour ids (kPackMask = hull) and, in bit 63, the
+//          "slow" flag (this face must be handled by the exact / reference-order pass)
+// The orientation tests of the fast pass run on the fp32-rounded edge vectors with an error bound that
+// covers the rounding (kFatK below), so a certified sign is the sign of the exact predicate on the
+// fp64 mesh; everything uncertain goes to k_interp2_full.  The gradient form is used only on faces
+// whose a-priori error bound (k_build_fat2) keeps it within 1e-13 of the exact interpolant relative
+// to the smallest |f| on the face; every other face carries the slow flag.
+// ---------------------------------------------------------------------------------------------
+constexpr unsigned long long kFatSlow = 1ull << 63;
+constexpr double kFatK = 1.1920928955078125e-07;  // 2^-23: twice the fp32 unit roundoff 2^-24
+
+__device__ __forceinline__ void ldg256(unsigned (&r)[8], const void *p) {
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "l"(p));
 }
 
 // Fast path: static filter only.  Returns true with the containing face's vertices loaded when every

@@ -125,6 +125,167 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
   if (STATS) flush_stats(stats, st);
 }
 
+// ---------------------------------------------------------------------------------------------
+// 2D fast pass on 64-byte self-contained walk records (see dli_device.cuh, "FatFace2")
+// ---------------------------------------------------------------------------------------------
+
+// Builds the walk records from the canonical vertex / face records.  One thread per face.
+// The slow flag is set when (a) an edge vector does not survive the fp32 conversion within 2^-24
+// relative (overflow, underflow, non-finite input), or (b) the a-priori bound on the error of the
+// gradient-form interpolant over the face exceeds 1e-13 * min|f_i| (slivers, faces on which f changes
+// sign or vanishes at a vertex): those faces are evaluated by k_interp2_full in the reference's own
+// operation order.
+__global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
+                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns) return;
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
+  double4 V0 = vrec[r0.x], V1 = vrec[r0.y], V2 = vrec[r0.z];
+  const double Ax = V1.x - V0.x, Ay = V1.y - V0.y, Bx = V2.x - V0.x, By = V2.y - V0.y;
+  const float ax = (float)Ax, ay = (float)Ay, bx = (float)Bx, by = (float)By;
+  const double u = 5.9604644775390625e-08;  // 2^-24
+  bool slow = false;
+  slow |= !(fabs((double)ax - Ax) <= u * fabs(Ax));
+  slow |= !(fabs((double)ay - Ay) <= u * fabs(Ay));
+  slow |= !(fabs((double)bx - Bx) <= u * fabs(Bx));
+  slow |= !(fabs((double)by - By) <= u * fabs(By));
+  // affine interpolant  y = f0 + gx (x - x0) + gy (y - y0)
+  const double eps = 1.1102230246251565e-16;  // 2^-53
+  const double d1 = V1.z - V0.z, d2 = V2.z - V0.z;
+  const double dl = Ax * By, dr = Ay * Bx, det = dl - dr, Sd = fabs(dl) + fabs(dr);
+  const double xl = d1 * By, xr = d2 * Ay, nx = xl - xr, Sx = fabs(xl) + fabs(xr);
+  const double yl = Ax * d2, yr = Bx * d1, ny = yl - yr, Sy = fabs(yl) + fabs(yr);
+  const double gx = nx / det, gy = ny / det;
+  // first-order rounding analysis with a factor 2 of slack (every input difference carries one rounding,
+  // each product one, each 2-term sum one): |d det| <= 4 eps Sd, |d nx| <= 4 eps Sx
+  const double ad = fabs(det);
+  const double dgx = 8.0 * eps * (Sx + fabs(gx) * Sd) / ad + 2.0 * eps * fabs(gx);
+  const double dgy = 8.0 * eps * (Sy + fabs(gy) * Sd) / ad + 2.0 * eps * fabs(gy);
+  const double wx = fmax(fabs(Ax), fabs(Bx)), wy = fmax(fabs(Ay), fabs(By));
+  const double E = dgx * wx + dgy * wy + 3.0 * eps * (fabs(V0.z) + fabs(gx) * wx + fabs(gy) * wy);
+  double mn = fmin(fabs(V0.z), fmin(fabs(V1.z), fabs(V2.z)));
+  const bool same_sign = (V0.z > 0.0 && V1.z > 0.0 && V2.z > 0.0) || (V0.z < 0.0 && V1.z < 0.0 && V2.z < 0.0);
+  const bool all_zero = (V0.z == 0.0 && V1.z == 0.0 && V2.z == 0.0);
+  if (!same_sign) mn = 0.0;
+  if (!all_zero) slow |= !(E <= 1e-13 * mn);   // (NaN compares false -> slow)
+  else slow |= !(gx == 0.0 && gy == 0.0);
+  auto enc = [](int nb) -> unsigned long long { return nb < 0 ? (unsigned long long)kPackMask : (unsigned long long)(unsigned)nb; };
+  unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42) | (slow ? kFatSlow : 0ull);
+  if (slow) atomicAdd(n_slow, 1u);
+  uint4 h0, h1, h2, h3;
+  h0.x = (unsigned)__double2loint(V0.x); h0.y = (unsigned)__double2hiint(V0.x);
+  h0.z = (unsigned)__double2loint(V0.y); h0.w = (unsigned)__double2hiint(V0.y);
+  h1.x = __float_as_uint(ax); h1.y = __float_as_uint(ay); h1.z = __float_as_uint(bx); h1.w = __float_as_uint(by);
+  h2.x = (unsigned)__double2loint(V0.z); h2.y = (unsigned)__double2hiint(V0.z);
+  h2.z = (unsigned)__double2loint(gx); h2.w = (unsigned)__double2hiint(gx);
+  h3.x = (unsigned)__double2loint(gy); h3.y = (unsigned)__double2hiint(gy);
+  h3.z = (unsigned)(nbr & 0xffffffffull); h3.w = (unsigned)(nbr >> 32);
+  uint4 *o = fat + 4 * (size_t)f;
+  o[0] = h0; o[1] = h1; o[2] = h2; o[3] = h3;
+}
+
+// Fast pass on the walk records.  Same warp-persistent lane state machine as k_interp2_fast (one walk step
+// per lane per iteration, ballot/popc refill), but a step costs ONE L1TEX wavefront per query instead of
+// four: the two 32-byte halves of a record are fetched by the two lanes of a lane pair in one LDG.E.256
+// (both addresses in the same 128-byte line), once for the even lane's face and once for the odd lane's,
+// and the halves are exchanged with 8 SHFL.BFLY ("pair-transposed load").
+template <bool STATS>
+__global__ void __launch_bounds__(256, 4)
+k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
+              int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
+              unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const bool odd = lane & 1;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * per_warp;
+  if (base >= n) return;  // warp-uniform
+  const int64_t end = min(n, base + (int64_t)per_warp);
+  const char *rec = reinterpret_cast<const char *>(m.fat) + (odd ? 32 : 0);
+  int64_t next = base;
+  bool active = false;
+  double px = 0.0, py = 0.0;
+  int f = 0, from = -1;
+  int64_t qi = 0;
+  unsigned int steps = 0;
+  StatsAcc st;
+  for (;;) {
+    unsigned need = __ballot_sync(FULL, !active);
+    if (need) {
+      int64_t idx = next + __popc(need & ((1u << lane) - 1u));
+      if (!active && idx < end) {
+        double2 q = __ldcs(xs + idx);
+        px = q.x; py = q.y;
+        qi = idx;
+        f = hint2(m, px, py);
+        from = -1;
+        steps = 0;
+        active = true;
+      }
+      next += __popc(need);
+    }
+    if (!__any_sync(FULL, active)) break;
+    // pair-transposed load of the two records of this lane pair
+    const int fs = active ? f : -1;
+    const int fp = __shfl_xor_sync(FULL, fs, 1);
+    const int fe = odd ? fp : fs, fo = odd ? fs : fp;
+    unsigned R1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, R2[8] = {0, 0, 0, 0, 0, 0, 0, 0}, X[8];
+    if (fe >= 0) ldg256(R1, rec + (size_t)fe * 64);
+    if (fo >= 0) ldg256(R2, rec + (size_t)fo * 64);
+#pragma unroll
+    for (int i = 0; i < 8; i++) X[i] = __shfl_xor_sync(FULL, odd ? R1[i] : R2[i], 1);
+    if (active) {
+      steps++;
+      unsigned G[8], V[8];  // geometry half, values half of this lane's own record
+#pragma unroll
+      for (int i = 0; i < 8; i++) { G[i] = odd ? X[i] : R1[i]; V[i] = odd ? R2[i] : X[i]; }
+      const double dx = px - __hiloint2double((int)G[1], (int)G[0]);
+      const double dy = py - __hiloint2double((int)G[3], (int)G[2]);
+      const double ax = (double)__uint_as_float(G[4]), ay = (double)__uint_as_float(G[5]);
+      const double bx = (double)__uint_as_float(G[6]), by = (double)__uint_as_float(G[7]);
+      // o2: edge v0->v1 (opposite v2), o1: edge v2->v0 (opposite v1), o0 = w - o2 - o1: edge v1->v2
+      const double l2 = ax * dy, r2 = ay * dx, o2 = l2 - r2, e2 = kFatK * (fabs(l2) + fabs(r2));
+      const double l1 = dx * by, r1 = dy * bx, o1 = l1 - r1, e1 = kFatK * (fabs(l1) + fabs(r1));
+      const double lw = ax * by, rw = ay * bx, w = lw - rw, ew = (2.0 * kFatK) * (fabs(lw) + fabs(rw));
+      const double o0 = (w - o2) - o1, e0 = (ew + e2) + e1;
+      const unsigned long long nbr = ((unsigned long long)V[7] << 32) | V[6];
+      const int n0 = (int)(nbr & kPackMask), n1 = (int)((nbr >> 21) & kPackMask), n2 = (int)((nbr >> 42) & kPackMask);
+      const bool c0 = n0 == from, c1 = n1 == from, c2 = n2 == from;  // hull code never equals a face id / -1
+      const bool neg0 = (-o0 > e0) & !c0, neg1 = (-o1 > e1) & !c1, neg2 = (-o2 > e2) & !c2;
+      bool give_up = (nbr & kFatSlow) != 0;
+      if (!give_up) {
+        if (neg0 | neg1 | neg2) {
+          int nb = neg0 ? n0 : (neg1 ? n1 : n2);
+          if (nb == (int)kPackMask || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
+          else { from = f; f = nb; }
+        } else {
+          bool pos = ((o0 > e0) | c0) & ((o1 > e1) | c1) & ((o2 > e2) | c2);
+          if (pos) {
+            if (ys) {
+              const double f0 = __hiloint2double((int)V[1], (int)V[0]);
+              const double gx = __hiloint2double((int)V[3], (int)V[2]);
+              const double gy = __hiloint2double((int)V[5], (int)V[4]);
+              __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
+            }
+            if (simplex_out) __stcs(simplex_out + qi, f);
+            if (status_out) status_out[qi] = DLI_STATUS_OK;
+            if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
+            active = false;
+          } else {
+            give_up = true;  // a decision the static filter cannot certify
+          }
+        }
+      }
+      if (give_up) {
+        unsigned int slot = atomicAdd(queue_count, 1u);
+        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        active = false;
+      }
+    }
+  }
+  if (STATS) flush_stats(stats, st);
+}
+
 // Straggler / exact pass over the queue written by the fast pass (count read on the device: no
 // host synchronisation between the two launches).
 template <bool STATS, int EPI>

@@ -24,7 +24,7 @@ def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, sort_
     o.hint_cells_per_simplex = float(hint_cells_per_simplex)
     o.max_walk_steps = int(max_walk_steps)
     o.sort_queries = int(sort_queries)
-    o.epilogue = {"reference": 0, "closed_form": 1}.get(epilogue, epilogue)
+    o.epilogue = {"auto": 0, "closed_form": 1, "reference": 2}.get(epilogue, epilogue)
     o.threads_per_block = int(threads_per_block)
     o.queries_per_warp = int(queries_per_warp)
     o.packed_faces = int(packed_faces)

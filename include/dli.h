@@ -51,6 +51,10 @@ extern "C" {
                                           (src/delaunay_2_interp.h:546-551) */
 #define DLI_STATUS_NO_MESH 4           /* mesh has no simplex (fewer than dim+1 affinely independent points) */
 
+#define DLI_EPILOGUE_AUTO 0
+#define DLI_EPILOGUE_CLOSED_FORM 1
+#define DLI_EPILOGUE_REFERENCE 2
+
 typedef struct dli_mesh dli_mesh; /* opaque: owns the device structure-of-arrays buffers and the hint grid */
 
 typedef struct dli_options {
@@ -59,8 +63,13 @@ typedef struct dli_options {
   float hint_cells_per_simplex;   /* start-hint grid resolution; <= 0 = default (2D: 2.0, dD: 1.0) */
   int32_t max_walk_steps;         /* <= 0 = default (n_simplices + 16) */
   int32_t sort_queries;           /* 0 = evaluate in input order (default), 1 = bin queries by hint cell first */
-  int32_t epilogue;               /* 0 = reference operation order (partial-pivot LU determinants, default),
-                                     1 = closed-form solve (faster, differs in the last ulps on slivers) */
+  int32_t epilogue;               /* DLI_EPILOGUE_*: 0 = AUTO (default): 2D meshes with < 2^21-1 faces use the 64-byte
+                                     walk records and evaluate each face's affine interpolant f0 + g.(p - p0) on faces
+                                     whose a-priori error bound keeps it within 1e-13 relative of the exact
+                                     interpolant, and the reference operation order everywhere else (other faces,
+                                     other dims, stragglers);  1 = closed-form barycentric solve everywhere
+                                     (differs in the last ulps on slivers);  2 = reference operation order
+                                     everywhere (partial-pivot LU determinants; bit-identical to a scalar restatement of the reference) */
   int32_t threads_per_block;      /* <= 0 = default */
   int32_t queries_per_warp;       /* 2D fast pass: contiguous queries owned by one warp; <= 0 = default (1024) */
   int32_t packed_faces;           /* 2D: 0 = use 16-byte packed face records in the fast pass when ids fit 21 bits

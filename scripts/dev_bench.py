@@ -19,6 +19,8 @@ g = torch.Generator(device="cuda"); g.manual_seed(2001)
 xq = torch.rand(a.nq, 2, dtype=torch.float64, device="cuda", generator=g) * 0.96 + 0.02
 ys = torch.empty(a.nq, dtype=torch.float64, device="cuda")
 VAR = {
+ "auto": dict(), "ref": dict(epilogue="reference"), "auto_cps4": dict(hint_cells_per_simplex=4.0), "auto_cps1": dict(hint_cells_per_simplex=1.0),
+ "auto_t128": dict(threads_per_block=128), "auto_qpw256": dict(queries_per_warp=256), "auto_qpw4096": dict(queries_per_warp=4096),
  "cps1": dict(hint_cells_per_simplex=1.0), "cps2": dict(hint_cells_per_simplex=2.0),
  "cps4": dict(hint_cells_per_simplex=4.0), "cps8": dict(hint_cells_per_simplex=8.0),
  "cf2": dict(hint_cells_per_simplex=2.0, epilogue="closed_form"), "cf4": dict(hint_cells_per_simplex=4.0, epilogue="closed_form"),
