@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdli.so")
+LIB_PATH = os.environ.get("DLI_LIB") or os.path.join(_HERE, "libdli.so")  # DLI_LIB: developer override (kernel experiments)
 
 DLI_MAX_DIM = 6
 DLI_MESH_HEADER_WORDS = 16
@@ -32,7 +32,8 @@ class Options(C.Structure):
         ("threads_per_block", C.c_int32),
         ("queries_per_warp", C.c_int32),
         ("packed_faces", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("prefetch_ring", C.c_int32),
+        ("reserved", C.c_int32 * 6),
     ]
 
 

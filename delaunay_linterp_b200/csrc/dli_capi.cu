@@ -106,6 +106,7 @@ extern "C" void dli_options_init(dli_options *o) {
   o->threads_per_block = 0;
   o->queries_per_warp = 0;
   o->packed_faces = 0;
+  o->prefetch_ring = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -479,8 +480,9 @@ template <bool STATS, int EPI>
 void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
   auto fast = L.m->d_fpack ? k_interp2_fast<STATS, EPI, true> : k_interp2_fast<STATS, EPI, false>;
   Mesh2View v = view2(L.m);
-  int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : 256;
-  tpb = std::min(256, std::max(32, tpb / 32 * 32));
+  const bool use_fat = (EPI == 0 && L.m->d_fat);
+  int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : (use_fat ? 128 : 256);
+  tpb = std::min(use_fat ? DLI_X_FAT_THREADS : 256, std::max(32, tpb / 32 * 32));  // never above the kernel's launch bound
   // queries per warp: large enough to amortise the drain at the end of a warp's range, small enough to
   // give every SM many CTAs
   int per_warp = L.m->opt.queries_per_warp > 0 ? L.m->opt.queries_per_warp : 1024;
@@ -488,9 +490,14 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int64_t warps = (n + per_warp - 1) / per_warp;
   int wpb = tpb / 32;
   L.mark(0);
-  if (EPI == 0 && L.m->d_fat)
-    k_interp2_fat<STATS><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
-        v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  if (use_fat) {
+    if (L.m->opt.prefetch_ring >= 0)
+      k_interp2_fat<STATS, true><<<(unsigned)((warps + wpb - 1) / wpb), tpb, (size_t)wpb * kRingBytesPerWarp, L.st>>>(
+          v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+    else
+      k_interp2_fat<STATS, false><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
+          v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  }
   else
     fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
         v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);

@@ -188,8 +188,13 @@ __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
 constexpr unsigned long long kFatSlow = 1ull << 63;
 constexpr double kFatK = 1.1920928955078125e-07;  // 2^-23: twice the fp32 unit roundoff 2^-24
 
+#ifdef DLI_X_L1NA
+#define DLI_LDG256 "ld.global.nc.L1::no_allocate.v8.b32"
+#else
+#define DLI_LDG256 "ld.global.nc.v8.b32"
+#endif
 __device__ __forceinline__ void ldg256(unsigned (&r)[8], const void *p) {
-  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+  asm volatile(DLI_LDG256 " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "l"(p));
 }

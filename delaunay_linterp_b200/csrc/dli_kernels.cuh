@@ -189,8 +189,20 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
 // four: the two 32-byte halves of a record are fetched by the two lanes of a lane pair in one LDG.E.256
 // (both addresses in the same 128-byte line), once for the even lane's face and once for the odd lane's,
 // and the halves are exchanged with 8 SHFL.BFLY ("pair-transposed load").
-template <bool STATS>
-__global__ void __launch_bounds__(256, 4)
+#ifndef DLI_X_FAT_THREADS   // developer experiment knobs (scripts/build_variants.py); defaults are the shipped values
+#define DLI_X_FAT_THREADS 128
+#endif
+#ifndef DLI_X_FAT_BLOCKS
+#define DLI_X_FAT_BLOCKS 9
+#endif
+// RING = true adds a per-warp shared-memory prefetch ring (cp.async): the queries of the block of 32 three blocks
+// ahead and the start hints of the block two ahead are in flight while the current block walks, so a loop
+// iteration waits for ONE dependent memory latency (the walk record) instead of three (query -> hint -> record).
+// Ring = 128 query slots (16 B) + 128 hint slots (4 B) per warp = 2.5 KB; slot = query index & 127.
+constexpr int kRingSlots = 128;
+constexpr int kRingBytesPerWarp = kRingSlots * (16 + 4);
+template <bool STATS, bool RING>
+__global__ void __launch_bounds__(DLI_X_FAT_THREADS, DLI_X_FAT_BLOCKS)
 k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
@@ -209,20 +221,78 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
   int64_t qi = 0;
   unsigned int steps = 0;
   StatsAcc st;
+  // ---- prefetch ring (RING only)
+  extern __shared__ __align__(16) unsigned char ring_smem[];
+  double2 *ringq = nullptr;
+  int *ringh = nullptr;
+  unsigned long long pol_last = 0, pol_first = 0;
+  int blk = 0;
+  auto issue_q = [&](int64_t j) {  // query j -> ring (streamed: L2 evict_first)
+    if (j < end)
+      asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(
+                       (unsigned)__cvta_generic_to_shared(ringq + (j & (kRingSlots - 1)))),
+                   "l"(xs + j), "l"(pol_first)
+                   : "memory");
+  };
+  auto issue_h = [&](int64_t j) {  // start hint of query j (already in the ring) -> ring (hint grid: L2 evict_last)
+    if (j < end) {
+      double2 q = ringq[j & (kRingSlots - 1)];
+      int ci = (int)((q.x - m.ox) * m.icx), cj = (int)((q.y - m.oy) * m.icy);
+      ci = max(0, min(m.gx - 1, ci));
+      cj = max(0, min(m.gy - 1, cj));
+      asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(
+                       (unsigned)__cvta_generic_to_shared(ringh + (j & (kRingSlots - 1)))),
+                   "l"(m.hint + ((size_t)cj * m.gx + ci)), "l"(pol_last)
+                   : "memory");
+    }
+  };
+  auto commit_wait = [&](bool commit) {
+    if (commit) asm volatile("cp.async.commit_group;" ::: "memory");
+    else { asm volatile("cp.async.wait_group 0;" ::: "memory"); __syncwarp(); }
+  };
+  if (RING) {
+    const int wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    ringq = reinterpret_cast<double2 *>(ring_smem) + wib * kRingSlots;
+    ringh = reinterpret_cast<int *>(ring_smem + (size_t)nw * kRingSlots * 16) + wib * kRingSlots;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
+    issue_q(base + lane); issue_q(base + 32 + lane); issue_q(base + 64 + lane);
+    commit_wait(true); commit_wait(false);
+    issue_h(base + lane); issue_h(base + 32 + lane);
+    commit_wait(true); commit_wait(false);
+    issue_h(base + 64 + lane); issue_q(base + 96 + lane);
+    commit_wait(true);
+  }
   for (;;) {
     unsigned need = __ballot_sync(FULL, !active);
     if (need) {
       int64_t idx = next + __popc(need & ((1u << lane) - 1u));
       if (!active && idx < end) {
-        double2 q = __ldcs(xs + idx);
-        px = q.x; py = q.y;
+        if (RING) {
+          double2 q = ringq[idx & (kRingSlots - 1)];
+          px = q.x; py = q.y;
+          f = ringh[idx & (kRingSlots - 1)];
+        } else {
+          double2 q = __ldcs(xs + idx);
+          px = q.x; py = q.y;
+          f = hint2(m, px, py);
+        }
         qi = idx;
-        f = hint2(m, px, py);
         from = -1;
         steps = 0;
         active = true;
       }
       next += __popc(need);
+      if (RING) {
+        const int nb = (int)((next - base) >> 5);
+        if (nb != blk) {  // warp-uniform: `next` entered a new block of 32 -> advance the pipeline by one block
+          blk = nb;
+          commit_wait(false);  // the previous group (hints of blk+1, queries of blk+2) has landed
+          issue_h(base + (int64_t)(blk + 2) * 32 + lane);
+          issue_q(base + (int64_t)(blk + 3) * 32 + lane);
+          commit_wait(true);
+        }
+      }
     }
     if (!__any_sync(FULL, active)) break;
     // pair-transposed load of the two records of this lane pair
@@ -283,6 +353,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
       }
     }
   }
+  if (RING) asm volatile("cp.async.wait_all;" ::: "memory");
   if (STATS) flush_stats(stats, st);
 }
 

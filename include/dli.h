@@ -74,7 +74,9 @@ typedef struct dli_options {
   int32_t queries_per_warp;       /* 2D fast pass: contiguous queries owned by one warp; <= 0 = default (1024) */
   int32_t packed_faces;           /* 2D: 0 = use 16-byte packed face records in the fast pass when ids fit 21 bits
                                      (default), -1 = never */
-  int32_t reserved[7];
+  int32_t prefetch_ring;          /* 2D walk-record fast pass: 0 = per-warp cp.async prefetch ring for queries and start
+                                     hints (default), -1 = plain loads */
+  int32_t reserved[6];
 } dli_options;
 
 /* fills *opt with the defaults */

@@ -19,8 +19,10 @@ g = torch.Generator(device="cuda"); g.manual_seed(2001)
 xq = torch.rand(a.nq, 2, dtype=torch.float64, device="cuda", generator=g) * 0.96 + 0.02
 ys = torch.empty(a.nq, dtype=torch.float64, device="cuda")
 VAR = {
+ "noring": dict(prefetch_ring=-1), "ring_qpw2048": dict(queries_per_warp=2048), "ring_qpw4096": dict(queries_per_warp=4096), "ring_qpw512": dict(queries_per_warp=512),
+ "ring_t64": dict(threads_per_block=64), "ring_t256": dict(threads_per_block=256),
  "auto": dict(), "ref": dict(epilogue="reference"), "auto_cps4": dict(hint_cells_per_simplex=4.0), "auto_cps1": dict(hint_cells_per_simplex=1.0),
- "auto_t128": dict(threads_per_block=128), "auto_qpw256": dict(queries_per_warp=256), "auto_qpw4096": dict(queries_per_warp=4096),
+ "auto_t128": dict(threads_per_block=128), "auto_t64": dict(threads_per_block=64), "auto_t256": dict(threads_per_block=256), "auto_qpw256": dict(queries_per_warp=256), "auto_qpw4096": dict(queries_per_warp=4096),
  "cps1": dict(hint_cells_per_simplex=1.0), "cps2": dict(hint_cells_per_simplex=2.0),
  "cps4": dict(hint_cells_per_simplex=4.0), "cps8": dict(hint_cells_per_simplex=8.0),
  "cf2": dict(hint_cells_per_simplex=2.0, epilogue="closed_form"), "cf4": dict(hint_cells_per_simplex=4.0, epilogue="closed_form"),
