@@ -45,6 +45,26 @@ struct DeviceGuard {
 // ---------------------------------------------------------------------------------------------
 // mesh object
 // ---------------------------------------------------------------------------------------------
+constexpr int64_t kHostChunk = 1ll << 22;  // queries per staged chunk of the host-pointer path (64 MB of 2D queries)
+struct HostPipe {
+  static constexpr int kSlots = 3;
+  bool ready = false;
+  cudaStream_t st[kSlots] = {nullptr, nullptr, nullptr};
+  cudaEvent_t done[kSlots] = {nullptr, nullptr, nullptr};
+  double *x[kSlots] = {nullptr, nullptr, nullptr}, *y[kSlots] = {nullptr, nullptr, nullptr};
+  int32_t *s[kSlots] = {nullptr, nullptr, nullptr};
+  uint8_t *t[kSlots] = {nullptr, nullptr, nullptr};
+};
+static void pipe_free(HostPipe &P) {
+  for (int i = 0; i < HostPipe::kSlots; i++) {
+    if (P.st[i]) { cudaStreamSynchronize(P.st[i]); cudaStreamDestroy(P.st[i]); }
+    if (P.done[i]) cudaEventDestroy(P.done[i]);
+    cudaFree(P.x[i]); cudaFree(P.y[i]); cudaFree(P.s[i]); cudaFree(P.t[i]);
+    P.st[i] = nullptr; P.done[i] = nullptr; P.x[i] = P.y[i] = nullptr; P.s[i] = nullptr; P.t[i] = nullptr;
+  }
+  P.ready = false;
+}
+
 struct dli_mesh {
   int dim = 0;
   int device = 0;
@@ -77,6 +97,9 @@ struct dli_mesh {
   mutable dli_stats last{};
   mutable std::mutex ev_mu;
   mutable std::vector<cudaEvent_t> ev;  // triples (before fast, after fast, after full)
+  // host-pointer path staging ring (created on first use)
+  mutable std::mutex pipe_mu;
+  mutable HostPipe pipe;
 };
 
 static void mesh_free(dli_mesh *m) {
@@ -90,6 +113,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_fat);
   cudaFree(m->d_item_verts);
   cudaFree(m->d_stats);
+  pipe_free(m->pipe);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
   delete m;
 }
@@ -580,54 +604,50 @@ bool is_device_ptr(const void *p, bool *known) {
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
-// host-pointer path: chunked H2D / compute / D2H pipeline over a ring of device slots
+// host-pointer path: chunked H2D / compute / D2H pipeline over a ring of device slots.  The ring (streams +
+// staging buffers + straggler queues) lives in the mesh and is created once: a call costs no cudaMalloc /
+// cudaFree / stream creation.  H2D of chunk k+1, the kernels of chunk k and the D2H of chunk k-1 run on
+// different streams, so both copy engines stay busy (PCIe is the bound: 24 B per 2D query).
 int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, int *launches) {
   if (n == 0) return DLI_OK;
   const int d = m->dim;
-  const int kSlots = 3;
-  const int64_t chunk = std::min<int64_t>(n, 1ll << 22);
-  struct Slot {
-    cudaStream_t st = nullptr;
-    double *x = nullptr, *y = nullptr;
-    int32_t *s = nullptr;
-    uint8_t *t = nullptr;
-  } slot[kSlots];
-  int rc = DLI_OK;
-  auto cleanup = [&]() {
-    for (auto &s : slot) {
-      if (s.st) cudaStreamSynchronize(s.st);
-      cudaFree(s.x); cudaFree(s.y); cudaFree(s.s); cudaFree(s.t);
-      if (s.st) cudaStreamDestroy(s.st);
+  std::lock_guard<std::mutex> lk(m->pipe_mu);  // one host-path call at a time per mesh
+  HostPipe &P = m->pipe;
+  const int64_t chunk = kHostChunk;
+  if (!P.ready) {
+    for (int i = 0; i < HostPipe::kSlots; i++) {
+      cudaError_t e = cudaStreamCreateWithFlags(&P.st[i], cudaStreamNonBlocking);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&P.done[i], cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaMalloc(&P.x[i], sizeof(double) * (size_t)chunk * d);
+      if (e == cudaSuccess) e = cudaMalloc(&P.y[i], sizeof(double) * (size_t)chunk);
+      if (e == cudaSuccess) e = cudaMalloc(&P.s[i], sizeof(int32_t) * (size_t)chunk);
+      if (e == cudaSuccess) e = cudaMalloc(&P.t[i], (size_t)chunk);
+      if (e != cudaSuccess) {
+        pipe_free(P);
+        return fail(DLI_ERR_CUDA, std::string("dli_interp: staging allocation failed: ") + cudaGetErrorString(e));
+      }
     }
-  };
-  int nslots = (int)std::min<int64_t>(kSlots, (n + chunk - 1) / chunk);
-  for (int i = 0; i < nslots && rc == DLI_OK; i++) {
-    cudaError_t e = cudaStreamCreateWithFlags(&slot[i].st, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaMalloc(&slot[i].x, sizeof(double) * (size_t)chunk * d);
-    if (e == cudaSuccess && ys) e = cudaMalloc(&slot[i].y, sizeof(double) * (size_t)chunk);
-    if (e == cudaSuccess && so) e = cudaMalloc(&slot[i].s, sizeof(int32_t) * (size_t)chunk);
-    if (e == cudaSuccess && sto) e = cudaMalloc(&slot[i].t, (size_t)chunk);
-    if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("dli_interp: staging allocation failed: ") + cudaGetErrorString(e));
+    P.ready = true;
   }
+  int rc = DLI_OK;
   int64_t c = 0;
   for (int64_t off = 0; off < n && rc == DLI_OK; off += chunk, c++) {
-    Slot &s = slot[c % nslots];
+    const int i = (int)(c % HostPipe::kSlots);
+    cudaStream_t st = P.st[i];
     int64_t cn = std::min(chunk, n - off);
-    cudaError_t e = cudaMemcpyAsync(s.x, xs + off * d, sizeof(double) * (size_t)cn * d, cudaMemcpyHostToDevice, s.st);
+    cudaError_t e = cudaMemcpyAsync(P.x[i], xs + off * d, sizeof(double) * (size_t)cn * d, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) { rc = fail(DLI_ERR_CUDA, std::string("H2D copy failed: ") + cudaGetErrorString(e)); break; }
-    rc = run_device(m, cn, s.x, s.y, s.s, s.t, s.st, launches);
+    rc = run_device(m, cn, P.x[i], ys ? P.y[i] : nullptr, so ? P.s[i] : nullptr, sto ? P.t[i] : nullptr, st, launches);
     if (rc != DLI_OK) break;
-    if (ys) e = cudaMemcpyAsync(ys + off, s.y, sizeof(double) * (size_t)cn, cudaMemcpyDeviceToHost, s.st);
-    if (e == cudaSuccess && so) e = cudaMemcpyAsync(so + off, s.s, sizeof(int32_t) * (size_t)cn, cudaMemcpyDeviceToHost, s.st);
-    if (e == cudaSuccess && sto) e = cudaMemcpyAsync(sto + off, s.t, (size_t)cn, cudaMemcpyDeviceToHost, s.st);
+    if (ys) e = cudaMemcpyAsync(ys + off, P.y[i], sizeof(double) * (size_t)cn, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && so) e = cudaMemcpyAsync(so + off, P.s[i], sizeof(int32_t) * (size_t)cn, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && sto) e = cudaMemcpyAsync(sto + off, P.t[i], (size_t)cn, cudaMemcpyDeviceToHost, st);
     if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(e));
   }
-  for (int i = 0; i < nslots; i++)
-    if (slot[i].st) {
-      cudaError_t e = cudaStreamSynchronize(slot[i].st);
-      if (e != cudaSuccess && rc == DLI_OK) rc = fail(DLI_ERR_CUDA, std::string("dli_interp: ") + cudaGetErrorString(e));
-    }
-  cleanup();
+  for (int i = 0; i < HostPipe::kSlots; i++) {
+    cudaError_t e = cudaStreamSynchronize(P.st[i]);
+    if (e != cudaSuccess && rc == DLI_OK) rc = fail(DLI_ERR_CUDA, std::string("dli_interp: ") + cudaGetErrorString(e));
+  }
   return rc;
 }
 
