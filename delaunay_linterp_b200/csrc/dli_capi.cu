@@ -79,6 +79,7 @@ struct dli_mesh {
   int32_t *d_srec = nullptr;
   int4 *d_hull = nullptr;
   int32_t *d_hint = nullptr;
+  int32_t *d_orig = nullptr;      // device simplex index -> caller's simplex id (simplices are stored in Morton order)
   ulonglong2 *d_fpack = nullptr;  // 2D packed face records (fast pass), NULL when ids do not fit 21 bits
   uint4 *d_fat = nullptr;         // 2D 64-byte walk records (k_interp2_fat), NULL when unused
   int64_t n_slow_faces = 0;       // faces carrying the slow flag in d_fat
@@ -109,6 +110,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_srec);
   cudaFree(m->d_hull);
   cudaFree(m->d_hint);
+  cudaFree(m->d_orig);
   cudaFree(m->d_fpack);
   cudaFree(m->d_fat);
   cudaFree(m->d_item_verts);
@@ -187,6 +189,44 @@ int derive_neighbors(int d, int64_t ns, const int32_t *sv, int32_t *sn) {
     }
   }
   return 0;
+}
+
+// Device order of the simplices: Morton (Z-curve) order of their centroids, so that simplices that are close in
+// space are close in memory (walk-record locality for coherent query batches; short neighbour deltas).
+// perm[i] = caller's id of the simplex stored at device index i.
+void morton_order(int d, int64_t nv, const double *coords, int64_t ns, const int32_t *sv, std::vector<int32_t> &perm) {
+  const int k = d + 1;
+  double lo[DLI_MAX_DIM], hi[DLI_MAX_DIM];
+  for (int c = 0; c < d; c++) { lo[c] = INFINITY; hi[c] = -INFINITY; }
+  for (int64_t v = 0; v < nv; v++)
+    for (int c = 0; c < d; c++) {
+      double x = coords[v * d + c];
+      if (x < lo[c]) lo[c] = x;
+      if (x > hi[c]) hi[c] = x;
+    }
+  const int bits = 63 / d > 21 ? 21 : 63 / d;  // 2D/3D: 21 bits per axis, 4D: 15
+  double scale[DLI_MAX_DIM];
+  for (int c = 0; c < d; c++) {
+    double ext = hi[c] - lo[c];
+    scale[c] = (ext > 0.0 && std::isfinite(ext)) ? (double)((1u << bits) - 1) / ext : 0.0;
+  }
+  std::vector<std::pair<uint64_t, int32_t>> keys((size_t)ns);
+  for (int64_t s = 0; s < ns; s++) {
+    uint64_t key = 0;
+    uint32_t q[DLI_MAX_DIM];
+    for (int c = 0; c < d; c++) {
+      double acc = 0.0;
+      for (int j = 0; j < k; j++) acc += coords[(size_t)sv[s * k + j] * d + c];
+      double t = (acc / k - lo[c]) * scale[c];
+      q[c] = (t > 0.0) ? (uint32_t)std::min<double>(t, (double)((1u << bits) - 1)) : 0u;  // NaN -> 0
+    }
+    for (int b = bits - 1; b >= 0; b--)
+      for (int c = d - 1; c >= 0; c--) key = (key << 1) | ((q[c] >> b) & 1u);
+    keys[(size_t)s] = {key, (int32_t)s};
+  }
+  std::sort(keys.begin(), keys.end());
+  perm.resize((size_t)ns);
+  for (int64_t i = 0; i < ns; i++) perm[(size_t)i] = keys[(size_t)i].second;
 }
 
 template <int D>
@@ -273,10 +313,11 @@ static int mesh_alloc_common(dli_mesh *m) {
   m->fast_steps = std::min(m->max_steps, d == 2 ? 24 : 32);
   CU(cudaMalloc(&m->d_vrec, sizeof(double) * (size_t)std::max<int64_t>(m->nv, 1) * m->vs));
   CU(cudaMalloc(&m->d_srec, sizeof(int32_t) * (size_t)std::max<int64_t>(m->ns, 1) * m->ss));
+  CU(cudaMalloc(&m->d_orig, sizeof(int32_t) * (size_t)std::max<int64_t>(m->ns, 1)));
   if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
   if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
     CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
-  if (d == 2 && m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0 && m->ns < (1 << 21) - 1)
+  if (d == 2 && m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0)
     CU(cudaMalloc(&m->d_fat, 64 * (size_t)m->ns));
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
@@ -289,13 +330,17 @@ static int mesh_alloc_common(dli_mesh *m) {
   return DLI_OK;
 }
 
+// walk records of meshes with >= 2^21-2 faces (or opt.packed_faces == 2: testing) use delta-encoded neighbours
+static bool fat_delta(const dli_mesh *m) { return m->ns >= (1 << 21) - 2 || m->opt.packed_faces == 2; }
+
 // (re)builds the 64-byte walk records from the canonical records (values and geometry)
 static int build_fat_records(dli_mesh *m) {
   if (!m->d_fat) return DLI_OK;
   unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
   CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
-  k_build_fat2<<<(unsigned)((m->ns + 255) / 256), 256>>>((int)m->ns, reinterpret_cast<const int4 *>(m->d_srec),
-                                                       reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
+  auto kb = fat_delta(m) ? k_build_fat2<true> : k_build_fat2<false>;
+  kb<<<(unsigned)((m->ns + 255) / 256), 256>>>((int)m->ns, reinterpret_cast<const int4 *>(m->d_srec),
+                                             reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
   CU(cudaGetLastError());
   unsigned int cnt = 0;
   CU(cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost));
@@ -395,14 +440,23 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
       for (int c = 0; c < d; c++) vrec[(size_t)v * m->vs + c] = coords[v * d + c];
       vrec[(size_t)v * m->vs + d] = f[v];
     }
+    // simplices in Morton order of their centroids; ids the caller sees go through d_orig
+    std::vector<int32_t> perm, inv((size_t)ns);
+    morton_order(d, nv, coords, ns, m->h_sv.data(), perm);
+    for (int64_t i = 0; i < ns; i++) inv[(size_t)perm[(size_t)i]] = (int32_t)i;
     std::vector<int32_t> srec((size_t)std::max<int64_t>(ns, 1) * m->ss, 0);
-    for (int64_t s = 0; s < ns; s++)
+    for (int64_t i = 0; i < ns; i++) {
+      const int64_t s = perm[(size_t)i];
       for (int j = 0; j < k; j++) {
-        srec[(size_t)s * m->ss + j] = m->h_sv[s * k + j];
-        srec[(size_t)s * m->ss + k + j] = enc_sn[s * k + j];
+        int32_t nb = enc_sn[s * k + j];
+        srec[(size_t)i * m->ss + j] = m->h_sv[s * k + j];
+        srec[(size_t)i * m->ss + k + j] = nb >= 0 ? inv[(size_t)nb] : nb;
       }
+    }
+    for (auto &h : hull) h.x = inv[(size_t)h.x];
     cudaError_t e = cudaMemcpy(m->d_vrec, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(m->d_srec, srec.data(), sizeof(int32_t) * srec.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && ns > 0) e = cudaMemcpy(m->d_orig, perm.data(), sizeof(int32_t) * perm.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && d == 2 && !hull.empty())
       e = cudaMemcpy(m->d_hull, hull.data(), sizeof(int4) * hull.size(), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { mesh_free(m); return fail(DLI_ERR_CUDA, std::string("mesh upload failed: ") + cudaGetErrorString(e)); }
@@ -439,7 +493,7 @@ extern "C" int64_t dli_mesh_num_simplices(const dli_mesh *m) { return m ? m->ns 
 extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
-                   sizeof(int32_t) * m->grid.cells + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
+                   sizeof(int32_t) * m->grid.cells + sizeof(int32_t) * m->ns + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
                    (m->d_fat ? 64 * m->ns : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
@@ -463,6 +517,7 @@ Mesh2View view2(const dli_mesh *m) {
   v.fat = m->d_fat;
   v.hull = m->d_hull;
   v.hint = m->d_hint;
+  v.orig = m->d_orig;
   v.ox = m->grid.o[0]; v.oy = m->grid.o[1];
   v.icx = m->grid.ic[0]; v.icy = m->grid.ic[1];
   v.gx = m->grid.g[0]; v.gy = m->grid.g[1];
@@ -472,7 +527,7 @@ Mesh2View view2(const dli_mesh *m) {
 }
 MeshDView viewD(const dli_mesh *m) {
   MeshDView v;
-  v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint;
+  v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint; v.orig = m->d_orig;
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   return v;
@@ -515,12 +570,11 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int wpb = tpb / 32;
   L.mark(0);
   if (use_fat) {
-    if (L.m->opt.prefetch_ring >= 0)
-      k_interp2_fat<STATS, true><<<(unsigned)((warps + wpb - 1) / wpb), tpb, (size_t)wpb * kRingBytesPerWarp, L.st>>>(
-          v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
-    else
-      k_interp2_fat<STATS, false><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
-          v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+    const bool ring = L.m->opt.prefetch_ring >= 0, delta = fat_delta(L.m);
+    auto kf = ring ? (delta ? k_interp2_fat<STATS, true, true> : k_interp2_fat<STATS, true, false>)
+                   : (delta ? k_interp2_fat<STATS, false, true> : k_interp2_fat<STATS, false, false>);
+    kf<<<(unsigned)((warps + wpb - 1) / wpb), tpb, ring ? (size_t)wpb * kRingBytesPerWarp : 0, L.st>>>(
+        v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   }
   else
     fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
@@ -882,10 +936,10 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   return DLI_OK;
 }
 
-extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 6 : 0; }
+extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 7 : 0; }
 
 // buffers 0..5: vertex records, simplex records, hull table, hint grid, packed 2D face records (may be empty),
-// 64-byte 2D walk records (may be empty)
+// 64-byte 2D walk records (may be empty), device-order -> caller simplex ids
 extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t *bytes) {
   if (!m || !ptr || !bytes) return fail(DLI_ERR_ARG, "NULL argument");
   switch (index) {
@@ -895,6 +949,7 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
     case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)64 * m->ns : 0; break;
+    case 6: *ptr = m->d_orig; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1); break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }
   return DLI_OK;

@@ -33,6 +33,7 @@ struct Mesh2View {
   const uint4 *fat;
   const int4 *hull;
   const int32_t *hint;
+  const int32_t *orig;  // device simplex index (Morton order of centroids) -> the caller's simplex id
   double ox, oy, icx, icy;  // hint grid origin and 1/cell size
   int gx, gy;
   int ns, nh;
@@ -51,6 +52,7 @@ struct MeshDView {
   const double *vrec;
   const int32_t *srec;
   const int32_t *hint;
+  const int32_t *orig;  // device simplex index -> the caller's simplex id
   double o[DLI_MAX_DIM], ic[DLI_MAX_DIM];
   int g[DLI_MAX_DIM];
   int ns;
@@ -186,13 +188,11 @@ __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
 // to the smallest |f| on the face; every other face carries the slow flag.
 // ---------------------------------------------------------------------------------------------
 constexpr unsigned long long kFatSlow = 1ull << 63;
+constexpr unsigned kFatFar = 0x1FFFFEu;  // DELTA encoding: neighbour index difference does not fit
+constexpr int kFatBias = 1 << 20;        // DELTA encoding: field = neighbour - face + kFatBias
 constexpr double kFatK = 1.1920928955078125e-07;  // 2^-23: twice the fp32 unit roundoff 2^-24
 
-#ifdef DLI_X_L1NA
-#define DLI_LDG256 "ld.global.nc.L1::no_allocate.v8.b32"
-#else
 #define DLI_LDG256 "ld.global.nc.v8.b32"
-#endif
 __device__ __forceinline__ void ldg256(unsigned (&r)[8], const void *p) {
   asm volatile(DLI_LDG256 " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])

@@ -107,7 +107,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
             double y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
             __stcs(ys + qi, y);
           }
-          if (simplex_out) __stcs(simplex_out + qi, f);
+          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
           if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
           active = false;
@@ -135,6 +135,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
 // gradient-form interpolant over the face exceeds 1e-13 * min|f_i| (slivers, faces on which f changes
 // sign or vanishes at a vertex): those faces are evaluated by k_interp2_full in the reference's own
 // operation order.
+template <bool DELTA>
 __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
                              uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
   int f = blockIdx.x * blockDim.x + threadIdx.x;
@@ -169,7 +170,15 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
   if (!same_sign) mn = 0.0;
   if (!all_zero) slow |= !(E <= 1e-13 * mn);   // (NaN compares false -> slow)
   else slow |= !(gx == 0.0 && gy == 0.0);
-  auto enc = [](int nb) -> unsigned long long { return nb < 0 ? (unsigned long long)kPackMask : (unsigned long long)(unsigned)nb; };
+  // neighbour field (21 bits): kPackMask = hull; ABS: the neighbour's index; DELTA (meshes with >= 2^21-2 faces):
+  // index difference + kFatBias, kFatFar when it does not fit (the kernel then reads the canonical face record;
+  // rare because faces are stored in Morton order)
+  auto enc = [f](int nb) -> unsigned long long {
+    if (nb < 0) return (unsigned long long)kPackMask;
+    if (!DELTA) return (unsigned long long)(unsigned)nb;
+    long long dlt = (long long)nb - f + kFatBias;
+    return (dlt < 0 || dlt >= (long long)kFatFar) ? (unsigned long long)kFatFar : (unsigned long long)dlt;
+  };
   unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42) | (slow ? kFatSlow : 0ull);
   if (slow) atomicAdd(n_slow, 1u);
   uint4 h0, h1, h2, h3;
@@ -201,7 +210,7 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
 // Ring = 128 query slots (16 B) + 128 hint slots (4 B) per warp = 2.5 KB; slot = query index & 127.
 constexpr int kRingSlots = 128;
 constexpr int kRingBytesPerWarp = kRingSlots * (16 + 4);
-template <bool STATS, bool RING>
+template <bool STATS, bool RING, bool DELTA>
 __global__ void __launch_bounds__(DLI_X_FAT_THREADS, DLI_X_FAT_BLOCKS)
 k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
@@ -319,14 +328,23 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
       const double lw = ax * by, rw = ay * bx, w = lw - rw, ew = (2.0 * kFatK) * (fabs(lw) + fabs(rw));
       const double o0 = (w - o2) - o1, e0 = (ew + e2) + e1;
       const unsigned long long nbr = ((unsigned long long)V[7] << 32) | V[6];
-      const int n0 = (int)(nbr & kPackMask), n1 = (int)((nbr >> 21) & kPackMask), n2 = (int)((nbr >> 42) & kPackMask);
-      const bool c0 = n0 == from, c1 = n1 == from, c2 = n2 == from;  // hull code never equals a face id / -1
+      const unsigned k0 = (unsigned)(nbr & kPackMask), k1 = (unsigned)((nbr >> 21) & kPackMask), k2 = (unsigned)((nbr >> 42) & kPackMask);
+      // neighbour indices; -2 = hull or (DELTA) far neighbour, never equal to `from`
+      const int n0 = DELTA ? (k0 >= kFatFar ? -2 : f + (int)k0 - kFatBias) : (k0 == kPackMask ? -2 : (int)k0);
+      const int n1 = DELTA ? (k1 >= kFatFar ? -2 : f + (int)k1 - kFatBias) : (k1 == kPackMask ? -2 : (int)k1);
+      const int n2 = DELTA ? (k2 >= kFatFar ? -2 : f + (int)k2 - kFatBias) : (k2 == kPackMask ? -2 : (int)k2);
+      const bool c0 = n0 == from, c1 = n1 == from, c2 = n2 == from;
       const bool neg0 = (-o0 > e0) & !c0, neg1 = (-o1 > e1) & !c1, neg2 = (-o2 > e2) & !c2;
       bool give_up = (nbr & kFatSlow) != 0;
       if (!give_up) {
         if (neg0 | neg1 | neg2) {
           int nb = neg0 ? n0 : (neg1 ? n1 : n2);
-          if (nb == (int)kPackMask || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
+          if (DELTA) {
+            const unsigned kc = neg0 ? k0 : (neg1 ? k1 : k2);
+            if (kc == kFatFar)  // neighbour too far away in index space for the 21-bit field: canonical record
+              nb = __ldg(reinterpret_cast<const int *>(m.frec) + 8 * (size_t)f + 3 + (neg0 ? 0 : (neg1 ? 1 : 2)));
+          }
+          if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
           else { from = f; f = nb; }
         } else {
           bool pos = ((o0 > e0) | c0) & ((o1 > e1) | c1) & ((o2 > e2) | c2);
@@ -337,7 +355,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
               const double gy = __hiloint2double((int)V[5], (int)V[4]);
               __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
             }
-            if (simplex_out) __stcs(simplex_out + qi, f);
+            if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
             if (status_out) status_out[qi] = DLI_STATUS_OK;
             if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
             active = false;
@@ -384,7 +402,7 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
       y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
     }
     if (ys) ys[i] = y;
-    if (simplex_out) simplex_out[i] = f;
+    if (simplex_out) simplex_out[i] = __ldg(m.orig + f);
     if (status_out) status_out[i] = status;
   }
   if (STATS) {
@@ -470,7 +488,7 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
           double y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
           __stcs(ys + qi, y);
         }
-        if (simplex_out) __stcs(simplex_out + qi, s);
+        if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + s));
         if (status_out) status_out[qi] = DLI_STATUS_OK;
         if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
         active = false;
@@ -513,7 +531,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
       y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
     }
     if (ys) ys[i] = y;
-    if (simplex_out) simplex_out[i] = s;
+    if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + s) : -1;
     if (status_out) status_out[i] = status;
   }
   if (STATS) {

@@ -10,7 +10,11 @@ pytestmark = pytest.mark.gpu
 REL_TOL = 1e-12  # north_star: values within 1e-12 relative in fp64
 
 
-EPILOGUES = ["auto", "reference"]  # auto = 64-byte walk records + guarded gradient form (default); reference = bit-exact
+# engine variants: auto = 64-byte walk records + guarded gradient form + prefetch ring (default); reference = reference
+# operation order everywhere (bit-exact vs the oracle); delta = the neighbour encoding meshes with >= 2^21-2 faces
+# get; noring = walk records without the cp.async prefetch ring
+VARIANTS = {"auto": {}, "reference": {"epilogue": "reference"}, "delta": {"packed_faces": 2}, "noring": {"prefetch_ring": -1}}
+EPILOGUES = list(VARIANTS)
 
 
 def _check_parity(mesh, om, q, ys, simplex, status, allow_outside=True, bit_exact=True):
@@ -40,7 +44,7 @@ def test_config1_readme_grid(gpu, epilogue):
     for lo, want in ((0.0, 5.800002), (0.01, 1.909975)):
         c, f, t = helpers.grid_mesh(lo)
         q = helpers.grid_queries(lo)
-        m = dl.Mesh(c, f, t, epilogue=epilogue)
+        m = dl.Mesh(c, f, t, **VARIANTS[epilogue])
         ys, s, st = m.interp(q, return_simplex=True, return_status=True)
         sse = float(np.sum((helpers.cobb_douglas(q) - ys) ** 2))
         assert abs(sse - want) < 5e-7, sse   # README.md:130 prints 5.800002
@@ -59,7 +63,7 @@ def test_random_mesh_inside_and_outside(gpu, nv, nq, seed, epilogue):
     q[:200] = pts[:200]
     q[200:400] = 0.5 * (pts[sv[:200, 0]] + pts[sv[:200, 1]])
     q[400:410] = [[-3.0, 0.5], [4.0, 0.5], [0.5, -7.0], [0.5, 9.0], [-2, -2], [3, 3], [-2, 3], [3, -2], [0.5, 1e6], [-1e6, 0.5]]
-    m = dl.Mesh(pts, f, sv, sn, epilogue=epilogue)
+    m = dl.Mesh(pts, f, sv, sn, **VARIANTS[epilogue])
     m.collect_stats(True)
     ys, s, st = m.interp(q, return_simplex=True, return_status=True)
     stats = m.stats()
@@ -68,7 +72,7 @@ def test_random_mesh_inside_and_outside(gpu, nv, nq, seed, epilogue):
     assert stats["outside"] == int((st == 1).sum())
     assert stats["walk_steps"] >= nq
     # neighbours derived by the library give the same answers
-    m2 = dl.Mesh(pts, f, sv, None, epilogue=epilogue)
+    m2 = dl.Mesh(pts, f, sv, None, **VARIANTS[epilogue])
     ys2 = m2.interp(q)
     assert np.array_equal(ys, ys2, equal_nan=True)
     # locate-only agrees with interp's simplex
@@ -177,3 +181,25 @@ def test_walk_record_guard_sign_changing_values(gpu):
     ys2, s2, st2 = m2.interp(q2, return_simplex=True, return_status=True)
     om2 = OracleMesh(pts * sc, np.abs(f) + 1.0, sv, sn)
     _check_parity(m2, om2, q2, ys2, s2, st2, bit_exact=True)
+
+
+def test_large_mesh_delta_encoded_walk_records(gpu):
+    """> 2^21 faces: walk records with delta-encoded neighbours over Morton-ordered faces (far neighbours read the
+    canonical record); parity on a sample vs the oracle, and the full batch vs the reference-order engine."""
+    import delaunay_linterp_b200 as dl
+    rng = np.random.default_rng(71)
+    pts = rng.random((1_150_000, 2))
+    t = dl.DelaunayInterp2()
+    t.insert_many(pts, helpers.cobb_douglas(pts), spatial_sort=True, use_gpu=False)
+    c, f, sv, sn = t.export()
+    assert len(sv) >= (1 << 21)
+    m = dl.Mesh(c, f, sv, sn)
+    q = rng.random((2_000_000, 2)) * 1.02 - 0.01
+    ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+    mr = dl.Mesh(c, f, sv, sn, epilogue="reference")
+    yr, sr, str_ = mr.interp(q, return_simplex=True, return_status=True)
+    assert np.array_equal(st, str_) and np.array_equal(s, sr)
+    assert np.max(np.abs(ys - yr) / np.maximum(np.abs(yr), 1e-300)) <= REL_TOL
+    om = OracleMesh(c, f, sv, sn)
+    k = 100_000
+    _check_parity(m, om, q[:k], ys[:k], s[:k], st[:k], bit_exact=False)
