@@ -1,0 +1,109 @@
+"""GPU, BASELINE.json's full sizes: size-independent properties of the batched interp path.
+
+The oracle cannot finish 100M queries in seconds, so at full size the CUDA path is checked through properties the
+domain offers (affine reproduction, batch-partition and permutation invariance, agreement of the two device
+engines -- walk records vs reference operation order -- on every query) plus oracle parity on a 1M-query subsample.
+"""
+import numpy as np
+import pytest
+
+import helpers
+from oracle.oracle import OracleMesh
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-12
+
+
+def _native_mesh(nv, seed):
+    import delaunay_linterp_b200 as dl
+    pts = np.random.default_rng(seed).random((nv, 2))
+    t = dl.DelaunayInterp2()
+    t.insert_many(pts, helpers.cobb_douglas(pts), spatial_sort=True, use_gpu=False)
+    return t.export()
+
+
+def test_cfg2_full_size_properties(gpu):
+    """configs[1]: 1M uniform-random vertices, 100M uniform queries in the hull, fp64."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    c, f, sv, sn = _native_mesh(1_000_000, 1001)
+    nq = 100_000_000
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2001)
+    xq = torch.rand(nq, 2, dtype=torch.float64, device="cuda", generator=g) * 0.96 + 0.02
+    m = dl.Mesh(c, f, sv, sn)
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert int(st.max().item()) == 0                       # every query inside the hull, none hit the step limit
+    assert bool(torch.isfinite(ys).all())
+    # (1) the two device engines agree on every one of the 100M queries: same face, values within 1e-12
+    mr = dl.Mesh(c, f, sv, sn, epilogue="reference")
+    yr, sr = mr.interp(xq, return_simplex=True)
+    torch.cuda.synchronize()
+    assert bool(torch.equal(s, sr))
+    rel = ((ys - yr).abs() / yr.abs().clamp_min(1e-300)).max().item()
+    assert rel <= REL_TOL, rel
+    # (2) batch-partition invariance: ragged shards give bit-identical results
+    cuts = [0, 1, 31, 33, 1_000_003, 37_000_001, 99_999_999, nq]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        assert bool(torch.equal(m.interp(xq[a:b]), ys[a:b]))
+    # (3) permutation equivariance on a 20M slice (the engine is order-independent)
+    k = 20_000_000
+    perm = torch.randperm(k, device="cuda", generator=g)
+    assert bool(torch.equal(m.interp(xq[:k][perm].contiguous()), ys[:k][perm]))
+    # (4) interpolant bounds: every value lies between the smallest and largest f of its face
+    svt = torch.from_numpy(sv.astype(np.int64)).cuda()
+    ft = torch.from_numpy(f).cuda()
+    fv = ft[svt[s.long()[:k]]]
+    lo, hi = fv.min(dim=1).values, fv.max(dim=1).values
+    assert bool(((ys[:k] >= lo * (1 - 1e-12)) & (ys[:k] <= hi * (1 + 1e-12))).all())
+    del fv, lo, hi, perm, yr, sr
+    # (5) affine reproduction over all 100M queries (set_values rebuilds the walk records)
+    m.set_values(2.0 + 3.0 * c[:, 0] - 1.5 * c[:, 1])
+    ya = m.interp(xq)
+    want = 2.0 + 3.0 * xq[:, 0] - 1.5 * xq[:, 1]
+    assert ((ya - want).abs() / want.abs()).max().item() <= REL_TOL
+    del ya, want
+    # (6) oracle parity on a 1M-query subsample (values, statuses, located faces)
+    m.set_values(f)
+    n1 = 1_000_000
+    q1 = xq[:n1].cpu().numpy()
+    yo, so, sto = OracleMesh(c, f, sv, sn).interp(q1, mode=1, nthreads=8)
+    assert np.array_equal(sto, st[:n1].cpu().numpy())
+    y1 = ys[:n1].cpu().numpy()
+    assert np.max(np.abs(y1 - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
+    # identical face wherever the oracle's face strictly contains the query (always, for random queries)
+    assert np.mean(s[:n1].cpu().numpy() == so) > 0.999999
+
+
+def test_cfg4_3d_full_size_properties(gpu):
+    """configs[3], 3D: 200k random vertices, 20M queries; outside the hull -> NaN, simplex -1."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(3, 200_000, 1003)
+    m = dl.Mesh(pts, f, sv, sn)
+    nq = 20_000_000
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2004)
+    xq = torch.rand(nq, 3, dtype=torch.float64, device="cuda", generator=g) * 0.8 + 0.1
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
+    for a, b in ((0, 7), (7, 5_000_001), (5_000_001, nq)):
+        assert bool(torch.equal(m.interp(xq[a:b]), ys[a:b]))
+    # affine reproduction
+    m.set_values(1.0 + pts @ np.array([0.5, -2.0, 3.0]))
+    ya = m.interp(xq)
+    want = 1.0 + xq @ torch.tensor([0.5, -2.0, 3.0], dtype=torch.float64, device="cuda")
+    assert ((ya - want).abs() / want.abs().clamp_min(1e-3)).max().item() <= 1e-12
+    # outside queries
+    out = torch.tensor([[2.0, 0.5, 0.5], [-1.0, -1.0, -1.0]], dtype=torch.float64, device="cuda")
+    yo, so, sto = m.interp(out, return_simplex=True, return_status=True)
+    assert bool(torch.isnan(yo).all()) and so.tolist() == [-1, -1] and sto.tolist() == [dl.STATUS_OUTSIDE_NAN] * 2
+    # oracle parity on a 200k subsample
+    m.set_values(f)
+    n1 = 200_000
+    yo, so, sto = OracleMesh(pts, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
+    y1 = ys[:n1].cpu().numpy()
+    assert np.max(np.abs(y1 - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
