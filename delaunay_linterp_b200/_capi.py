@@ -48,6 +48,8 @@ class Stats(C.Structure):
         ("fast_kernel_launches", C.c_int64),
         ("fast_kernel_ms", C.c_double),
         ("full_kernel_ms", C.c_double),
+        ("straggler_queries", C.c_int64),
+        ("slow_simplices", C.c_int64),
     ]
 
 

@@ -103,6 +103,9 @@ struct dli_mesh {
   mutable HostPipe pipe;
 };
 
+// bytes per walk record (2D: 64, 3D: 128, 4D: 192)
+static int fat_record_bytes(int dim) { return dim == 2 ? 64 : (dim == 3 ? FatD<3>::BYTES : FatD<4>::BYTES); }
+
 static void mesh_free(dli_mesh *m) {
   if (!m) return;
   DeviceGuard g(m->device);
@@ -317,8 +320,8 @@ static int mesh_alloc_common(dli_mesh *m) {
   if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
   if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
     CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
-  if (d == 2 && m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0)
-    CU(cudaMalloc(&m->d_fat, 64 * (size_t)m->ns));
+  if (m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0)
+    CU(cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(d) * (size_t)m->ns));
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
   // keep stream-ordered allocations cached between calls
@@ -338,9 +341,15 @@ static int build_fat_records(dli_mesh *m) {
   if (!m->d_fat) return DLI_OK;
   unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
   CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
-  auto kb = fat_delta(m) ? k_build_fat2<true> : k_build_fat2<false>;
-  kb<<<(unsigned)((m->ns + 255) / 256), 256>>>((int)m->ns, reinterpret_cast<const int4 *>(m->d_srec),
-                                             reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
+  if (m->dim == 2) {
+    auto kb = fat_delta(m) ? k_build_fat2<true> : k_build_fat2<false>;
+    kb<<<(unsigned)((m->ns + 255) / 256), 256>>>((int)m->ns, reinterpret_cast<const int4 *>(m->d_srec),
+                                               reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
+  } else if (m->dim == 3) {
+    k_build_fatD<3><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
+  } else {
+    k_build_fatD<4><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
+  }
   CU(cudaGetLastError());
   unsigned int cnt = 0;
   CU(cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost));
@@ -494,7 +503,7 @@ extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
                    sizeof(int32_t) * m->grid.cells + sizeof(int32_t) * m->ns + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
-                   (m->d_fat ? 64 * m->ns : 0));
+                   (m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->ns : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
@@ -528,6 +537,7 @@ Mesh2View view2(const dli_mesh *m) {
 MeshDView viewD(const dli_mesh *m) {
   MeshDView v;
   v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint; v.orig = m->d_orig;
+  v.fat = m->d_fat;
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   return v;
@@ -594,8 +604,12 @@ void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int64_t warps = (n + per_warp - 1) / per_warp;
   int wpb = tpb / 32;
   L.mark(0);
-  k_interpD_fast<D, STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(v, n, per_warp, xs, ys, so, sto, L.queue,
-                                                                                      L.qcount, L.qcap, L.stats);
+  if (EPI == 0 && L.m->d_fat)
+    k_interpD_fat<D, STATS><<<(unsigned)((warps + wpb - 1) / wpb), tpb, (size_t)wpb * FatD<D>::SMEM_PER_WARP, L.st>>>(
+        v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  else
+    k_interpD_fast<D, STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(v, n, per_warp, xs, ys, so, sto, L.queue,
+                                                                                        L.qcount, L.qcap, L.stats);
   L.mark(1);
   k_interpD_full<D, STATS, EPI><<<148 * 2, 64, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
   L.mark(2);
@@ -765,6 +779,8 @@ extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
   out->exact_fallbacks = (int64_t)w[ST_EXACT];
   out->outside = (int64_t)w[ST_OUTSIDE];
   out->kernel_launches = m->last.kernel_launches;
+  out->straggler_queries = (int64_t)w[ST_HARD];
+  out->slow_simplices = m->n_slow_faces;
   out->fast_kernel_launches = 0;
   out->fast_kernel_ms = out->full_kernel_ms = 0.0;
   {
@@ -925,7 +941,8 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   if (rc == DLI_OK && !h[13] && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
   if (rc == DLI_OK && h[12] && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "packed face allocation failed");
-  if (rc == DLI_OK && h[13] && !m->d_fat && cudaMalloc(&m->d_fat, 64 * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
+  if (rc == DLI_OK && h[13] && !m->d_fat &&
+      cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m->dim) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "walk record allocation failed");
   m->max_steps = (int)h[10];
   m->fast_steps = (int)h[11];
@@ -948,7 +965,7 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
-    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)64 * m->ns : 0; break;
+    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->ns : 0; break;
     case 6: *ptr = m->d_orig; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1); break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }

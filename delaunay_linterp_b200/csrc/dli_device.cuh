@@ -53,12 +53,37 @@ struct MeshDView {
   const int32_t *srec;
   const int32_t *hint;
   const int32_t *orig;  // device simplex index -> the caller's simplex id
+  const uint4 *fat;     // optional walk records (FatD<D>), NULL when unused
   double o[DLI_MAX_DIM], ic[DLI_MAX_DIM];
   int g[DLI_MAX_DIM];
   int ns;
   int max_steps;
   int fast_steps;
 };
+
+// ---------------------------------------------------------------------------------------------
+// dD walk records (fast pass k_interpD_fat).  Self-contained per simplex, in 16-byte chunks so that a warp can
+// stage the 32 records of a walk step into shared memory with coalesced cp.async (LPR lanes per record):
+//   p0 = vertex 0 (fp64 x D) | f0, grad f (fp64 x (D+1)): affine interpolant y = f0 + g.(p - p0) | flags (u64)
+//   G (fp32, D x D): row i = gradient of the barycentric coordinate of vertex i+1, so b_{i+1} = G_i . (p - p0)
+//   n_0..n_D (int32, device simplex indices, < 0 = hull)
+// D = 3: 8 chunks (128 B):  c0 p0x p0y | c1 p0z f0 | c2 gx gy | c3 gz flags | c4 G0..3 | c5 G4..7 | c6 G8 - - - | c7 n0..n3
+// D = 4: 12 chunks (192 B): c0 p0x p0y | c1 p0z p0w | c2 f0 gx | c3 gy gz | c4 gw flags | c5 n0..n3 | c6..c9 G0..15 |
+//                           c10 n4 - - - | c11 unused (not loaded)
+// The fp32 rounding of G (and the fp64 rounding error of computing it, bounded per entry at build time to at most
+// half an fp32 ulp) is covered by the filter constant kFatKD, so a certified barycentric sign is the sign of the exact
+// orientation predicate on the fp64 mesh.
+// ---------------------------------------------------------------------------------------------
+template <int D>
+struct FatD {
+  static constexpr int CHUNKS = (D == 3) ? 8 : 12;        // global record size in 16-byte chunks
+  static constexpr int LOADED = (D == 3) ? 8 : 11;        // chunks actually staged
+  static constexpr int LPR = (D == 3) ? 8 : 16;           // lanes cooperating on one record
+  static constexpr int SSTRIDE = (D == 3) ? 9 : 13;       // shared-memory record stride in chunks (odd: conflict-free)
+  static constexpr int BYTES = CHUNKS * 16;
+  static constexpr int SMEM_PER_WARP = 32 * SSTRIDE * 16;
+};
+constexpr double kFatKD = 2.384185791015625e-07;  // 2^-22 = 4 fp32 unit roundoffs
 
 struct StatsAcc {  // per-thread accumulators, flushed by the kernels when stats are enabled
   unsigned long long steps = 0, exact = 0, outside = 0;

@@ -540,6 +540,362 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// dD fast pass on walk records (see dli_device.cuh, FatD<D>)
+// ---------------------------------------------------------------------------------------------
+
+// double-double helpers for the one-time record build (relative error of one operation < 2^-100)
+struct dd { double hi, lo; };
+__device__ __forceinline__ dd dd_make(double a, double b) { dd r; two_sum(a, b, r.hi, r.lo); return r; }
+__device__ __forceinline__ dd dd_neg(dd a) { dd r; r.hi = -a.hi; r.lo = -a.lo; return r; }
+__device__ __forceinline__ dd dd_add(dd a, dd b) {
+  double s, e, t, f2;
+  two_sum(a.hi, b.hi, s, e);
+  two_sum(a.lo, b.lo, t, f2);
+  e += t;
+  double s2, e2;
+  two_sum(s, e, s2, e2);   // (fast renormalisation is enough: |e| << |s| after the first pass or both tiny)
+  e2 += f2;
+  dd r;
+  two_sum(s2, e2, r.hi, r.lo);
+  return r;
+}
+__device__ __forceinline__ dd dd_mul(dd a, dd b) {
+  double p, e;
+  two_prod(a.hi, b.hi, p, e);
+  e += a.hi * b.lo + a.lo * b.hi;
+  dd r;
+  two_sum(p, e, r.hi, r.lo);
+  return r;
+}
+__device__ __forceinline__ dd dd_div(dd a, dd b) {
+  double q1 = a.hi / b.hi;
+  dd q; q.hi = q1; q.lo = 0.0;
+  dd r = dd_add(a, dd_neg(dd_mul(b, q)));
+  double q2 = r.hi / b.hi;
+  q.hi = q2;
+  r = dd_add(r, dd_neg(dd_mul(b, q)));
+  double q3 = r.hi / b.hi;
+  dd res = dd_make(q1, q2);
+  dd t; t.hi = q3; t.lo = 0.0;
+  return dd_add(res, t);
+}
+// determinant of the K x K dd matrix m (row-major) by cofactor expansion along column 0
+template <int K>
+struct DetDD {
+  __device__ static dd eval(const dd *m) {
+    dd det; det.hi = 0.0; det.lo = 0.0;
+    for (int r = 0; r < K; r++) {
+      dd sub[(K - 1) * (K - 1)];
+      int rr = 0;
+      for (int i = 0; i < K; i++) {
+        if (i == r) continue;
+        for (int c = 1; c < K; c++) sub[rr * (K - 1) + (c - 1)] = m[i * K + c];
+        rr++;
+      }
+      dd t = dd_mul(m[r * K], DetDD<K - 1>::eval(sub));
+      det = dd_add(det, (r & 1) ? dd_neg(t) : t);
+    }
+    return det;
+  }
+};
+template <>
+struct DetDD<1> {
+  __device__ static dd eval(const dd *m) { return m[0]; }
+};
+
+// Builds the dD walk records.  One thread per simplex.  G = (E^-1)^T (E rows = v_i - v_0, formed exactly as
+// double-doubles) by cofactors in double-double arithmetic, so the stored fp64 gradient g = sum_i (f_i - f_0) G_i is
+// the correctly rounded exact gradient unless the simplex is so flat that even 2^-94 * permanent / |W| matters (the
+// bound below accounts for it).  The slow flag is set when an entry of the fp32 G is not within 1.5 fp32
+// ulps-of-the-row-maximum of the exact value, or when the a-priori error bound of the affine interpolant exceeds
+// 1e-13 * min|f_i| (see k_build_fat2): k_interpD_full handles those simplices in the reference's operation order.
+template <int D>
+__global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, const double *__restrict__ vrec, int vs,
+                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  const double eps = 1.1102230246251565e-16, u = 5.9604644775390625e-08;
+  const double edd = 5.048709793414476e-29;  // 2^-94: bound on the accumulated double-double error per unit of permanent
+  int v[D + 1], nb[D + 1];
+  for (int i = 0; i <= D; i++) { v[i] = srec[(size_t)s * ss + i]; nb[i] = srec[(size_t)s * ss + D + 1 + i]; }
+  double x0[D], f[D + 1], E[D * D];
+  dd Ed[D * D];
+  for (int k = 0; k < D; k++) x0[k] = vrec[(size_t)v[0] * vs + k];
+  f[0] = vrec[(size_t)v[0] * vs + D];
+  for (int i = 0; i < D; i++) {
+    for (int k = 0; k < D; k++) {
+      Ed[i * D + k] = dd_make(vrec[(size_t)v[i + 1] * vs + k], -x0[k]);   // exact difference
+      E[i * D + k] = Ed[i * D + k].hi;
+    }
+    f[i + 1] = vrec[(size_t)v[i + 1] * vs + D];
+  }
+  // cofactors (double-double) and their permanents (double)
+  dd Cd[D * D];
+  double P[D * D];
+  for (int i = 0; i < D; i++)
+    for (int k = 0; k < D; k++) {
+      dd subd[(D - 1) * (D - 1)];
+      double sub[(D - 1) * (D - 1)];
+      int rr = 0;
+      for (int a = 0; a < D; a++) {
+        if (a == i) continue;
+        int cc = 0;
+        for (int b = 0; b < D; b++) {
+          if (b == k) continue;
+          subd[rr * (D - 1) + cc] = Ed[a * D + b];
+          sub[rr * (D - 1) + cc] = E[a * D + b];
+          cc++;
+        }
+        rr++;
+      }
+      double sp;
+      DetPerm<D - 1>::eval(sub, sp);
+      dd sd = DetDD<D - 1>::eval(subd);
+      Cd[i * D + k] = ((i + k) & 1) ? dd_neg(sd) : sd;
+      P[i * D + k] = sp;
+    }
+  dd Wd; Wd.hi = 0.0; Wd.lo = 0.0;
+  double PW = 0.0;
+  for (int k = 0; k < D; k++) { Wd = dd_add(Wd, dd_mul(Ed[k], Cd[k])); PW += fabs(E[k]) * P[k]; }
+  const double aW = fabs(Wd.hi);
+  bool slow = !(aW > 0.0);
+  dd Gd[D * D];
+  double G[D * D], dG[D * D];
+  float g32[D * D];
+  for (int i = 0; i < D * D; i++) {
+    Gd[i] = dd_div(Cd[i], Wd);
+    G[i] = Gd[i].hi;
+    // error of the fp64 G[i] against the exact entry: one rounding + the double-double residue
+    dG[i] = eps * fabs(G[i]) + edd * (P[i] + fabs(G[i]) * PW) / aW;
+    g32[i] = (float)G[i];
+  }
+  for (int i = 0; i < D; i++) {
+    double gmax = 0.0;
+    for (int k = 0; k < D; k++) gmax = fmax(gmax, fabs((double)g32[i * D + k]));
+    slow |= !(gmax > 0.0 && gmax < 1e300);
+    for (int k = 0; k < D; k++) slow |= !(fabs((double)g32[i * D + k] - G[i * D + k]) + dG[i * D + k] <= 1.5 * u * gmax);
+  }
+  // affine interpolant (gradient accumulated in double-double) and its a-priori error bound over the simplex
+  double g[D], E_eval = (D + 2) * eps * fabs(f[0]);
+  double mn = fabs(f[0]);
+  bool pos = f[0] > 0.0, neg = f[0] < 0.0, zero = f[0] == 0.0;
+  for (int i = 1; i <= D; i++) {
+    mn = fmin(mn, fabs(f[i]));
+    pos &= f[i] > 0.0; neg &= f[i] < 0.0; zero &= f[i] == 0.0;
+  }
+  for (int k = 0; k < D; k++) {
+    dd gk; gk.hi = 0.0; gk.lo = 0.0;
+    double dk = 0.0, wk = 0.0;
+    for (int i = 0; i < D; i++) {
+      const dd df = dd_make(f[i + 1], -f[0]);
+      gk = dd_add(gk, dd_mul(df, Gd[i * D + k]));
+      dk += fabs(df.hi) * (edd * (P[i * D + k] + fabs(G[i * D + k]) * PW) / aW + 8.0 * edd * fabs(G[i * D + k]));
+      wk = fmax(wk, fabs(E[i * D + k]));
+    }
+    g[k] = gk.hi;
+    // rounding of g[k] to fp64 + propagated double-double residue, then the (D + 2) roundings of the evaluation
+    E_eval += (eps * fabs(g[k]) + dk) * wk + (D + 2) * eps * fabs(g[k]) * wk;
+  }
+  if (zero) {
+    for (int k = 0; k < D; k++) slow |= !(g[k] == 0.0);
+  } else {
+    if (!(pos || neg)) mn = 0.0;
+    slow |= !(E_eval <= 1e-13 * mn);
+  }
+  if (slow) atomicAdd(n_slow, 1u);
+  // ---- pack
+  auto d2 = [](double a, double b) {
+    uint4 r;
+    r.x = (unsigned)__double2loint(a); r.y = (unsigned)__double2hiint(a);
+    r.z = (unsigned)__double2loint(b); r.w = (unsigned)__double2hiint(b);
+    return r;
+  };
+  auto f4 = [](float a, float b, float c, float d) {
+    return make_uint4(__float_as_uint(a), __float_as_uint(b), __float_as_uint(c), __float_as_uint(d));
+  };
+  const double flags = __longlong_as_double(slow ? 1ll : 0ll);
+  uint4 *o = fat + (size_t)s * FatD<D>::CHUNKS;
+  if constexpr (D == 3) {
+    o[0] = d2(x0[0], x0[1]);
+    o[1] = d2(x0[2], f[0]);
+    o[2] = d2(g[0], g[1]);
+    o[3] = d2(g[2], flags);
+    o[4] = f4(g32[0], g32[1], g32[2], g32[3]);
+    o[5] = f4(g32[4], g32[5], g32[6], g32[7]);
+    o[6] = f4(g32[8], 0.f, 0.f, 0.f);
+    o[7] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
+  } else {
+    o[0] = d2(x0[0], x0[1]);
+    o[1] = d2(x0[2], x0[3]);
+    o[2] = d2(f[0], g[0]);
+    o[3] = d2(g[1], g[2]);
+    o[4] = d2(g[3], flags);
+    o[5] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
+    o[6] = f4(g32[0], g32[1], g32[2], g32[3]);
+    o[7] = f4(g32[4], g32[5], g32[6], g32[7]);
+    o[8] = f4(g32[8], g32[9], g32[10], g32[11]);
+    o[9] = f4(g32[12], g32[13], g32[14], g32[15]);
+    o[10] = make_uint4((unsigned)nb[4], 0u, 0u, 0u);
+    o[11] = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+// dD fast pass on walk records.  Lane state machine as k_interpD_fast; per iteration the warp stages the 32 records
+// of this step into shared memory with coalesced cp.async (FatD<D>::LPR lanes x 16 B per record, one or two
+// 128-byte lines per record instead of D+2 scattered gathers), then every lane reads its own record with LDS.128.
+// A step is D dot products against the fp32 barycentric gradients with the bound kFatKD * max|G_i| * |d|_1.
+template <int D, bool STATS>
+__global__ void __launch_bounds__(128)
+k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
+              int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
+              unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
+  using F = FatD<D>;
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(16) unsigned char stage_smem[];
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * per_warp;
+  if (base >= n) return;  // warp-uniform
+  const int64_t end = min(n, base + (int64_t)per_warp);
+  uint4 *stage = reinterpret_cast<uint4 *>(stage_smem) + (size_t)(threadIdx.x >> 5) * 32 * F::SSTRIDE;
+  const uint4 *mine = stage + lane * F::SSTRIDE;                    // this lane's staged record
+  const int rsub = lane / F::LPR, csub = lane % F::LPR;             // staging role: record within the group, chunk
+  const unsigned sdst = (unsigned)__cvta_generic_to_shared(stage + csub);
+  int64_t next = base;
+  bool active = false;
+  double p[D];
+#pragma unroll
+  for (int k = 0; k < D; k++) p[k] = 0.0;
+  int s = 0, from = -1;
+  int64_t qi = 0;
+  unsigned int steps = 0;
+  StatsAcc st;
+  for (;;) {
+    unsigned need = __ballot_sync(FULL, !active);
+    if (need) {
+      int64_t idx = next + __popc(need & ((1u << lane) - 1u));
+      if (!active && idx < end) {
+#pragma unroll
+        for (int k = 0; k < D; k++) p[k] = __ldcs(xs + idx * D + k);
+        qi = idx;
+        s = hintD<D>(m, p);
+        from = -1;
+        steps = 0;
+        active = true;
+      }
+      next += __popc(need);
+    }
+    if (!__any_sync(FULL, active)) break;
+    // ---- stage the records of this step
+    const int fs = active ? s : -1;
+    __syncwarp();  // every lane has finished reading the previous step's records
+#pragma unroll
+    for (int j = 0; j < F::LPR; j++) {     // 32 / (32 / LPR) instructions, 32 / LPR records each
+      const int r = j * (32 / F::LPR) + rsub;
+      const int fr = __shfl_sync(FULL, fs, r);
+      if (fr >= 0 && csub < F::LOADED)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + (unsigned)(r * F::SSTRIDE * 16)),
+                     "l"(m.fat + (size_t)fr * F::CHUNKS + csub)
+                     : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    if (active) {
+      steps++;
+      double x0[D], f0, g[D];
+      float G[D * D];
+      int nb[D + 1];
+      unsigned long long flags;
+      {
+        auto lo = [](const uint4 &c) { return __hiloint2double((int)c.y, (int)c.x); };
+        auto hi = [](const uint4 &c) { return __hiloint2double((int)c.w, (int)c.z); };
+        if constexpr (D == 3) {
+          uint4 c0 = mine[0], c1 = mine[1], c2 = mine[2], c3 = mine[3], c4 = mine[4], c5 = mine[5], c6 = mine[6], c7 = mine[7];
+          x0[0] = lo(c0); x0[1] = hi(c0); x0[2] = lo(c1); f0 = hi(c1);
+          g[0] = lo(c2); g[1] = hi(c2); g[2] = lo(c3);
+          flags = ((unsigned long long)c3.w << 32) | c3.z;
+          G[0] = __uint_as_float(c4.x); G[1] = __uint_as_float(c4.y); G[2] = __uint_as_float(c4.z); G[3] = __uint_as_float(c4.w);
+          G[4] = __uint_as_float(c5.x); G[5] = __uint_as_float(c5.y); G[6] = __uint_as_float(c5.z); G[7] = __uint_as_float(c5.w);
+          G[8] = __uint_as_float(c6.x);
+          nb[0] = (int)c7.x; nb[1] = (int)c7.y; nb[2] = (int)c7.z; nb[3] = (int)c7.w;
+        } else {
+          uint4 c0 = mine[0], c1 = mine[1], c2 = mine[2], c3 = mine[3], c4 = mine[4], c5 = mine[5];
+          x0[0] = lo(c0); x0[1] = hi(c0); x0[2] = lo(c1); x0[3] = hi(c1);
+          f0 = lo(c2); g[0] = hi(c2); g[1] = lo(c3); g[2] = hi(c3); g[3] = lo(c4);
+          flags = ((unsigned long long)c4.w << 32) | c4.z;
+          nb[0] = (int)c5.x; nb[1] = (int)c5.y; nb[2] = (int)c5.z; nb[3] = (int)c5.w;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            uint4 c = mine[6 + q];
+            G[4 * q] = __uint_as_float(c.x); G[4 * q + 1] = __uint_as_float(c.y);
+            G[4 * q + 2] = __uint_as_float(c.z); G[4 * q + 3] = __uint_as_float(c.w);
+          }
+          nb[4] = (int)mine[10].x;
+        }
+      }
+      double d[D], d1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < D; k++) { d[k] = p[k] - x0[k]; d1 += fabs(d[k]); }
+      // barycentric coordinates b[1..D] = G_i . d, b[0] = 1 - sum; bounds e[j]
+      double b[D + 1], e[D + 1], sb = 0.0, se = 0.0;
+#pragma unroll
+      for (int i = 0; i < D; i++) {
+        double acc = 0.0;
+        float gm = 0.f;
+#pragma unroll
+        for (int k = 0; k < D; k++) { acc = fma((double)G[i * D + k], d[k], acc); gm = fmaxf(gm, fabsf(G[i * D + k])); }
+        b[i + 1] = acc;
+        e[i + 1] = (kFatKD * (double)gm) * d1;
+        sb += acc;
+        se += e[i + 1];
+      }
+      b[0] = 1.0 - sb;
+      e[0] = se * 1.0000001 + 8.881784197001252e-16;  // + 2^-50: roundings of the sum and of 1 - sum
+      int mv = -1;
+      bool all_pos = true;
+#pragma unroll
+      for (int j = D; j >= 0; j--) {
+        const bool came = nb[j] == from;   // from = -1 only matches a hull slot, which is never "came from"... guard below
+        if (!(came && nb[j] >= 0)) {
+          if (-b[j] > e[j]) mv = j;        // lowest such j wins (loop runs downwards)
+          else if (!(b[j] > e[j])) all_pos = false;
+        }
+      }
+      bool give_up = (flags & 1ull) != 0;
+      if (!give_up) {
+        if (mv >= 0) {
+          int t = nb[0];
+#pragma unroll
+          for (int j = 1; j <= D; j++) t = (mv == j) ? nb[j] : t;
+          if (t < 0 || (int)steps >= m.fast_steps) give_up = true;
+          else { from = s; s = t; }
+        } else if (all_pos) {
+          if (ys) {
+            double y = 0.0;
+#pragma unroll
+            for (int k = D - 1; k >= 0; k--) y = fma(g[k], d[k], y);
+            __stcs(ys + qi, f0 + y);
+          }
+          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + s));
+          if (status_out) status_out[qi] = DLI_STATUS_OK;
+          if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
+          active = false;
+        } else {
+          give_up = true;
+        }
+      }
+      if (give_up) {
+        unsigned int slot = atomicAdd(queue_count, 1u);
+        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        active = false;
+      }
+    }
+  }
+  if (STATS) flush_stats(stats, st);
+}
+
 // 32-byte face records -> 16-byte packed records (see Mesh2View::fpack)
 __global__ void k_pack_faces(int ns, const int4 *__restrict__ frec, ulonglong2 *__restrict__ fpack) {
   int f = blockIdx.x * blockDim.x + threadIdx.x;

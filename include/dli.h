@@ -184,6 +184,8 @@ typedef struct dli_stats {
   int64_t fast_kernel_launches;
   double fast_kernel_ms;    /* sum of the fast-pass kernel durations */
   double full_kernel_ms;    /* sum of the straggler/exact-pass kernel durations */
+  int64_t straggler_queries; /* queries the fast pass handed to the straggler/exact pass (counters mode) */
+  int64_t slow_simplices;    /* simplices whose walk record carries the slow flag (always served by the exact pass) */
 } dli_stats;
 /* enable: 0 = off, bit 0 = counters (adds atomics to the kernels), bit 1 = per-launch CUDA-event timing of the
    two interp kernels on the launching stream.  Enabling resets the accumulated timing. */

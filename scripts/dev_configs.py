@@ -30,7 +30,7 @@ def report(name, m, dim, nq, lo, hi, seed, extra=None):
     ms = timeit(m, xq, ys, a.reps)
     out = dict(cfg=name, dim=dim, nq=nq, ns=int(m.n_simplices), mesh_MB=round(m.device_bytes / 1e6, 1), ms=round(ms, 3), gqps=round(nq / ms / 1e6, 3),
                roofline_frac=round(nq / ms * 1e3 * BALG[dim] / 6562.6e9, 4), steps_per_q=round(st["walk_steps"] / st["queries"], 3),
-               max_steps=st["max_walk_steps"], nan_frac=float(torch.isnan(ys).float().mean()))
+               max_steps=st["max_walk_steps"], stragglers=st["straggler_queries"], slow_simplices=st["slow_simplices"], nan_frac=float(torch.isnan(ys).float().mean()))
     if extra: out.update(extra)
     print(json.dumps(out), flush=True)
 
