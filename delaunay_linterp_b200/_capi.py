@@ -13,6 +13,7 @@ DLI_MAX_DIM = 6
 DLI_MESH_HEADER_WORDS = 16
 
 STATUS_OK, STATUS_OUTSIDE_PROJECTED, STATUS_OUTSIDE_NAN, STATUS_STEP_LIMIT, STATUS_NO_MESH = 0, 1, 2, 3, 4
+STATUS_ON_EDGE, STATUS_ON_VERTEX = 5, 6
 
 
 class DliError(RuntimeError):
@@ -70,6 +71,7 @@ SYMBOLS = [
     ("dli_mesh_get_simplices", C.c_int, [_vp, _vp, _vp]),
     ("dli_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_locate", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp]),
+    ("dli_gradient", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_simplex_error_count", C.c_int64, [_vp]),
     ("dli_simplex_error_prepare", C.c_int, [_vp, _vp, _vp, _vp]),
     ("dli_simplex_error_finish", C.c_int, [_vp, C.c_int64, _vp, _vp]),
@@ -106,6 +108,7 @@ HOST_SYMBOLS = [
     ("dli_di2_dimension", C.c_int, [_vp]),
     ("dli_di2_export", C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     ("dli_di2_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_di2_gradient", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_di2_device_mesh", _vp, [_vp]),
     ("dli_di2_set_options", C.c_int, [_vp, C.POINTER(Options)]),
     ("dli_di2_get_all_vertices", C.c_int64, [_vp, _vp]),

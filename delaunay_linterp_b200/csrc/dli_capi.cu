@@ -565,9 +565,9 @@ struct Launch {
   }
 };
 
-template <bool STATS, int EPI>
+template <bool STATS, int EPI, int OUT = 0>
 void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
-  auto fast = L.m->d_fpack ? k_interp2_fast<STATS, EPI, true> : k_interp2_fast<STATS, EPI, false>;
+  auto fast = L.m->d_fpack ? k_interp2_fast<STATS, EPI, true, OUT> : k_interp2_fast<STATS, EPI, false, OUT>;
   Mesh2View v = view2(L.m);
   const bool use_fat = (EPI == 0 && L.m->d_fat);
   int tpb = L.m->opt.threads_per_block > 0 ? L.m->opt.threads_per_block : (use_fat ? 128 : 256);
@@ -581,8 +581,8 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   L.mark(0);
   if (use_fat) {
     const bool ring = L.m->opt.prefetch_ring >= 0, delta = fat_delta(L.m);
-    auto kf = ring ? (delta ? k_interp2_fat<STATS, true, true> : k_interp2_fat<STATS, true, false>)
-                   : (delta ? k_interp2_fat<STATS, false, true> : k_interp2_fat<STATS, false, false>);
+    auto kf = ring ? (delta ? k_interp2_fat<STATS, true, true, OUT> : k_interp2_fat<STATS, true, false, OUT>)
+                   : (delta ? k_interp2_fat<STATS, false, true, OUT> : k_interp2_fat<STATS, false, false, OUT>);
     kf<<<(unsigned)((warps + wpb - 1) / wpb), tpb, ring ? (size_t)wpb * kRingBytesPerWarp : 0, L.st>>>(
         v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   }
@@ -590,7 +590,7 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
     fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
         v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   L.mark(1);
-  k_interp2_full<STATS, EPI><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
+  k_interp2_full<STATS, EPI, OUT><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
                                                          L.qcount, L.qcap, n, L.stats);
   L.mark(2);
   L.launches += 2;
@@ -625,12 +625,13 @@ void launch_any(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so,
   }
 }
 
-// all pointers are device pointers; enqueues on `st`
+// all pointers are device pointers; enqueues on `st`.  out = 0: ys[n] values; out = 1: ys[n][2] gradients (2D)
 int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto,
-               cudaStream_t st, int *launches) {
+               cudaStream_t st, int *launches, int out = 0) {
   if (n == 0) return DLI_OK;
   if (m->ns == 0) {
-    k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, ys, so, sto);
+    k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out == 1 ? 2 * n : n, ys, nullptr, nullptr);
+    if (so || sto) k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, nullptr, so, sto);
     CU(cudaGetLastError());
     if (launches) *launches += 1;
     return DLI_OK;
@@ -648,10 +649,13 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     int64_t cn = std::min(kChunk, n - off);
     CU(cudaMemsetAsync(qcount, 0, sizeof(unsigned int), st));
     const double *cx = xs + off * d;
-    double *cy = ys ? ys + off : nullptr;
+    double *cy = ys ? ys + off * (out == 1 ? 2 : 1) : nullptr;
     int32_t *cs = so ? so + off : nullptr;
     uint8_t *ct = sto ? sto + off : nullptr;
-    if (m->collect_stats) {
+    if (out == 1) {
+      if (m->collect_stats) launch2<true, 0, 1>(L, cn, cx, cy, cs, ct);
+      else launch2<false, 0, 1>(L, cn, cx, cy, cs, ct);
+    } else if (m->collect_stats) {
       if (m->opt.epilogue != DLI_EPILOGUE_CLOSED_FORM) launch_any<true, 0>(L, cn, cx, cy, cs, ct);
       else launch_any<true, 1>(L, cn, cx, cy, cs, ct);
     } else {
@@ -676,7 +680,8 @@ bool is_device_ptr(const void *p, bool *known) {
 // staging buffers + straggler queues) lives in the mesh and is created once: a call costs no cudaMalloc /
 // cudaFree / stream creation.  H2D of chunk k+1, the kernels of chunk k and the D2H of chunk k-1 run on
 // different streams, so both copy engines stay busy (PCIe is the bound: 24 B per 2D query).
-int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, int *launches) {
+int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, int *launches,
+             int out = 0) {
   if (n == 0) return DLI_OK;
   const int d = m->dim;
   std::lock_guard<std::mutex> lk(m->pipe_mu);  // one host-path call at a time per mesh
@@ -687,7 +692,7 @@ int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t
       cudaError_t e = cudaStreamCreateWithFlags(&P.st[i], cudaStreamNonBlocking);
       if (e == cudaSuccess) e = cudaEventCreateWithFlags(&P.done[i], cudaEventDisableTiming);
       if (e == cudaSuccess) e = cudaMalloc(&P.x[i], sizeof(double) * (size_t)chunk * d);
-      if (e == cudaSuccess) e = cudaMalloc(&P.y[i], sizeof(double) * (size_t)chunk);
+      if (e == cudaSuccess) e = cudaMalloc(&P.y[i], sizeof(double) * (size_t)chunk * (d == 2 ? 2 : 1));  // 2D: room for gradients
       if (e == cudaSuccess) e = cudaMalloc(&P.s[i], sizeof(int32_t) * (size_t)chunk);
       if (e == cudaSuccess) e = cudaMalloc(&P.t[i], (size_t)chunk);
       if (e != cudaSuccess) {
@@ -705,9 +710,10 @@ int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t
     int64_t cn = std::min(chunk, n - off);
     cudaError_t e = cudaMemcpyAsync(P.x[i], xs + off * d, sizeof(double) * (size_t)cn * d, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) { rc = fail(DLI_ERR_CUDA, std::string("H2D copy failed: ") + cudaGetErrorString(e)); break; }
-    rc = run_device(m, cn, P.x[i], ys ? P.y[i] : nullptr, so ? P.s[i] : nullptr, sto ? P.t[i] : nullptr, st, launches);
+    rc = run_device(m, cn, P.x[i], ys ? P.y[i] : nullptr, so ? P.s[i] : nullptr, sto ? P.t[i] : nullptr, st, launches, out);
     if (rc != DLI_OK) break;
-    if (ys) e = cudaMemcpyAsync(ys + off, P.y[i], sizeof(double) * (size_t)cn, cudaMemcpyDeviceToHost, st);
+    const int yw = out == 1 ? 2 : 1;
+    if (ys) e = cudaMemcpyAsync(ys + off * yw, P.y[i], sizeof(double) * (size_t)cn * yw, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess && so) e = cudaMemcpyAsync(so + off, P.s[i], sizeof(int32_t) * (size_t)cn, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess && sto) e = cudaMemcpyAsync(sto + off, P.t[i], (size_t)cn, cudaMemcpyDeviceToHost, st);
     if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("D2H copy failed: ") + cudaGetErrorString(e));
@@ -720,7 +726,7 @@ int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t
 }
 
 int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, void *stream,
-                  const char *who) {
+                  const char *who, int out = 0) {
   if (!m) return fail(DLI_ERR_ARG, std::string(who) + ": NULL mesh");
   if (n < 0) return fail(DLI_ERR_ARG, std::string(who) + ": negative n");
   if (n == 0) return DLI_OK;
@@ -737,8 +743,8 @@ int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, in
     }
   int launches = 0;
   int rc;
-  if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches);
-  else rc = run_host(m, n, xs, ys, so, sto, &launches);
+  if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches, out);
+  else rc = run_host(m, n, xs, ys, so, sto, &launches, out);
   m->last.kernel_launches = launches;
   m->last.queries = n;
   return rc;
@@ -754,6 +760,13 @@ extern "C" int dli_interp(const dli_mesh *m, int64_t n, const double *xs, double
 extern "C" int dli_locate(const dli_mesh *m, int64_t n, const double *xs, int32_t *so, uint8_t *sto, void *stream) {
   if (n > 0 && !so) return fail(DLI_ERR_ARG, "dli_locate: simplex_out is NULL");
   return interp_common(m, n, xs, nullptr, so, sto, stream, "dli_locate");
+}
+
+extern "C" int dli_gradient(const dli_mesh *m, int64_t n, const double *xs, double *grads, int32_t *so, uint8_t *sto,
+                            void *stream) {
+  if (m && m->dim != 2) return fail(DLI_ERR_UNSUPPORTED, "dli_gradient: 2D meshes only (the reference's dD class has no gradient)");
+  if (n > 0 && !grads) return fail(DLI_ERR_ARG, "dli_gradient: grads is NULL");
+  return interp_common(m, n, xs, grads, so, sto, stream, "dli_gradient", 1);
 }
 
 extern "C" int dli_mesh_collect_stats(dli_mesh *m, int enable) {

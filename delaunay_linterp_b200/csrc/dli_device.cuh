@@ -289,6 +289,9 @@ __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px,
 
 // Full path: exact-sign walk over closed faces, outside-hull projection loop, status codes.
 // Returns the face in f with its vertices loaded; p is updated to the projected point.
+// PROJECT = false (gradient queries, src/delaunay_2_interp.h:618): leaving the hull ends the query with
+// DLI_STATUS_OUTSIDE_NAN instead of projecting.
+template <bool PROJECT = true>
 __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &py, int &f, double4 &A, double4 &B,
                                        double4 &C, StatsAcc &st) {
   uint8_t status = DLI_STATUS_OK;
@@ -323,6 +326,11 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
     }
     if (found) break;
     if (status == DLI_STATUS_OK) st.outside++;
+    if (!PROJECT) {
+      st.steps += steps;
+      if (steps > st.max_steps) st.max_steps = steps;
+      return DLI_STATUS_OUTSIDE_NAN;
+    }
     status = DLI_STATUS_OUTSIDE_PROJECTED;
     if (proj >= kMaxProjections) break;  // accept the hull face (ulp-level extrapolation)
     int h = canonical_visible_hull_edge(m, px, py, exit_h, st);
@@ -337,6 +345,100 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
   st.steps += steps;
   if (steps > st.max_steps) st.max_steps = steps;
   return status;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 2D gradient queries (Delaunay_incremental_interp_2::gradient, src/delaunay_2_interp.h:608-642)
+// ---------------------------------------------------------------------------------------------
+
+// Gradient of the linear interpolant on face (A, B, C): (V^-1)^T df with the columns of V = B - A, C - A and
+// df = (f_B - f_A, f_C - f_A) (simplex_gradient :242-263 via set_simplex_gradient :574-588), written out
+// through the adjugate.  Same operations, in the same order, as the gradient stored in the walk records
+// (k_build_fat2), so the fast pass and the exact pass return the same bits.
+__device__ __forceinline__ double2 face_gradient2(const double4 &A, const double4 &B, const double4 &C) {
+  const double Ax = B.x - A.x, Ay = B.y - A.y, Bx = C.x - A.x, By = C.y - A.y;
+  const double d1 = B.z - A.z, d2 = C.z - A.z;
+  const double dl = Ax * By, dr = Ay * Bx, det = dl - dr;
+  const double xl = d1 * By, xr = d2 * Ay, yl = Ax * d2, yr = Bx * d1;
+  return make_double2((xl - xr) / det, (yl - yr) / det);
+}
+__device__ inline double2 face_gradient2_of(const Mesh2View &m, int f) {
+  Face2 F = load_face(m, f);
+  return face_gradient2(load_vert(m, F.v0), load_vert(m, F.v1), load_vert(m, F.v2));
+}
+__device__ __forceinline__ int face_slot_of(const Face2 &F, int v) { return F.v0 == v ? 0 : (F.v1 == v ? 1 : 2); }
+__device__ __forceinline__ int face_nb(const Face2 &F, int j) { return j == 0 ? F.n0 : (j == 1 ? F.n1 : F.n2); }
+
+// Average of the gradients of the finite faces around vertex v, starting the circulation in face f0
+// (:619-632 + get_avg_simplex_gradient :594-606 + get_centroid :108-121: sequential sum, then / count).
+// CGAL's circulator starts at an arbitrary incident face, so the summation order is canonicalised: a closed
+// fan is summed counter-clockwise from its face with the smallest caller id, an open fan (hull vertex) from
+// its clockwise-most face (the convention is part of the ABI contract, include/dli.h).
+__device__ inline double2 vertex_avg_gradient2(const Mesh2View &m, int f0, int v) {
+  // clockwise sweep: find the start face
+  int start = f0, best_id = __ldg(m.orig + f0), f = f0;
+  bool open = false;
+  for (int it = 0; it < m.max_steps; it++) {
+    Face2 F = load_face(m, f);
+    int nb = face_nb(F, (face_slot_of(F, v) + 2) % 3);  // across the edge (v, next vertex): clockwise neighbour
+    if (nb < 0) { open = true; start = f; break; }
+    if (nb == f0) break;
+    f = nb;
+    int id = __ldg(m.orig + f);
+    if (id < best_id) { best_id = id; start = f; }
+  }
+  // counter-clockwise sum from `start`
+  double sx = 0.0, sy = 0.0;
+  int cnt = 0;
+  f = start;
+  for (int it = 0; it < m.max_steps; it++) {
+    double2 g = face_gradient2_of(m, f);
+    sx += g.x; sy += g.y; cnt++;
+    Face2 F = load_face(m, f);
+    int nb = face_nb(F, (face_slot_of(F, v) + 1) % 3);  // across the edge (v, previous vertex): counter-clockwise
+    if (nb < 0 || (!open && nb == start)) break;
+    f = nb;
+  }
+  return make_double2(sx / cnt, sy / cnt);
+}
+
+// One gradient query on the exact path.  Status: DLI_STATUS_OK (strictly inside a face), DLI_STATUS_ON_EDGE,
+// DLI_STATUS_ON_VERTEX, DLI_STATUS_OUTSIDE_NAN (no projection for gradients: NaN, :610-611), STEP_LIMIT.
+__device__ inline uint8_t gradient2_full(const Mesh2View &m, double px, double py, int &f, double2 &g, StatsAcc &st) {
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+  g = make_double2(nan, nan);
+  double4 A, B, C;
+  uint8_t status = locate2_full<false>(m, px, py, f, A, B, C, st);
+  if (status != DLI_STATUS_OK) return status;
+  Face2 F = load_face(m, f);
+  int zero[3], nz = 0;
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const double4 &X = (j == 0) ? B : (j == 1 ? C : A);
+    const double4 &Y = (j == 0) ? C : (j == 1 ? A : B);
+    int s = orient2d_filtered(X.x, X.y, Y.x, Y.y, px, py);
+    if (s == 2) { st.exact++; s = orient2d_exact(X.x, X.y, Y.x, Y.y, px, py); }
+    zero[j] = (s == 0);
+    nz += zero[j];
+  }
+  if (nz == 0) { g = face_gradient2(A, B, C); return DLI_STATUS_OK; }
+  if (nz == 1) {  // EDGE: this face and the one across the edge (:633-636); an infinite neighbour is skipped
+    int li = zero[0] ? 0 : (zero[1] ? 1 : 2);
+    double2 g1 = face_gradient2(A, B, C);
+    int nb = face_nb(F, li);
+    if (nb >= 0) {
+      double2 g2 = face_gradient2_of(m, nb);
+      g = make_double2((g1.x + g2.x) / 2, (g1.y + g2.y) / 2);
+    } else {
+      g = g1;
+    }
+    return DLI_STATUS_ON_EDGE;
+  }
+  // VERTEX: on two edges = the vertex opposite the third
+  int k = !zero[0] ? 0 : (!zero[1] ? 1 : 2);
+  int v = k == 0 ? F.v0 : (k == 1 ? F.v1 : F.v2);
+  g = vertex_avg_gradient2(m, f, v);
+  return DLI_STATUS_ON_VERTEX;
 }
 
 // ---------------------------------------------------------------------------------------------

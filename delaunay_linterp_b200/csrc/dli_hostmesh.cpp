@@ -583,6 +583,13 @@ int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t 
   if (rc != DLI_OK) return rc;
   return dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);
 }
+int dli_di2_gradient(dli_di2 *d, int64_t n, const double *xs, double *grads, int32_t *simplex_out, uint8_t *status_out,
+                     void *stream) {
+  if (!d) return DLI_ERR_ARG;
+  int rc = di2_refresh(d);
+  if (rc != DLI_OK) return rc;
+  return dli_gradient(d->mesh, n, xs, grads, simplex_out, status_out, stream);
+}
 const dli_mesh *dli_di2_device_mesh(dli_di2 *d) {
   if (!d) return nullptr;
   if (di2_refresh(d) != DLI_OK) return nullptr;

@@ -49,7 +49,9 @@ __device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAc
 // Predicates are filter-only here; queries it cannot certify (filter failure, hull exit, long walk)
 // are appended to `queue` for k_interp2_full.  If the queue overflows (`queue_cap`), the counter
 // keeps growing and k_interp2_full re-runs the whole batch (degenerate inputs only).
-template <bool STATS, int EPI, bool PACKED>
+// OUT = 0: ys[n] receives the interpolated value; OUT = 1 (dli_gradient): ys is a double2 array and receives the
+// gradient of the located face (strictly interior queries only; everything else goes to the exact pass).
+template <bool STATS, int EPI, bool PACKED, int OUT = 0>
 __global__ void __launch_bounds__(256, 4)
 k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
@@ -104,8 +106,12 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
         bool pos = ((d0 > e0) | c0) & ((d1 > e1) | c1) & ((d2 > e2) | c2);
         if (pos) {
           if (ys) {
-            double y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
-            __stcs(ys + qi, y);
+            if (OUT == 1) {
+              __stcs(reinterpret_cast<double2 *>(ys) + qi, face_gradient2(A, B, C));
+            } else {
+              double y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
+              __stcs(ys + qi, y);
+            }
           }
           if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
@@ -210,7 +216,7 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
 // Ring = 128 query slots (16 B) + 128 hint slots (4 B) per warp = 2.5 KB; slot = query index & 127.
 constexpr int kRingSlots = 128;
 constexpr int kRingBytesPerWarp = kRingSlots * (16 + 4);
-template <bool STATS, bool RING, bool DELTA>
+template <bool STATS, bool RING, bool DELTA, int OUT = 0>
 __global__ void __launch_bounds__(DLI_X_FAT_THREADS, DLI_X_FAT_BLOCKS)
 k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
@@ -335,6 +341,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
       const int n2 = DELTA ? (k2 >= kFatFar ? -2 : f + (int)k2 - kFatBias) : (k2 == kPackMask ? -2 : (int)k2);
       const bool c0 = n0 == from, c1 = n1 == from, c2 = n2 == from;
       const bool neg0 = (-o0 > e0) & !c0, neg1 = (-o1 > e1) & !c1, neg2 = (-o2 > e2) & !c2;
+      // (gradient queries honour the slow flag too: it also marks faces whose fp32 edge vectors are unusable)
       bool give_up = (nbr & kFatSlow) != 0;
       if (!give_up) {
         if (neg0 | neg1 | neg2) {
@@ -353,7 +360,8 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
               const double f0 = __hiloint2double((int)V[1], (int)V[0]);
               const double gx = __hiloint2double((int)V[3], (int)V[2]);
               const double gy = __hiloint2double((int)V[5], (int)V[4]);
-              __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
+              if (OUT == 1) __stcs(reinterpret_cast<double2 *>(ys) + qi, make_double2(gx, gy));
+              else __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
             }
             if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
             if (status_out) status_out[qi] = DLI_STATUS_OK;
@@ -377,7 +385,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
 
 // Straggler / exact pass over the queue written by the fast pass (count read on the device: no
 // host synchronisation between the two launches).
-template <bool STATS, int EPI>
+template <bool STATS, int EPI, int OUT = 0>
 __global__ void __launch_bounds__(128)
 k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
@@ -393,6 +401,14 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
     double2 q = xs[i];
     double px = q.x, py = q.y;
     int f = hint2(m, px, py);
+    if (OUT == 1) {
+      double2 g;
+      uint8_t status = gradient2_full(m, px, py, f, g, st);
+      if (ys) reinterpret_cast<double2 *>(ys)[i] = g;
+      if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN) ? -1 : __ldg(m.orig + f);
+      if (status_out) status_out[i] = status;
+      continue;
+    }
     double4 A, B, C;
     uint8_t status = locate2_full(m, px, py, f, A, B, C, st);
     double y;

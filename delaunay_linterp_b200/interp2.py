@@ -102,6 +102,28 @@ class DelaunayInterp2:
             return float(ys[0])
         return (ys, st) if return_status else ys
 
+    def gradient(self, x, return_status=False):
+        """gradient([x, y]) -> [gx, gy] (reference form, src/delaunay_2_python.cpp:231 / delaunay_2_interp.h:608-642)
+        or gradient(ndarray (n, 2) / torch CUDA tensor) -> (n, 2).  NaN outside the hull."""
+        if _is_torch_tensor(x):
+            import torch
+            xs = x.contiguous().view(-1, 2)
+            gs = torch.empty((xs.shape[0], 2), dtype=torch.float64, device=xs.device)
+            st = torch.empty(xs.shape[0], dtype=torch.uint8, device=xs.device) if return_status else None
+            check(lib().dli_di2_gradient(self._h, xs.shape[0], xs.data_ptr(), gs.data_ptr(), None,
+                                         st.data_ptr() if st is not None else None,
+                                         torch.cuda.current_stream(xs.device).cuda_stream))
+            return (gs, st) if return_status else gs
+        scalar = isinstance(x, (list, tuple)) and len(x) == 2 and not isinstance(x[0], (list, tuple, np.ndarray))
+        xs = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, 2)
+        n = xs.shape[0]
+        gs = np.empty((n, 2), np.float64)
+        st = np.empty(n, np.uint8)
+        check(lib().dli_di2_gradient(self._h, n, xs.ctypes.data, gs.ctypes.data, None, st.ctypes.data, None))
+        if scalar:
+            return [float(gs[0, 0]), float(gs[0, 1])]
+        return (gs, st) if return_status else gs
+
     # ---- introspection / plot data
     def get_all_vertices(self):
         n = lib().dli_di2_get_all_vertices(self._h, None)

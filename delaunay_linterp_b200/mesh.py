@@ -140,6 +140,33 @@ class Mesh:
                                status.ctypes.data if status is not None else None, None))
         return (simplex, status) if return_status else simplex
 
+    def gradient(self, xs, return_simplex=False, return_status=False, stream=None):
+        """Batched gradient(xs) -> (n, 2) (2D meshes; src/delaunay_2_interp.h:608-642).  NaN outside the hull."""
+        if self.dim != 2:
+            raise ValueError("gradient: 2D meshes only (the reference's dD class has no gradient)")
+        if _is_torch_tensor(xs):
+            import torch
+            if not xs.is_cuda or xs.dtype != torch.float64:
+                raise ValueError("torch input must be a float64 CUDA tensor")
+            xs = xs.contiguous().view(-1, 2)
+            n = xs.shape[0]
+            gs = torch.empty((n, 2), dtype=torch.float64, device=xs.device)
+            simplex = torch.empty(n, dtype=torch.int32, device=xs.device) if return_simplex else None
+            status = torch.empty(n, dtype=torch.uint8, device=xs.device) if return_status else None
+            st = stream if stream is not None else torch.cuda.current_stream(xs.device).cuda_stream
+            ptr = lambda t: t.data_ptr() if t is not None else None
+            check(lib().dli_gradient(self._h, n, xs.data_ptr(), gs.data_ptr(), ptr(simplex), ptr(status), st))
+        else:
+            xs = np.ascontiguousarray(xs, dtype=np.float64).reshape(-1, 2)
+            n = xs.shape[0]
+            gs = np.empty((n, 2), np.float64)
+            simplex = np.empty(n, np.int32) if return_simplex else None
+            status = np.empty(n, np.uint8) if return_status else None
+            ptr = lambda a: a.ctypes.data if a is not None else None
+            check(lib().dli_gradient(self._h, n, xs.ctypes.data, gs.ctypes.data, ptr(simplex), ptr(status), None))
+        res = tuple(t for t in (gs, simplex, status) if t is not None)
+        return res[0] if len(res) == 1 else res
+
     def _interp_torch(self, xs, return_simplex, return_status, out, stream, values):
         import torch
         if not xs.is_cuda or xs.dtype != torch.float64:

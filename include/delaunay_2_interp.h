@@ -120,6 +120,19 @@ class Delaunay_incremental_interp_2 {
     check(dli_di2_interp(h_, (int64_t)n, xs, ys, nullptr, status, cuda_stream), "interp_batch");
   }
 
+  // gradient of the interpolant at x (:608-642): the face's gradient; the mean of the incident faces on an edge or
+  // a vertex; quiet NaN outside the hull
+  std::array<double, 2> gradient(Point const &x) const {
+    double xs[2] = {x.x(), x.y()};
+    std::array<double, 2> g;
+    check(dli_di2_gradient(h_, 1, xs, g.data(), nullptr, nullptr, nullptr), "gradient");
+    return g;
+  }
+  // batched gradient (new): xs [n][2] -> grads [n][2]; host or device pointers
+  void gradient_batch(const double *xs, size_t n, double *grads, unsigned char *status = nullptr, void *cuda_stream = nullptr) const {
+    check(dli_di2_gradient(h_, (int64_t)n, xs, grads, nullptr, status, cuda_stream), "gradient_batch");
+  }
+
   std::vector<ErrorTuple> get_error_queue() const {
     int64_t n = dli_di2_error_queue_size(h_);
     std::vector<double> e((size_t)n), f((size_t)n), xy((size_t)n * 2);

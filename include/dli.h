@@ -50,6 +50,10 @@ extern "C" {
                                           The 2D header wrapper turns this into std::invalid_argument
                                           (src/delaunay_2_interp.h:546-551) */
 #define DLI_STATUS_NO_MESH 4           /* mesh has no simplex (fewer than dim+1 affinely independent points) */
+#define DLI_STATUS_ON_EDGE 5           /* dli_gradient only: query exactly on an edge (CGAL Locate_type EDGE): average of
+                                          the two incident faces (src/delaunay_2_interp.h:633-636) */
+#define DLI_STATUS_ON_VERTEX 6         /* dli_gradient only: query exactly on a vertex (Locate_type VERTEX): average over
+                                          the incident finite faces (src/delaunay_2_interp.h:619-632) */
 
 #define DLI_EPILOGUE_AUTO 0
 #define DLI_EPILOGUE_CLOSED_FORM 1
@@ -134,6 +138,23 @@ int dli_interp(const dli_mesh *mesh, int64_t n, const double *xs, double *ys, in
    2D queries outside the hull report the hull face behind the canonical visible hull edge. */
 int dli_locate(const dli_mesh *mesh, int64_t n, const double *xs, int32_t *simplex_out, uint8_t *status_out,
                void *stream);
+
+/*
+ * Batched gradient of the piecewise-linear interpolant (2D only, as in the reference).  Replaces, for n queries,
+ *   Delaunay_incremental_interp_2::gradient              (src/delaunay_2_interp.h:608-642)
+ * with the per-face gradients of set_simplex_gradient / simplex_gradient (:574-588, :242-263).
+ *   strictly inside a face  -> that face's gradient                                   status DLI_STATUS_OK
+ *   exactly on an edge      -> mean of the two incident faces (a hull edge: the one)  status DLI_STATUS_ON_EDGE
+ *   exactly on a vertex     -> mean over the incident finite faces                    status DLI_STATUS_ON_VERTEX
+ *   outside the hull        -> (NaN, NaN), simplex -1; gradients are NOT projected    status DLI_STATUS_OUTSIDE_NAN
+ * EDGE / VERTEX are decided by the exact orientation predicate.  The vertex mean is summed counter-clockwise
+ * starting from the incident face with the smallest id (a hull vertex: from the clockwise-most face); CGAL's
+ * circulator starts at an arbitrary incident face, so the reference's own sum order is not reproducible.
+ * xs    [n][2]  host or device
+ * grads [n][2]  same memory space as xs
+ */
+int dli_gradient(const dli_mesh *mesh, int64_t n, const double *xs, double *grads, int32_t *simplex_out,
+                 uint8_t *status_out, void *stream);
 
 /*
  * Batched per-simplex error evaluator.  Replaces compute_simplex_error + add_error_of_boundary_subsimplices

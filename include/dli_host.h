@@ -14,6 +14,7 @@
  *   insert_largest_error_point     :498-504   -> dli_di2_insert_largest_error_point
  *   get_largest_error_tuple        :506-508   -> dli_di2_get_largest_error_tuple
  *   interp / interp_point          :510-572   -> dli_di2_interp (batched, on the GPU)
+ *   gradient                       :608-642   -> dli_di2_gradient (batched, on the GPU)
  *   get_error_queue                :743-746   -> dli_di2_get_error_queue
  *   get_all_vertices               :806-840   -> dli_di2_get_all_vertices
  *   get_line_segments              :842-862   -> dli_di2_get_line_segments
@@ -66,6 +67,9 @@ int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, in
    With dimension < 2 every query reports DLI_STATUS_NO_MESH (the reference throws, :546-551). */
 int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
                    void *stream);
+/* batched gradient on the GPU (dli_gradient): grads [n][2]; NaN outside the hull (:610-611, :618) */
+int dli_di2_gradient(dli_di2 *d, int64_t n, const double *xs, double *grads, int32_t *simplex_out, uint8_t *status_out,
+                     void *stream);
 /* the device mesh currently backing dli_di2_interp (NULL before the first interp); owned by d */
 const dli_mesh *dli_di2_device_mesh(dli_di2 *d);
 int dli_di2_set_options(dli_di2 *d, const dli_options *opt);

@@ -22,6 +22,7 @@
  *   dD volume / bary     src/delaunay_d_interp.h:601-624, 628-650
  *   dD locate semantics  modified_cgal/Delaunay_d.h:811-850, 793-808 (closed simplices, null outside)
  *   error metric         src/delaunay_2_interp.h:725-741, 166-192, 125-151, 108-121
+ *   2D gradient          src/delaunay_2_interp.h:608-642, 574-606, 242-263  -> dlo_gradient
  *   boundary subsimplex  src/delaunay_2_interp.h:657-699, 331-342
  * Third-party behaviour restated from its published algorithm (not in the tree):
  *   CGAL Triangulation_2::locate: exact-sign visibility walk, closed faces
@@ -683,6 +684,106 @@ int dlo_interp(const dlo_mesh *m, int64_t n, const double *xs, double *ys, int32
   int64_t s = 0;
   for (int t = 0; t < 256; t++) s += c.steps[t];
   if (total_steps) *total_steps = s;
+  return 0;
+}
+
+/* ------------------------------------------------------------------------- */
+/* 2D gradient (src/delaunay_2_interp.h:608-642)                              */
+/* ------------------------------------------------------------------------- */
+#define DLO_ON_EDGE 5
+#define DLO_ON_VERTEX 6
+
+/* simplex_gradient (:242-263) as called by set_simplex_gradient (:574-588): V(j,i) = P[i+1][j] - P[0][j],
+ * df(i) = f[i+1] - f[0], gradient = transpose(inverse(V)) * df.  CGAL's Linear_algebraCd<double>::inverse is
+ * not in the tree; restated through the adjugate: inverse(V) = adj(V) / det(V). */
+static void face_gradient(const dlo_mesh *m, int32_t s, double *g) {
+  const int32_t *v = m->sv + (size_t)s * 3;
+  const double *A = m->x + (size_t)v[0] * 2, *B = m->x + (size_t)v[1] * 2, *C = m->x + (size_t)v[2] * 2;
+  double fa = m->f[v[0]], fb = m->f[v[1]], fc = m->f[v[2]];
+  double a = B[0] - A[0], c = B[1] - A[1], b = C[0] - A[0], d = C[1] - A[1]; /* V = [[a, b], [c, d]] */
+  double df0 = fb - fa, df1 = fc - fa;
+  double det = a * d - c * b;
+  g[0] = (df0 * d - df1 * c) / det;
+  g[1] = (a * df1 - b * df0) / det;
+}
+static int slot_of(const dlo_mesh *m, int32_t s, int32_t v) {
+  const int32_t *sv = m->sv + (size_t)s * 3;
+  return sv[0] == v ? 0 : (sv[1] == v ? 1 : 2);
+}
+/* VERTEX case (:619-632): get_avg_simplex_gradient (:594-606) over the incident finite faces = get_centroid
+ * (:108-121): sequential sum from 0, then / count.  CGAL's circulator starts at vertex->face(), which is
+ * arbitrary; canonical order used here (and by the CUDA path): counter-clockwise, a closed fan starting from
+ * its lowest-numbered face, an open fan (hull vertex) from its clockwise-most face. */
+static void vertex_avg_gradient(const dlo_mesh *m, int32_t f0, int32_t v, double *g) {
+  int32_t start = f0, best = f0, f = f0;
+  int open = 0;
+  for (int64_t it = 0; it < m->ns + 16; it++) {
+    int32_t nb = m->sn[(size_t)f * 3 + (slot_of(m, f, v) + 2) % 3]; /* clockwise neighbour */
+    if (nb < 0) { open = 1; start = f; break; }
+    if (nb == f0) break;
+    f = nb;
+    if (f < best) { best = f; start = f; }
+  }
+  double sx = 0.0, sy = 0.0;
+  int cnt = 0;
+  f = start;
+  for (int64_t it = 0; it < m->ns + 16; it++) {
+    double gf[2];
+    face_gradient(m, f, gf);
+    sx += gf[0]; sy += gf[1]; cnt++;
+    int32_t nb = m->sn[(size_t)f * 3 + (slot_of(m, f, v) + 1) % 3]; /* counter-clockwise neighbour */
+    if (nb < 0 || (!open && nb == start)) break;
+    f = nb;
+  }
+  g[0] = sx / cnt; g[1] = sy / cnt;
+}
+static void gradient_one(const dlo_mesh *m, const double *x, int32_t start, double *g, int32_t *simplex_out,
+                         uint8_t *status_out, int64_t *steps) {
+  g[0] = g[1] = NAN;
+  if (m->ns <= 0) { *simplex_out = -1; *status_out = DLO_NO_MESH; return; }
+  int slot;
+  int32_t s = walk(m, x, start, &slot, steps, m->ns + 16);
+  if (slot == -2) { *simplex_out = s; *status_out = DLO_STEP_LIMIT; return; }
+  if (slot != -1) { *simplex_out = -1; *status_out = DLO_OUTSIDE_NAN; return; } /* :618: not found -> NaN */
+  const int32_t *v = m->sv + (size_t)s * 3;
+  int zero[3], nz = 0;
+  const double *pp[3];
+  for (int j = 0; j < 3; j++) {
+    for (int i = 0; i < 3; i++) pp[i] = (i == j) ? x : m->x + (size_t)v[i] * 2;
+    zero[j] = (orient_sign(2, pp) == 0);
+    nz += zero[j];
+  }
+  *simplex_out = s;
+  if (nz == 0) { face_gradient(m, s, g); *status_out = DLO_OK; return; }
+  if (nz == 1) { /* EDGE (:633-636) */
+    int li = zero[0] ? 0 : (zero[1] ? 1 : 2);
+    double g1[2], g2[2];
+    face_gradient(m, s, g1);
+    int32_t nb = m->sn[(size_t)s * 3 + li];
+    if (nb >= 0) {
+      face_gradient(m, nb, g2);
+      g[0] = (g1[0] + g2[0]) / 2; g[1] = (g1[1] + g2[1]) / 2;
+    } else { g[0] = g1[0]; g[1] = g1[1]; }
+    *status_out = DLO_ON_EDGE;
+    return;
+  }
+  int k = !zero[0] ? 0 : (!zero[1] ? 1 : 2);
+  vertex_avg_gradient(m, s, v[k], g);
+  *status_out = DLO_ON_VERTEX;
+}
+/* serial; mode as dlo_interp */
+int dlo_gradient(const dlo_mesh *m, int64_t n, const double *xs, double *gs, int32_t *simplex_out,
+                 uint8_t *status_out, int mode) {
+  if (m->dim != 2) return -1;
+  int32_t last = m->start;
+  int64_t steps = 0;
+  for (int64_t i = 0; i < n; i++) {
+    int32_t so; uint8_t st;
+    gradient_one(m, xs + 2 * (size_t)i, mode == 1 ? last : m->start, gs + 2 * (size_t)i, &so, &st, &steps);
+    if (simplex_out) simplex_out[i] = so;
+    if (status_out) status_out[i] = st;
+    if (so >= 0) last = so;
+  }
   return 0;
 }
 

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "_ref", "libdli_oracle.so")
 
-OK, OUTSIDE_PROJECTED, OUTSIDE_NAN, STEP_LIMIT, NO_MESH = 0, 1, 2, 3, 4
+OK, OUTSIDE_PROJECTED, OUTSIDE_NAN, STEP_LIMIT, NO_MESH, ON_EDGE, ON_VERTEX = 0, 1, 2, 3, 4, 5, 6
 
 
 def build(force=False):
@@ -40,6 +40,7 @@ def lib():
         L.dlo_mesh_start.argtypes = [C.c_void_p]
         L.dlo_mesh_get_simplices.argtypes = [C.c_void_p, ip, ip]
         L.dlo_interp.argtypes = [C.c_void_p, C.c_int64, dp, dp, ip, bp, C.c_int, C.c_int, C.POINTER(C.c_int64)]
+        L.dlo_gradient.argtypes = [C.c_void_p, C.c_int64, dp, dp, ip, bp, C.c_int]
         L.dlo_classify.argtypes = [C.c_void_p, C.c_int64, dp, ip, bp, bp]
         L.dlo_orient_exact.argtypes = [C.c_int, dp]
         L.dlo_orient_filtered.argtypes = [C.c_int, dp]
@@ -114,6 +115,18 @@ class OracleMesh:
         if return_steps:
             return ys, simplex, status, steps.value
         return ys, simplex, status
+
+    def gradient(self, xs, mode=1):
+        """2D gradient queries (src/delaunay_2_interp.h:608-642): (grads (n, 2), simplex, status)."""
+        xs = np.ascontiguousarray(xs, dtype=np.float64).reshape(-1, 2)
+        n = xs.shape[0]
+        gs = np.empty((n, 2), np.float64)
+        simplex = np.empty(n, np.int32)
+        status = np.empty(n, np.uint8)
+        rc = lib().dlo_gradient(self._h, n, _dp(xs), _dp(gs), _ip(simplex), _bp(status), mode)
+        if rc != 0:
+            raise ValueError("oracle gradient: 2D meshes only")
+        return gs, simplex, status
 
     def classify(self, xs, simplex):
         """(contains, strictly_inside) of each query w.r.t. the given simplex ids; exact."""

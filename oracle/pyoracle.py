@@ -61,3 +61,24 @@ def interp_exact(coords, f, simplices, p):
     b = barycentric([coords[v] for v in sv], p)
     val = sum(bi * Fr(float(f[v])) for bi, v in zip(b, sv))
     return val, hits
+
+
+def face_gradient_exact(coords, f, sv):
+    """exact gradient of the linear interpolant on one triangle (src/delaunay_2_interp.h:242-263)."""
+    (x0, y0), (x1, y1), (x2, y2) = [[Fr(float(c)) for c in coords[v]] for v in sv]
+    f0, f1, f2 = [Fr(float(f[v])) for v in sv]
+    a, b, c, d = x1 - x0, x2 - x0, y1 - y0, y2 - y0
+    dt = a * d - b * c
+    return ((f1 - f0) * d - (f2 - f0) * c) / dt, (a * (f2 - f0) - b * (f1 - f0)) / dt
+
+
+def gradient_exact(coords, f, simplices, p):
+    """Reference semantics of gradient() (src/delaunay_2_interp.h:608-642) in exact arithmetic: the mean of the
+    gradients of every finite face whose closed hull contains p (1 face inside, 2 on an interior edge, the whole
+    fan on a vertex); (None, []) outside the hull."""
+    hits = locate_all(coords, simplices, p)
+    if not hits:
+        return None, []
+    gs = [face_gradient_exact(coords, f, simplices[s]) for s in hits]
+    n = len(gs)
+    return (sum(g[0] for g in gs) / n, sum(g[1] for g in gs) / n), hits

@@ -82,6 +82,21 @@ static int run(double lo, const char *want_regular, const char *want_adaptive, b
   if (want_adaptive) CHECK(strcmp(b2, want_adaptive) == 0);
   // outside the hull: projected, not an error (:530-545)
   CHECK(std::fabs(triang.interp_point(Point(-1.0, 2.5)) - triang.interp_point(Point(lo, 2.5))) < 1e-14);
+  // gradient (:608-642): the face's gradient = slope of interp inside the face; batch == scalar; NaN outside
+  {
+    array<double, 2> g = triang.gradient(Point(1.3, 2.1));
+    double q[2] = {1.3, 2.1}, gb[2];
+    unsigned char gst;
+    triang.gradient_batch(q, 1, gb, &gst);
+    CHECK(g[0] == gb[0] && g[1] == gb[1] && gst == DLI_STATUS_OK);
+    const double h = 1e-3, y0 = triang.interp_point(Point(1.3, 2.1));
+    CHECK(std::fabs((triang.interp_point(Point(1.3 + h, 2.1)) - y0) / h - g[0]) < 1e-9);
+    CHECK(std::fabs((triang.interp_point(Point(1.3, 2.1 + h)) - y0) / h - g[1]) < 1e-9);
+    CHECK(std::isnan(triang.gradient(Point(-1.0, 2.5))[0]));
+    double vq[2] = {grid[3], grid[4]};   // a grid vertex: mean over its fan
+    triang.gradient_batch(vq, 1, gb, &gst);
+    CHECK(gst == DLI_STATUS_ON_VERTEX && std::isfinite(gb[0]) && std::isfinite(gb[1]));
+  }
   // no triangulation yet: std::invalid_argument (:546-551)
   Delaunay_incremental_interp_2 empty;
   bool threw = false;

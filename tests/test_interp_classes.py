@@ -92,3 +92,25 @@ def test_dd_class_on_gpu(gpu):
     t.rebuild_error_queue()                                            # GPU batch == per-insert host tuples
     after = sorted(e[0] for e in t.get_error_queue())
     assert len(before) == len(after) and np.allclose(before, after, rtol=1e-8, atol=1e-18)
+
+
+@pytest.mark.gpu
+def test_interp2_class_gradient_on_gpu(gpu):
+    """DelaunayInterp2.gradient (src/delaunay_2_python.cpp:231 -> src/delaunay_2_interp.h:608-642)."""
+    import delaunay_linterp_b200 as dl
+    fn = lambda x: 1.0 + 2.0 * x[0] - 0.5 * x[1]
+    a = dl.DelaunayInterp2(fn)
+    pts = np.random.default_rng(8).random((500, 2))
+    for p in pts.tolist() + [[0.0, 0.0], [0.0, 1.0], [1.0, 0.0], [1.0, 1.0]]:
+        a.insert(p, fn(p))
+    g = a.gradient([0.4, 0.6])
+    assert isinstance(g, list) and len(g) == 2 and abs(g[0] - 2.0) < 1e-9 and abs(g[1] + 0.5) < 1e-9
+    assert all(math.isnan(v) for v in a.gradient([2.0, 2.0]))            # outside the hull: NaN, not projected
+    gs, st = a.gradient(np.vstack([pts[:10], [[0.5, 0.5]]]), return_status=True)
+    assert (st[:10] == dl.STATUS_ON_VERTEX).all() and np.abs(gs - [2.0, -0.5]).max() < 1e-8
+    # parity with the oracle on the exported triangulation
+    c, f, t, nb = a.export()
+    q = np.random.default_rng(9).random((20000, 2)) * 1.2 - 0.1
+    gq, sq = a.gradient(q, return_status=True)
+    go, _, so = OracleMesh(c, f, t, nb).gradient(q)
+    assert np.array_equal(sq, so) and np.array_equal(gq[so != 2], go[so != 2])
