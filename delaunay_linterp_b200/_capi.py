@@ -83,6 +83,8 @@ SYMBOLS = [
     ("dli_mesh_buffer_write", C.c_int, [_vp, C.c_int, _vp]),
     ("dli_mesh_get_grid_params", C.c_int, [_vp, _vp]),
     ("dli_mesh_set_grid_params", C.c_int, [_vp, _vp]),
+    ("dli_mesh_save", C.c_int, [_vp, C.c_char_p]),
+    ("dli_mesh_load", C.c_int, [C.c_char_p, C.POINTER(Options), C.POINTER(_vp)]),
     ("dli_mesh_collect_stats", C.c_int, [_vp, C.c_int]),
     ("dli_mesh_get_stats", C.c_int, [_vp, C.POINTER(Stats)]),
     ("dli_debug_orient", C.c_int, [C.c_int, C.c_int64, _vp, _vp, _vp]),

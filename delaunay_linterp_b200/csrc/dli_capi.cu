@@ -1020,6 +1020,76 @@ extern "C" int dli_mesh_set_grid_params(dli_mesh *m, const double *in) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// mesh snapshot: one flat file = magic, header words, grid parameters, then every device buffer
+// (length-prefixed).  The same bytes the replication path broadcasts; a loaded mesh is a replica
+// (no host copy of the connectivity: dli_mesh_get_simplices / the error evaluator are unavailable).
+// ---------------------------------------------------------------------------------------------
+static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '1'};
+
+extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
+  if (!m || !path) return fail(DLI_ERR_ARG, "dli_mesh_save: NULL argument");
+  FILE *fp = fopen(path, "wb");
+  if (!fp) return fail(DLI_ERR_ARG, std::string("dli_mesh_save: cannot open ") + path);
+  int64_t h[DLI_MESH_HEADER_WORDS];
+  double gp[3 * DLI_MAX_DIM];
+  dli_mesh_header(m, h);
+  h[14] = m->n_slow_faces;
+  dli_mesh_get_grid_params(m, gp);
+  bool ok = fwrite(kSnapMagic, 1, 8, fp) == 8 && fwrite(h, sizeof(int64_t), DLI_MESH_HEADER_WORDS, fp) == DLI_MESH_HEADER_WORDS &&
+            fwrite(gp, sizeof(double), 3 * DLI_MAX_DIM, fp) == 3 * DLI_MAX_DIM;
+  std::vector<char> host;
+  int rc = DLI_OK;
+  for (int i = 0; ok && rc == DLI_OK && i < dli_mesh_num_buffers(m); i++) {
+    void *p; int64_t b;
+    rc = dli_mesh_buffer(m, i, &p, &b);
+    if (rc != DLI_OK) break;
+    ok = fwrite(&b, sizeof b, 1, fp) == 1;
+    if (!ok || b == 0) continue;
+    host.resize((size_t)b);
+    rc = dli_mesh_buffer_read(m, i, host.data());
+    if (rc == DLI_OK) ok = fwrite(host.data(), 1, (size_t)b, fp) == (size_t)b;
+  }
+  if (fclose(fp) != 0) ok = false;
+  if (rc != DLI_OK) return rc;
+  if (!ok) return fail(DLI_ERR_ARG, std::string("dli_mesh_save: write failed: ") + path);
+  return DLI_OK;
+}
+
+extern "C" int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh **out) {
+  if (!path || !out) return fail(DLI_ERR_ARG, "dli_mesh_load: NULL argument");
+  *out = nullptr;
+  FILE *fp = fopen(path, "rb");
+  if (!fp) return fail(DLI_ERR_ARG, std::string("dli_mesh_load: cannot open ") + path);
+  char magic[8];
+  int64_t h[DLI_MESH_HEADER_WORDS];
+  double gp[3 * DLI_MAX_DIM];
+  bool ok = fread(magic, 1, 8, fp) == 8 && memcmp(magic, kSnapMagic, 8) == 0 &&
+            fread(h, sizeof(int64_t), DLI_MESH_HEADER_WORDS, fp) == DLI_MESH_HEADER_WORDS &&
+            fread(gp, sizeof(double), 3 * DLI_MAX_DIM, fp) == 3 * DLI_MAX_DIM;
+  if (!ok) { fclose(fp); return fail(DLI_ERR_ARG, std::string("dli_mesh_load: not a mesh snapshot: ") + path); }
+  dli_mesh *m = nullptr;
+  int rc = dli_mesh_create_from_header(h, opt, &m);
+  if (rc != DLI_OK) { fclose(fp); return rc; }
+  dli_mesh_set_grid_params(m, gp);
+  m->n_slow_faces = h[14];
+  std::vector<char> host;
+  for (int i = 0; rc == DLI_OK && i < dli_mesh_num_buffers(m); i++) {
+    void *p; int64_t b, want;
+    rc = dli_mesh_buffer(m, i, &p, &want);
+    if (rc != DLI_OK) break;
+    if (fread(&b, sizeof b, 1, fp) != 1 || b != want) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: truncated or inconsistent snapshot"); break; }
+    if (b == 0) continue;
+    host.resize((size_t)b);
+    if (fread(host.data(), 1, (size_t)b, fp) != (size_t)b) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: truncated snapshot"); break; }
+    rc = dli_mesh_buffer_write(m, i, host.data());
+  }
+  fclose(fp);
+  if (rc != DLI_OK) { mesh_free(m); return rc; }
+  *out = m;
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // predicate test hook
 // ---------------------------------------------------------------------------------------------
 extern "C" int dli_debug_orient(int dim, int64_t n, const double *pts, int8_t *sign_out, uint8_t *exact_used) {

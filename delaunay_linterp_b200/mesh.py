@@ -239,6 +239,18 @@ class Mesh:
         check(lib().dli_mesh_set_grid_params(handle, gp.ctypes.data))
         return cls._from_handle(handle, int(header[1]))
 
+    # ---- snapshot (flat file: header, grid parameters, device buffers)
+    def save(self, path):
+        check(lib().dli_mesh_save(self._h, str(path).encode()))
+
+    @classmethod
+    def load(cls, path, **options):
+        """a replica of a saved mesh: interp / locate / gradient only (no host connectivity)."""
+        handle = C.c_void_p()
+        opt = _make_options(**options)
+        check(lib().dli_mesh_load(str(path).encode(), C.byref(opt), C.byref(handle)))
+        return cls._from_handle(handle, lib().dli_mesh_dim(handle))
+
     def buffers(self):
         """[(device_ptr, nbytes)] of the mesh's device buffers."""
         out = []

@@ -193,6 +193,15 @@ int dli_mesh_buffer_write(dli_mesh *mesh, int index, const void *src);
 int dli_mesh_get_grid_params(const dli_mesh *mesh, double *out /* [3 * DLI_MAX_DIM] */);
 int dli_mesh_set_grid_params(dli_mesh *mesh, const double *in /* [3 * DLI_MAX_DIM] */);
 
+/*
+ * Mesh snapshot (no counterpart in the reference, which has no serialisation): the flattened device mesh as one
+ * flat file -- magic "DLIMESH1", the 16 header words, the grid parameters, then every device buffer
+ * length-prefixed -- so that a large triangulation is built and flattened once.  A loaded mesh is a replica:
+ * interp / locate / gradient work, dli_mesh_get_simplices and the error evaluator need the creating process.
+ */
+int dli_mesh_save(const dli_mesh *mesh, const char *path);
+int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh **out);
+
 /* instrumentation: counters of the most recent interp/locate on this mesh that had `collect_stats` enabled */
 typedef struct dli_stats {
   int64_t queries;

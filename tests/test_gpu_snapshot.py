@@ -1,0 +1,48 @@
+"""GPU: mesh snapshot (dli_mesh_save / dli_mesh_load) -- a loaded replica answers bit-identically."""
+import numpy as np
+import pytest
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dim,opts", [(2, {}), (2, {"epilogue": "reference"}), (2, {"packed_faces": 2}), (3, {}), (4, {})])
+def test_save_load_roundtrip(gpu, tmp_path, dim, opts):
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(dim, 3000 if dim < 4 else 600, 40 + dim)
+    m = dl.Mesh(pts, f, sv, sn, **opts)
+    path = tmp_path / "mesh.dli"
+    m.save(path)
+    r = dl.Mesh.load(path, **opts)
+    assert r.dim == dim and r.n_simplices == m.n_simplices and r.n_vertices == m.n_vertices
+    q = np.random.default_rng(7).random((50000, dim)) * 1.1 - 0.05
+    y0, s0, t0 = m.interp(q, return_simplex=True, return_status=True)
+    y1, s1, t1 = r.interp(q, return_simplex=True, return_status=True)
+    assert np.array_equal(t0, t1) and np.array_equal(s0, s1)
+    assert np.array_equal(y0[np.isfinite(y0)], y1[np.isfinite(y0)]) and np.array_equal(np.isnan(y0), np.isnan(y1))
+    if dim == 2:
+        g0, g1 = m.gradient(q), r.gradient(q)
+        assert np.array_equal(np.isnan(g0), np.isnan(g1)) and np.array_equal(g0[np.isfinite(g0)], g1[np.isfinite(g1)])
+    assert r.stats()["slow_simplices"] == m.stats()["slow_simplices"]
+    with pytest.raises(dl.DliError):
+        r.simplices()          # replicas carry no host connectivity
+
+
+def test_load_rejects_garbage(gpu, tmp_path):
+    import delaunay_linterp_b200 as dl
+    p = tmp_path / "bad.dli"
+    p.write_bytes(b"not a mesh snapshot at all" * 10)
+    with pytest.raises(dl.DliError):
+        dl.Mesh.load(p)
+    with pytest.raises(dl.DliError):
+        dl.Mesh.load(tmp_path / "missing.dli")
+    # truncated file
+    pts, f, sv, sn = helpers.random_mesh(2, 500, 3)
+    m = dl.Mesh(pts, f, sv, sn)
+    good = tmp_path / "good.dli"
+    m.save(good)
+    data = good.read_bytes()
+    (tmp_path / "trunc.dli").write_bytes(data[: len(data) // 2])
+    with pytest.raises(dl.DliError):
+        dl.Mesh.load(tmp_path / "trunc.dli")
