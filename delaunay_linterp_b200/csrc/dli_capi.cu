@@ -256,7 +256,7 @@ int build_hint_grid(dli_mesh *m, const double *coords) {
       if (x > hi[k]) hi[k] = x;
     }
   float cps = m->opt.hint_cells_per_simplex;
-  if (!(cps > 0.f)) cps = (d == 2) ? 2.0f : 1.0f;
+  if (!(cps > 0.f)) cps = (d == 2) ? 2.0f : (d == 3 ? 4.0f : 8.0f);  // measured optima
   double target = std::max(1.0, (double)m->ns * cps);
   int g = (int)std::ceil(std::pow(target, 1.0 / d));
   g = std::max(1, std::min(g, d == 2 ? 16384 : (d == 3 ? 1024 : 128)));
