@@ -8,6 +8,8 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_scan.cuh>
+
 #include "dli_kernels.cuh"
 
 using namespace dli;
@@ -83,6 +85,11 @@ struct dli_mesh {
   ulonglong2 *d_fpack = nullptr;  // 2D packed face records (fast pass), NULL when ids do not fit 21 bits
   uint4 *d_fat = nullptr;         // 2D 64-byte walk records (k_interp2_fat), NULL when unused
   int64_t n_slow_faces = 0;       // faces carrying the slow flag in d_fat
+  // cell-indexed walk records (2D meshes far larger than L2): d_fat has nslots = cells + extra records
+  bool cellmode = false;
+  int64_t nslots = 0;             // records in d_fat (== ns unless cellmode)
+  int32_t *d_slot_face = nullptr; // [nslots] slot -> face
+  int *d_rowstart = nullptr;      // [gy + 1] first slot of every hint-grid row
   GridView grid{};
   int max_steps = 0, fast_steps = 0;
   // error items (lazy)
@@ -103,6 +110,9 @@ struct dli_mesh {
   mutable HostPipe pipe;
 };
 
+// 2D meshes with at least this many faces (512 MB of walk records, 4 x L2) use cell-indexed walk records
+constexpr int64_t kCellModeFaces = 8ll << 20;
+
 // bytes per walk record (2D: 64, 3D: 128, 4D: 192)
 static int fat_record_bytes(int dim) { return dim == 2 ? 64 : (dim == 3 ? FatD<3>::BYTES : FatD<4>::BYTES); }
 
@@ -116,6 +126,8 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_orig);
   cudaFree(m->d_fpack);
   cudaFree(m->d_fat);
+  cudaFree(m->d_slot_face);
+  cudaFree(m->d_rowstart);
   cudaFree(m->d_item_verts);
   cudaFree(m->d_stats);
   pipe_free(m->pipe);
@@ -320,8 +332,12 @@ static int mesh_alloc_common(dli_mesh *m) {
   if (d == 2) CU(cudaMalloc(&m->d_hull, sizeof(int4) * (size_t)std::max<int32_t>(m->nh, 1)));
   if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
     CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
-  if (m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0)
-    CU(cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(d) * (size_t)m->ns));
+  m->nslots = m->ns;
+  if (m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0) {
+    // 2D meshes whose records are far larger than L2 get cell-indexed records (allocated once the hint grid exists)
+    m->cellmode = d == 2 && (m->opt.packed_faces == 3 || (m->opt.packed_faces == 0 && m->ns >= kCellModeFaces));
+    if (!m->cellmode) CU(cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(d) * (size_t)m->ns));
+  }
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
   // keep stream-ordered allocations cached between calls
@@ -336,8 +352,81 @@ static int mesh_alloc_common(dli_mesh *m) {
 // walk records of meshes with >= 2^21-2 faces (or opt.packed_faces == 2: testing) use delta-encoded neighbours
 static bool fat_delta(const dli_mesh *m) { return m->ns >= (1 << 21) - 2 || m->opt.packed_faces == 2; }
 
+static SlotGrid slot_grid(const dli_mesh *m) {
+  SlotGrid g;
+  g.ox = m->grid.o[0]; g.oy = m->grid.o[1]; g.icx = m->grid.ic[0]; g.icy = m->grid.ic[1];
+  g.gx = m->grid.g[0]; g.gy = m->grid.g[1];
+  return g;
+}
+// Lays out the cell-indexed record array (creating rank): row starts, slot -> face table, record buffer.
+static int build_slots(dli_mesh *m) {
+  const int64_t cells = m->grid.cells;
+  const int gx = m->grid.g[0], gy = m->grid.g[1];
+  const SlotGrid g = slot_grid(m);
+  const int4 *frec = reinterpret_cast<const int4 *>(m->d_srec);
+  const double4 *vrec = reinterpret_cast<const double4 *>(m->d_vrec);
+  const unsigned fb = (unsigned)((m->ns + 255) / 256), cb = (unsigned)((cells + 255) / 256);
+  int *d_owner = nullptr, *d_rowcount = nullptr;
+  std::vector<int> rowcount((size_t)gy), rowstart((size_t)gy + 1);
+  cudaError_t e = cudaMalloc(&d_owner, sizeof(int) * (size_t)m->ns);
+  if (e == cudaSuccess) e = cudaMalloc(&d_rowcount, sizeof(int) * (size_t)gy);
+  if (e == cudaSuccess) e = cudaMemset(d_owner, 0x7f, sizeof(int) * (size_t)m->ns);
+  if (e == cudaSuccess) e = cudaMemset(d_rowcount, 0, sizeof(int) * (size_t)gy);
+  if (e == cudaSuccess) {
+    k_slot_owner<<<cb, 256>>>(cells, m->d_hint, d_owner);
+    k_slot_rowcount<<<fb, 256>>>((int)m->ns, g, d_owner, frec, vrec, d_rowcount);
+    e = cudaMemcpy(rowcount.data(), d_rowcount, sizeof(int) * (size_t)gy, cudaMemcpyDeviceToHost);
+  }
+  int64_t acc = 0;
+  for (int j = 0; j < gy; j++) { rowstart[(size_t)j] = (int)acc; acc += gx + rowcount[(size_t)j]; }
+  rowstart[(size_t)gy] = (int)acc;
+  if (e == cudaSuccess && acc >= 0x7fffff00ll) e = cudaErrorInvalidValue;
+  m->nslots = acc;
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_rowstart, sizeof(int) * ((size_t)gy + 1));
+  if (e == cudaSuccess) e = cudaMemcpy(m->d_rowstart, rowstart.data(), sizeof(int) * ((size_t)gy + 1), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)m->nslots);
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_fat, 64 * (size_t)m->nslots);
+  if (e == cudaSuccess) e = cudaMemset(d_rowcount, 0, sizeof(int) * (size_t)gy);   // reused as the per-row cursor
+  if (e == cudaSuccess) {
+    k_slot_fill_cells<<<cb, 256>>>(cells, gx, m->d_hint, m->d_rowstart, m->d_slot_face);
+    k_slot_fill_extra<<<fb, 256>>>((int)m->ns, g, d_owner, frec, vrec, m->d_rowstart, d_rowcount, m->d_slot_face);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  cudaFree(d_owner); cudaFree(d_rowcount);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("cell-indexed record layout failed: ") + cudaGetErrorString(e));
+  return DLI_OK;
+}
+
 // (re)builds the 64-byte walk records from the canonical records (values and geometry)
 static int build_fat_records(dli_mesh *m) {
+  if (m->cellmode) {
+    if (!m->d_fat) {            // first build on the creating rank: lay the slots out, allocate
+      int rc = build_slots(m);
+      if (rc != DLI_OK) return rc;
+    }
+    // face -> lowest slot holding a copy of it (build-time table, ns ints)
+    int *d_canon = nullptr;
+    CU(cudaMalloc(&d_canon, sizeof(int) * (size_t)m->ns));
+    cudaError_t e = cudaMemset(d_canon, 0x7f, sizeof(int) * (size_t)m->ns);
+    unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
+    if (e == cudaSuccess) e = cudaMemset(d_cnt, 0, sizeof(unsigned int));
+    unsigned int cnt = 0;
+    if (e == cudaSuccess) {
+      const unsigned sb = (unsigned)((m->nslots + 255) / 256);
+      k_slot_canon<<<sb, 256>>>(m->nslots, m->d_slot_face, d_canon);
+      k_build_fat2_slots<<<sb, 256>>>(m->nslots, slot_grid(m), m->d_hint, m->d_rowstart, m->d_slot_face, d_canon,
+                                      reinterpret_cast<const int4 *>(m->d_srec), reinterpret_cast<const double4 *>(m->d_vrec),
+                                      m->d_fat, d_cnt);
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemset(d_cnt, 0, sizeof(unsigned int));
+    cudaFree(d_canon);
+    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("cell-indexed record build failed: ") + cudaGetErrorString(e));
+    m->n_slow_faces = cnt;
+    return DLI_OK;
+  }
   if (!m->d_fat) return DLI_OK;
   unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
   CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
@@ -503,7 +592,8 @@ extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
                    sizeof(int32_t) * m->grid.cells + sizeof(int32_t) * m->ns + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
-                   (m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->ns : 0));
+                   (m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->nslots : 0) +
+                   (m->cellmode ? (int64_t)sizeof(int32_t) * (m->nslots + m->grid.g[1] + 1) : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
@@ -527,6 +617,8 @@ Mesh2View view2(const dli_mesh *m) {
   v.hull = m->d_hull;
   v.hint = m->d_hint;
   v.orig = m->d_orig;
+  v.slot_face = m->d_slot_face;
+  v.rowstart = m->d_rowstart;
   v.ox = m->grid.o[0]; v.oy = m->grid.o[1];
   v.icx = m->grid.ic[0]; v.icy = m->grid.ic[1];
   v.gx = m->grid.g[0]; v.gy = m->grid.g[1];
@@ -583,7 +675,9 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
     const bool ring = L.m->opt.prefetch_ring >= 0, delta = fat_delta(L.m);
     auto kf = ring ? (delta ? k_interp2_fat<STATS, true, true, OUT> : k_interp2_fat<STATS, true, false, OUT>)
                    : (delta ? k_interp2_fat<STATS, false, true, OUT> : k_interp2_fat<STATS, false, false, OUT>);
-    kf<<<(unsigned)((warps + wpb - 1) / wpb), tpb, ring ? (size_t)wpb * kRingBytesPerWarp : 0, L.st>>>(
+    // cell-indexed records: no hint to prefetch, and the query prefetch alone does not pay
+    if (L.m->cellmode) kf = k_interp2_fat<STATS, false, true, OUT, true>;
+    kf<<<(unsigned)((warps + wpb - 1) / wpb), tpb, (ring && !L.m->cellmode) ? (size_t)wpb * kRingBytesPerWarp : 0, L.st>>>(
         v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   }
   else
@@ -604,9 +698,15 @@ void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   int64_t warps = (n + per_warp - 1) / per_warp;
   int wpb = tpb / 32;
   L.mark(0);
-  if (EPI == 0 && L.m->d_fat)
-    k_interpD_fat<D, STATS><<<(unsigned)((warps + wpb - 1) / wpb), tpb, (size_t)wpb * FatD<D>::SMEM_PER_WARP, L.st>>>(
-        v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  if (EPI == 0 && L.m->d_fat) {
+    const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
+    if (L.m->opt.prefetch_ring >= 0)
+      k_interpD_fat<D, STATS, true><<<grid, tpb, (size_t)wpb * (FatD<D>::SMEM_PER_WARP + RingD<D>::BYTES), L.st>>>(
+          v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+    else
+      k_interpD_fat<D, STATS, false><<<grid, tpb, (size_t)wpb * FatD<D>::SMEM_PER_WARP, L.st>>>(
+          v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+  }
   else
     k_interpD_fast<D, STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(v, n, per_warp, xs, ys, so, sto, L.queue,
                                                                                         L.qcount, L.qcap, L.stats);
@@ -922,7 +1022,8 @@ extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORD
   h[0] = DLI_VERSION; h[1] = m->dim; h[2] = m->nv; h[3] = m->ns; h[4] = m->nh; h[5] = m->grid.cells;
   for (int k = 0; k < 4; k++) h[6 + k] = m->grid.g[k];
   h[10] = m->max_steps; h[11] = m->fast_steps;
-  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? 1 : 0;  // optional buffers the replica must mirror
+  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : 1) : 0;  // optional buffers the replica must mirror
+  h[15] = m->nslots;
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
   // (see dli_mesh_buffer): index 0 = 96-byte parameter block.
@@ -951,11 +1052,17 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   int rc = mesh_alloc_common(m);
   // mirror the source's optional buffers exactly (every rank must see the same buffer list)
   if (rc == DLI_OK && !h[12] && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
-  if (rc == DLI_OK && !h[13] && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
+  if (rc == DLI_OK && h[13] != 1 && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
+  m->cellmode = h[13] == 2;
+  m->nslots = h[13] == 2 ? h[15] : m->ns;
+  if (rc == DLI_OK && m->cellmode &&
+      (cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess ||
+       cudaMalloc(&m->d_rowstart, sizeof(int) * ((size_t)m->grid.g[1] + 1)) != cudaSuccess))
+    rc = fail(DLI_ERR_CUDA, "slot table allocation failed");
   if (rc == DLI_OK && h[12] && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "packed face allocation failed");
   if (rc == DLI_OK && h[13] && !m->d_fat &&
-      cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m->dim) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
+      cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m->dim) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "walk record allocation failed");
   m->max_steps = (int)h[10];
   m->fast_steps = (int)h[11];
@@ -966,7 +1073,7 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   return DLI_OK;
 }
 
-extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 7 : 0; }
+extern "C" int dli_mesh_num_buffers(const dli_mesh *m) { return m ? 9 : 0; }
 
 // buffers 0..5: vertex records, simplex records, hull table, hint grid, packed 2D face records (may be empty),
 // 64-byte 2D walk records (may be empty), device-order -> caller simplex ids
@@ -978,8 +1085,10 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
-    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->ns : 0; break;
+    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->nslots : 0; break;
     case 6: *ptr = m->d_orig; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1); break;
+    case 7: *ptr = m->d_slot_face; *bytes = m->cellmode ? (int64_t)sizeof(int32_t) * m->nslots : 0; break;
+    case 8: *ptr = m->d_rowstart; *bytes = m->cellmode ? (int64_t)sizeof(int) * (m->grid.g[1] + 1) : 0; break;
     default: return fail(DLI_ERR_ARG, "dli_mesh_buffer: bad index");
   }
   return DLI_OK;

@@ -34,6 +34,10 @@ struct Mesh2View {
   const int4 *hull;
   const int32_t *hint;
   const int32_t *orig;  // device simplex index (Morton order of centroids) -> the caller's simplex id
+  // cell-indexed walk records (optional, big meshes): `fat` is laid out by hint-grid rows, the start slot of a query
+  // in cell (i, j) is rowstart[j] + i (a copy of the record of face hint[j * gx + i]); slot_face maps slots to faces
+  const int32_t *slot_face;
+  const int *rowstart;
   double ox, oy, icx, icy;  // hint grid origin and 1/cell size
   int gx, gy;
   int ns, nh;
@@ -167,6 +171,15 @@ __device__ __forceinline__ int hint2(const Mesh2View &m, double x, double y) {
   i = max(0, min(m.gx - 1, i));
   j = max(0, min(m.gy - 1, j));
   return __ldg(m.hint + (size_t)j * m.gx + i);
+}
+
+// hint-grid cell index of a point (the start slot of cell-indexed walk records)
+__device__ __forceinline__ int cell2(const Mesh2View &m, double x, double y) {
+  int i = (int)((x - m.ox) * m.icx);
+  int j = (int)((y - m.oy) * m.icy);
+  i = max(0, min(m.gx - 1, i));
+  j = max(0, min(m.gy - 1, j));
+  return __ldg(m.rowstart + j) + i;
 }
 
 struct Face2 {

@@ -141,13 +141,10 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
 // gradient-form interpolant over the face exceeds 1e-13 * min|f_i| (slivers, faces on which f changes
 // sign or vanishes at a vertex): those faces are evaluated by k_interp2_full in the reference's own
 // operation order.
-template <bool DELTA>
-__global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
-                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
-  int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= ns) return;
-  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
-  double4 V0 = vrec[r0.x], V1 = vrec[r0.y], V2 = vrec[r0.z];
+// numeric core shared by the two record builders: writes the 64-byte record of the face (V0, V1, V2) with the packed
+// neighbour word `nbr` (slow flag added here) to `o`; returns the slow flag
+__device__ __forceinline__ bool make_fat2(const double4 &V0, const double4 &V1, const double4 &V2, unsigned long long nbr,
+                                          uint4 *__restrict__ o) {
   const double Ax = V1.x - V0.x, Ay = V1.y - V0.y, Bx = V2.x - V0.x, By = V2.y - V0.y;
   const float ax = (float)Ax, ay = (float)Ay, bx = (float)Bx, by = (float)By;
   const double u = 5.9604644775390625e-08;  // 2^-24
@@ -176,6 +173,25 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
   if (!same_sign) mn = 0.0;
   if (!all_zero) slow |= !(E <= 1e-13 * mn);   // (NaN compares false -> slow)
   else slow |= !(gx == 0.0 && gy == 0.0);
+  if (slow) nbr |= kFatSlow;
+  uint4 h0, h1, h2, h3;
+  h0.x = (unsigned)__double2loint(V0.x); h0.y = (unsigned)__double2hiint(V0.x);
+  h0.z = (unsigned)__double2loint(V0.y); h0.w = (unsigned)__double2hiint(V0.y);
+  h1.x = __float_as_uint(ax); h1.y = __float_as_uint(ay); h1.z = __float_as_uint(bx); h1.w = __float_as_uint(by);
+  h2.x = (unsigned)__double2loint(V0.z); h2.y = (unsigned)__double2hiint(V0.z);
+  h2.z = (unsigned)__double2loint(gx); h2.w = (unsigned)__double2hiint(gx);
+  h3.x = (unsigned)__double2loint(gy); h3.y = (unsigned)__double2hiint(gy);
+  h3.z = (unsigned)(nbr & 0xffffffffull); h3.w = (unsigned)(nbr >> 32);
+  o[0] = h0; o[1] = h1; o[2] = h2; o[3] = h3;
+  return slow;
+}
+
+template <bool DELTA>
+__global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
+                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns) return;
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
   // neighbour field (21 bits): kPackMask = hull; ABS: the neighbour's index; DELTA (meshes with >= 2^21-2 faces):
   // index difference + kFatBias, kFatFar when it does not fit (the kernel then reads the canonical face record;
   // rare because faces are stored in Morton order)
@@ -185,18 +201,94 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
     long long dlt = (long long)nb - f + kFatBias;
     return (dlt < 0 || dlt >= (long long)kFatFar) ? (unsigned long long)kFatFar : (unsigned long long)dlt;
   };
-  unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42) | (slow ? kFatSlow : 0ull);
-  if (slow) atomicAdd(n_slow, 1u);
-  uint4 h0, h1, h2, h3;
-  h0.x = (unsigned)__double2loint(V0.x); h0.y = (unsigned)__double2hiint(V0.x);
-  h0.z = (unsigned)__double2loint(V0.y); h0.w = (unsigned)__double2hiint(V0.y);
-  h1.x = __float_as_uint(ax); h1.y = __float_as_uint(ay); h1.z = __float_as_uint(bx); h1.w = __float_as_uint(by);
-  h2.x = (unsigned)__double2loint(V0.z); h2.y = (unsigned)__double2hiint(V0.z);
-  h2.z = (unsigned)__double2loint(gx); h2.w = (unsigned)__double2hiint(gx);
-  h3.x = (unsigned)__double2loint(gy); h3.y = (unsigned)__double2hiint(gy);
-  h3.z = (unsigned)(nbr & 0xffffffffull); h3.w = (unsigned)(nbr >> 32);
-  uint4 *o = fat + 4 * (size_t)f;
-  o[0] = h0; o[1] = h1; o[2] = h2; o[3] = h3;
+  unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42);
+  if (make_fat2(vrec[r0.x], vrec[r0.y], vrec[r0.z], nbr, fat + 4 * (size_t)f)) atomicAdd(n_slow, 1u);
+}
+
+// ---- cell-indexed walk records ("implicit hint" layout for meshes far larger than L2) ----
+// The record array is laid out by hint-grid rows: row j owns the slots rowstart[j] .. rowstart[j+1]-1 = gx cell
+// slots (slot rowstart[j] + i is a copy of the record of the face the hint grid assigns to cell (i, j)) followed by
+// the records of the faces that own no cell and whose centroid lies in row j.  A query therefore starts at
+// slot = rowstart[cj] + ci without reading a hint, and every neighbour of a record lives at most about one row
+// away, so its slot delta fits the 21-bit DELTA field.  Neighbour fields point to a copy of the neighbour face in
+// the 3 x 3 cell neighbourhood if there is one, else to the neighbour's canonical (lowest) slot.
+constexpr int kNoSlot = 0x7f7f7f7f;  // canon[] initial value (memset 0x7f): no slot yet
+struct SlotGrid {
+  double ox, oy, icx, icy;
+  int gx, gy;
+};
+__device__ __forceinline__ int face_row(const SlotGrid &g, const int4 *__restrict__ frec, const double4 *__restrict__ vrec, int f,
+                                        int *col = nullptr) {
+  int4 r0 = frec[2 * (size_t)f];
+  double4 A = vrec[r0.x], B = vrec[r0.y], C = vrec[r0.z];
+  int j = (int)(((A.y + B.y + C.y) / 3.0 - g.oy) * g.icy);
+  if (col) { int i = (int)(((A.x + B.x + C.x) / 3.0 - g.ox) * g.icx); *col = max(0, min(g.gx - 1, i)); }
+  return max(0, min(g.gy - 1, j));
+}
+// owner[f] = lowest cell whose hint is f (kNoSlot: the face owns no cell)
+__global__ void k_slot_owner(int64_t cells, const int32_t *__restrict__ hint, int *__restrict__ owner) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < cells) atomicMin(owner + hint[c], (int)c);
+}
+__global__ void k_slot_rowcount(int ns, SlotGrid g, const int *__restrict__ owner, const int4 *__restrict__ frec,
+                                const double4 *__restrict__ vrec, int *__restrict__ rowcount) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f < ns && owner[f] == kNoSlot) atomicAdd(rowcount + face_row(g, frec, vrec, f), 1);
+}
+// slot -> face table: cell slots from the hint grid, extra slots handed out per row
+__global__ void k_slot_fill_cells(int64_t cells, int gx, const int32_t *__restrict__ hint, const int *__restrict__ rowstart,
+                                  int32_t *__restrict__ slot_face) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < cells) slot_face[rowstart[c / gx] + (int)(c % gx)] = hint[c];
+}
+__global__ void k_slot_fill_extra(int ns, SlotGrid g, const int *__restrict__ owner, const int4 *__restrict__ frec,
+                                  const double4 *__restrict__ vrec, const int *__restrict__ rowstart, int *__restrict__ cursor,
+                                  int32_t *__restrict__ slot_face) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns || owner[f] != kNoSlot) return;
+  int j = face_row(g, frec, vrec, f);
+  slot_face[rowstart[j] + g.gx + atomicAdd(cursor + j, 1)] = f;
+}
+// canon[f] = lowest slot holding a copy of face f
+__global__ void k_slot_canon(int64_t nslots, const int32_t *__restrict__ slot_face, int *__restrict__ canon) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nslots) atomicMin(canon + slot_face[s], (int)s);
+}
+__global__ void k_build_fat2_slots(int64_t nslots, SlotGrid g, const int32_t *__restrict__ hint, const int *__restrict__ rowstart,
+                                   const int32_t *__restrict__ slot_face, const int *__restrict__ canon,
+                                   const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
+                                   uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nslots) return;
+  const int f = slot_face[s];
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
+  // row of this slot: the last j with rowstart[j] <= s
+  int lo = 0, hi = g.gy - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (rowstart[mid] <= s) lo = mid; else hi = mid - 1;
+  }
+  int cj = lo, ci = (int)(s - rowstart[cj]);
+  if (ci >= g.gx) face_row(g, frec, vrec, f, &ci);   // an extra slot: search around the face's centroid cell
+  auto enc = [&](int nb) -> unsigned long long {
+    if (nb < 0) return (unsigned long long)kPackMask;
+    long long target = canon[nb];
+    long long best = -1;
+    for (int dj = -1; dj <= 1; dj++)
+      for (int di = -1; di <= 1; di++) {
+        int i = ci + di, j = cj + dj;
+        if (i < 0 || j < 0 || i >= g.gx || j >= g.gy) continue;
+        if (hint[(size_t)j * g.gx + i] != nb) continue;
+        long long c = (long long)rowstart[j] + i;
+        if (best < 0 || llabs(c - s) < llabs(best - s)) best = c;
+      }
+    if (best >= 0) target = best;
+    long long dlt = target - s + kFatBias;
+    return (dlt < 0 || dlt >= (long long)kFatFar) ? (unsigned long long)kFatFar : (unsigned long long)dlt;
+  };
+  unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42);
+  bool slow = make_fat2(vrec[r0.x], vrec[r0.y], vrec[r0.z], nbr, fat + 4 * (size_t)s);
+  if (slow && s == canon[f]) atomicAdd(n_slow, 1u);   // count faces, not copies
 }
 
 // Fast pass on the walk records.  Same warp-persistent lane state machine as k_interp2_fast (one walk step
@@ -216,7 +308,9 @@ __global__ void k_build_fat2(int ns, const int4 *__restrict__ frec, const double
 // Ring = 128 query slots (16 B) + 128 hint slots (4 B) per warp = 2.5 KB; slot = query index & 127.
 constexpr int kRingSlots = 128;
 constexpr int kRingBytesPerWarp = kRingSlots * (16 + 4);
-template <bool STATS, bool RING, bool DELTA, int OUT = 0>
+// CELL = true: cell-indexed records (k_build_fat2_slots): the start slot IS the query's hint cell, no hint is read
+// (the ring issues an L2 prefetch of the start record instead); a far neighbour hands the query to the exact pass.
+template <bool STATS, bool RING, bool DELTA, int OUT = 0, bool CELL = false>
 __global__ void __launch_bounds__(DLI_X_FAT_THREADS, DLI_X_FAT_BLOCKS)
 k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
@@ -250,7 +344,10 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
                    : "memory");
   };
   auto issue_h = [&](int64_t j) {  // start hint of query j (already in the ring) -> ring (hint grid: L2 evict_last)
-    if (j < end) {
+    // (CELL: the start slot is computed from the query at refill time, nothing to fetch.  Prefetching the start
+    // record into L2 here was measured and is harmful on DRAM-resident meshes: 4.2 -> 7.0 ms on cfg5, the
+    // prefetched lines are evicted before use and fetched twice)
+    if (!CELL && j < end) {
       double2 q = ringq[j & (kRingSlots - 1)];
       int ci = (int)((q.x - m.ox) * m.icx), cj = (int)((q.y - m.oy) * m.icy);
       ci = max(0, min(m.gx - 1, ci));
@@ -286,11 +383,11 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
         if (RING) {
           double2 q = ringq[idx & (kRingSlots - 1)];
           px = q.x; py = q.y;
-          f = ringh[idx & (kRingSlots - 1)];
+          f = CELL ? cell2(m, px, py) : ringh[idx & (kRingSlots - 1)];
         } else {
           double2 q = __ldcs(xs + idx);
           px = q.x; py = q.y;
-          f = hint2(m, px, py);
+          f = CELL ? cell2(m, px, py) : hint2(m, px, py);
         }
         qi = idx;
         from = -1;
@@ -349,7 +446,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
           if (DELTA) {
             const unsigned kc = neg0 ? k0 : (neg1 ? k1 : k2);
             if (kc == kFatFar)  // neighbour too far away in index space for the 21-bit field: canonical record
-              nb = __ldg(reinterpret_cast<const int *>(m.frec) + 8 * (size_t)f + 3 + (neg0 ? 0 : (neg1 ? 1 : 2)));
+              nb = CELL ? -1 : __ldg(reinterpret_cast<const int *>(m.frec) + 8 * (size_t)f + 3 + (neg0 ? 0 : (neg1 ? 1 : 2)));
           }
           if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
           else { from = f; f = nb; }
@@ -363,7 +460,10 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
               if (OUT == 1) __stcs(reinterpret_cast<double2 *>(ys) + qi, make_double2(gx, gy));
               else __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
             }
-            if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
+            if (simplex_out) {
+              const int face = CELL ? __ldg(m.slot_face + f) : f;
+              __stcs(simplex_out + qi, __ldg(m.orig + face));
+            }
             if (status_out) status_out[qi] = DLI_STATUS_OK;
             if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
             active = false;
@@ -761,7 +861,17 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
 // of this step into shared memory with coalesced cp.async (FatD<D>::LPR lanes x 16 B per record, one or two
 // 128-byte lines per record instead of D+2 scattered gathers), then every lane reads its own record with LDS.128.
 // A step is D dot products against the fp32 barycentric gradients with the bound kFatKD * max|G_i| * |d|_1.
-template <int D, bool STATS>
+// RING = true: per-warp prefetch ring for queries and start hints, as in k_interp2_fat, but fed through registers
+// (the record staging owns the cp.async groups, which retire in order): at every block-of-32 transition a lane
+// stores the query / hint it loaded one transition ago into the ring and issues the loads for the next block, so a
+// refill is D+1 LDS and the only dependent global latency of an iteration is the record itself.
+// Ring per warp: 3 blocks of queries (block b, b+1 complete, b+2 just stored) + 2 blocks of hints.
+template <int D>
+struct RingD {
+  static constexpr int QBYTES = 96 * D * 8, HBYTES = 64 * 4;
+  static constexpr int BYTES = QBYTES + HBYTES;
+};
+template <int D, bool STATS, bool RING = false>
 __global__ void __launch_bounds__(128)
 k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
@@ -787,15 +897,70 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
   int64_t qi = 0;
   unsigned int steps = 0;
   StatsAcc st;
+  // ---- prefetch ring (RING only)
+  double *ringq = nullptr;
+  int *ringh = nullptr;
+  double hq[D];      // query (blk + 2) * 32 + lane, in flight since the previous transition
+  int hh = 0;        // hint of query (blk + 1) * 32 + lane, in flight since the previous transition
+  int blk = 0, b3 = 0;  // block of 32 that `next` is in; blk % 3
+#pragma unroll
+  for (int k = 0; k < D; k++) hq[k] = 0.0;
+  auto load_q = [&](int b, double *q) {   // query b * 32 + lane of this warp's range (zeros past the end)
+    const int64_t j = base + (int64_t)b * 32 + lane;
+#pragma unroll
+    for (int k = 0; k < D; k++) q[k] = j < end ? __ldcs(xs + j * D + k) : 0.0;
+  };
+  auto store_q = [&](int bm3, const double *q) {
+#pragma unroll
+    for (int k = 0; k < D; k++) ringq[(bm3 * 32 + lane) * D + k] = q[k];
+  };
+  if (RING) {
+    const int nw = blockDim.x >> 5, wib = threadIdx.x >> 5;
+    unsigned char *rb = stage_smem + (size_t)nw * F::SMEM_PER_WARP + (size_t)wib * RingD<D>::BYTES;
+    ringq = reinterpret_cast<double *>(rb);
+    ringh = reinterpret_cast<int *>(rb + RingD<D>::QBYTES);
+    // state "just entered block 0": queries of blocks 0..2 and hints of blocks 0, 1 in the ring; the hint of
+    // block 2 and the queries of block 3 in flight
+    double q0[D], q1[D];
+    load_q(0, q0); load_q(1, q1); load_q(2, hq);
+    store_q(0, q0); store_q(1, q1); store_q(2, hq);
+    ringh[lane] = hintD<D>(m, q0);
+    ringh[32 + lane] = hintD<D>(m, q1);
+    hh = hintD<D>(m, hq);
+    load_q(3, hq);
+    __syncwarp();
+  }
   for (;;) {
+    if (RING) {
+      const int nb = (int)((next - base) >> 5);
+      if (nb != blk) {  // warp-uniform: `next` entered block nb = blk + 1 (a refill consumes at most 32 queries)
+        blk = nb;
+        b3 = b3 == 2 ? 0 : b3 + 1;
+        // (all ring reads of block blk - 1 were consumed by the previous iterations' arithmetic)
+        ringh[((blk + 1) & 1) * 32 + lane] = hh;                 // hints of block blk + 1
+        store_q(b3 == 0 ? 2 : b3 - 1, hq);                       // queries of block blk + 2  ((blk + 2) % 3 == (b3 + 2) % 3)
+        hh = hintD<D>(m, hq);                                    // hint of block blk + 2: in flight until the next transition
+        load_q(blk + 3, hq);                                     // queries of block blk + 3: likewise
+        __syncwarp();
+      }
+    }
     unsigned need = __ballot_sync(FULL, !active);
     if (need) {
       int64_t idx = next + __popc(need & ((1u << lane) - 1u));
       if (!active && idx < end) {
+        if (RING) {
+          const int lb = (int)((idx - base) >> 5);               // blk or blk + 1
+          const int m3 = lb == blk ? b3 : (b3 == 2 ? 0 : b3 + 1);
+          const int sl = (int)((idx - base) & 31);
 #pragma unroll
-        for (int k = 0; k < D; k++) p[k] = __ldcs(xs + idx * D + k);
+          for (int k = 0; k < D; k++) p[k] = ringq[(m3 * 32 + sl) * D + k];
+          s = ringh[(lb & 1) * 32 + sl];
+        } else {
+#pragma unroll
+          for (int k = 0; k < D; k++) p[k] = __ldcs(xs + idx * D + k);
+          s = hintD<D>(m, p);
+        }
         qi = idx;
-        s = hintD<D>(m, p);
         from = -1;
         steps = 0;
         active = true;

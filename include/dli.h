@@ -78,7 +78,9 @@ typedef struct dli_options {
   int32_t queries_per_warp;       /* 2D fast pass: contiguous queries owned by one warp; <= 0 = default (1024) */
   int32_t packed_faces;           /* 2D: 0 = compact fast-pass records (16-byte packed faces / 64-byte walk records; default),
                                      -1 = never, 2 = walk records with delta-encoded neighbours even on small meshes
-                                     (the encoding large meshes get; for tests) */
+                                     (the encoding large meshes get; for tests), 3 = cell-indexed walk records even on
+                                     small meshes (the layout meshes with >= 8M faces get: a query's start record is
+                                     addressed by its hint cell, no hint read; for tests) */
   int32_t prefetch_ring;          /* 2D walk-record fast pass: 0 = per-warp cp.async prefetch ring for queries and start
                                      hints (default), -1 = plain loads */
   int32_t reserved[6];

@@ -13,7 +13,9 @@ ap.add_argument("--nq", type=int, default=125000000)
 ap.add_argument("--mode", default="sweep")
 ap.add_argument("--cps", default="2,0.5,1,4")
 ap.add_argument("--tiles", default="8,16,32,64,256")
+ap.add_argument("--opts", default="{}")
 a = ap.parse_args()
+OPTS = json.loads(a.opts)
 
 pts = np.random.default_rng(1005).random((a.nv, 2))
 t0 = time.time(); t = dl.DelaunayInterp2(); t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False)
@@ -32,16 +34,16 @@ def timeit(m, x, reps=3):
     return min(ts)
 
 if a.mode == "ncu":
-    m = dl.Mesh(c, f, tri, nb)
+    m = dl.Mesh(c, f, tri, nb, **OPTS)
     for _ in range(5): m.interp(xq, out=ys)
     torch.cuda.synchronize()
     sys.exit(0)
 
 for cps in [float(v) for v in a.cps.split(",")]:
-    t0 = time.time(); m = dl.Mesh(c, f, tri, nb, hint_cells_per_simplex=cps); tf = time.time() - t0
+    t0 = time.time(); m = dl.Mesh(c, f, tri, nb, hint_cells_per_simplex=cps, **OPTS); tf = time.time() - t0
     m.collect_stats(True); m.interp(xq[:4000000], out=ys[:4000000]); st = m.stats(); m.collect_stats(False)
     ms = timeit(m, xq)
-    print(json.dumps(dict(cps=cps, order="random", ms=round(ms, 3), gqps=round(a.nq / ms / 1e6, 2), steps=round(st["walk_steps"] / st["queries"], 3),
+    print(json.dumps(dict(opts=OPTS, stragglers=st["straggler_queries"], cps=cps, order="random", ms=round(ms, 3), gqps=round(a.nq / ms / 1e6, 2), steps=round(st["walk_steps"] / st["queries"], 3),
                           mesh_MB=round(m.device_bytes / 1e6), flatten_s=round(tf, 2))), flush=True)
     if cps == 2.0:
         for B in [int(v) for v in a.tiles.split(",")]:

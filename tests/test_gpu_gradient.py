@@ -8,7 +8,8 @@ from oracle.oracle import OracleMesh, OK, ON_EDGE, ON_VERTEX, OUTSIDE_NAN
 
 pytestmark = pytest.mark.gpu
 
-VARIANTS = {"auto": {}, "reference": {"epilogue": "reference"}, "delta": {"packed_faces": 2}, "noring": {"prefetch_ring": -1}}
+VARIANTS = {"auto": {}, "reference": {"epilogue": "reference"}, "delta": {"packed_faces": 2}, "noring": {"prefetch_ring": -1},
+            "cells": {"packed_faces": 3}, "cells_noring": {"packed_faces": 3, "prefetch_ring": -1}}
 
 
 def _check(om, q, gs, simplex, status):

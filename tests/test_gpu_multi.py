@@ -20,8 +20,8 @@ dist.init_process_group("nccl", device_id=dev)
 mesh = None
 if rank == 0:
     pts, f, sv, sn = helpers.random_mesh(2, 50000, 5)
-    mesh = dl.Mesh(pts, f, sv, sn, device=lr)
-mesh = parallel.replicate_mesh(mesh, src=0, device=dev)
+    mesh = dl.Mesh(pts, f, sv, sn, device=lr, **%(opts)r)
+mesh = parallel.replicate_mesh(mesh, src=0, device=dev, **%(opts)r)
 q = np.random.default_rng(6).random((400000, 2)) * 1.04 - 0.02
 lo, hi = parallel.shard_bounds(len(q), world, rank)
 ys = mesh.interp(torch.from_numpy(q[lo:hi]).to(dev))
@@ -36,11 +36,12 @@ dist.barrier(); dist.destroy_process_group()
 '''
 
 
-def test_sharded_equals_single(gpu, tmp_path):
+@pytest.mark.parametrize("opts", [{}, {"packed_faces": 3}])
+def test_sharded_equals_single(gpu, tmp_path, opts):
     if gpu < 2:
         pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
     script = tmp_path / "multi.py"
-    script.write_text(SCRIPT % {"root": ROOT})
+    script.write_text(SCRIPT % {"root": ROOT, "opts": opts})
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                         "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
                        capture_output=True, text=True, timeout=600)

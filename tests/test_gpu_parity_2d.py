@@ -12,8 +12,10 @@ REL_TOL = 1e-12  # north_star: values within 1e-12 relative in fp64
 
 # engine variants: auto = 64-byte walk records + guarded gradient form + prefetch ring (default); reference = reference
 # operation order everywhere (bit-exact vs the oracle); delta = the neighbour encoding meshes with >= 2^21-2 faces
-# get; noring = walk records without the cp.async prefetch ring
-VARIANTS = {"auto": {}, "reference": {"epilogue": "reference"}, "delta": {"packed_faces": 2}, "noring": {"prefetch_ring": -1}}
+# get; noring = walk records without the cp.async prefetch ring; cells = cell-indexed walk records (the layout meshes
+# with >= 8M faces get: start record addressed by the hint cell)
+VARIANTS = {"auto": {}, "reference": {"epilogue": "reference"}, "delta": {"packed_faces": 2}, "noring": {"prefetch_ring": -1},
+            "cells": {"packed_faces": 3}, "cells_noring": {"packed_faces": 3, "prefetch_ring": -1}}
 EPILOGUES = list(VARIANTS)
 
 
@@ -104,10 +106,11 @@ def test_closed_form_epilogue_within_tolerance(gpu):
     assert np.median(rel) < 1e-15
 
 
-def test_affine_reproduction_and_set_values(gpu):
+@pytest.mark.parametrize("opts", [{}, {"packed_faces": 2}, {"packed_faces": 3}])
+def test_affine_reproduction_and_set_values(gpu, opts):
     import delaunay_linterp_b200 as dl
     pts, f, sv, sn = helpers.random_mesh(2, 3000, 41)
-    m = dl.Mesh(pts, f, sv, sn)
+    m = dl.Mesh(pts, f, sv, sn, **opts)
     g = 2.0 + 3.0 * pts[:, 0] - 1.5 * pts[:, 1]
     m.set_values(g)
     q = np.random.default_rng(42).random((50000, 2)) * 0.9 + 0.05
@@ -203,3 +206,30 @@ def test_large_mesh_delta_encoded_walk_records(gpu):
     om = OracleMesh(c, f, sv, sn)
     k = 100_000
     _check_parity(m, om, q[:k], ys[:k], s[:k], st[:k], bit_exact=False)
+
+
+def test_cell_indexed_records_on_a_graded_mesh(gpu):
+    """cell-indexed walk records (packed_faces = 3) on an adaptively refined mesh: faces of very different sizes, so
+    big faces own thousands of cells, tiny faces none (extra slots), and neighbour copies may be out of delta range
+    (those queries go to the exact pass).  Same answers as the default layout, parity with the oracle."""
+    import delaunay_linterp_b200 as dl
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
+    t = dl.DelaunayInterp2(fn)
+    for p in ([0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]):
+        t.insert(p, fn(p))
+    for _ in range(3000):
+        t.insert_largest_error_point()
+    c, f, sv, sn = t.export()
+    q = np.random.default_rng(81).random((400000, 2)) * 5.2 - 0.1
+    m0 = dl.Mesh(c, f, sv, sn)
+    for cps in (2.0, 16.0):
+        m = dl.Mesh(c, f, sv, sn, packed_faces=3, hint_cells_per_simplex=cps)
+        m.collect_stats(True)
+        ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+        stats = m.stats()
+        y0, s0, st0 = m0.interp(q, return_simplex=True, return_status=True)
+        assert np.array_equal(st, st0) and np.array_equal(s, s0) and np.array_equal(ys, y0)
+        assert stats["straggler_queries"] < 0.2 * len(q)
+        assert m.device_bytes > m0.device_bytes
+    om = OracleMesh(c, f, sv, sn)
+    _check_parity(m, om, q, ys, s, st, bit_exact=False)
