@@ -841,6 +841,10 @@ int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, in
       bool k2;
       if (is_device_ptr(p, &k2) != dev) return fail(DLI_ERR_ARG, std::string(who) + ": xs and outputs must all be host or all be device pointers");
     }
+  if (dev && m->dim == 2 && (((uintptr_t)xs & 15) || (out == 1 && ((uintptr_t)ys & 15))))
+    return fail(DLI_ERR_ARG, std::string(who) + ": 2D device arrays of coordinate pairs must be 16-byte aligned");
+  if (dev && (((uintptr_t)xs & 7) || ((uintptr_t)ys & 7) || ((uintptr_t)so & 3)))
+    return fail(DLI_ERR_ARG, std::string(who) + ": misaligned device pointer");
   int launches = 0;
   int rc;
   if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches, out);

@@ -500,6 +500,13 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
     int64_t i = direct ? k : (int64_t)queue[k];
     double2 q = xs[i];
     double px = q.x, py = q.y;
+    if (!(isfinite(px) && isfinite(py))) {  // NaN / Inf coordinates: no face can be certified, report instead of walking
+      const double nan = __longlong_as_double(0x7ff8000000000000LL);
+      if (ys) { if (OUT == 1) reinterpret_cast<double2 *>(ys)[i] = make_double2(nan, nan); else ys[i] = nan; }
+      if (simplex_out) simplex_out[i] = -1;
+      if (status_out) status_out[i] = DLI_STATUS_STEP_LIMIT;
+      continue;
+    }
     int f = hint2(m, px, py);
     if (OUT == 1) {
       double2 g;
@@ -636,6 +643,15 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
     double p[D];
 #pragma unroll
     for (int a = 0; a < D; a++) p[a] = xs[i * D + a];
+    bool finite = true;
+#pragma unroll
+    for (int a = 0; a < D; a++) finite = finite && isfinite(p[a]);
+    if (!finite) {  // NaN / Inf coordinates: report instead of walking
+      if (ys) ys[i] = __longlong_as_double(0x7ff8000000000000LL);
+      if (simplex_out) simplex_out[i] = -1;
+      if (status_out) status_out[i] = DLI_STATUS_STEP_LIMIT;
+      continue;
+    }
     int s = hintD<D>(m, p);
     SimplexD<D> S;
     uint8_t status = locateD_full<D>(m, p, s, S, st);

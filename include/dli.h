@@ -46,7 +46,8 @@ extern "C" {
                                           (src/delaunay_2_interp.h:530-545) */
 #define DLI_STATUS_OUTSIDE_NAN 2       /* dD: outside the hull; value is quiet NaN, simplex -1
                                           (src/delaunay_d_interp.h:1005-1008) */
-#define DLI_STATUS_STEP_LIMIT 3        /* walk exceeded max_walk_steps (invalid / non-Delaunay mesh); value NaN.
+#define DLI_STATUS_STEP_LIMIT 3        /* no simplex found: walk exceeded max_walk_steps (invalid / non-Delaunay mesh), or
+                                          the query has a NaN / Inf coordinate; value NaN, simplex -1.
                                           The 2D header wrapper turns this into std::invalid_argument
                                           (src/delaunay_2_interp.h:546-551) */
 #define DLI_STATUS_NO_MESH 4           /* mesh has no simplex (fewer than dim+1 affinely independent points) */

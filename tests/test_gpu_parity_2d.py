@@ -233,3 +233,39 @@ def test_cell_indexed_records_on_a_graded_mesh(gpu):
         assert m.device_bytes > m0.device_bytes
     om = OracleMesh(c, f, sv, sn)
     _check_parity(m, om, q, ys, s, st, bit_exact=False)
+
+
+def test_non_finite_queries_are_reported_not_walked(gpu):
+    """NaN / Inf coordinates: status STEP_LIMIT ("no simplex found"), NaN value, simplex -1 -- immediately, not after
+    max_walk_steps; the neighbouring queries of the batch are unaffected."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 20000, 91)
+    q = np.random.default_rng(92).random((100000, 2)) * 0.9 + 0.05
+    bad = np.arange(0, len(q), 7)
+    qb = q.copy()
+    qb[bad[0::3], 0] = np.nan
+    qb[bad[1::3], 1] = np.inf
+    qb[bad[2::3]] = -np.inf
+    for opts in ({}, {"epilogue": "reference"}, {"packed_faces": 3}):
+        m = dl.Mesh(pts, f, sv, sn, **opts)
+        y0 = m.interp(q)
+        ys, s, st = m.interp(qb, return_simplex=True, return_status=True)
+        good = np.ones(len(q), bool); good[bad] = False
+        assert np.array_equal(ys[good], y0[good]) and (st[good] == 0).all()
+        assert np.isnan(ys[bad]).all() and (s[bad] == -1).all() and (st[bad] == dl.STATUS_STEP_LIMIT).all()
+        g, gst = m.gradient(qb, return_status=True)
+        assert np.isnan(g[bad]).all() and (gst[bad] == dl.STATUS_STEP_LIMIT).all() and np.isfinite(g[good]).all()
+    p3, f3, sv3, sn3 = helpers.random_mesh(3, 3000, 93)
+    q3 = np.random.default_rng(94).random((20000, 3)) * 0.8 + 0.1
+    q3[::5, 1] = np.nan
+    q3[1::5, 2] = np.inf
+    y3, s3, st3 = dl.Mesh(p3, f3, sv3, sn3).interp(q3, return_simplex=True, return_status=True)
+    assert (st3[::5] == dl.STATUS_STEP_LIMIT).all() and (st3[1::5] == dl.STATUS_STEP_LIMIT).all() and np.isnan(y3[::5]).all()
+    assert (st3[2::5] == 0).all()
+    # misaligned device pointer: rejected, not a misaligned-address fault
+    m = dl.Mesh(pts, f, sv, sn)
+    x = torch.rand(1001, 2, dtype=torch.float64, device="cuda")
+    flat = x.view(-1)[1:2001]
+    with pytest.raises(dl.DliError):
+        m.interp_device_ptr(1000, flat.data_ptr(), torch.empty(1000, dtype=torch.float64, device="cuda").data_ptr())
