@@ -28,7 +28,7 @@ class Options(C.Structure):
         ("device", C.c_int32),
         ("hint_cells_per_simplex", C.c_float),
         ("max_walk_steps", C.c_int32),
-        ("sort_queries", C.c_int32),
+        ("reserved0", C.c_int32),
         ("epilogue", C.c_int32),
         ("threads_per_block", C.c_int32),
         ("queries_per_warp", C.c_int32),

@@ -142,7 +142,7 @@ extern "C" void dli_options_init(dli_options *o) {
   o->device = -1;
   o->hint_cells_per_simplex = 0.f;
   o->max_walk_steps = 0;
-  o->sort_queries = 0;
+  o->reserved0 = 0;
   o->epilogue = 0;
   o->threads_per_block = 0;
   o->queries_per_warp = 0;

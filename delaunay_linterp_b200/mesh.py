@@ -16,14 +16,13 @@ def _is_torch_tensor(x):
     return hasattr(x, "data_ptr") and hasattr(x, "is_cuda")
 
 
-def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, sort_queries=0, epilogue=0,
+def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, epilogue=0,
                   threads_per_block=0, queries_per_warp=0, packed_faces=0, prefetch_ring=0):
     o = Options()
     lib().dli_options_init(C.byref(o))
     o.device = int(device)
     o.hint_cells_per_simplex = float(hint_cells_per_simplex)
     o.max_walk_steps = int(max_walk_steps)
-    o.sort_queries = int(sort_queries)
     o.epilogue = {"auto": 0, "closed_form": 1, "reference": 2}.get(epilogue, epilogue)
     o.threads_per_block = int(threads_per_block)
     o.queries_per_warp = int(queries_per_warp)

@@ -67,7 +67,7 @@ typedef struct dli_options {
   int32_t device;                 /* CUDA device ordinal, -1 = current device */
   float hint_cells_per_simplex;   /* start-hint grid resolution; <= 0 = default (2D: 2, 3D: 4, 4D: 8) */
   int32_t max_walk_steps;         /* <= 0 = default (n_simplices + 16) */
-  int32_t sort_queries;           /* 0 = evaluate in input order (default), 1 = bin queries by hint cell first */
+  int32_t reserved0;              /* must be 0 (was: device-side query binning; measured not to pay) */
   int32_t epilogue;               /* DLI_EPILOGUE_*: 0 = AUTO (default): 2D meshes with < 2^21-1 faces use the 64-byte
                                      walk records and evaluate each face's affine interpolant f0 + g.(p - p0) on faces
                                      whose a-priori error bound keeps it within 1e-13 relative of the exact

@@ -107,3 +107,107 @@ def test_cfg4_3d_full_size_properties(gpu):
     yo, so, sto = OracleMesh(pts, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
     y1 = ys[:n1].cpu().numpy()
     assert np.max(np.abs(y1 - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
+
+
+def test_cfg3_adaptive_full_size_properties(gpu):
+    """configs[2]: 100k points placed by insert_largest_error_point, 50M unsorted queries, plus one batched
+    per-simplex error evaluation over all faces + hull edges."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
+    t = dl.DelaunayInterp2(fn)
+    for p in ([0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]):
+        t.insert(p, fn(p))
+    for _ in range(99_996):
+        t.insert_largest_error_point()
+    c, f, sv, sn = t.export()
+    assert len(c) == 100_000
+    m = dl.Mesh(c, f, sv, sn)
+    nq = 50_000_000
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2003)
+    xq = torch.rand(nq, 2, dtype=torch.float64, device="cuda", generator=g) * 4.99 + 0.01
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
+    # the two device engines agree on all 50M queries (strongly graded mesh: tiny faces near the axes)
+    yr, sr = dl.Mesh(c, f, sv, sn, epilogue="reference").interp(xq, return_simplex=True)
+    assert bool(torch.equal(s, sr))
+    assert ((ys - yr).abs() / yr.abs().clamp_min(1e-300)).max().item() <= REL_TOL
+    for a, b in ((0, 1), (1, 12_345_679), (12_345_679, nq)):
+        assert bool(torch.equal(m.interp(xq[a:b]), ys[a:b]))
+    # the adaptive mesh interpolates f much better than a regular grid of the same size would: sanity on the error
+    err = (ys - xq[:, 0] ** 0.3 * xq[:, 1] ** 0.6).abs().max().item()
+    assert err < 0.05
+    # oracle parity on a 500k subsample
+    n1 = 500_000
+    yo, so, sto = OracleMesh(c, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
+    assert np.max(np.abs(ys[:n1].cpu().numpy() - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
+    # batched error evaluation of every face + hull edge == the oracle's SVD form, and == the host queue's entries
+    cent, isx, iv = m.simplex_error_items()
+    errs = m.simplex_error(helpers.cobb_douglas(cent))
+    om = OracleMesh(c, f, sv, sn)
+    o_simplex, o_nv, o_verts, o_cent = om.error_items()
+    assert len(errs) == len(o_nv) and np.array_equal(cent, o_cent)
+    want = om.error_eval(o_nv, o_verts, o_cent, helpers.cobb_douglas(o_cent))
+    assert np.allclose(errs, want, rtol=1e-7, atol=1e-22)
+    assert np.all(np.diff([e[0] for e in t.get_error_queue()[:1000]]) <= 0)
+
+
+def test_cfg4_4d_full_size_properties(gpu):
+    """configs[3], 4D: 200k random vertices (6.2M simplices), 20M queries."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(4, 200_000, 1004)
+    m = dl.Mesh(pts, f, sv, sn)
+    nq = 20_000_000
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2005)
+    xq = torch.rand(nq, 4, dtype=torch.float64, device="cuda", generator=g) * 0.8 + 0.1
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
+    for a, b in ((0, 33), (33, 9_000_001), (9_000_001, nq)):
+        assert bool(torch.equal(m.interp(xq[a:b]), ys[a:b]))
+    yr, sr = dl.Mesh(pts, f, sv, sn, epilogue="reference").interp(xq[:5_000_000], return_simplex=True)
+    assert bool(torch.equal(s[:5_000_000], sr))
+    assert ((ys[:5_000_000] - yr).abs() / yr.abs().clamp_min(1e-300)).max().item() <= REL_TOL
+    m.set_values(1.0 + pts @ np.array([0.5, -2.0, 3.0, 0.25]))
+    ya = m.interp(xq)
+    want = 1.0 + xq @ torch.tensor([0.5, -2.0, 3.0, 0.25], dtype=torch.float64, device="cuda")
+    assert ((ya - want).abs() / want.abs().clamp_min(1e-3)).max().item() <= 1e-12
+    n1 = 100_000
+    yo, so, sto = OracleMesh(pts, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
+    assert np.max(np.abs(ys[:n1].cpu().numpy() - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
+
+
+def test_cfg5_one_shard_full_size_properties(gpu):
+    """configs[4], one GPU's share: 16M-vertex mesh (32M faces, cell-indexed walk records), 125M queries = 1B / 8."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    c, f, sv, sn = _native_mesh(16_000_000, 1005)
+    m = dl.Mesh(c, f, sv, sn)
+    nq = 125_000_000
+    g = torch.Generator(device="cuda")
+    g.manual_seed(2006)
+    xq = torch.rand(nq, 2, dtype=torch.float64, device="cuda", generator=g) * 0.96 + 0.02
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
+    # the Morton-ordered layout (delta-encoded neighbours) gives the same faces and bit-identical values
+    m2 = dl.Mesh(c, f, sv, sn, packed_faces=2)
+    k = 40_000_000
+    y2, s2 = m2.interp(xq[:k], return_simplex=True)
+    assert bool(torch.equal(s[:k], s2)) and bool(torch.equal(ys[:k], y2))
+    del m2, y2, s2
+    for a, b in ((0, 5), (5, 60_000_001), (60_000_001, nq)):
+        assert bool(torch.equal(m.interp(xq[a:b]), ys[a:b]))
+    m.set_values(2.0 + 3.0 * c[:, 0] - 1.5 * c[:, 1])
+    ya = m.interp(xq)
+    want = 2.0 + 3.0 * xq[:, 0] - 1.5 * xq[:, 1]
+    assert ((ya - want).abs() / want.abs()).max().item() <= REL_TOL
+    del ya, want
+    n1 = 300_000
+    yo, so, sto = OracleMesh(c, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
+    assert np.max(np.abs(ys[:n1].cpu().numpy() - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
+    assert np.mean(s[:n1].cpu().numpy() == so) > 0.99999
