@@ -630,6 +630,7 @@ MeshDView viewD(const dli_mesh *m) {
   MeshDView v;
   v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint; v.orig = m->d_orig;
   v.fat = m->d_fat;
+  v.epi = (m->d_fat && m->dim == 4) ? m->d_fat + (size_t)m->ns * FatD<4>::CHUNKS : nullptr;
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   return v;

@@ -58,6 +58,7 @@ struct MeshDView {
   const int32_t *hint;
   const int32_t *orig;  // device simplex index -> the caller's simplex id
   const uint4 *fat;     // optional walk records (FatD<D>), NULL when unused
+  const uint4 *epi;     // D = 4: the 64-byte affine-interpolant records that follow the walk records
   double o[DLI_MAX_DIM], ic[DLI_MAX_DIM];
   int g[DLI_MAX_DIM];
   int ns;
@@ -72,20 +73,26 @@ struct MeshDView {
 //   G (fp32, D x D): row i = gradient of the barycentric coordinate of vertex i+1, so b_{i+1} = G_i . (p - p0)
 //   n_0..n_D (int32, device simplex indices, < 0 = hull)
 // D = 3: 8 chunks (128 B):  c0 p0x p0y | c1 p0z f0 | c2 gx gy | c3 gz flags | c4 G0..3 | c5 G4..7 | c6 G8 - - - | c7 n0..n3
-// D = 4: 12 chunks (192 B): c0 p0x p0y | c1 p0z p0w | c2 f0 gx | c3 gy gz | c4 gw flags | c5 n0..n3 | c6..c9 G0..15 |
-//                           c10 n4 - - - | c11 unused (not loaded)
+// D = 4: the 192 bytes per simplex are split so that a walk step touches ONE 128-byte line (a 192-byte record straddles
+//        two): 8 chunks of geometry (128 B): c0 p0x p0y | c1 p0z p0w | c2..c5 G0..15 | c6 n0..n3 | c7 n4 flags - -
+//        and, in a second array behind the ns geometry records, 4 chunks (64 B, 3 loaded) of affine interpolant:
+//        e0 f0 gx | e1 gy gz | e2 gw - | e3 unused.  Only the simplex a query ends in reads its interpolant record.
 // The fp32 rounding of G (and the fp64 rounding error of computing it, bounded per entry at build time to at most
 // half an fp32 ulp) is covered by the filter constant kFatKD, so a certified barycentric sign is the sign of the exact
 // orientation predicate on the fp64 mesh.
 // ---------------------------------------------------------------------------------------------
 template <int D>
 struct FatD {
-  static constexpr int CHUNKS = (D == 3) ? 8 : 12;        // global record size in 16-byte chunks
-  static constexpr int LOADED = (D == 3) ? 8 : 11;        // chunks actually staged
-  static constexpr int LPR = (D == 3) ? 8 : 16;           // lanes cooperating on one record
-  static constexpr int SSTRIDE = (D == 3) ? 9 : 13;       // shared-memory record stride in chunks (odd: conflict-free)
-  static constexpr int BYTES = CHUNKS * 16;
-  static constexpr int SMEM_PER_WARP = 32 * SSTRIDE * 16;
+  static constexpr int CHUNKS = 8;                        // walk record size in 16-byte chunks (one 128-byte line)
+  static constexpr int LOADED = 8;                        // chunks actually staged
+  static constexpr int LPR = 8;                           // lanes cooperating on one record
+  static constexpr int SSTRIDE = 9;                       // shared-memory record stride in chunks (odd: conflict-free)
+  static constexpr bool SPLIT = (D == 4);                 // affine interpolant in a separate record array
+  static constexpr int EPI_CHUNKS = SPLIT ? 4 : 0;        // interpolant record stride in chunks (64 B)
+  static constexpr int EPI_LOADED = SPLIT ? 3 : 0;
+  static constexpr int ESTRIDE = 5;                       // per-lane shared slot: 3 interpolant chunks + d[4] (conflict-free)
+  static constexpr int BYTES = (CHUNKS + EPI_CHUNKS) * 16;  // bytes per simplex in d_fat
+  static constexpr int SMEM_PER_WARP = 32 * SSTRIDE * 16 + (SPLIT ? 32 * ESTRIDE * 16 : 0);
 };
 constexpr double kFatKD = 2.384185791015625e-07;  // 2^-22 = 4 fp32 unit roundoffs
 

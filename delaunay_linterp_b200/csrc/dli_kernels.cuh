@@ -858,18 +858,20 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
     o[6] = f4(g32[8], 0.f, 0.f, 0.f);
     o[7] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
   } else {
+    const unsigned fl = slow ? 1u : 0u;
     o[0] = d2(x0[0], x0[1]);
     o[1] = d2(x0[2], x0[3]);
-    o[2] = d2(f[0], g[0]);
-    o[3] = d2(g[1], g[2]);
-    o[4] = d2(g[3], flags);
-    o[5] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
-    o[6] = f4(g32[0], g32[1], g32[2], g32[3]);
-    o[7] = f4(g32[4], g32[5], g32[6], g32[7]);
-    o[8] = f4(g32[8], g32[9], g32[10], g32[11]);
-    o[9] = f4(g32[12], g32[13], g32[14], g32[15]);
-    o[10] = make_uint4((unsigned)nb[4], 0u, 0u, 0u);
-    o[11] = make_uint4(0u, 0u, 0u, 0u);
+    o[2] = f4(g32[0], g32[1], g32[2], g32[3]);
+    o[3] = f4(g32[4], g32[5], g32[6], g32[7]);
+    o[4] = f4(g32[8], g32[9], g32[10], g32[11]);
+    o[5] = f4(g32[12], g32[13], g32[14], g32[15]);
+    o[6] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
+    o[7] = make_uint4((unsigned)nb[4], fl, 0u, 0u);
+    uint4 *e = fat + (size_t)ns * FatD<D>::CHUNKS + (size_t)s * FatD<D>::EPI_CHUNKS;   // interpolant records follow
+    e[0] = d2(f[0], g[0]);
+    e[1] = d2(g[1], g[2]);
+    e[2] = d2(g[3], 0.0);
+    e[3] = make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -900,8 +902,14 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
   const int64_t base = warp * per_warp;
   if (base >= n) return;  // warp-uniform
   const int64_t end = min(n, base + (int64_t)per_warp);
-  uint4 *stage = reinterpret_cast<uint4 *>(stage_smem) + (size_t)(threadIdx.x >> 5) * 32 * F::SSTRIDE;
+  uint4 *stage = reinterpret_cast<uint4 *>(stage_smem) + (size_t)(threadIdx.x >> 5) * (F::SMEM_PER_WARP / 16);
   const uint4 *mine = stage + lane * F::SSTRIDE;                    // this lane's staged record
+  // SPLIT (D = 4): the interpolant record of the simplex a lane's previous query ended in is fetched into the lane's
+  // own slot together with the next step's walk records, so its latency hides behind that staging
+  uint4 *eslot = stage + 32 * F::SSTRIDE + lane * F::ESTRIDE;
+  const unsigned edst = (unsigned)__cvta_generic_to_shared(eslot);
+  int64_t pqi = -1;   // query whose value is pending on its interpolant record
+  int ps = 0;         // ... and the simplex it ended in
   const int rsub = lane / F::LPR, csub = lane % F::LPR;             // staging role: record within the group, chunk
   const unsigned sdst = (unsigned)__cvta_generic_to_shared(stage + csub);
   int64_t next = base;
@@ -983,7 +991,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
       }
       next += __popc(need);
     }
-    if (!__any_sync(FULL, active)) break;
+    if (!__any_sync(FULL, active || (F::SPLIT && pqi >= 0))) break;
     // ---- stage the records of this step
     const int fs = active ? s : -1;
     __syncwarp();  // every lane has finished reading the previous step's records
@@ -996,9 +1004,27 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
                      "l"(m.fat + (size_t)fr * F::CHUNKS + csub)
                      : "memory");
     }
+    if (F::SPLIT && pqi >= 0) {
+      const uint4 *er = m.epi + (size_t)ps * F::EPI_CHUNKS;
+#pragma unroll
+      for (int c = 0; c < F::EPI_LOADED; c++)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(edst + (unsigned)(c * 16)), "l"(er + c) : "memory");
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
+    if (F::SPLIT && pqi >= 0) {   // finish the pending query: y = f0 + g . d, same operations as the in-record form
+      auto lo = [](const uint4 &c) { return __hiloint2double((int)c.y, (int)c.x); };
+      auto hi = [](const uint4 &c) { return __hiloint2double((int)c.w, (int)c.z); };
+      const uint4 e0 = eslot[0], e1 = eslot[1], e2 = eslot[2], d01 = eslot[3], d23 = eslot[4];
+      double y = 0.0;
+      y = fma(lo(e2), hi(d23), y);
+      y = fma(hi(e1), lo(d23), y);
+      y = fma(lo(e1), hi(d01), y);
+      y = fma(hi(e0), lo(d01), y);
+      __stcs(ys + pqi, lo(e0) + y);
+      pqi = -1;
+    }
     if (active) {
       steps++;
       double x0[D], f0, g[D];
@@ -1018,18 +1044,20 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
           G[8] = __uint_as_float(c6.x);
           nb[0] = (int)c7.x; nb[1] = (int)c7.y; nb[2] = (int)c7.z; nb[3] = (int)c7.w;
         } else {
-          uint4 c0 = mine[0], c1 = mine[1], c2 = mine[2], c3 = mine[3], c4 = mine[4], c5 = mine[5];
+          uint4 c0 = mine[0], c1 = mine[1], c6 = mine[6], c7 = mine[7];
           x0[0] = lo(c0); x0[1] = hi(c0); x0[2] = lo(c1); x0[3] = hi(c1);
-          f0 = lo(c2); g[0] = hi(c2); g[1] = lo(c3); g[2] = hi(c3); g[3] = lo(c4);
-          flags = ((unsigned long long)c4.w << 32) | c4.z;
-          nb[0] = (int)c5.x; nb[1] = (int)c5.y; nb[2] = (int)c5.z; nb[3] = (int)c5.w;
+          f0 = 0.0;
+#pragma unroll
+          for (int k = 0; k < D; k++) g[k] = 0.0;
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            uint4 c = mine[6 + q];
+            uint4 c = mine[2 + q];
             G[4 * q] = __uint_as_float(c.x); G[4 * q + 1] = __uint_as_float(c.y);
             G[4 * q + 2] = __uint_as_float(c.z); G[4 * q + 3] = __uint_as_float(c.w);
           }
-          nb[4] = (int)mine[10].x;
+          nb[0] = (int)c6.x; nb[1] = (int)c6.y; nb[2] = (int)c6.z; nb[3] = (int)c6.w;
+          nb[4] = (int)c7.x;
+          flags = c7.y;
         }
       }
       double d[D], d1 = 0.0;
@@ -1070,10 +1098,21 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
           else { from = s; s = t; }
         } else if (all_pos) {
           if (ys) {
-            double y = 0.0;
+            if constexpr (F::SPLIT) {   // value written once the interpolant record has arrived (next iteration)
+              auto pk = [](double a, double b) {
+                return make_uint4((unsigned)__double2loint(a), (unsigned)__double2hiint(a), (unsigned)__double2loint(b),
+                                  (unsigned)__double2hiint(b));
+              };
+              eslot[3] = pk(d[0], d[1]);
+              eslot[4] = pk(d[D - 2], d[D - 1]);
+              pqi = qi;
+              ps = s;
+            } else {
+              double y = 0.0;
 #pragma unroll
-            for (int k = D - 1; k >= 0; k--) y = fma(g[k], d[k], y);
-            __stcs(ys + qi, f0 + y);
+              for (int k = D - 1; k >= 0; k--) y = fma(g[k], d[k], y);
+              __stcs(ys + qi, f0 + y);
+            }
           }
           if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + s));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
