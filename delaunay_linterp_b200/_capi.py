@@ -63,6 +63,7 @@ SYMBOLS = [
     ("dli_options_init", None, [C.POINTER(Options)]),
     ("dli_mesh_create", C.c_int, [C.c_int, C.c_int64, _vp, _vp, C.c_int64, _vp, _vp, C.POINTER(Options), C.POINTER(_vp)]),
     ("dli_mesh_set_values", C.c_int, [_vp, _vp]),
+    ("dli_mesh_update", C.c_int, [_vp, C.c_int64, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp]),
     ("dli_mesh_destroy", None, [_vp]),
     ("dli_mesh_dim", C.c_int, [_vp]),
     ("dli_mesh_num_vertices", C.c_int64, [_vp]),
@@ -111,6 +112,7 @@ HOST_SYMBOLS = [
     ("dli_di2_export", C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     ("dli_di2_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_di2_gradient", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_di2_sync_counts", None, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     ("dli_di2_device_mesh", _vp, [_vp]),
     ("dli_di2_set_options", C.c_int, [_vp, C.POINTER(Options)]),
     ("dli_di2_get_all_vertices", C.c_int64, [_vp, _vp]),

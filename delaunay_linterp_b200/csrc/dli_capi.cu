@@ -76,6 +76,13 @@ struct dli_mesh {
   int vs = 0, ss = 0;  // record strides (doubles / ints)
   // host copies of the canonical connectivity (error items, get_simplices)
   std::vector<int32_t> h_sv, h_sn;
+  // dli_mesh_update (2D meshes created here, not replicas): caller id -> device index, vertex coordinates,
+  // capacities of the growable device buffers
+  std::vector<int32_t> h_inv;
+  std::vector<double> h_xy;
+  int64_t cap_v = 0, cap_s = 0;
+  int32_t cap_h = 0;
+  int64_t n_updates = 0;
   // device buffers
   double *d_vrec = nullptr;
   int32_t *d_srec = nullptr;
@@ -333,6 +340,7 @@ static int mesh_alloc_common(dli_mesh *m) {
   if (d == 2 && m->opt.packed_faces >= 0 && m->ns > 0 && m->nv <= (1 << 21) && m->ns < (1 << 21) - 1)
     CU(cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)m->ns));
   m->nslots = m->ns;
+  m->cap_v = std::max<int64_t>(m->nv, 1); m->cap_s = std::max<int64_t>(m->ns, 1); m->cap_h = std::max<int32_t>(m->nh, 1);
   if (m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0) {
     // 2D meshes whose records are far larger than L2 get cell-indexed records (allocated once the hint grid exists)
     m->cellmode = d == 2 && (m->opt.packed_faces == 3 || (m->opt.packed_faces == 0 && m->ns >= kCellModeFaces));
@@ -457,6 +465,28 @@ static int resolve_options(const dli_options *opt, dli_options *out) {
   return DLI_OK;
 }
 
+// 2D hull-edge table {face (caller id), slot, next, prev} in the order (face id, slot) ascending; enc_sn gets ~h in
+// the hull slots (the device encoding of a hull neighbour)
+static void hull_table2(int64_t nv, int64_t ns, const std::vector<int32_t> &sv, const std::vector<int32_t> &sn,
+                        std::vector<int4> &hull, std::vector<int32_t> &enc_sn) {
+  hull.clear();
+  std::vector<int32_t> from((size_t)nv, -1), to((size_t)nv, -1);
+  for (int64_t s = 0; s < ns; s++)
+    for (int j = 0; j < 3; j++)
+      if (sn[s * 3 + j] < 0) {
+        int32_t h = (int32_t)hull.size();
+        hull.push_back(make_int4((int)s, j, -1, -1));
+        from[sv[s * 3 + (j + 1) % 3]] = h;
+        to[sv[s * 3 + (j + 2) % 3]] = h;
+        enc_sn[s * 3 + j] = ~h;
+      }
+  for (auto &h : hull) {
+    int32_t P = sv[(size_t)h.x * 3 + (h.y + 1) % 3], Q = sv[(size_t)h.x * 3 + (h.y + 2) % 3];
+    h.z = from[Q];
+    h.w = to[P];
+  }
+}
+
 extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const double *f, int64_t ns,
                                const int32_t *sv_in, const int32_t *sn_in, const dli_options *opt, dli_mesh **out) {
   if (!out) return fail(DLI_ERR_ARG, "dli_mesh_create: out is NULL");
@@ -510,21 +540,7 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
   std::vector<int4> hull;
   std::vector<int32_t> enc_sn(m->h_sn);  // device encoding of neighbours
   if (d == 2) {
-    std::vector<int32_t> from((size_t)nv, -1), to((size_t)nv, -1);
-    for (int64_t s = 0; s < ns; s++)
-      for (int j = 0; j < 3; j++)
-        if (m->h_sn[s * 3 + j] < 0) {
-          int32_t h = (int32_t)hull.size();
-          hull.push_back(make_int4((int)s, j, -1, -1));
-          from[m->h_sv[s * 3 + (j + 1) % 3]] = h;
-          to[m->h_sv[s * 3 + (j + 2) % 3]] = h;
-          enc_sn[s * 3 + j] = ~h;
-        }
-    for (auto &h : hull) {
-      int32_t P = m->h_sv[(size_t)h.x * 3 + (h.y + 1) % 3], Q = m->h_sv[(size_t)h.x * 3 + (h.y + 2) % 3];
-      h.z = from[Q];
-      h.w = to[P];
-    }
+    hull_table2(nv, ns, m->h_sv, m->h_sn, hull, enc_sn);
     m->nh = (int32_t)hull.size();
   }
 
@@ -552,6 +568,10 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
       }
     }
     for (auto &h : hull) h.x = inv[(size_t)h.x];
+    if (d == 2 && ns > 0 && ns < (1 << 21) - 2) {   // what dli_mesh_update needs later
+      m->h_inv = inv;
+      m->h_xy.assign(coords, coords + (size_t)nv * 2);
+    }
     cudaError_t e = cudaMemcpy(m->d_vrec, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(m->d_srec, srec.data(), sizeof(int32_t) * srec.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && ns > 0) e = cudaMemcpy(m->d_orig, perm.data(), sizeof(int32_t) * perm.size(), cudaMemcpyHostToDevice);
@@ -582,6 +602,194 @@ extern "C" int dli_mesh_set_values(dli_mesh *m, const double *f) {
   CU(cudaMemcpy2D(m->d_vrec + m->dim, sizeof(double) * m->vs, f, sizeof(double), sizeof(double), (size_t)m->nv,
                   cudaMemcpyHostToDevice));
   return build_fat_records(m);
+}
+
+// grows a device buffer to new_bytes keeping the first keep_bytes
+template <class T>
+static cudaError_t grow_buffer(T *&p, size_t keep_bytes, size_t new_bytes) {
+  T *q = nullptr;
+  cudaError_t e = cudaMalloc(&q, new_bytes);
+  if (e != cudaSuccess) return e;
+  if (p && keep_bytes) e = cudaMemcpy(q, p, keep_bytes, cudaMemcpyDeviceToDevice);
+  if (e != cudaSuccess) { cudaFree(q); return e; }
+  cudaFree(p);
+  p = q;
+  return cudaSuccess;
+}
+
+extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_coords, const double *new_f,
+                               int64_t n_fchg, const int32_t *fchg_ids, const double *fchg_vals, int64_t ns_total,
+                               int64_t n_dirty, const int32_t *dirty_ids, const int32_t *dirty_sv, const int32_t *dirty_sn) {
+  if (!m) return fail(DLI_ERR_ARG, "dli_mesh_update: NULL mesh");
+  const int64_t nv0 = m->nv, ns0 = m->ns;
+  if (nv_total < nv0 || ns_total < ns0 || n_fchg < 0 || n_dirty < 0 || nv_total > 0x7fffffff)
+    return fail(DLI_ERR_ARG, "dli_mesh_update: sizes must not shrink");
+  if ((nv_total > nv0 && (!new_coords || !new_f)) || (n_fchg > 0 && (!fchg_ids || !fchg_vals)) ||
+      (n_dirty > 0 && (!dirty_ids || !dirty_sv || !dirty_sn)))
+    return fail(DLI_ERR_ARG, "dli_mesh_update: NULL array");
+  // ---- can this mesh be patched?
+  if (m->dim != 2 || m->cellmode || ns0 == 0 || m->h_inv.empty() || m->h_sv.empty())
+    return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: mesh cannot be patched (not 2D, replica, empty or cell-indexed records)");
+  if (ns_total >= (1 << 21) - 2 || (m->d_fpack && nv_total > (1 << 21)) || fat_delta(m))
+    return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: ids no longer fit the packed records");
+  for (int64_t v = 0; v < nv_total - nv0; v++)
+    for (int c = 0; c < 2; c++) {
+      const double x = new_coords[2 * v + c], lo = m->grid.o[c], hi = lo + m->grid.cell[c] * m->grid.g[c];
+      if (!(x >= lo && x <= hi)) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: new vertex outside the start-hint grid");
+    }
+  // ---- validate the dirty set
+  {
+    int64_t appended = 0;
+    std::vector<uint8_t> seen((size_t)(ns_total - ns0), 0);
+    for (int64_t i = 0; i < n_dirty; i++) {
+      const int32_t id = dirty_ids[i];
+      if (id < 0 || id >= ns_total) return fail(DLI_ERR_MESH, "dli_mesh_update: simplex id out of range");
+      if (id >= ns0) {
+        if (seen[(size_t)(id - ns0)]) return fail(DLI_ERR_MESH, "dli_mesh_update: simplex id listed twice");
+        seen[(size_t)(id - ns0)] = 1;
+        appended++;
+      }
+      for (int j = 0; j < 3; j++) {
+        if (dirty_sv[3 * i + j] < 0 || dirty_sv[3 * i + j] >= nv_total) return fail(DLI_ERR_MESH, "dli_mesh_update: vertex index out of range");
+        if (dirty_sn[3 * i + j] >= ns_total) return fail(DLI_ERR_MESH, "dli_mesh_update: neighbour index out of range");
+      }
+    }
+    if (appended != ns_total - ns0) return fail(DLI_ERR_MESH, "dli_mesh_update: every new simplex id must be listed");
+    for (int64_t i = 0; i < n_fchg; i++)
+      if (fchg_ids[i] < 0 || fchg_ids[i] >= nv0) return fail(DLI_ERR_MESH, "dli_mesh_update: value-change vertex out of range");
+  }
+  DeviceGuard guard(m->device);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_update: cannot select device");
+  // ---- host connectivity: orientation-canonical rows of the dirty simplices
+  std::vector<double> xy(m->h_xy);
+  xy.insert(xy.end(), new_coords, new_coords + (size_t)(nv_total - nv0) * 2);
+  std::vector<int32_t> sv(m->h_sv), sn(m->h_sn);
+  sv.resize((size_t)ns_total * 3, 0);
+  sn.resize((size_t)ns_total * 3, -1);
+  bool hull_touched = false;
+  for (int64_t i = 0; i < n_dirty; i++) {
+    const int64_t s = dirty_ids[i];
+    int32_t v[3] = {dirty_sv[3 * i], dirty_sv[3 * i + 1], dirty_sv[3 * i + 2]};
+    int32_t nb[3] = {dirty_sn[3 * i], dirty_sn[3 * i + 1], dirty_sn[3 * i + 2]};
+    const int o = orient2d(xy[2 * (size_t)v[0]], xy[2 * (size_t)v[0] + 1], xy[2 * (size_t)v[1]], xy[2 * (size_t)v[1] + 1],
+                           xy[2 * (size_t)v[2]], xy[2 * (size_t)v[2] + 1]);
+    if (o == 0) return fail(DLI_ERR_MESH, "dli_mesh_update: degenerate simplex (zero area)");
+    if (o < 0) { std::swap(v[0], v[1]); std::swap(nb[0], nb[1]); }
+    for (int j = 0; j < 3; j++) {
+      if (nb[j] < 0) nb[j] = -1;
+      if (nb[j] < 0 || (s < ns0 && sn[(size_t)s * 3 + j] < 0)) hull_touched = true;
+      sv[(size_t)s * 3 + j] = v[j];
+      sn[(size_t)s * 3 + j] = nb[j];
+    }
+  }
+  // ---- the set of simplices to re-send: the dirty ones, plus every hull-adjacent one when the hull table is rebuilt
+  std::vector<int32_t> list(dirty_ids, dirty_ids + n_dirty);
+  std::vector<int4> hull;
+  std::vector<int32_t> enc(sn);
+  if (hull_touched) {
+    hull_table2(nv_total, ns_total, sv, sn, hull, enc);
+    std::vector<uint8_t> in_list((size_t)ns_total, 0);
+    for (int32_t s : list) in_list[(size_t)s] = 1;
+    for (const int4 &h : hull)
+      if (!in_list[(size_t)h.x]) { in_list[(size_t)h.x] = 1; list.push_back(h.x); }
+    if (hull.size() > 0x7ffffff0u) return fail(DLI_ERR_MESH, "dli_mesh_update: hull too large");
+  }
+  // (without a hull change the ~h encodings of untouched simplices stay valid and no dirty simplex has a hull slot)
+  auto dev_index = [&](int64_t s) -> int32_t { return s < ns0 ? m->h_inv[(size_t)s] : (int32_t)s; };
+  const int64_t nl = (int64_t)list.size();
+  std::vector<int32_t> idx((size_t)nl), rows((size_t)nl * 8, 0);
+  for (int64_t i = 0; i < nl; i++) {
+    const int64_t s = list[(size_t)i];
+    idx[(size_t)i] = dev_index(s);
+    for (int j = 0; j < 3; j++) {
+      const int32_t nb = enc[(size_t)s * 3 + j];
+      rows[(size_t)i * 8 + j] = sv[(size_t)s * 3 + j];
+      rows[(size_t)i * 8 + 3 + j] = nb >= 0 ? dev_index(nb) : nb;
+    }
+  }
+  for (auto &h : hull) h.x = dev_index(h.x);
+  // ---- capacity
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess && nv_total > m->cap_v) {
+    const int64_t cap = nv_total + nv_total / 2 + 1024;
+    e = grow_buffer(m->d_vrec, sizeof(double) * (size_t)nv0 * m->vs, sizeof(double) * (size_t)cap * m->vs);
+    if (e == cudaSuccess) m->cap_v = cap;
+  }
+  if (e == cudaSuccess && ns_total > m->cap_s) {
+    const int64_t cap = std::min<int64_t>(ns_total + ns_total / 2 + 1024, (1 << 21) - 2);
+    e = grow_buffer(m->d_srec, sizeof(int32_t) * (size_t)ns0 * m->ss, sizeof(int32_t) * (size_t)cap * m->ss);
+    if (e == cudaSuccess) e = grow_buffer(m->d_orig, sizeof(int32_t) * (size_t)ns0, sizeof(int32_t) * (size_t)cap);
+    if (e == cudaSuccess && m->d_fpack) e = grow_buffer(m->d_fpack, sizeof(ulonglong2) * (size_t)ns0, sizeof(ulonglong2) * (size_t)cap);
+    if (e == cudaSuccess && m->d_fat) e = grow_buffer(m->d_fat, (size_t)64 * (size_t)ns0, (size_t)64 * (size_t)cap);
+    if (e == cudaSuccess) m->cap_s = cap;
+  }
+  if (e == cudaSuccess && hull_touched && (int64_t)hull.size() > m->cap_h) {
+    const int32_t cap = (int32_t)hull.size() * 2 + 64;
+    e = grow_buffer(m->d_hull, 0, sizeof(int4) * (size_t)cap);
+    if (e == cudaSuccess) m->cap_h = cap;
+  }
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed: ") + cudaGetErrorString(e));
+  // ---- upload + rebuild the derived records of the listed simplices
+  int32_t *d_idx = nullptr, *d_ids = nullptr, *d_vid = nullptr;
+  int4 *d_rows = nullptr;
+  double *d_val = nullptr;
+  int *d_delta = nullptr;
+  int delta = 0;
+  const int64_t nnew = nv_total - nv0;
+  if (nnew > 0) {
+    std::vector<double> vrec((size_t)nnew * 4, 0.0);
+    for (int64_t v = 0; v < nnew; v++) { vrec[4 * v] = new_coords[2 * v]; vrec[4 * v + 1] = new_coords[2 * v + 1]; vrec[4 * v + 2] = new_f[v]; }
+    e = cudaMemcpy(m->d_vrec + (size_t)nv0 * 4, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess && n_fchg > 0) {
+    e = cudaMalloc(&d_vid, sizeof(int32_t) * (size_t)n_fchg);
+    if (e == cudaSuccess) e = cudaMalloc(&d_val, sizeof(double) * (size_t)n_fchg);
+    if (e == cudaSuccess) e = cudaMemcpy(d_vid, fchg_ids, sizeof(int32_t) * (size_t)n_fchg, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_val, fchg_vals, sizeof(double) * (size_t)n_fchg, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess)
+      k_update_values<<<(unsigned)((n_fchg + 127) / 128), 128>>>((int)n_fchg, d_vid, d_val, reinterpret_cast<double4 *>(m->d_vrec));
+  }
+  if (e == cudaSuccess && nl > 0) {
+    e = cudaMalloc(&d_idx, sizeof(int32_t) * (size_t)nl);
+    if (e == cudaSuccess) e = cudaMalloc(&d_ids, sizeof(int32_t) * (size_t)nl);
+    if (e == cudaSuccess) e = cudaMalloc(&d_rows, sizeof(int32_t) * (size_t)nl * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_delta, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(d_delta, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemcpy(d_idx, idx.data(), sizeof(int32_t) * (size_t)nl, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_ids, list.data(), sizeof(int32_t) * (size_t)nl, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_rows, rows.data(), sizeof(int32_t) * (size_t)nl * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+      const unsigned gb = (unsigned)((nl + 127) / 128);
+      int4 *frec = reinterpret_cast<int4 *>(m->d_srec);
+      k_update_faces<<<gb, 128>>>((int)nl, d_idx, d_rows, d_ids, frec, m->d_orig);
+      if (m->d_fpack) k_pack_faces_list<<<gb, 128>>>((int)nl, d_idx, frec, m->d_fpack);
+      if (m->d_fat)
+        k_build_fat2_list<<<gb, 128>>>((int)nl, d_idx, (int)ns0, frec, reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_delta);
+      e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaMemcpy(&delta, d_delta, sizeof delta, cudaMemcpyDeviceToHost);
+    }
+  }
+  if (e == cudaSuccess && hull_touched && !hull.empty())
+    e = cudaMemcpy(m->d_hull, hull.data(), sizeof(int4) * hull.size(), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  cudaFree(d_idx); cudaFree(d_ids); cudaFree(d_rows); cudaFree(d_vid); cudaFree(d_val); cudaFree(d_delta);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
+  // ---- commit the host side
+  m->h_xy.swap(xy);
+  m->h_sv.swap(sv);
+  m->h_sn.swap(sn);
+  m->h_inv.resize((size_t)ns_total);
+  for (int64_t s = ns0; s < ns_total; s++) m->h_inv[(size_t)s] = (int32_t)s;
+  m->nv = nv_total; m->ns = ns_total; m->nslots = ns_total;
+  if (hull_touched) m->nh = (int32_t)hull.size();
+  m->n_slow_faces += delta;
+  if (!(m->opt.max_walk_steps > 0)) m->max_steps = (int)std::min<int64_t>(m->ns + 16, 0x7fffffff);
+  {
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (m->items_ready) { cudaFree(m->d_item_verts); m->d_item_verts = nullptr; m->items_ready = false; }
+  }
+  m->n_updates++;
+  return DLI_OK;
 }
 
 extern "C" void dli_mesh_destroy(dli_mesh *m) { mesh_free(m); }

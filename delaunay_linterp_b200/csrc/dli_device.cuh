@@ -283,11 +283,27 @@ __device__ __forceinline__ bool locate2_fast(const Mesh2View &m, double px, doub
   return false;
 }
 
-// among the hull edges strictly visible from p (a contiguous chain containing h0) the one with the
-// smallest index; canonical stand-in for "whichever infinite face CGAL's walk ended in"
+// Among the hull edges strictly visible from p (a contiguous chain containing h0) the one whose supporting line is
+// farthest from p (largest det^2 / |PQ|^2 in plain fp64, ties: smallest index); canonical stand-in for "whichever
+// infinite face CGAL's walk ended in".  Farthest-line-first guarantees progress: after a projection p sits on the
+// line of its edge within rounding and that edge may still test strictly visible by an ulp; a fixed preference for
+// it would re-project p on the same line until the round cap.
+__device__ __forceinline__ double hull_edge_score(double Px, double Py, double Qx, double Qy, double px, double py) {
+  const double dx = Qx - Px, dy = Qy - Py;
+  const double det = dx * (py - Py) - dy * (px - Px);
+  return (det * det) / (dx * dx + dy * dy);
+}
 __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px, double py, int h0,
                                                   StatsAcc &st) {
   int best = h0;
+  double best_score;
+  {
+    int4 r = __ldg(m.hull + h0);
+    Face2 F = load_face(m, r.x);
+    int vs[3] = {F.v0, F.v1, F.v2};
+    double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
+    best_score = hull_edge_score(P.x, P.y, Q.x, Q.y, px, py);
+  }
   for (int dir = 0; dir < 2; dir++) {
     int h = h0;
     for (int it = 0; it < m.nh; it++) {
@@ -301,7 +317,8 @@ __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px,
       int s = orient2d_filtered(P.x, P.y, Q.x, Q.y, px, py);
       if (s == 2) { st.exact++; s = orient2d_exact(P.x, P.y, Q.x, Q.y, px, py); }
       if (s >= 0) break;
-      if (h < best) best = h;
+      const double sc = hull_edge_score(P.x, P.y, Q.x, Q.y, px, py);
+      if (sc > best_score || (sc == best_score && h < best)) { best = h; best_score = sc; }
     }
   }
   return best;

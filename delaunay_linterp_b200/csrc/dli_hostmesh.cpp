@@ -110,6 +110,14 @@ struct HostMesh2 {
   int last = -1;  // some alive finite face
   int64_t n_finite = 0;
   std::vector<int> new_faces, removed_faces;  // finite faces touched by the last insertion
+  std::vector<int> ring_faces;                // finite faces around the cavity (one neighbour link changed)
+  // Stable compact ids of the finite faces (the ids the device mesh and export() use): an insertion hands the ids of
+  // the finite faces it removes to the faces it creates and appends the rest -- the number of finite faces never
+  // decreases (+2 inside, +1 on a hull edge, +visible edges outside), so the id space stays 0 .. n_finite-1 and an
+  // insertion changes only the ids of its own star (incremental device update, dli_mesh_update).
+  std::vector<int> fid;       // face slot -> id (-1: infinite or dead)
+  std::vector<int> fid_free;  // ids released by the current insertion
+  bool fid_compact = true;    // false: ids must be reassigned (renumber) before the next export
   // scratch
   std::vector<int> cavity, stack;
   std::vector<uint8_t> mark;
@@ -118,9 +126,24 @@ struct HostMesh2 {
   int new_face() {
     int id;
     if (!freelist.empty()) { id = freelist.back(); freelist.pop_back(); }
-    else { id = (int)fc.size(); fc.push_back(Face()); alive.push_back(0); gen.push_back(0); mark.push_back(0); }
+    else { id = (int)fc.size(); fc.push_back(Face()); alive.push_back(0); gen.push_back(0); mark.push_back(0); fid.push_back(-1); }
     alive[id] = 1;
+    fid[id] = -1;
     return id;
+  }
+  // ids for the finite faces created by an insertion (after the removed ones released theirs)
+  void assign_ids(int64_t finite_before) {
+    int64_t next_id = finite_before;  // ids in use before this insertion: 0 .. finite_before-1
+    for (int f : new_faces) {
+      if (!fid_free.empty()) { fid[f] = fid_free.back(); fid_free.pop_back(); }
+      else fid[f] = (int)next_id++;
+    }
+    if (!fid_free.empty()) { fid_free.clear(); fid_compact = false; }  // cannot happen for a Delaunay insertion
+  }
+  void renumber() {
+    int c = 0;
+    for (int f = 0; f < (int)fc.size(); f++) fid[f] = (alive[f] && !is_inf(f)) ? c++ : -1;
+    fid_compact = true;
   }
   int o3(int a, int b, double px, double py) const { return orient(X[a], Y[a], X[b], Y[b], px, py); }
   bool lex_less(int a, int b) const { return X[a] < X[b] || (X[a] == X[b] && Y[a] < Y[b]); }
@@ -209,7 +232,9 @@ struct HostMesh2 {
   int insert(double px, double py, double fv, bool *is_new) {
     new_faces.clear();
     removed_faces.clear();
+    ring_faces.clear();
     *is_new = true;
+    const int64_t finite_before = n_finite;
     int nv = (int)X.size();
     if (dim < 2) {
       for (int v = 0; v < nv; v++)
@@ -237,6 +262,7 @@ struct HostMesh2 {
       link_all();
       last = new_faces[0];
       dim = 2;
+      assign_ids(finite_before);
       return p;
     }
     int loc = locate(px, py);
@@ -282,6 +308,7 @@ struct HostMesh2 {
       Face &o = fc[be[i].out];
       for (int k = 0; k < 3; k++)
         if (o.v[(k + 1) % 3] == be[i].b && o.v[(k + 2) % 3] == be[i].a) o.n[k] = id;
+      if (!is_inf(be[i].out)) ring_faces.push_back(be[i].out);
       start_at[be[i].a] = id;
     }
     for (size_t i = 0; i < be.size(); i++) {
@@ -294,11 +321,13 @@ struct HostMesh2 {
       mark[f] = 0;
       alive[f] = 0;
       gen[f]++;
-      if (!is_inf(f)) { removed_faces.push_back(f); n_finite--; }
+      if (!is_inf(f)) { removed_faces.push_back(f); n_finite--; fid_free.push_back(fid[f]); }
+      fid[f] = -1;
       freelist.push_back(f);
     }
     for (int id : created)
       if (!is_inf(id)) { new_faces.push_back(id); n_finite++; }
+    assign_ids(finite_before);
     last = new_faces.empty() ? last : new_faces[0];
     return p;
   }
@@ -346,7 +375,38 @@ struct dli_di2 {
   bool dirty = true;
   dli_options opt;
   bool have_opt = false;
+  // incremental device update (the reference's dirty set is the star returned by
+  // insert_and_get_modifications, src/delaunay_2_interp.h:434-448): face slots and vertices changed since the device
+  // mesh was last in step with the triangulation
+  bool need_full = true;            // the next refresh re-creates the device mesh
+  std::vector<int> pend_faces;      // face slots created or re-linked since the last refresh (may hold dead slots)
+  std::vector<int> pend_values;     // existing vertices whose value was overwritten
+  int64_t nv_synced = 0;            // vertices the device mesh holds
+  int64_t n_full = 0, n_incremental = 0;
 
+  // flattened triangulation under the stable face ids (HostMesh2::fid); any pointer may be NULL
+  void flatten(double *coords, int32_t *tri, int32_t *nbr, int32_t *handle) {
+    if (!hm.fid_compact) { hm.renumber(); need_full = true; }
+    int64_t nv = (int64_t)hm.X.size();
+    if (coords) for (int64_t v = 0; v < nv; v++) { coords[2 * v] = hm.X[v]; coords[2 * v + 1] = hm.Y[v]; }
+    if (!(tri || nbr || handle) || hm.dim < 2) return;
+    for (int fi = 0; fi < (int)hm.fc.size(); fi++) {
+      int t = hm.alive[fi] ? hm.fid[fi] : -1;
+      if (t < 0) continue;
+      if (handle) handle[t] = fi;
+      for (int j = 0; j < 3; j++) {
+        if (tri) tri[3 * t + j] = hm.fc[fi].v[j];
+        if (nbr) nbr[3 * t + j] = hm.fid[hm.fc[fi].n[j]];   // -1 for an infinite neighbour
+      }
+    }
+  }
+
+  void synced(bool full) {
+    dirty = false; need_full = false;
+    pend_faces.clear(); pend_values.clear();
+    nv_synced = (int64_t)hm.X.size();
+    (full ? n_full : n_incremental)++;
+  }
   bool entry_live(const QEntry &e) const { return hm.alive[e.face] && hm.gen[e.face] == e.gen; }
   void push(double err, double f, double x, double y, int face) {
     pq.push(QEntry{err, f, x, y, seq++, face, hm.gen[face]});
@@ -381,8 +441,21 @@ struct dli_di2 {
   }
   int insert(double x, double y, double f) {
     bool is_new;
+    const bool had_mesh = hm.dim == 2;
     int v = hm.insert(x, y, f, &is_new);
     dirty = true;
+    if (!had_mesh) need_full = true;
+    if (!need_full) {
+      if (!is_new) {
+        pend_values.push_back(v);
+        for (int fi = 0; fi < (int)hm.fc.size(); fi++)   // the star's interpolants change with the value
+          if (hm.alive[fi] && !hm.is_inf(fi) && (hm.fc[fi].v[0] == v || hm.fc[fi].v[1] == v || hm.fc[fi].v[2] == v))
+            pend_faces.push_back(fi);
+      }
+      pend_faces.insert(pend_faces.end(), hm.new_faces.begin(), hm.new_faces.end());
+      pend_faces.insert(pend_faces.end(), hm.ring_faces.begin(), hm.ring_faces.end());
+      if ((int64_t)pend_faces.size() > hm.n_finite) need_full = true;   // cheaper to start over
+    }
     if (fn) {
       for (int r : hm.removed_faces) drop_face_entries(r);
       if (nent.size() < hm.fc.size()) nent.resize(hm.fc.size(), 0);
@@ -422,6 +495,7 @@ int32_t dli_di2_insert(dli_di2 *d, double x, double y, double f) {
 
 int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f, int spatial_sort, int use_gpu) {
   if (!d || n < 0 || (n > 0 && (!xy || !f))) return DLI_ERR_ARG;
+  d->need_full = true;
   std::vector<int64_t> order((size_t)n);
   for (int64_t i = 0; i < n; i++) order[i] = i;
   if (spatial_sort && n > 1) {
@@ -457,24 +531,12 @@ int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f
   int64_t nv = (int64_t)hm.X.size(), nf = hm.n_finite;
   std::vector<double> coords((size_t)nv * 2);
   std::vector<int32_t> tri((size_t)nf * 3), nbr((size_t)nf * 3), handle((size_t)nf);
-  {
-    std::vector<int> compact(hm.fc.size(), -1);
-    int c = 0;
-    for (int fi = 0; fi < (int)hm.fc.size(); fi++)
-      if (hm.alive[fi] && !hm.is_inf(fi)) { compact[fi] = c; handle[c] = fi; c++; }
-    for (int64_t v = 0; v < nv; v++) { coords[2 * v] = hm.X[v]; coords[2 * v + 1] = hm.Y[v]; }
-    for (int64_t t = 0; t < nf; t++)
-      for (int j = 0; j < 3; j++) {
-        tri[3 * t + j] = hm.fc[handle[t]].v[j];
-        int nb = hm.fc[handle[t]].n[j];
-        nbr[3 * t + j] = hm.is_inf(nb) ? -1 : compact[nb];
-      }
-  }
+  d->flatten(coords.data(), tri.data(), nbr.data(), handle.data());
   if (d->mesh) { dli_mesh_destroy(d->mesh); d->mesh = nullptr; }
   int rc = dli_mesh_create(2, nv, coords.data(), hm.F.data(), nf, tri.data(), nbr.data(), d->have_opt ? &d->opt : nullptr,
                            &d->mesh);
   if (rc != DLI_OK) return rc;
-  d->dirty = false;
+  d->synced(true);
   int64_t ni = dli_simplex_error_count(d->mesh);
   if (ni < 0) return (int)ni;
   std::vector<double> cent((size_t)ni * 2), phi((size_t)ni), err((size_t)ni);
@@ -534,22 +596,8 @@ int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, in
   if (!d) return DLI_ERR_ARG;
   const HostMesh2 &hm = d->hm;
   int64_t nv = (int64_t)hm.X.size();
-  if (coords) for (int64_t v = 0; v < nv; v++) { coords[2 * v] = hm.X[v]; coords[2 * v + 1] = hm.Y[v]; }
   if (f) memcpy(f, hm.F.data(), sizeof(double) * (size_t)nv);
-  if (tri || nbr) {
-    std::vector<int> compact(hm.fc.size(), -1);
-    int c = 0;
-    for (int fi = 0; fi < (int)hm.fc.size(); fi++)
-      if (hm.alive[fi] && !hm.is_inf(fi)) compact[fi] = c++;
-    for (int fi = 0; fi < (int)hm.fc.size(); fi++) {
-      int t = compact[fi];
-      if (t < 0) continue;
-      for (int j = 0; j < 3; j++) {
-        if (tri) tri[3 * t + j] = hm.fc[fi].v[j];
-        if (nbr) { int nb = hm.fc[fi].n[j]; nbr[3 * t + j] = hm.is_inf(nb) ? -1 : compact[nb]; }
-      }
-    }
-  }
+  const_cast<dli_di2 *>(d)->flatten(coords, tri, nbr, nullptr);   // (renumbers only after a non-compact insertion)
   return DLI_OK;
 }
 
@@ -558,22 +606,57 @@ int dli_di2_set_options(dli_di2 *d, const dli_options *opt) {
   d->have_opt = opt != nullptr;
   if (opt) d->opt = *opt;
   d->dirty = true;
+  d->need_full = true;
   return DLI_OK;
+}
+
+// incremental path: hand the dirty star(s) to dli_mesh_update; DLI_ERR_UNSUPPORTED = the mesh cannot be patched
+static int di2_patch(dli_di2 *d) {
+  HostMesh2 &hm = d->hm;
+  const int64_t nv = (int64_t)hm.X.size(), nv0 = d->nv_synced, nf = hm.n_finite;
+  std::vector<double> nxy((size_t)(nv - nv0) * 2 + 2), nf_((size_t)(nv - nv0) + 1);
+  for (int64_t v = nv0; v < nv; v++) { nxy[2 * (v - nv0)] = hm.X[v]; nxy[2 * (v - nv0) + 1] = hm.Y[v]; nf_[v - nv0] = hm.F[v]; }
+  std::vector<int32_t> vid;
+  std::vector<double> vval;
+  for (int v : d->pend_values)
+    if (v < nv0) { vid.push_back(v); vval.push_back(hm.F[v]); }
+  // live finite faces among the pending slots, once each
+  std::vector<int32_t> ids, sv, sn;
+  for (int fi : d->pend_faces) {
+    if (!hm.alive[fi] || hm.fid[fi] < 0 || hm.mark[fi]) continue;
+    hm.mark[fi] = 1;
+    ids.push_back(hm.fid[fi]);
+    for (int j = 0; j < 3; j++) sv.push_back(hm.fc[fi].v[j]);
+    for (int j = 0; j < 3; j++) sn.push_back(hm.fid[hm.fc[fi].n[j]]);
+  }
+  for (int fi : d->pend_faces) hm.mark[fi] = 0;
+  return dli_mesh_update(d->mesh, nv, nxy.data(), nf_.data(), (int64_t)vid.size(), vid.data(), vval.data(), nf,
+                         (int64_t)ids.size(), ids.data(), sv.data(), sn.data());
 }
 
 static int di2_refresh(dli_di2 *d) {
   if (!d->dirty && d->mesh) return DLI_OK;
+  if (d->mesh && !d->need_full && d->hm.fid_compact && d->hm.dim == 2) {
+    int rc = di2_patch(d);
+    if (rc == DLI_OK) { d->synced(false); return DLI_OK; }
+    if (rc != DLI_ERR_UNSUPPORTED) return rc;
+  }
   if (d->mesh) { dli_mesh_destroy(d->mesh); d->mesh = nullptr; }
   int64_t nv = (int64_t)d->hm.X.size(), nf = d->hm.dim == 2 ? d->hm.n_finite : 0;
   std::vector<double> coords((size_t)nv * 2 + 2);
   std::vector<int32_t> tri((size_t)nf * 3 + 3), nbr((size_t)nf * 3 + 3);
-  dli_di2_export(d, coords.data(), nullptr, nf ? tri.data() : nullptr, nf ? nbr.data() : nullptr);
+  d->flatten(coords.data(), nf ? tri.data() : nullptr, nf ? nbr.data() : nullptr, nullptr);
   std::vector<double> fv(d->hm.F);
   fv.push_back(0.0);
   int rc = dli_mesh_create(2, nv, coords.data(), fv.data(), nf, tri.data(), nbr.data(), d->have_opt ? &d->opt : nullptr,
                            &d->mesh);
-  if (rc == DLI_OK) d->dirty = false;
+  if (rc == DLI_OK) d->synced(true);
   return rc;
+}
+
+void dli_di2_sync_counts(const dli_di2 *d, int64_t *n_full, int64_t *n_incremental) {
+  if (n_full) *n_full = d ? d->n_full : 0;
+  if (n_incremental) *n_incremental = d ? d->n_incremental : 0;
 }
 
 int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,

@@ -1145,6 +1145,50 @@ __global__ void k_pack_faces(int ns, const int4 *__restrict__ frec, ulonglong2 *
   fpack[f] = r;
 }
 
+// ---- incremental update (dli_mesh_update): the same record builders over a list of device face indices ----
+// canonical face records + id map of the listed faces
+__global__ void k_update_faces(int n, const int32_t *__restrict__ idx, const int4 *__restrict__ rows,
+                               const int32_t *__restrict__ ids, int4 *__restrict__ frec, int32_t *__restrict__ orig) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int f = idx[i];
+  frec[2 * (size_t)f] = rows[2 * (size_t)i];
+  frec[2 * (size_t)f + 1] = rows[2 * (size_t)i + 1];
+  orig[f] = ids[i];
+}
+__global__ void k_update_values(int n, const int32_t *__restrict__ vid, const double *__restrict__ val, double4 *__restrict__ vrec) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) vrec[vid[i]].z = val[i];
+}
+__global__ void k_pack_faces_list(int n, const int32_t *__restrict__ idx, const int4 *__restrict__ frec,
+                                  ulonglong2 *__restrict__ fpack) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int f = idx[i];
+  int4 a = frec[2 * (size_t)f], b = frec[2 * (size_t)f + 1];
+  unsigned long long n0 = a.w < 0 ? kPackMask : (unsigned)a.w, n1 = b.x < 0 ? kPackMask : (unsigned)b.x,
+                     n2 = b.y < 0 ? kPackMask : (unsigned)b.y;
+  ulonglong2 r;
+  r.x = (unsigned long long)(unsigned)a.x | ((unsigned long long)(unsigned)a.y << 21) | ((unsigned long long)(unsigned)a.z << 42);
+  r.y = n0 | (n1 << 21) | (n2 << 42);
+  fpack[f] = r;
+}
+// walk records of the listed faces (absolute neighbour ids); n_slow_delta accumulates (new slow flag - old slow flag),
+// faces at index >= old_ns had no record
+__global__ void k_build_fat2_list(int n, const int32_t *__restrict__ idx, int old_ns, const int4 *__restrict__ frec,
+                                  const double4 *__restrict__ vrec, uint4 *__restrict__ fat, int *__restrict__ n_slow_delta) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int f = idx[i];
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
+  auto enc = [](int nb) -> unsigned long long { return nb < 0 ? (unsigned long long)kPackMask : (unsigned long long)(unsigned)nb; };
+  unsigned long long nbr = enc(r0.w) | (enc(r1.x) << 21) | (enc(r1.y) << 42);
+  int was = 0;
+  if (f < old_ns) was = (fat[4 * (size_t)f + 3].w >> 31) & 1u;   // kFatSlow = bit 63 of the neighbour word
+  const int is = make_fat2(vrec[r0.x], vrec[r0.y], vrec[r0.z], nbr, fat + 4 * (size_t)f) ? 1 : 0;
+  if (is != was) atomicAdd(n_slow_delta, is - was);
+}
+
 __global__ void k_fill_nomesh(int64_t n, double *ys, int32_t *simplex_out, uint8_t *status_out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;

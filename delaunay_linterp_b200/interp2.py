@@ -79,8 +79,9 @@ class DelaunayInterp2:
         return [(float(err[i]), float(f[i]), [float(xy[i, 0]), float(xy[i, 1])]) for i in range(n)]
 
     # ---- the hot path (GPU)
-    def interp(self, x, return_status=False):
-        """interp([x, y]) -> float (reference form) or interp(ndarray (n, 2) / torch CUDA tensor) -> array."""
+    def interp(self, x, return_status=False, return_simplex=False):
+        """interp([x, y]) -> float (reference form) or interp(ndarray (n, 2) / torch CUDA tensor) -> array.
+        return_simplex (numpy form): also the located face, in the numbering of export()."""
         if _is_torch_tensor(x):
             import torch
             xs = x.contiguous().view(-1, 2)
@@ -95,11 +96,15 @@ class DelaunayInterp2:
         n = xs.shape[0]
         ys = np.empty(n, np.float64)
         st = np.empty(n, np.uint8)
-        check(lib().dli_di2_interp(self._h, n, xs.ctypes.data, ys.ctypes.data, None, st.ctypes.data, None))
+        sx = np.empty(n, np.int32) if return_simplex else None
+        check(lib().dli_di2_interp(self._h, n, xs.ctypes.data, ys.ctypes.data, sx.ctypes.data if return_simplex else None,
+                                   st.ctypes.data, None))
         if scalar:
             if st[0] >= 3:   # no simplex contains the point: the reference throws std::invalid_argument (:546-551)
                 raise ValueError("interp: no simplex containing the point could be found")
             return float(ys[0])
+        if return_simplex:
+            return (ys, sx, st) if return_status else (ys, sx)
         return (ys, st) if return_status else ys
 
     def gradient(self, x, return_status=False):
@@ -145,6 +150,13 @@ class DelaunayInterp2:
         check(lib().dli_di2_export(self._h, c.ctypes.data, f.ctypes.data, t.ctypes.data if nf else None,
                                    nb.ctypes.data if nf else None))
         return c, f, t, nb
+
+    def sync_counts(self):
+        """(full re-flattens, in-place patches) of the device mesh so far: after insert / insert_largest_error_point
+        the next interp only re-sends the stars of the inserted points (dli_mesh_update, SURVEY 8(f) #2)."""
+        a, b = C.c_int64(), C.c_int64()
+        lib().dli_di2_sync_counts(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
 
     @property
     def n_vertices(self):

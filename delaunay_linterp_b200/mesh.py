@@ -106,6 +106,27 @@ class Mesh:
             raise ValueError("f must be (n_vertices,)")
         check(lib().dli_mesh_set_values(self._h, f.ctypes.data))
 
+    def update(self, new_coords, new_f, n_simplices_total, dirty_ids, dirty_vertices, dirty_neighbors,
+               value_ids=None, values=None):
+        """Patch the device mesh in place after insertions (dli_mesh_update; the reference's dirty set is the star
+        of the inserted vertex, src/delaunay_2_interp.h:434-448).  Returns False when the mesh cannot be patched
+        (DLI_ERR_UNSUPPORTED) and has to be re-created; the mesh is unchanged in that case."""
+        nc = np.ascontiguousarray(new_coords, dtype=np.float64).reshape(-1, self.dim)
+        nf = np.ascontiguousarray(new_f, dtype=np.float64).reshape(-1)
+        ids = np.ascontiguousarray(dirty_ids, dtype=np.int32).reshape(-1)
+        sv = np.ascontiguousarray(dirty_vertices, dtype=np.int32).reshape(-1, self.dim + 1)
+        sn = np.ascontiguousarray(dirty_neighbors, dtype=np.int32).reshape(-1, self.dim + 1)
+        vi = np.ascontiguousarray(value_ids if value_ids is not None else [], dtype=np.int32).reshape(-1)
+        vv = np.ascontiguousarray(values if values is not None else [], dtype=np.float64).reshape(-1)
+        assert nc.shape[0] == nf.shape[0] and ids.shape[0] == sv.shape[0] == sn.shape[0] and vi.shape[0] == vv.shape[0]
+        rc = lib().dli_mesh_update(self._h, self.n_vertices + nc.shape[0], nc.ctypes.data, nf.ctypes.data, vi.shape[0],
+                                   vi.ctypes.data, vv.ctypes.data, int(n_simplices_total), ids.shape[0], ids.ctypes.data,
+                                   sv.ctypes.data, sn.ctypes.data)
+        if rc == -5:
+            return False
+        check(rc)
+        return True
+
     # ---- the hot path
     def interp(self, xs, return_simplex=False, return_status=False, out=None, stream=None):
         """Batched interp(xs) -> ys.  xs: (n, dim) float64 numpy array or torch CUDA tensor."""

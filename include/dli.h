@@ -111,6 +111,31 @@ int dli_mesh_create(int dim, int64_t n_vertices, const double *coords, const dou
 /* same geometry, new vertex values (vertex->info() = f, src/delaunay_2_interp.h:446) */
 int dli_mesh_set_values(dli_mesh *mesh, const double *f /* [n_vertices], host */);
 
+/*
+ * Incremental update after insertions (2D).  Replaces the reference's per-insert bookkeeping: the dirty set of an
+ * insertion is the star of the new vertex (insert_and_get_modifications, src/delaunay_2_interp.h:434-448; value
+ * overwrite of an existing vertex :446) -- only those simplices are re-sent and re-derived on the device (canonical
+ * records, packed records, walk records, hull-edge table when the hull changed) instead of flattening the whole mesh.
+ *   n_vertices_total   vertices after the update; the (n_vertices_total - old n_vertices) new ones are appended:
+ *                      new_coords [.][2], new_f [.]
+ *   n_value_changes    existing vertices whose value changed: value_ids [.], values [.]
+ *   n_simplices_total  simplices after the update.  The caller's id space stays compact: a simplex that disappeared
+ *                      hands its id to a new one, further new simplices are appended (ids >= old n_simplices)
+ *   n_dirty            simplices whose vertex list, neighbour list or vertex values differ from what the mesh holds:
+ *                      dirty_ids [.] (each id once), dirty_vertices [.][3] (any orientation), dirty_neighbors [.][3]
+ *                      (-1 across the hull).  Every id >= old n_simplices must be listed.
+ * Start hints are kept (an id that is reused stays in the neighbourhood of its old simplex), so hint quality decays
+ * slowly with many updates; re-create the mesh now and then (dli_host.h does, see di2_refresh).
+ * Returns DLI_ERR_UNSUPPORTED -- mesh unchanged -- when the mesh cannot be patched and must be re-created: not 2D, a
+ * replica or loaded snapshot (no host connectivity), cell-indexed or delta-encoded walk records, ids that no longer
+ * fit the packed records, or a new vertex outside the bounding box of the start-hint grid.
+ * No interp / locate call may be in flight on the mesh.
+ */
+int dli_mesh_update(dli_mesh *mesh, int64_t n_vertices_total, const double *new_coords, const double *new_f,
+                    int64_t n_value_changes, const int32_t *value_ids, const double *values, int64_t n_simplices_total,
+                    int64_t n_dirty, const int32_t *dirty_ids, const int32_t *dirty_vertices,
+                    const int32_t *dirty_neighbors);
+
 void dli_mesh_destroy(dli_mesh *mesh);
 
 int dli_mesh_dim(const dli_mesh *mesh);

@@ -63,13 +63,17 @@ int dli_di2_dimension(const dli_di2 *d);
 /* flattened triangulation: coords [nv][2], f [nv], tri [nf][3] (ccw), nbr [nf][3] (-1 = hull); any may be NULL */
 int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, int32_t *nbr);
 
-/* batched interp on the GPU; (re)flattens lazily after insertions.  Host or device pointers as dli_interp.
+/* batched interp on the GPU; after insertions the device mesh is brought in step lazily: the stars of the inserted
+   points are patched in place (dli_mesh_update, ids of export() are stable across insertions), a full re-flatten
+   happens after bulk insertion, when more faces changed than exist, or when the mesh cannot be patched.  Host or device pointers as dli_interp.
    With dimension < 2 every query reports DLI_STATUS_NO_MESH (the reference throws, :546-551). */
 int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
                    void *stream);
 /* batched gradient on the GPU (dli_gradient): grads [n][2]; NaN outside the hull (:610-611, :618) */
 int dli_di2_gradient(dli_di2 *d, int64_t n, const double *xs, double *grads, int32_t *simplex_out, uint8_t *status_out,
                      void *stream);
+/* how often the device mesh was re-created / patched in place (dli_mesh_update) so far */
+void dli_di2_sync_counts(const dli_di2 *d, int64_t *n_full, int64_t *n_incremental);
 /* the device mesh currently backing dli_di2_interp (NULL before the first interp); owned by d */
 const dli_mesh *dli_di2_device_mesh(dli_di2 *d);
 int dli_di2_set_options(dli_di2 *d, const dli_options *opt);

@@ -580,11 +580,24 @@ static void project_on_line(const double *P, const double *Q, double *p) {
   p[0] = x; p[1] = y;
 }
 
-/* among the hull edges strictly visible from p (a contiguous chain containing h0) pick the
-   one with the smallest index: a canonical stand-in for "whichever infinite face CGAL's walk
-   ended in" (src/delaunay_2_interp.h:530-545), which is walk-dependent in the reference. */
+/* Among the hull edges strictly visible from p (a contiguous chain containing h0) pick the one whose supporting
+   line is farthest from p (largest det^2 / |PQ|^2 in plain fp64, ties: smallest index): a canonical stand-in for
+   "whichever infinite face CGAL's walk ended in" (src/delaunay_2_interp.h:530-545), which is walk-dependent in the
+   reference.  Farthest-line-first guarantees progress: after a projection p sits on the line of the edge it was
+   projected on, within rounding, and that edge may still test "strictly visible" by an ulp; preferring it again
+   (e.g. a smallest-index rule) would re-project p on the same line forever while the edge that p is really
+   outside of is never chosen -- the reference escapes that loop through CGAL's stochastic walk. */
+static double hull_edge_score(const dlo_mesh *m, const double *p, int32_t h) {
+  int32_t t = m->ht[h], s = m->hs[h];
+  const double *P = m->x + (size_t)m->sv[t * 3 + (s + 1) % 3] * 2;
+  const double *Q = m->x + (size_t)m->sv[t * 3 + (s + 2) % 3] * 2;
+  double dx = Q[0] - P[0], dy = Q[1] - P[1];
+  double det = dx * (p[1] - P[1]) - dy * (p[0] - P[0]);
+  return (det * det) / (dx * dx + dy * dy);
+}
 static int32_t canonical_visible_hull_edge(const dlo_mesh *m, const double *p, int32_t h0) {
   int32_t best = h0;
+  double best_score = hull_edge_score(m, p, h0);
   const double *pp[3];
   for (int dir = 0; dir < 2; dir++) {
     int32_t h = h0;
@@ -596,7 +609,8 @@ static int32_t canonical_visible_hull_edge(const dlo_mesh *m, const double *p, i
       pp[1] = m->x + (size_t)m->sv[t * 3 + (s + 2) % 3] * 2;
       pp[2] = p;
       if (orient_sign(2, pp) >= 0) break;
-      if (h < best) best = h;
+      double sc = hull_edge_score(m, p, h);
+      if (sc > best_score || (sc == best_score && h < best)) { best = h; best_score = sc; }
     }
   }
   return best;

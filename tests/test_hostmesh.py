@@ -122,3 +122,33 @@ def test_degenerate_sequences():
         area += 0.5 * ((c[b, 0] - c[a, 0]) * (c[cc, 1] - c[a, 1]) - (c[cc, 0] - c[a, 0]) * (c[b, 1] - c[a, 1]))
     from scipy.spatial import ConvexHull
     assert abs(area - ConvexHull(c).volume) < 1e-12
+
+
+def test_export_ids_are_stable_and_compact_across_insertions():
+    """an insertion changes only the ids of its own star (ids of removed faces are handed to new
+    ones, the rest appended), the id space stays 0..n_faces-1 and the export stays a consistent triangulation."""
+    import delaunay_linterp_b200 as dl
+    rng = np.random.default_rng(5)
+    t = dl.DelaunayInterp2()
+    pts = rng.random((400, 2))
+    t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False)
+    c0, f0, tri0, nb0 = t.export()
+    extra = np.concatenate([rng.random((150, 2)), rng.random((30, 2)) * 3.0 - 1.0])   # inside and outside the hull
+    for p in extra:
+        c_prev, _, tri_prev, _ = t.export()
+        t.insert([float(p[0]), float(p[1])], 1.0)
+        c, f, tri, nb = t.export()
+        assert tri.shape[0] == t.n_faces and tri.shape[0] > tri_prev.shape[0]
+        same = np.all(tri[: tri_prev.shape[0]] == tri_prev, axis=1)
+        changed = int((~same).sum()) + tri.shape[0] - tri_prev.shape[0]
+        star = int(np.sum(np.any(tri == c.shape[0] - 1, axis=1)))
+        assert changed == star                   # exactly the faces of the new vertex's star carry new content
+    # neighbour links consistent: nb[t][k] shares the edge opposite vertex k
+    for s in range(tri.shape[0]):
+        for k in range(3):
+            n = nb[s, k]
+            if n >= 0:
+                e = {tri[s, (k + 1) % 3], tri[s, (k + 2) % 3]}
+                assert e <= set(tri[n].tolist()) and s in nb[n]
+    sv, _ = helpers.scipy_mesh(c)
+    assert _tri_key(tri, c) == _tri_key(sv, c)
