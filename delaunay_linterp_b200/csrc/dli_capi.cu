@@ -6,6 +6,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
@@ -83,6 +84,8 @@ struct dli_mesh {
   int64_t cap_v = 0, cap_s = 0;
   int32_t cap_h = 0;
   int64_t n_updates = 0;
+  unsigned char *d_upd = nullptr;   // grow-only device scratch of dli_mesh_update
+  size_t upd_cap = 0;
   // device buffers
   double *d_vrec = nullptr;
   int32_t *d_srec = nullptr;
@@ -136,6 +139,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_slot_face);
   cudaFree(m->d_rowstart);
   cudaFree(m->d_item_verts);
+  cudaFree(m->d_upd);
   cudaFree(m->d_stats);
   pipe_free(m->pipe);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
@@ -468,7 +472,7 @@ static int resolve_options(const dli_options *opt, dli_options *out) {
 // 2D hull-edge table {face (caller id), slot, next, prev} in the order (face id, slot) ascending; enc_sn gets ~h in
 // the hull slots (the device encoding of a hull neighbour)
 static void hull_table2(int64_t nv, int64_t ns, const std::vector<int32_t> &sv, const std::vector<int32_t> &sn,
-                        std::vector<int4> &hull, std::vector<int32_t> &enc_sn) {
+                        std::vector<int4> &hull, std::vector<int32_t> *enc_sn) {
   hull.clear();
   std::vector<int32_t> from((size_t)nv, -1), to((size_t)nv, -1);
   for (int64_t s = 0; s < ns; s++)
@@ -478,7 +482,7 @@ static void hull_table2(int64_t nv, int64_t ns, const std::vector<int32_t> &sv, 
         hull.push_back(make_int4((int)s, j, -1, -1));
         from[sv[s * 3 + (j + 1) % 3]] = h;
         to[sv[s * 3 + (j + 2) % 3]] = h;
-        enc_sn[s * 3 + j] = ~h;
+        if (enc_sn) (*enc_sn)[s * 3 + j] = ~h;
       }
   for (auto &h : hull) {
     int32_t P = sv[(size_t)h.x * 3 + (h.y + 1) % 3], Q = sv[(size_t)h.x * 3 + (h.y + 2) % 3];
@@ -540,7 +544,7 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
   std::vector<int4> hull;
   std::vector<int32_t> enc_sn(m->h_sn);  // device encoding of neighbours
   if (d == 2) {
-    hull_table2(nv, ns, m->h_sv, m->h_sn, hull, enc_sn);
+    hull_table2(nv, ns, m->h_sv, m->h_sn, hull, &enc_sn);
     m->nh = (int32_t)hull.size();
   }
 
@@ -660,39 +664,46 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
   }
   DeviceGuard guard(m->device);
   if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_update: cannot select device");
-  // ---- host connectivity: orientation-canonical rows of the dirty simplices
-  std::vector<double> xy(m->h_xy);
-  xy.insert(xy.end(), new_coords, new_coords + (size_t)(nv_total - nv0) * 2);
-  std::vector<int32_t> sv(m->h_sv), sn(m->h_sn);
-  sv.resize((size_t)ns_total * 3, 0);
-  sn.resize((size_t)ns_total * 3, -1);
+  // ---- host connectivity: orientation-canonical rows of the dirty simplices (checked first, then applied in place)
+  auto X = [&](int32_t v, int c) { return v < nv0 ? m->h_xy[2 * (size_t)v + c] : new_coords[2 * (size_t)(v - nv0) + c]; };
+  std::vector<uint8_t> flip((size_t)n_dirty, 0);
   bool hull_touched = false;
+  for (int64_t i = 0; i < n_dirty; i++) {
+    const int64_t s = dirty_ids[i];
+    const int32_t *v = dirty_sv + 3 * i;
+    const int o = orient2d(X(v[0], 0), X(v[0], 1), X(v[1], 0), X(v[1], 1), X(v[2], 0), X(v[2], 1));
+    if (o == 0) return fail(DLI_ERR_MESH, "dli_mesh_update: degenerate simplex (zero area)");
+    flip[(size_t)i] = o < 0;
+    for (int j = 0; j < 3; j++)
+      if (dirty_sn[3 * i + j] < 0 || (s < ns0 && m->h_sn[(size_t)s * 3 + j] < 0)) hull_touched = true;
+  }
+  m->h_xy.insert(m->h_xy.end(), new_coords, new_coords + (size_t)(nv_total - nv0) * 2);
+  m->h_sv.resize((size_t)ns_total * 3, 0);
+  m->h_sn.resize((size_t)ns_total * 3, -1);
+  std::vector<int32_t> &sv = m->h_sv, &sn = m->h_sn;
   for (int64_t i = 0; i < n_dirty; i++) {
     const int64_t s = dirty_ids[i];
     int32_t v[3] = {dirty_sv[3 * i], dirty_sv[3 * i + 1], dirty_sv[3 * i + 2]};
     int32_t nb[3] = {dirty_sn[3 * i], dirty_sn[3 * i + 1], dirty_sn[3 * i + 2]};
-    const int o = orient2d(xy[2 * (size_t)v[0]], xy[2 * (size_t)v[0] + 1], xy[2 * (size_t)v[1]], xy[2 * (size_t)v[1] + 1],
-                           xy[2 * (size_t)v[2]], xy[2 * (size_t)v[2] + 1]);
-    if (o == 0) return fail(DLI_ERR_MESH, "dli_mesh_update: degenerate simplex (zero area)");
-    if (o < 0) { std::swap(v[0], v[1]); std::swap(nb[0], nb[1]); }
+    if (flip[(size_t)i]) { std::swap(v[0], v[1]); std::swap(nb[0], nb[1]); }
     for (int j = 0; j < 3; j++) {
-      if (nb[j] < 0) nb[j] = -1;
-      if (nb[j] < 0 || (s < ns0 && sn[(size_t)s * 3 + j] < 0)) hull_touched = true;
       sv[(size_t)s * 3 + j] = v[j];
-      sn[(size_t)s * 3 + j] = nb[j];
+      sn[(size_t)s * 3 + j] = nb[j] < 0 ? -1 : nb[j];
     }
   }
   // ---- the set of simplices to re-send: the dirty ones, plus every hull-adjacent one when the hull table is rebuilt
   std::vector<int32_t> list(dirty_ids, dirty_ids + n_dirty);
   std::vector<int4> hull;
-  std::vector<int32_t> enc(sn);
+  std::unordered_map<int64_t, int32_t> hull_of;   // face * 3 + slot -> hull edge (only filled when the hull is rebuilt)
   if (hull_touched) {
-    hull_table2(nv_total, ns_total, sv, sn, hull, enc);
+    hull_table2(nv_total, ns_total, sv, sn, hull, nullptr);
     std::vector<uint8_t> in_list((size_t)ns_total, 0);
     for (int32_t s : list) in_list[(size_t)s] = 1;
-    for (const int4 &h : hull)
-      if (!in_list[(size_t)h.x]) { in_list[(size_t)h.x] = 1; list.push_back(h.x); }
-    if (hull.size() > 0x7ffffff0u) return fail(DLI_ERR_MESH, "dli_mesh_update: hull too large");
+    hull_of.reserve(hull.size() * 2);
+    for (size_t h = 0; h < hull.size(); h++) {
+      hull_of[(int64_t)hull[h].x * 3 + hull[h].y] = (int32_t)h;
+      if (!in_list[(size_t)hull[h].x]) { in_list[(size_t)hull[h].x] = 1; list.push_back(hull[h].x); }
+    }
   }
   // (without a hull change the ~h encodings of untouched simplices stay valid and no dirty simplex has a hull slot)
   auto dev_index = [&](int64_t s) -> int32_t { return s < ns0 ? m->h_inv[(size_t)s] : (int32_t)s; };
@@ -702,9 +713,9 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
     const int64_t s = list[(size_t)i];
     idx[(size_t)i] = dev_index(s);
     for (int j = 0; j < 3; j++) {
-      const int32_t nb = enc[(size_t)s * 3 + j];
+      const int32_t nb = sn[(size_t)s * 3 + j];
       rows[(size_t)i * 8 + j] = sv[(size_t)s * 3 + j];
-      rows[(size_t)i * 8 + 3 + j] = nb >= 0 ? dev_index(nb) : nb;
+      rows[(size_t)i * 8 + 3 + j] = nb >= 0 ? dev_index(nb) : ~hull_of.at(s * 3 + j);
     }
   }
   for (auto &h : hull) h.x = dev_index(h.x);
@@ -729,55 +740,57 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
     if (e == cudaSuccess) m->cap_h = cap;
   }
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed: ") + cudaGetErrorString(e));
-  // ---- upload + rebuild the derived records of the listed simplices
-  int32_t *d_idx = nullptr, *d_ids = nullptr, *d_vid = nullptr;
-  int4 *d_rows = nullptr;
-  double *d_val = nullptr;
-  int *d_delta = nullptr;
-  int delta = 0;
+  // ---- upload + rebuild the derived records of the listed simplices (one scratch buffer, one upload)
   const int64_t nnew = nv_total - nv0;
-  if (nnew > 0) {
-    std::vector<double> vrec((size_t)nnew * 4, 0.0);
-    for (int64_t v = 0; v < nnew; v++) { vrec[4 * v] = new_coords[2 * v]; vrec[4 * v + 1] = new_coords[2 * v + 1]; vrec[4 * v + 2] = new_f[v]; }
-    e = cudaMemcpy(m->d_vrec + (size_t)nv0 * 4, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t o_idx = 0, o_ids = al(o_idx + sizeof(int32_t) * (size_t)nl), o_rows = al(o_ids + sizeof(int32_t) * (size_t)nl),
+               o_vid = al(o_rows + sizeof(int32_t) * 8 * (size_t)nl), o_val = al(o_vid + sizeof(int32_t) * (size_t)n_fchg),
+               o_new = al(o_val + sizeof(double) * (size_t)n_fchg), o_delta = al(o_new + sizeof(double) * 4 * (size_t)nnew),
+               total = o_delta + 256;
+  if (total > m->upd_cap) {
+    cudaFree(m->d_upd); m->d_upd = nullptr; m->upd_cap = 0;
+    e = cudaMalloc(&m->d_upd, total * 2);
+    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: scratch allocation failed: ") + cudaGetErrorString(e));
+    m->upd_cap = total * 2;
   }
-  if (e == cudaSuccess && n_fchg > 0) {
-    e = cudaMalloc(&d_vid, sizeof(int32_t) * (size_t)n_fchg);
-    if (e == cudaSuccess) e = cudaMalloc(&d_val, sizeof(double) * (size_t)n_fchg);
-    if (e == cudaSuccess) e = cudaMemcpy(d_vid, fchg_ids, sizeof(int32_t) * (size_t)n_fchg, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(d_val, fchg_vals, sizeof(double) * (size_t)n_fchg, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess)
-      k_update_values<<<(unsigned)((n_fchg + 127) / 128), 128>>>((int)n_fchg, d_vid, d_val, reinterpret_cast<double4 *>(m->d_vrec));
+  std::vector<unsigned char> stage(total, 0);
+  memcpy(stage.data() + o_idx, idx.data(), sizeof(int32_t) * (size_t)nl);
+  memcpy(stage.data() + o_ids, list.data(), sizeof(int32_t) * (size_t)nl);
+  memcpy(stage.data() + o_rows, rows.data(), sizeof(int32_t) * 8 * (size_t)nl);
+  if (n_fchg > 0) {
+    memcpy(stage.data() + o_vid, fchg_ids, sizeof(int32_t) * (size_t)n_fchg);
+    memcpy(stage.data() + o_val, fchg_vals, sizeof(double) * (size_t)n_fchg);
   }
+  {
+    double *vr = reinterpret_cast<double *>(stage.data() + o_new);
+    for (int64_t v = 0; v < nnew; v++) { vr[4 * v] = new_coords[2 * v]; vr[4 * v + 1] = new_coords[2 * v + 1]; vr[4 * v + 2] = new_f[v]; }
+  }
+  int delta = 0;
+  e = cudaMemcpy(m->d_upd, stage.data(), total, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && nnew > 0)
+    e = cudaMemcpyAsync(m->d_vrec + (size_t)nv0 * 4, m->d_upd + o_new, sizeof(double) * 4 * (size_t)nnew, cudaMemcpyDeviceToDevice, 0);
+  if (e == cudaSuccess && n_fchg > 0)
+    k_update_values<<<(unsigned)((n_fchg + 127) / 128), 128>>>((int)n_fchg, reinterpret_cast<const int32_t *>(m->d_upd + o_vid),
+                                                               reinterpret_cast<const double *>(m->d_upd + o_val),
+                                                               reinterpret_cast<double4 *>(m->d_vrec));
   if (e == cudaSuccess && nl > 0) {
-    e = cudaMalloc(&d_idx, sizeof(int32_t) * (size_t)nl);
-    if (e == cudaSuccess) e = cudaMalloc(&d_ids, sizeof(int32_t) * (size_t)nl);
-    if (e == cudaSuccess) e = cudaMalloc(&d_rows, sizeof(int32_t) * (size_t)nl * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&d_delta, sizeof(int));
-    if (e == cudaSuccess) e = cudaMemset(d_delta, 0, sizeof(int));
-    if (e == cudaSuccess) e = cudaMemcpy(d_idx, idx.data(), sizeof(int32_t) * (size_t)nl, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(d_ids, list.data(), sizeof(int32_t) * (size_t)nl, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(d_rows, rows.data(), sizeof(int32_t) * (size_t)nl * 8, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) {
-      const unsigned gb = (unsigned)((nl + 127) / 128);
-      int4 *frec = reinterpret_cast<int4 *>(m->d_srec);
-      k_update_faces<<<gb, 128>>>((int)nl, d_idx, d_rows, d_ids, frec, m->d_orig);
-      if (m->d_fpack) k_pack_faces_list<<<gb, 128>>>((int)nl, d_idx, frec, m->d_fpack);
-      if (m->d_fat)
-        k_build_fat2_list<<<gb, 128>>>((int)nl, d_idx, (int)ns0, frec, reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_delta);
-      e = cudaGetLastError();
-      if (e == cudaSuccess) e = cudaMemcpy(&delta, d_delta, sizeof delta, cudaMemcpyDeviceToHost);
-    }
+    const unsigned gb = (unsigned)((nl + 127) / 128);
+    int4 *frec = reinterpret_cast<int4 *>(m->d_srec);
+    const int32_t *d_idx = reinterpret_cast<const int32_t *>(m->d_upd + o_idx);
+    k_update_faces<<<gb, 128>>>((int)nl, d_idx, reinterpret_cast<const int4 *>(m->d_upd + o_rows),
+                                reinterpret_cast<const int32_t *>(m->d_upd + o_ids), frec, m->d_orig);
+    if (m->d_fpack) k_pack_faces_list<<<gb, 128>>>((int)nl, d_idx, frec, m->d_fpack);
+    if (m->d_fat)
+      k_build_fat2_list<<<gb, 128>>>((int)nl, d_idx, (int)ns0, frec, reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat,
+                                     reinterpret_cast<int *>(m->d_upd + o_delta));
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpy(&delta, m->d_upd + o_delta, sizeof delta, cudaMemcpyDeviceToHost);
   }
   if (e == cudaSuccess && hull_touched && !hull.empty())
     e = cudaMemcpy(m->d_hull, hull.data(), sizeof(int4) * hull.size(), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
-  cudaFree(d_idx); cudaFree(d_ids); cudaFree(d_rows); cudaFree(d_vid); cudaFree(d_val); cudaFree(d_delta);
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
   // ---- commit the host side
-  m->h_xy.swap(xy);
-  m->h_sv.swap(sv);
-  m->h_sn.swap(sn);
   m->h_inv.resize((size_t)ns_total);
   for (int64_t s = ns0; s < ns_total; s++) m->h_inv[(size_t)s] = (int32_t)s;
   m->nv = nv_total; m->ns = ns_total; m->nslots = ns_total;
