@@ -95,6 +95,7 @@ SYMBOLS = [
 ]
 
 DLI_FN = C.CFUNCTYPE(C.c_double, C.c_int, C.POINTER(C.c_double), C.c_void_p)
+DLI_FN_BATCH = C.CFUNCTYPE(None, C.c_int, C.c_int64, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_void_p)
 
 # include/dli_host.h
 HOST_SYMBOLS = [
@@ -104,6 +105,7 @@ HOST_SYMBOLS = [
     ("dli_di2_insert_many", C.c_int, [_vp, C.c_int64, _vp, _vp, C.c_int, C.c_int]),
     ("dli_di2_insert_largest_error_point", C.c_int, [_vp, _dp, _dp, _dp]),
     ("dli_di2_get_largest_error_tuple", C.c_int, [_vp, _dp, _dp, _dp]),
+    ("dli_di2_refine", C.c_int64, [_vp, C.c_int64, C.c_double, DLI_FN_BATCH, _vp, _vp, _vp, _vp]),
     ("dli_di2_error_queue_size", C.c_int64, [_vp]),
     ("dli_di2_get_error_queue", C.c_int, [_vp, _vp, _vp, _vp]),
     ("dli_di2_num_vertices", C.c_int64, [_vp]),

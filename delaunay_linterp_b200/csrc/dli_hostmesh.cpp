@@ -11,6 +11,7 @@
 #include <cstring>
 #include <queue>
 #include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 #include "../../include/dli_error_math.h"
@@ -570,6 +571,82 @@ int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, doubl
   if (xy) { xy[0] = e.x; xy[1] = e.y; }
   d->insert(e.x, e.y, e.f);
   return DLI_OK;
+}
+// k-at-a-time adaptive refinement.  Sequential semantics are kept wherever the k insertions do not
+// interact: tuples are taken in queue order; a tuple whose face shares a vertex with a face already taken in this
+// round stays in the queue (its star could overlap the earlier one); a tuple whose face a previous insertion of the
+// round destroyed is dropped with its face, exactly as insert() drops the entries of removed faces (:459-474).  The
+// errors of every face created in the round are then evaluated in ONE batch: centroids of the faces and of their
+// hull edges -> one call of the batched callback -> the closed form of include/dli_error_math.h (the same code
+// k_error_finish runs on the device; a round holds a few items per inserted point, so it is evaluated on the host).
+int64_t dli_di2_refine(dli_di2 *d, int64_t k, double rel_threshold, dli_fn_batch fnb, void *user_b, double *err_out, double *f_out,
+                       double *xy_out) {
+  if (!d || k < 0 || (!d->fn && !fnb)) return DLI_ERR_ARG;
+  double top_err = -1.0;
+  HostMesh2 &hm = d->hm;
+  std::vector<QEntry> deferred;
+  std::vector<int> round_faces;          // faces created in this round (may die again within the round)
+  std::unordered_set<int> taken;         // vertices of the faces taken in this round
+  dli_fn fn = d->fn;
+  int64_t done = 0;
+  while (done < k) {
+    d->prune();
+    if (d->pq.empty()) break;
+    QEntry e = d->pq.top();
+    if (top_err < 0.0) top_err = e.err;
+    else if (e.err < rel_threshold * top_err) break;   // the rest of the queue is not worth a point yet
+    d->pq.pop();
+    d->nent[e.face]--; d->live--;        // (entry is live: prune() left it on top)
+    const Face &t = hm.fc[e.face];
+    if (taken.count(t.v[0]) || taken.count(t.v[1]) || taken.count(t.v[2])) { deferred.push_back(e); continue; }
+    for (int j = 0; j < 3; j++) taken.insert(t.v[j]);
+    d->fn = nullptr;                     // insert without per-face callbacks; the queue entries of removed faces are
+    d->insert(e.x, e.y, e.f);            // dropped below
+    d->fn = fn;
+    for (int r : hm.removed_faces) d->drop_face_entries(r);
+    if (d->nent.size() < hm.fc.size()) d->nent.resize(hm.fc.size(), 0);
+    round_faces.insert(round_faces.end(), hm.new_faces.begin(), hm.new_faces.end());
+    if (err_out) err_out[done] = e.err;
+    if (f_out) f_out[done] = e.f;
+    if (xy_out) { xy_out[2 * done] = e.x; xy_out[2 * done + 1] = e.y; }
+    done++;
+  }
+  for (const QEntry &e : deferred)       // back into the queue, unless their face died meanwhile
+    if (d->entry_live(e)) { d->pq.push(e); d->nent[e.face]++; d->live++; }
+  // ---- items of the faces that survived the round: the face, then its hull edges by ascending slot (the order
+  //      add_face_errors pushes them in)
+  std::vector<int> item_face;
+  std::vector<double> w, cent;           // lifted vertices [item][<=3][3] (padded), centroids [item][2]
+  std::vector<int> item_nv;
+  for (int fi : round_faces) {
+    if (!hm.alive[fi] || hm.is_inf(fi) || hm.mark[fi]) continue;
+    hm.mark[fi] = 1;
+    const Face &t = hm.fc[fi];
+    double tw[9];
+    for (int i = 0; i < 3; i++) { tw[i * 3] = hm.X[t.v[i]]; tw[i * 3 + 1] = hm.Y[t.v[i]]; tw[i * 3 + 2] = hm.F[t.v[i]]; }
+    item_face.push_back(fi); item_nv.push_back(3);
+    w.insert(w.end(), tw, tw + 9);
+    cent.push_back((tw[0] + tw[3] + tw[6]) / 3); cent.push_back((tw[1] + tw[4] + tw[7]) / 3);
+    for (int j = 0; j < 3; j++)
+      if (hm.is_inf(t.n[j])) {
+        double e[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        int c = 0;
+        for (int i = 0; i < 3; i++)
+          if (i != j) { e[c * 3] = tw[i * 3]; e[c * 3 + 1] = tw[i * 3 + 1]; e[c * 3 + 2] = tw[i * 3 + 2]; c++; }
+        item_face.push_back(fi); item_nv.push_back(2);
+        w.insert(w.end(), e, e + 9);
+        cent.push_back((e[0] + e[3]) / 2); cent.push_back((e[1] + e[4]) / 2);
+      }
+  }
+  for (int fi : round_faces) hm.mark[fi] = 0;
+  const int64_t ni = (int64_t)item_face.size();
+  std::vector<double> phi((size_t)ni);
+  if (fnb) { if (ni > 0) fnb(2, ni, cent.data(), phi.data(), user_b); }
+  else for (int64_t i = 0; i < ni; i++) phi[(size_t)i] = fn(2, &cent[2 * (size_t)i], d->user);
+  for (int64_t i = 0; i < ni; i++)
+    d->push(dli_simplex_error<2>(item_nv[(size_t)i], &w[9 * (size_t)i], phi[(size_t)i]), phi[(size_t)i], cent[2 * (size_t)i],
+            cent[2 * (size_t)i + 1], item_face[(size_t)i]);
+  return done;
 }
 int64_t dli_di2_error_queue_size(dli_di2 *d) { return d ? d->live : 0; }
 int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy) {

@@ -10,7 +10,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._capi import DLI_FN, DliError, check, lib
+from ._capi import DLI_FN, DLI_FN_BATCH, DliError, check, lib
 from .mesh import _is_torch_tensor, _make_options
 
 
@@ -69,6 +69,26 @@ class DelaunayInterp2:
         if rc != 0:
             raise AssertionError("insert_largest_error_point: empty queue or no callback")   # the reference asserts
         return (e.value, f.value, [xy[0], xy[1]])
+
+    def insert_largest_error_points(self, k, fn_batch=None, rel_threshold=0.25):
+        """k-at-a-time adaptive refinement (dli_di2_refine): up to k largest-error tuples on pairwise non-adjacent faces
+        are inserted, then the errors of all new faces are evaluated in one batch.  fn_batch(ndarray (n, 2)) ->
+        ndarray (n,) is called ONCE per round; None: the scalar callback is called per item.  A round stops at the first
+        tuple whose error is below rel_threshold x the round's largest error.  k = 1 is
+        insert_largest_error_point.  Returns the inserted tuples [(err, f, [x, y]), ...]."""
+        k = int(k)
+        err, f, xy = np.empty(max(k, 1)), np.empty(max(k, 1)), np.empty((max(k, 1), 2))
+        if fn_batch is not None:
+            def _tramp(nd, n, xs, out, _user):
+                a = np.ctypeslib.as_array(xs, shape=(n, nd))
+                np.ctypeslib.as_array(out, shape=(n,))[:] = np.asarray(fn_batch(a.copy()), dtype=np.float64).reshape(n)
+            cb = DLI_FN_BATCH(_tramp)
+        else:
+            cb = C.cast(None, DLI_FN_BATCH)
+        n = lib().dli_di2_refine(self._h, k, float(rel_threshold), cb, None, err.ctypes.data, f.ctypes.data, xy.ctypes.data)
+        if n < 0:
+            raise AssertionError("insert_largest_error_points: no callback")
+        return [(float(err[i]), float(f[i]), [float(xy[i, 0]), float(xy[i, 1])]) for i in range(n)]
 
     def get_largest_error_tuple(self):
         e, f, xy = C.c_double(), C.c_double(), (C.c_double * 2)()

@@ -91,6 +91,18 @@ class Delaunay_incremental_interp_2 {
     if (rc != DLI_OK) throw std::logic_error("insert_largest_error_point: empty queue or no callback");
     return ErrorTuple(e, f, Point(xy[0], xy[1]));
   }
+  // k-at-a-time form (new, dli_di2_refine): up to k largest-error tuples on pairwise non-adjacent faces are inserted,
+  // then the errors of all new faces are evaluated in one batch; fn_batch(n_dims, n, xs, out, user) is called once
+  // per round (nullptr: the scalar callback per item).  k = 1 is insert_largest_error_point().
+  std::vector<ErrorTuple> insert_largest_error_points(size_t k, dli_fn_batch fn_batch = nullptr, void *user = nullptr,
+                                                      double rel_threshold = 0.25) {
+    std::vector<double> e(k + 1), f(k + 1), xy(2 * k + 2);
+    int64_t n = dli_di2_refine(h_, (int64_t)k, rel_threshold, fn_batch, user, e.data(), f.data(), xy.data());
+    if (n < 0) throw std::logic_error("insert_largest_error_points: no callback");
+    std::vector<ErrorTuple> out;
+    for (int64_t i = 0; i < n; i++) out.push_back(ErrorTuple(e[i], f[i], Point(xy[2 * i], xy[2 * i + 1])));
+    return out;
+  }
   ErrorTuple get_largest_error_tuple() const {
     double e, f, xy[2];
     if (dli_di2_get_largest_error_tuple(h_, &e, &f, xy) != DLI_OK)

@@ -51,6 +51,19 @@ int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f
    DLI_ERR_ARG if the queue is empty or there is no callback (the reference asserts, :499-500). */
 int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, double *xy);
 int dli_di2_get_largest_error_tuple(dli_di2 *d, double *err, double *f, double *xy);
+/* batched callback: out[i] = f(xs[i]), xs [n][n_dims] */
+typedef void (*dli_fn_batch)(int n_dims, int64_t n, const double *xs, double *out, void *user);
+/* k-at-a-time adaptive refinement: takes up to k largest-error tuples in queue order -- skipping, and leaving queued,
+   tuples whose face shares a vertex with a face already taken in this round -- inserts their points with the stored
+   f (insert_largest_error_point :498-504 for each), then evaluates the errors of all faces created in the round
+   (compute_simplex_error :725-741 + add_error_of_boundary_subsimplices :683-699) in one batch with ONE call of fn_batch
+   (NULL: the scalar callback of dli_di2_create is called per item).  A round ends early at the first tuple whose error
+   is below rel_threshold x (the round's largest error), so that a large k does not spend points on faces that are
+   already good (0 = take everything).  k = 1 is insert_largest_error_point.  Returns the
+   number of points inserted (< k when the queue runs out) or a negative error; err/f/xy [k] receive the tuples (may
+   be NULL). */
+int64_t dli_di2_refine(dli_di2 *d, int64_t k, double rel_threshold, dli_fn_batch fn_batch, void *user, double *err,
+                       double *f, double *xy);
 int64_t dli_di2_error_queue_size(dli_di2 *d);
 /* all live tuples ordered by decreasing error; arrays of dli_di2_error_queue_size() entries */
 int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy);

@@ -105,8 +105,29 @@ static int run(double lo, const char *want_regular, const char *want_adaptive, b
   return 0;
 }
 
+static void fn_batch(int nd, int64_t n, const double *xs, double *out, void *) {
+  for (int64_t i = 0; i < n; i++) out[i] = pow(xs[i * nd], 0.3) * pow(xs[i * nd + 1], 0.6);
+}
+// k-at-a-time refinement through the header: k = 1 equals the sequential call; a batched round inserts several points
+static int run_refine() {
+  Delaunay_incremental_interp_2 a(fn), b(fn), c(fn);
+  double corners[4][2] = {{0.01, 0.01}, {0.01, 5.0}, {5.0, 0.01}, {5.0, 5.0}};
+  for (auto &p : corners) { a.insert(p, p + 2, fn(2, p)); b.insert(p, p + 2, fn(2, p)); c.insert(p, p + 2, fn(2, p)); }
+  for (int i = 0; i < 50; i++) {
+    ErrorTuple ta = a.insert_largest_error_point();
+    vector<ErrorTuple> tb = b.insert_largest_error_points(1, fn_batch);
+    CHECK(tb.size() == 1 && tb[0].m_err == ta.m_err && tb[0].m_f == ta.m_f);
+  }
+  CHECK(a.get_largest_error_tuple().m_err == b.get_largest_error_tuple().m_err);
+  size_t total = 0, rounds = 0;
+  while (total < 300) { total += c.insert_largest_error_points(32, fn_batch).size(); rounds++; }
+  CHECK(rounds * 4 < total);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   bool host_only = argc > 1 && strcmp(argv[1], "--host") == 0;
+  if (run_refine()) return 1;
   // README.md:130-131 (grid on [0,5]) and the src/delaunay_2_test2.cpp variant (grid on [0.01,5])
   if (run(0.0, "5.800002", "0.044019", host_only)) return 1;
   if (run(0.01, "1.909975", nullptr, host_only)) return 1;

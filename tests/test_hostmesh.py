@@ -152,3 +152,68 @@ def test_export_ids_are_stable_and_compact_across_insertions():
                 assert e <= set(tri[n].tolist()) and s in nb[n]
     sv, _ = helpers.scipy_mesh(c)
     assert _tri_key(tri, c) == _tri_key(sv, c)
+
+
+def _corners(t):
+    for p in ([0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]):
+        t.insert(p, _fn(p))
+
+
+def test_refine_with_k_1_is_insert_largest_error_point():
+    """the batched refinement with k = 1 reproduces the sequential loop tuple by tuple and leaves
+    the same queue (same entries, same order)."""
+    import delaunay_linterp_b200 as dl
+    a, b = dl.DelaunayInterp2(_fn), dl.DelaunayInterp2(_fn)
+    _corners(a); _corners(b)
+    for _ in range(150):
+        ta = a.insert_largest_error_point()
+        tb = b.insert_largest_error_points(1)
+        assert [ta] == tb
+    assert a.get_error_queue() == b.get_error_queue()
+    assert np.array_equal(a.export()[2], b.export()[2])
+
+
+def test_refine_k_at_a_time_batched_callback():
+    import delaunay_linterp_b200 as dl
+    calls = []
+
+    def fb(x):
+        calls.append(x.shape[0])
+        return x[:, 0] ** 0.3 * x[:, 1] ** 0.6
+
+    t = dl.DelaunayInterp2(_fn)
+    _corners(t)
+    n_ins = rounds = 0
+    while n_ins < 1500:
+        got = t.insert_largest_error_points(64, fn_batch=fb)
+        assert 1 <= len(got) <= 64
+        errs = [g[0] for g in got]
+        assert errs == sorted(errs, reverse=True)          # taken in queue order
+        assert errs[-1] >= 0.25 * errs[0]                  # default rel_threshold
+        n_ins += len(got)
+        rounds += 1
+    assert len(calls) == rounds and t.n_vertices == 4 + n_ins   # ONE callback per round
+    assert rounds * 8 < n_ins                                   # rounds really are batched
+    # the triangulation is the Delaunay triangulation of its vertices, and the queue holds exactly the entries a
+    # from-scratch evaluation of this triangulation gives (every face + every hull edge, nothing stale)
+    c, f, tri, nb = t.export()
+    sv, _ = helpers.scipy_mesh(c)
+    assert _tri_key(tri, c) == _tri_key(sv, c)
+    q = sorted((round(e, 18), round(x[0], 12), round(x[1], 12)) for e, _, x in t.get_error_queue())
+    u = dl.DelaunayInterp2(_fn)
+    u.insert_many(c, f, use_gpu=False)
+    qu = sorted((round(e, 18), round(x[0], 12), round(x[1], 12)) for e, _, x in u.get_error_queue())
+    assert len(q) == len(qu) == tri.shape[0] + int((nb < 0).sum())
+    assert np.allclose([a[0] for a in q], [a[0] for a in qu], rtol=1e-9, atol=1e-300)
+    # quality: same budget of points, error of the same order as the one-at-a-time loop
+    s = dl.DelaunayInterp2(_fn)
+    _corners(s)
+    for _ in range(n_ins):
+        s.insert_largest_error_point()
+    q = np.random.default_rng(1).random((20000, 2)) * 4.99 + 0.01
+    sse = []
+    for m in (t, s):
+        cm, fm, trim, nbm = m.export()
+        ys, _, _ = OracleMesh(cm, fm, trim, nbm).interp(q, nthreads=4)
+        sse.append(float(np.sum((helpers.cobb_douglas(q) - ys) ** 2)))
+    assert sse[0] <= 1.5 * sse[1], sse
