@@ -76,6 +76,8 @@ SYMBOLS = [
     ("dli_simplex_error_count", C.c_int64, [_vp]),
     ("dli_simplex_error_prepare", C.c_int, [_vp, _vp, _vp, _vp]),
     ("dli_simplex_error_finish", C.c_int, [_vp, C.c_int64, _vp, _vp]),
+    ("dli_mesh_num_edges", C.c_int64, [_vp]),
+    ("dli_mesh_line_segments", C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     ("dli_mesh_header", C.c_int, [_vp, C.POINTER(C.c_int64)]),
     ("dli_mesh_create_from_header", C.c_int, [C.POINTER(C.c_int64), C.POINTER(Options), C.POINTER(_vp)]),
     ("dli_mesh_num_buffers", C.c_int, [_vp]),
@@ -119,6 +121,7 @@ HOST_SYMBOLS = [
     ("dli_di2_set_options", C.c_int, [_vp, C.POINTER(Options)]),
     ("dli_di2_get_all_vertices", C.c_int64, [_vp, _vp]),
     ("dli_di2_get_line_segments", C.c_int64, [_vp, _vp]),
+    ("dli_di2_line_segments", C.c_int64, [_vp, _vp, _vp, _vp, _vp]),
 ]
 
 _lib = None

@@ -1,6 +1,7 @@
 // dli_capi.cu -- the C ABI (include/dli.h): flattener, hint-grid build, batched interp / locate
 // dispatch (device-pointer and host-pointer paths), error evaluator, replication support.
 #include <algorithm>
+#include <cfloat>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -1134,6 +1135,72 @@ extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
       }
     }
   }
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// plot data (2D)
+// ---------------------------------------------------------------------------------------------
+extern "C" int64_t dli_mesh_num_edges(const dli_mesh *m) {
+  if (!m) return fail(DLI_ERR_ARG, "dli_mesh_num_edges: NULL mesh");
+  if (m->dim != 2) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_num_edges: 2D meshes only");
+  return (3 * m->ns + m->nh) / 2;   // every interior edge is shared by two faces, every hull edge by one
+}
+
+extern "C" int dli_mesh_line_segments(const dli_mesh *m, double *segments, int32_t *concave, double *min_coords,
+                                      double *max_coords) {
+  if (!m) return fail(DLI_ERR_ARG, "dli_mesh_line_segments: NULL mesh");
+  if (m->dim != 2) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_line_segments: 2D meshes only (as is_edge_concave)");
+  DeviceGuard guard(m->device);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_line_segments: cannot select device");
+  const int64_t ne = (3 * m->ns + m->nh) / 2;
+  const int ns = (int)m->ns;
+  if (ne == 0) {   // no finite edge: nothing visited (:845-846)
+    for (int k = 0; k < 3; k++) { if (min_coords) min_coords[k] = DBL_MAX; if (max_coords) max_coords[k] = -DBL_MAX; }
+    return DLI_OK;
+  }
+  int *d_cnt = nullptr, *d_off = nullptr;
+  double *d_seg = nullptr;
+  int32_t *d_cc = nullptr;
+  void *d_tmp = nullptr;
+  size_t tmp_bytes = 0;
+  cudaError_t e = cudaMalloc(&d_cnt, sizeof(int) * (size_t)ns);
+  if (e == cudaSuccess) e = cudaMalloc(&d_off, sizeof(int) * (size_t)ns);
+  if (e == cudaSuccess) e = cudaMalloc(&d_seg, sizeof(double) * 6 * (size_t)ne);
+  if (e == cudaSuccess) e = cudaMalloc(&d_cc, sizeof(int32_t) * (size_t)ne);
+  if (e == cudaSuccess) e = cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_cnt, d_off, ns);
+  if (e == cudaSuccess) e = cudaMalloc(&d_tmp, std::max<size_t>(tmp_bytes, 16));
+  if (e == cudaSuccess) {
+    const unsigned gb = (unsigned)((ns + 127) / 128);
+    const int4 *frec = reinterpret_cast<const int4 *>(m->d_srec);
+    k_edge_count<<<gb, 128>>>(ns, frec, m->d_orig, d_cnt);
+    e = cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_cnt, d_off, ns);
+    if (e == cudaSuccess) {
+      k_edge_emit<<<gb, 128>>>(ns, frec, reinterpret_cast<const double4 *>(m->d_vrec), m->d_orig, d_off, d_seg, d_cc);
+      e = cudaGetLastError();
+    }
+  }
+  if (e == cudaSuccess && (min_coords || max_coords)) {
+    const int nb = 296;
+    double *d_part = nullptr;
+    std::vector<double> part((size_t)nb * 6);
+    e = cudaMalloc(&d_part, sizeof(double) * part.size());
+    if (e == cudaSuccess) {
+      k_point_minmax<<<nb, 256>>>(2 * ne, d_seg, d_part);
+      e = cudaMemcpy(part.data(), d_part, sizeof(double) * part.size(), cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_part);
+    for (int k = 0; k < 3 && e == cudaSuccess; k++) {
+      double lo = DBL_MAX, hi = -DBL_MAX;     // the reference's initial values (:845-846)
+      for (int b = 0; b < nb; b++) { lo = std::min(lo, part[(size_t)b * 6 + k]); hi = std::max(hi, part[(size_t)b * 6 + 3 + k]); }
+      if (min_coords) min_coords[k] = lo;
+      if (max_coords) max_coords[k] = hi;
+    }
+  }
+  if (e == cudaSuccess && segments) e = cudaMemcpy(segments, d_seg, sizeof(double) * 6 * (size_t)ne, cudaMemcpyDefault);
+  if (e == cudaSuccess && concave) e = cudaMemcpy(concave, d_cc, sizeof(int32_t) * (size_t)ne, cudaMemcpyDefault);
+  cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_seg); cudaFree(d_cc); cudaFree(d_tmp);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_line_segments: ") + cudaGetErrorString(e));
   return DLI_OK;
 }
 

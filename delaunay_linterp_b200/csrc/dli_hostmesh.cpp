@@ -756,6 +756,20 @@ const dli_mesh *dli_di2_device_mesh(dli_di2 *d) {
   return d->mesh;
 }
 
+// get_line_segments with concavity flags and min / max (src/delaunay_2_interp.h:842-862, :766-803), batched on the GPU
+int64_t dli_di2_line_segments(dli_di2 *d, double *segments, int32_t *concave, double *min_coords, double *max_coords) {
+  if (!d) return DLI_ERR_ARG;
+  int rc = di2_refresh(d);
+  if (rc != DLI_OK) return rc;
+  int64_t ne = dli_mesh_num_edges(d->mesh);
+  if (ne < 0) return ne;
+  if (segments || concave || min_coords || max_coords) {
+    rc = dli_mesh_line_segments(d->mesh, segments, concave, min_coords, max_coords);
+    if (rc != DLI_OK) return rc;
+  }
+  return ne;
+}
+
 int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz) {
   if (!d) return 0;
   int64_t nv = (int64_t)d->hm.X.size();

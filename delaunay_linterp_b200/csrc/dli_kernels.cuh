@@ -1,6 +1,7 @@
 // dli_kernels.cuh -- __global__ kernels (sm_100a): batched interp (fast + straggler/exact pass),
 // hint-grid construction, per-simplex error evaluator, predicate test hook.
 #pragma once
+#include <cfloat>
 #include "dli_device.cuh"
 #include "../../include/dli_error_math.h"
 
@@ -1130,6 +1131,108 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
     }
   }
   if (STATS) flush_stats(stats, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Plot data (2D): get_line_segments (src/delaunay_2_interp.h:842-862) with the concavity flag of is_edge_concave
+// (:766-803), every finite edge once, from the face with the lower caller id (CGAL's edge order is arbitrary).
+// ---------------------------------------------------------------------------------------------
+// exact sign of a x + b y + c for double coefficients (Line_2::oriented_side, filtered-exact in Epick)
+__device__ inline int line_side_exact(double a, double b, double c, double x, double y) {
+  double e[5], p, q;
+  int n = 0;
+  two_prod(a, x, p, q);
+  grow(e, n, q); grow(e, n, p);
+  two_prod(b, y, p, q);
+  grow(e, n, q); grow(e, n, p);
+  grow(e, n, c);
+  return expansion_sign(e, n);
+}
+// CGAL Cartesian Line_2(P, Q) in plain doubles (same construction as project_on_line)
+__device__ inline void line_from_points(double Px, double Py, double Qx, double Qy, double &a, double &b, double &c) {
+  if (Py == Qy) {
+    a = 0.0;
+    if (Qx > Px) { b = 1.0; c = -Py; }
+    else if (Qx == Px) { b = 0.0; c = 0.0; }
+    else { b = -1.0; c = Py; }
+  } else if (Qx == Px) {
+    b = 0.0;
+    if (Qy > Py) { a = -1.0; c = Px; }
+    else { a = 1.0; c = -Px; }
+  } else {
+    a = Py - Qy;
+    b = Qx - Px;
+    c = -Px * a - Py * b;
+  }
+}
+__device__ __forceinline__ bool edge_emitted(const int32_t *__restrict__ orig, int f, int nb) {
+  return nb < 0 || __ldg(orig + f) < __ldg(orig + nb);
+}
+// per face: number of edges it emits
+__global__ void k_edge_count(int ns, const int4 *__restrict__ frec, const int32_t *__restrict__ orig, int *__restrict__ cnt) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns) return;
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
+  cnt[f] = (int)edge_emitted(orig, f, r0.w) + (int)edge_emitted(orig, f, r1.x) + (int)edge_emitted(orig, f, r1.y);
+}
+// segments [ne][2][3] = (P.x, P.y, f_P, Q.x, Q.y, f_Q) with P = vertex ccw(j), Q = vertex cw(j) of the emitting face
+__global__ void k_edge_emit(int ns, const int4 *__restrict__ frec, const double4 *__restrict__ vrec,
+                            const int32_t *__restrict__ orig, const int *__restrict__ offs, double *__restrict__ seg,
+                            int32_t *__restrict__ concave) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= ns) return;
+  int4 r0 = frec[2 * (size_t)f], r1 = frec[2 * (size_t)f + 1];
+  const int v[3] = {r0.x, r0.y, r0.z}, nbs[3] = {r0.w, r1.x, r1.y};
+  const double4 V[3] = {vrec[v[0]], vrec[v[1]], vrec[v[2]]};
+  int o = offs[f];
+  double2 g1 = make_double2(0.0, 0.0);
+  bool have_g1 = false;
+  for (int j = 0; j < 3; j++) {
+    const int nb = nbs[j];
+    if (!edge_emitted(orig, f, nb)) continue;
+    const double4 P = V[(j + 1) % 3], Q = V[(j + 2) % 3], R = V[j];
+    double *row = seg + 6 * (size_t)o;
+    row[0] = P.x; row[1] = P.y; row[2] = P.z; row[3] = Q.x; row[4] = Q.y; row[5] = Q.z;
+    int flag = 1;                                   // an infinite face on either side (:778-780)
+    if (nb >= 0) {
+      if (!have_g1) { g1 = face_gradient2(V[0], V[1], V[2]); have_g1 = true; }
+      int4 n0 = frec[2 * (size_t)nb];
+      const double2 g2 = face_gradient2(vrec[n0.x], vrec[n0.y], vrec[n0.z]);
+      double dgx = g2.x - g1.x, dgy = g2.y - g1.y;
+      double a, b, c;
+      line_from_points(P.x, P.y, Q.x, Q.y, a, b, c);
+      const int side1 = line_side_exact(a, b, c, R.x, R.y);
+      const int sl = line_side_exact(a, b, c, P.x - 1.0, P.y), sd = line_side_exact(a, b, c, P.x, P.y - 1.0);
+      if (sl == 0) dgx = 0.0; else if (sl != side1) dgx = -dgx;
+      if (sd == 0) dgy = 0.0; else if (sd != side1) dgy = -dgy;
+      flag = (dgx <= 0.0 && dgy <= 0.0) ? 1 : 0;
+    }
+    concave[o] = flag;
+    o++;
+  }
+}
+// min / max of (x, y, f) over the n end points ([n][3]) of the segments: per-block partials [gridDim.x][6]
+__global__ void k_point_minmax(int64_t n, const double *__restrict__ pts, double *__restrict__ part) {
+  double mn[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, mx[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    const double3 a = make_double3(pts[3 * v], pts[3 * v + 1], pts[3 * v + 2]);
+    mn[0] = fmin(mn[0], a.x); mn[1] = fmin(mn[1], a.y); mn[2] = fmin(mn[2], a.z);
+    mx[0] = fmax(mx[0], a.x); mx[1] = fmax(mx[1], a.y); mx[2] = fmax(mx[2], a.z);
+  }
+  __shared__ double sh[6][8];
+  for (int k = 0; k < 3; k++)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) for (int k = 0; k < 3; k++) { sh[k][w] = mn[k]; sh[3 + k][w] = mx[k]; }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    double r = sh[threadIdx.x][0];
+    for (int i = 1; i < (int)(blockDim.x >> 5); i++) r = threadIdx.x < 3 ? fmin(r, sh[threadIdx.x][i]) : fmax(r, sh[threadIdx.x][i]);
+    part[(size_t)blockIdx.x * 6 + threadIdx.x] = r;
+  }
 }
 
 // 32-byte face records -> 16-byte packed records (see Mesh2View::fpack)

@@ -162,6 +162,19 @@ class DelaunayInterp2:
         return a.tolist()
 
     def get_line_segments(self):
+        """(all_segments, min_coords, max_coords) as the reference returns it (src/delaunay_2_interp.h:842-862,
+        delaunay_2.py:65): all_segments = [([x, y, f], [x, y, f], is_concave), ...] with the flag of is_edge_concave
+        (:766-803); computed on the GPU (dli_mesh_line_segments)."""
+        ne = check(lib().dli_di2_line_segments(self._h, None, None, None, None))
+        seg = np.empty((ne, 2, 3))
+        cc = np.empty(ne, np.int32)
+        mn, mx = np.empty(3), np.empty(3)
+        check(lib().dli_di2_line_segments(self._h, seg.ctypes.data, cc.ctypes.data, mn.ctypes.data, mx.ctypes.data))
+        s = seg.tolist()
+        return [(s[i][0], s[i][1], int(cc[i])) for i in range(ne)], mn.tolist(), mx.tolist()
+
+    def get_edges(self):
+        """host-side list of the finite edges [[x, y, f], [x, y, f]] (no GPU, no flags)."""
         n = lib().dli_di2_get_line_segments(self._h, None)
         a = np.empty((n, 2, 3))
         lib().dli_di2_get_line_segments(self._h, a.ctypes.data)

@@ -196,14 +196,26 @@ class Delaunay_incremental_interp_d:
         return [list(p) + [f] for p, f in zip(self._pts, self._f)]
 
     def get_line_segments(self):
+        """(all_segments, min_coords, max_coords) as the reference returns it (src/delaunay_d_interp.h:1115-1142): the
+        segments of a simplex are its consecutive vertex pairs (i, i+1 mod N+1) (:1103-1112), every pair once, flag 1."""
+        n1 = self.N + 1
+        lo, hi = [float(np.finfo(np.float64).max)] * n1, [-float(np.finfo(np.float64).max)] * n1
         if self._tri is None:
-            return []
+            return [], lo, hi
         sv, _ = self._current()
         edges = set()
         for s in sv:
-            for a, b in itertools.combinations(sorted(int(v) for v in s), 2):
-                edges.add((a, b))
-        return [[list(self._pts[a]) + [self._f[a]], list(self._pts[b]) + [self._f[b]]] for a, b in sorted(edges)]
+            for i in range(n1):
+                a, b = int(s[i]), int(s[(i + 1) % n1])
+                edges.add((min(a, b), max(a, b)))
+        out = []
+        for a, b in sorted(edges):
+            pa, pb = list(self._pts[a]) + [self._f[a]], list(self._pts[b]) + [self._f[b]]
+            out.append((pa, pb, 1))
+            for p in (pa, pb):
+                lo = [min(u, v) for u, v in zip(lo, p)]
+                hi = [max(u, v) for u, v in zip(hi, p)]
+        return out, lo, hi
 
     def export(self):
         sv, sn = self._current() if self._tri is not None else (np.zeros((0, self.N + 1), np.int32),) * 2

@@ -231,6 +231,17 @@ class Mesh:
         check(lib().dli_simplex_error_finish(self._h, phi.shape[0], phi.ctypes.data, err.ctypes.data))
         return err
 
+    # ---- plot data
+    def line_segments(self):
+        """2D: (segments (ne, 2, 3), concave (ne,), min (3,), max (3,)) -- get_line_segments + is_edge_concave
+        (src/delaunay_2_interp.h:842-862, :766-803) for every finite edge, computed on the device."""
+        ne = check(lib().dli_mesh_num_edges(self._h))
+        seg = np.empty((ne, 2, 3), np.float64)
+        cc = np.empty(ne, np.int32)
+        mn, mx = np.empty(3), np.empty(3)
+        check(lib().dli_mesh_line_segments(self._h, seg.ctypes.data, cc.ctypes.data, mn.ctypes.data, mx.ctypes.data))
+        return seg, cc, mn, mx
+
     # ---- instrumentation
     def collect_stats(self, enable=True, timing=False):
         """counters add atomics to the kernels; timing records CUDA events around every interp launch."""

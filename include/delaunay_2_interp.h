@@ -28,7 +28,9 @@
 #include <limits>
 #include <memory>
 #include <stdexcept>
+#include <algorithm>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "dli_host.h"
@@ -161,10 +163,28 @@ class Delaunay_incremental_interp_2 {
     if (!v.empty()) dli_di2_get_all_vertices(h_, &v[0][0]);
     return v;
   }
-  std::vector<std::array<std::array<double, 3>, 2>> get_line_segments() const {
+  // host-side list of the finite edges (no GPU, no flags)
+  std::vector<std::array<std::array<double, 3>, 2>> get_edges() const {
     std::vector<std::array<std::array<double, 3>, 2>> s((size_t)dli_di2_get_line_segments(h_, nullptr));
     if (!s.empty()) dli_di2_get_line_segments(h_, &s[0][0][0]);
     return s;
+  }
+  // for plotting (:842-862): all line segments with the is_edge_concave flag (:766-803), and the min / max at each
+  // coordinate; evaluated on the GPU for all edges at once (dli_mesh_line_segments)
+  typedef std::tuple<std::array<double, 3>, std::array<double, 3>, int> Segment;
+  std::tuple<std::vector<Segment>, std::array<double, 3>, std::array<double, 3>> get_line_segments() const {
+    int64_t ne = dli_di2_line_segments(h_, nullptr, nullptr, nullptr, nullptr);
+    check((int)std::min<int64_t>(ne, 0), "get_line_segments");
+    std::vector<double> seg((size_t)ne * 6 + 6);
+    std::vector<int32_t> cc((size_t)ne + 1);
+    std::array<double, 3> mn, mx;
+    check((int)std::min<int64_t>(dli_di2_line_segments(h_, seg.data(), cc.data(), mn.data(), mx.data()), 0), "get_line_segments");
+    std::vector<Segment> out;
+    for (int64_t i = 0; i < ne; i++) {
+      std::array<double, 3> p = {{seg[6 * i], seg[6 * i + 1], seg[6 * i + 2]}}, q = {{seg[6 * i + 3], seg[6 * i + 4], seg[6 * i + 5]}};
+      out.push_back(Segment(p, q, (int)cc[i]));
+    }
+    return std::make_tuple(out, mn, mx);
   }
 
   size_t number_of_vertices() const { return (size_t)dli_di2_num_vertices(h_); }

@@ -260,6 +260,20 @@ int dli_debug_orient_host(int dim, int64_t n, const double *pts, int8_t *sign_ou
 
 /* thread-local message for the last non-zero return on this thread */
 const char *dli_last_error(void);
+/*
+ * Plot data (2D), batched.  Replaces get_line_segments (src/delaunay_2_interp.h:842-862) and, per edge,
+ * is_edge_concave (:766-803): every finite edge once as (P.x, P.y, f_P, Q.x, Q.y, f_Q) with its concavity flag
+ * (1 on the hull, :778-780; else both components of the gradient jump across the edge, oriented by the side the
+ * first face lies on, are <= 0), and the min / max of (x, y, f) over the edge end points (:853-858).
+ * CGAL's edge iterator order is arbitrary; here: the order of the engine's face storage, an interior edge emitted
+ * by its face with the lower caller id (P = vertex ccw(slot), Q = vertex cw(slot) of that face).
+ * segments [n_edges][2][3] and concave [n_edges]: host or device pointers, either may be NULL;
+ * min_coords / max_coords [3]: host, may be NULL (DBL_MAX / -DBL_MAX when there is no edge, as the reference).
+ */
+int64_t dli_mesh_num_edges(const dli_mesh *mesh);
+int dli_mesh_line_segments(const dli_mesh *mesh, double *segments, int32_t *concave, double *min_coords,
+                           double *max_coords);
+
 /* number of CUDA devices visible (0 if none / no driver) */
 int dli_device_count(void);
 

@@ -94,6 +94,10 @@ int dli_di2_set_options(dli_di2 *d, const dli_options *opt);
 /* plot data: vertices as (x, y, f) triples [nv][3]; finite edges as segments [ne][2][3]; count query with NULL */
 int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz);
 int64_t dli_di2_get_line_segments(const dli_di2 *d, double *segments);
+/* get_line_segments as the reference returns it (:842-862): segments [ne][2][3], the is_edge_concave flag of every
+   edge (:766-803) and the min / max of (x, y, f); evaluated on the GPU (dli_mesh_line_segments).  Returns ne (call
+   with NULL arrays first), or a negative error. */
+int64_t dli_di2_line_segments(dli_di2 *d, double *segments, int32_t *concave, double *min_coords, double *max_coords);
 
 #ifdef __cplusplus
 }

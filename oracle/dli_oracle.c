@@ -24,6 +24,7 @@
  *   error metric         src/delaunay_2_interp.h:725-741, 166-192, 125-151, 108-121
  *   2D gradient          src/delaunay_2_interp.h:608-642, 574-606, 242-263  -> dlo_gradient
  *   boundary subsimplex  src/delaunay_2_interp.h:657-699, 331-342
+ *   plot data            src/delaunay_2_interp.h:842-862 (get_line_segments), 766-803 (is_edge_concave)  -> dlo_line_segments
  * Third-party behaviour restated from its published algorithm (not in the tree):
  *   CGAL Triangulation_2::locate: exact-sign visibility walk, closed faces
  *   CGAL Line_2(P,Q) / projection (Cartesian, plain double constructions)
@@ -37,6 +38,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
+#include <float.h>
 #include <stdio.h>
 #include <pthread.h>
 
@@ -987,4 +989,80 @@ void dlo_error_eval(const dlo_mesh *m, int64_t n, const int32_t *item_nv, const 
     q[d] = phi[i];
     err[i] = sqdist_point_hplane(N, q, np, w);
   }
+}
+
+/* ------------------------------------------------------------------------- */
+/* Plot data: get_line_segments (src/delaunay_2_interp.h:842-862) with the    */
+/* concavity flag of is_edge_concave (:766-803).  2D only.                    */
+/* ------------------------------------------------------------------------- */
+
+/* CGAL Cartesian Line_2(P, Q) coefficients in plain doubles (the construction project_on_line uses) */
+static void line_from_points(const double *P, const double *Q, double *a, double *b, double *c) {
+  if (P[1] == Q[1]) {
+    *a = 0.0;
+    if (Q[0] > P[0]) { *b = 1.0; *c = -P[1]; }
+    else if (Q[0] == P[0]) { *b = 0.0; *c = 0.0; }
+    else { *b = -1.0; *c = P[1]; }
+  } else if (Q[0] == P[0]) {
+    *b = 0.0;
+    if (Q[1] > P[1]) { *a = -1.0; *c = P[0]; }
+    else { *a = 1.0; *c = -P[0]; }
+  } else {
+    *a = P[1] - Q[1];
+    *b = Q[0] - P[0];
+    *c = -P[0] * *a - P[1] * *b;
+  }
+}
+/* Line_2::oriented_side: exact sign of a x + b y + c for the double coefficients (filtered-exact in Epick) */
+static int line_side(double a, double b, double c, double x, double y) {
+  double e[8], p, q;
+  int n = 0;
+  two_prod(a, x, &p, &q);
+  n = grow_expansion(n, e, q, e);
+  n = grow_expansion(n, e, p, e);
+  two_prod(b, y, &p, &q);
+  n = grow_expansion(n, e, q, e);
+  n = grow_expansion(n, e, p, e);
+  n = grow_expansion(n, e, c, e);
+  return expansion_sign(n, e);
+}
+/* is_edge_concave for the edge opposite slot j of face s (face1 = s, face2 = its neighbour) */
+static int edge_concave(const dlo_mesh *m, int32_t s, int j) {
+  int32_t nb = m->sn[(size_t)s * 3 + j];
+  if (nb < 0) return 1; /* an infinite face on either side (:778-780) */
+  const int32_t *v = m->sv + (size_t)s * 3;
+  const double *P = m->x + (size_t)v[(j + 1) % 3] * 2, *Q = m->x + (size_t)v[(j + 2) % 3] * 2;
+  const double *R = m->x + (size_t)v[j] * 2;
+  double g1[2], g2[2];
+  face_gradient(m, s, g1);
+  face_gradient(m, nb, g2);
+  double dgx = g2[0] - g1[0], dgy = g2[1] - g1[1];
+  double a, b, c;
+  line_from_points(P, Q, &a, &b, &c);
+  int side1 = line_side(a, b, c, R[0], R[1]);
+  int side_left = line_side(a, b, c, P[0] - 1.0, P[1]);
+  int side_down = line_side(a, b, c, P[0], P[1] - 1.0);
+  if (side_left == 0) dgx = 0.0; else if (side_left != side1) dgx = -dgx;
+  if (side_down == 0) dgy = 0.0; else if (side_down != side1) dgy = -dgy;
+  return (dgx <= 0.0 && dgy <= 0.0) ? 1 : 0;
+}
+/* Every finite edge once, from its lower-numbered face (CGAL's edge iterator order is arbitrary): segments
+ * [ne][2][3] = (P.x, P.y, f_P, Q.x, Q.y, f_Q) with P = vertex ccw(j), Q = vertex cw(j) of that face; concave [ne];
+ * min/max [3] over the segment end points (:853-858).  Returns ne; arrays may be NULL. */
+int64_t dlo_line_segments(const dlo_mesh *m, double *seg, int32_t *concave, double *mn, double *mx) {
+  if (m->dim != 2) return -1;
+  int64_t ne = 0;
+  if (mn) for (int k = 0; k < 3; k++) { mn[k] = DBL_MAX; mx[k] = -DBL_MAX; }
+  for (int64_t s = 0; s < m->ns; s++)
+    for (int j = 0; j < 3; j++) {
+      int32_t nb = m->sn[s * 3 + j];
+      if (nb >= 0 && nb < s) continue;
+      int32_t p = m->sv[s * 3 + (j + 1) % 3], q = m->sv[s * 3 + (j + 2) % 3];
+      double row[6] = {m->x[(size_t)p * 2], m->x[(size_t)p * 2 + 1], m->f[p], m->x[(size_t)q * 2], m->x[(size_t)q * 2 + 1], m->f[q]};
+      if (seg) memcpy(seg + 6 * ne, row, sizeof row);
+      if (concave) concave[ne] = edge_concave(m, (int32_t)s, j);
+      if (mn) for (int k = 0; k < 6; k++) { if (row[k] < mn[k % 3]) mn[k % 3] = row[k]; if (row[k] > mx[k % 3]) mx[k % 3] = row[k]; }
+      ne++;
+    }
+  return ne;
 }

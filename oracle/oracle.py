@@ -46,6 +46,8 @@ def lib():
         L.dlo_orient_filtered.argtypes = [C.c_int, dp]
         L.dlo_error_items.restype = C.c_int64
         L.dlo_error_items.argtypes = [C.c_void_p, ip, ip, ip, dp]
+        L.dlo_line_segments.restype = C.c_int64
+        L.dlo_line_segments.argtypes = [C.c_void_p, dp, ip, dp, dp]
         L.dlo_error_eval.argtypes = [C.c_void_p, C.c_int64, ip, ip, dp, dp, dp]
         _lib = L
     return _lib
@@ -137,6 +139,18 @@ class OracleMesh:
         s = np.empty(n, np.uint8)
         lib().dlo_classify(self._h, n, _dp(xs), _ip(simplex), _bp(c), _bp(s))
         return c.astype(bool), s.astype(bool)
+
+    def line_segments(self):
+        """get_line_segments (src/delaunay_2_interp.h:842-862) + is_edge_concave (:766-803):
+        (segments (ne, 2, 3), concave (ne,), min (3,), max (3,))."""
+        ne = lib().dlo_line_segments(self._h, None, None, None, None)
+        if ne < 0:
+            raise ValueError("oracle line_segments: 2D meshes only")
+        seg = np.empty((ne, 2, 3), np.float64)
+        cc = np.empty(ne, np.int32)
+        mn, mx = np.empty(3), np.empty(3)
+        lib().dlo_line_segments(self._h, _dp(seg), _ip(cc), _dp(mn), _dp(mx))
+        return seg, cc, mn, mx
 
     def error_items(self):
         n = lib().dlo_error_items(self._h, None, None, None, None)

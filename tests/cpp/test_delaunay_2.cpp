@@ -51,8 +51,16 @@ static int run(double lo, const char *want_regular, const char *want_adaptive, b
   vector<ErrorTuple> q = adaptive_triang.get_error_queue();
   for (size_t i = 0; i + 1 < q.size(); i++) CHECK(!(q[i] < q[i + 1]));
   CHECK(adaptive_triang.get_all_vertices().size() == 100);
-  CHECK(adaptive_triang.get_line_segments().size() == 100 + adaptive_triang.number_of_faces() - 1);  // Euler: E = V + F - 1
+  CHECK(adaptive_triang.get_edges().size() == 100 + adaptive_triang.number_of_faces() - 1);  // Euler: E = V + F - 1
   if (host_only) { printf("host-only checks ok (lo=%g)\n", lo); return 0; }
+  {  // get_line_segments as the reference returns it (:842-862): flags (hull edges are always 1, :778-780) + min / max
+    auto ls = adaptive_triang.get_line_segments();
+    CHECK(std::get<0>(ls).size() == 100 + adaptive_triang.number_of_faces() - 1);
+    size_t n_concave = 0;
+    for (auto &sg : std::get<0>(ls)) n_concave += std::get<2>(sg);
+    CHECK(n_concave >= 4 && n_concave <= std::get<0>(ls).size());
+    CHECK(std::get<1>(ls)[0] == lo && std::get<2>(ls)[0] == 5.0 && std::get<1>(ls)[1] == lo && std::get<2>(ls)[1] == 5.0);
+  }
 
   vector<double> interp_grid = linspace(lo, 5., 2 * n_points), true_f, reg, ada, xs;
   for (size_t i = 0; i < interp_grid.size(); i++)
