@@ -384,6 +384,7 @@ struct dli_di2 {
   std::vector<int> pend_values;     // existing vertices whose value was overwritten
   int64_t nv_synced = 0;            // vertices the device mesh holds
   int64_t n_full = 0, n_incremental = 0;
+  int64_t patched_since_full = 0, faces_at_full = 0;   // re-flatten once half the mesh has been patched (hint decay)
 
   // flattened triangulation under the stable face ids (HostMesh2::fid); any pointer may be NULL
   void flatten(double *coords, int32_t *tri, int32_t *nbr, int32_t *handle) {
@@ -407,6 +408,7 @@ struct dli_di2 {
     pend_faces.clear(); pend_values.clear();
     nv_synced = (int64_t)hm.X.size();
     (full ? n_full : n_incremental)++;
+    if (full) { patched_since_full = 0; faces_at_full = hm.n_finite; }
   }
   bool entry_live(const QEntry &e) const { return hm.alive[e.face] && hm.gen[e.face] == e.gen; }
   void push(double err, double f, double x, double y, int face) {
@@ -707,13 +709,16 @@ static int di2_patch(dli_di2 *d) {
     for (int j = 0; j < 3; j++) sn.push_back(hm.fid[hm.fc[fi].n[j]]);
   }
   for (int fi : d->pend_faces) hm.mark[fi] = 0;
+  d->patched_since_full += (int64_t)ids.size();
   return dli_mesh_update(d->mesh, nv, nxy.data(), nf_.data(), (int64_t)vid.size(), vid.data(), vval.data(), nf,
                          (int64_t)ids.size(), ids.data(), sv.data(), sn.data());
 }
 
 static int di2_refresh(dli_di2 *d) {
   if (!d->dirty && d->mesh) return DLI_OK;
-  if (d->mesh && !d->need_full && d->hm.fid_compact && d->hm.dim == 2) {
+  // the start-hint grid is not patched: once half of the mesh it was built for has been replaced, start over
+  const bool stale_hints = d->patched_since_full > std::max<int64_t>(4096, d->faces_at_full / 2);
+  if (d->mesh && !d->need_full && !stale_hints && d->hm.fid_compact && d->hm.dim == 2) {
     int rc = di2_patch(d);
     if (rc == DLI_OK) { d->synced(false); return DLI_OK; }
     if (rc != DLI_ERR_UNSUPPORTED) return rc;

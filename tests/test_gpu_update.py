@@ -72,14 +72,17 @@ def test_value_overwrite_and_growth(gpu):
     assert t.interp([float(pts[v, 0]), float(pts[v, 1])]) == 123.5
     _check_against_fresh(t, q, dl)
     assert t.sync_counts() == (1, 1)
-    # grow far past the initial capacity of the device buffers (3x the faces), refreshing as we go
+    # grow past the initial capacity of the device buffers (3x the faces), refreshing as we go; once half of the mesh
+    # has been patched the class re-flattens (the start-hint grid is not patched), so both paths alternate
     for rnd in range(10):
         new = rng.random((300, 2)) * 0.96 + 0.02
         for p in new:
             t.insert([float(p[0]), float(p[1])], float(helpers.cobb_douglas(p[None, :])[0]))
         t.interp(q[:100])
     fresh = _check_against_fresh(t, q, dl)
-    assert t.n_vertices == 4500 and t.sync_counts()[0] == 1
+    assert t.n_vertices == 4500
+    n_full, n_patch = t.sync_counts()
+    assert 2 <= n_full <= 6 and n_patch >= 6
     # the error evaluator sees the patched connectivity
     m = dl.Mesh._from_handle(dl.lib().dli_di2_device_mesh(t._h), 2)
     try:
