@@ -15,8 +15,9 @@
  *     and returns; with host pointers it runs a chunked H2D / compute / D2H pipeline and returns
  *     when the results are in the host buffers.
  *   - per-query conditions are reported in status_out, never as an error return.
- *   - a mesh handle is immutable apart from dli_mesh_set_values(); interp/locate calls on the
- *     same mesh may be issued concurrently from several host threads / streams.
+ *   - a mesh handle is immutable apart from dli_mesh_set_values() and dli_mesh_update(), which must
+ *     not run while queries on the mesh are in flight; interp/locate calls on the same mesh may be
+ *     issued concurrently from several host threads / streams.
  *   - the library needs a CUDA device (sm_100a).  There is no CPU fallback: without a device
  *     every call that touches the GPU fails with DLI_ERR_CUDA.
  */
