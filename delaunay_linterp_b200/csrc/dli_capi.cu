@@ -828,6 +828,12 @@ extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *s
 // ---------------------------------------------------------------------------------------------
 // interp / locate dispatch
 // ---------------------------------------------------------------------------------------------
+#ifndef DLI_X_FULL_CTAS
+#define DLI_X_FULL_CTAS 6     // CTAs per SM of the 2D exact pass (grid-stride over the straggler queue)
+#endif
+#ifndef DLI_X_FULL_THREADS
+#define DLI_X_FULL_THREADS 128
+#endif
 namespace {
 
 Mesh2View view2(const dli_mesh *m) {
@@ -907,7 +913,7 @@ void launch2(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
     fast<<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(
         v, n, per_warp, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
   L.mark(1);
-  k_interp2_full<STATS, EPI, OUT><<<148 * 4, 128, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
+  k_interp2_full<STATS, EPI, OUT><<<148 * DLI_X_FULL_CTAS, DLI_X_FULL_THREADS, 0, L.st>>>(v, reinterpret_cast<const double2 *>(xs), ys, so, sto, L.queue,
                                                          L.qcount, L.qcap, n, L.stats);
   L.mark(2);
   L.launches += 2;

@@ -84,6 +84,24 @@ DLI_HDI int expansion_sign(const double *e, int n) {
 // exact sign of (ax-cx)(by-cy) - (ay-cy)(bx-cx): the six surviving products of raw coordinates,
 // each split exactly with two_prod, summed exactly.
 DLI_HD inline int orient2d_exact(double ax, double ay, double bx, double by, double cx, double cy) {
+  // Common case first (Shewchuk's adaptive stage B): when the four coordinate differences are exact -- always for
+  // points on a lattice, and for most near-degenerate inputs, where the operands are close -- the determinant is the
+  // difference of two products of doubles: two two_prods and a 4-term expansion.
+  {
+    double acx, acxt, bcx, bcxt, acy, acyt, bcy, bcyt;
+    two_sum(ax, -cx, acx, acxt);
+    two_sum(bx, -cx, bcx, bcxt);
+    two_sum(ay, -cy, acy, acyt);
+    two_sum(by, -cy, bcy, bcyt);
+    if (acxt == 0.0 && bcxt == 0.0 && acyt == 0.0 && bcyt == 0.0) {
+      double l1, l0, r1, r0, e[4];
+      int n = 0;
+      two_prod(acx, bcy, l1, l0);
+      two_prod(acy, bcx, r1, r0);
+      grow(e, n, l0); grow(e, n, -r0); grow(e, n, l1); grow(e, n, -r1);
+      return expansion_sign(e, n);
+    }
+  }
   double e[12];
   int n = 0;
   const double pa[6] = {ax, -ax, -cx, -ay, ay, cy};
