@@ -20,6 +20,8 @@
 #define DLI_HDI inline
 #endif
 
+#include <cstring>
+
 namespace dli {
 
 constexpr double kEps = 1.1102230246251565e-16;  // 2^-53
@@ -205,10 +207,143 @@ struct ExactCap {  // components of the full expansion (before zero elimination)
   static constexpr int value = (D + 1) * fact * (1 << (D - 1));
 };
 
+// ---- exact sign through fixed-point integers (the common case of the exact fallback) ----
+// Every finite double is an integer multiple of a power of two.  When all (D+1) x D coordinates of a predicate fit a
+// common grid 2^g with at most 61 significant bits (coordinates of similar magnitude: true for meshes in a box unless
+// a coordinate is within 2^-8 of zero relative to the largest), the differences are 63-bit integers and the D x D
+// determinant is evaluated exactly in 128 / 256-bit two's-complement arithmetic: a few dozen integer multiplies
+// instead of an expansion of up to 96 (3D) / 960 (4D) components.  Queries that sit exactly on facets of a regular
+// grid -- every orientation test an exact zero, the filter can never certify them -- depend on this path.
+struct I256 {
+  unsigned long long w[4];  // little-endian limbs, two's complement
+};
+DLI_HDI I256 i256_from_i128(__int128 v) {
+  I256 r;
+  r.w[0] = (unsigned long long)v;
+  r.w[1] = (unsigned long long)(v >> 64);
+  r.w[2] = r.w[3] = (v < 0) ? ~0ull : 0ull;
+  return r;
+}
+DLI_HDI I256 i256_neg(const I256 &a) {
+  I256 r;
+  unsigned long long c = 1;
+  for (int i = 0; i < 4; i++) {
+    unsigned long long t = ~a.w[i] + c;
+    c = (c && t == 0) ? 1ull : 0ull;
+    r.w[i] = t;
+  }
+  return r;
+}
+DLI_HDI I256 i256_add(const I256 &a, const I256 &b) {
+  I256 r;
+  unsigned long long c = 0;
+  for (int i = 0; i < 4; i++) {
+    unsigned __int128 t = (unsigned __int128)a.w[i] + b.w[i] + c;
+    r.w[i] = (unsigned long long)t;
+    c = (unsigned long long)(t >> 64);
+  }
+  return r;
+}
+DLI_HDI I256 i256_mul_i64(const I256 &a, long long b) {  // no overflow by construction (see the bit budget above)
+  const bool na = (a.w[3] >> 63) != 0, nb = b < 0;
+  const I256 ma = na ? i256_neg(a) : a;
+  const unsigned long long mb = nb ? (unsigned long long)(-(b + 1)) + 1ull : (unsigned long long)b;
+  I256 r;
+  unsigned long long c = 0;
+  for (int i = 0; i < 4; i++) {
+    unsigned __int128 t = (unsigned __int128)ma.w[i] * mb + c;
+    r.w[i] = (unsigned long long)t;
+    c = (unsigned long long)(t >> 64);
+  }
+  return (na != nb) ? i256_neg(r) : r;
+}
+DLI_HDI int i256_sign(const I256 &a) {
+  if (a.w[3] >> 63) return -1;
+  return (a.w[0] | a.w[1] | a.w[2] | a.w[3]) ? 1 : 0;
+}
+DLI_HDI int dli_ctz64(unsigned long long m) {
+#ifdef __CUDA_ARCH__
+  return __ffsll((long long)m) - 1;
+#else
+  return __builtin_ctzll(m);
+#endif
+}
+DLI_HDI long long dli_double_bits(double x) {
+#ifdef __CUDA_ARCH__
+  return __double_as_longlong(x);
+#else
+  long long b;
+  memcpy(&b, &x, sizeof b);
+  return b;
+#endif
+}
+DLI_HDI __int128 i128_minor2(long long a, long long b, long long c, long long d) { return (__int128)a * d - (__int128)b * c; }
+// 3 x 3 determinant of 63-bit entries (row-major, stride ld)
+DLI_HDI I256 i256_det3(const long long *m, int ld) {
+  I256 r = i256_mul_i64(i256_from_i128(i128_minor2(m[ld + 1], m[ld + 2], m[2 * ld + 1], m[2 * ld + 2])), m[0]);
+  r = i256_add(r, i256_neg(i256_mul_i64(i256_from_i128(i128_minor2(m[ld], m[ld + 2], m[2 * ld], m[2 * ld + 2])), m[1])));
+  r = i256_add(r, i256_mul_i64(i256_from_i128(i128_minor2(m[ld], m[ld + 1], m[2 * ld], m[2 * ld + 1])), m[2]));
+  return r;
+}
+// exact sign of det[p_i - p_D]; false = the coordinates do not fit the fixed-point budget (caller falls back)
+template <int D>
+DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
+  static_assert(D == 3 || D == 4, "integer path is written for D = 3, 4");
+  int gexp = 1 << 30, top = -(1 << 30);
+  for (int i = 0; i < (D + 1) * D; i++) {
+    const long long b = dli_double_bits(pts[i]);
+    const int e = (int)((b >> 52) & 0x7ff);
+    const unsigned long long frac = (unsigned long long)b & ((1ull << 52) - 1);
+    if (e == 0x7ff) return false;                 // Inf / NaN
+    if (e == 0) { if (frac == 0) continue; return false; }   // zero: no constraint; subnormal: fall back
+    const unsigned long long m = frac | (1ull << 52);
+    const int lsb = e - 1075 + dli_ctz64(m), msb = e - 1023;
+    gexp = lsb < gexp ? lsb : gexp;
+    top = msb > top ? msb : top;
+  }
+  if (top < gexp) { sign = 0; return true; }      // all coordinates zero
+  if (top - gexp > 60) return false;
+  long long X[(D + 1) * D];
+  for (int i = 0; i < (D + 1) * D; i++) {
+    const long long b = dli_double_bits(pts[i]);
+    const int e = (int)((b >> 52) & 0x7ff);
+    if (e == 0) { X[i] = 0; continue; }
+    const unsigned long long m = ((unsigned long long)b & ((1ull << 52) - 1)) | (1ull << 52);
+    const int sh = e - 1075 - gexp;               // >= -ctz(m)
+    const long long v = (long long)(sh >= 0 ? m << sh : m >> (-sh));
+    X[i] = b < 0 ? -v : v;
+  }
+  long long M[D * D];
+  for (int i = 0; i < D; i++)
+    for (int j = 0; j < D; j++) M[i * D + j] = X[i * D + j] - X[D * D + j];
+  if (D == 3) {
+    sign = i256_sign(i256_det3(M, 3));
+  } else {
+    I256 acc;
+    acc.w[0] = acc.w[1] = acc.w[2] = acc.w[3] = 0;
+    for (int k = 0; k < 4; k++) {                 // Laplace expansion along row 0
+      long long sub[9];
+      for (int i = 1; i < 4; i++) {
+        int c = 0;
+        for (int j = 0; j < 4; j++)
+          if (j != k) sub[(i - 1) * 3 + c++] = M[i * 4 + j];
+      }
+      I256 t = i256_mul_i64(i256_det3(sub, 3), M[k]);
+      acc = i256_add(acc, (k & 1) ? i256_neg(t) : t);
+    }
+    sign = i256_sign(acc);
+  }
+  return true;
+}
+
 // merge-free exact accumulation: products are generated one at a time and added with grow_ze.
 // Cost O(n^2) two_sums in the worst case; n <= 96 (D=3) / 960 (D=4); it only runs when the filter fails.
 template <int D>
 DLI_HD inline int orient_exact(const double *pts) {
+  {
+    int s;
+    if (orient_exact_int<D>(pts, s)) return s;
+  }
   double e[ExactCap<D>::value];
   int n = 0;
   // iterate over the rows r left out (the Laplace expansion along the ones column) and over all

@@ -630,7 +630,7 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
 }
 
 template <int D, bool STATS, int EPI>
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(128, 3)
 k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,

@@ -49,3 +49,18 @@ def random_mesh(dim, nv, seed):
     pts = rng.random((nv, dim))
     sv, sn = scipy_mesh(pts)
     return pts, cobb_douglas(pts), sv, sn
+
+
+def lattice_predicate_inputs(d, seed=4):
+    """orientation-predicate inputs (n, d+1, d) on a regular grid i/(n-1) (full 53-bit mantissas): generic, all points
+    on an axis-aligned facet hyperplane, on a Kuhn diagonal hyperplane x_1 - x_0 = c (exact zeros), one coordinate far
+    below the others (outside the fixed-point bit budget), and a negated / shifted copy."""
+    rng = np.random.default_rng(seed)
+    n = 47
+    lat = rng.integers(0, n, (400, d + 1, d)) / float(n - 1)
+    lat[:100, :, 0] = lat[:100, :1, 0]
+    lat[100:200, :, 1] = lat[100:200, :, 0] + (lat[100:200, :1, 1] - lat[100:200, :1, 0])
+    tiny = lat.copy()[:100]
+    tiny[:, 0, 0] = 1e-30
+    neg = -lat[:100] * 3.0 + 1.0
+    return np.concatenate([lat, tiny, neg])

@@ -70,3 +70,17 @@ def test_product_does_not_touch_the_oracle():
                     if re.search(r"\boracle\b", txt) or "dlo_" in txt:
                         bad.append(os.path.join(dp, fn))
     assert not bad, bad
+
+
+def test_host_predicate_on_lattice_points_fixed_point_path():
+    """exact zeros and near-zeros on regular grids: the exact fallback's fixed-point integer path (coordinates on a
+    common 2^g grid, 256-bit determinant) against exact rationals, including inputs that do NOT fit its bit budget."""
+    import delaunay_linterp_b200 as dl
+    from oracle import pyoracle
+    import helpers
+    for d in (3, 4):
+        pts = helpers.lattice_predicate_inputs(d)
+        sign = dl.debug_orient(pts, on_device=False)
+        want = np.array([pyoracle.orient(p.tolist()) for p in pts], dtype=np.int8)
+        assert np.array_equal(sign, want)
+        assert (want == 0).sum() >= 100 and (want != 0).sum() >= 100

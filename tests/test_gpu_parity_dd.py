@@ -144,3 +144,15 @@ def test_dd_walk_record_guards(gpu, dim):
     assert cg[sto == 0].all()
     rel = np.abs(ys - yo) / np.maximum(np.abs(yo), 1e-300)
     assert rel[sto == 0].max() <= REL_TOL, rel[sto == 0].max()
+
+
+@pytest.mark.parametrize("dim", [3, 4])
+def test_device_predicate_on_lattice_points(gpu, dim):
+    """exact zeros on regular grids through the device predicate (fixed-point integer path of the exact fallback)."""
+    import delaunay_linterp_b200 as dl
+    from oracle import pyoracle
+    pts = helpers.lattice_predicate_inputs(dim)
+    sign, used_exact = dl.debug_orient(pts, on_device=True)
+    want = np.array([pyoracle.orient(p.tolist()) for p in pts], dtype=np.int8)
+    assert np.array_equal(sign, want)
+    assert used_exact[want == 0].all()
