@@ -656,12 +656,36 @@ __device__ inline uint8_t locateD_full(const MeshDView &m, const double *p, int 
     steps++;
     load_simplex_ids<D>(m, s, S);
     load_simplex_verts<D>(m, S);
-    int mv = -1;
+    // First the filter on every facet (cheap, the whole warp together), then the exact predicate only on the
+    // uncertain facets below the first certainly-negative one, lowest first: the same decision as testing the facets
+    // in order and leaving at the first negative one, but lanes resolve their k-th uncertain facet together whatever
+    // its index, instead of serialising by facet index (exact evaluation is ~10^3 instructions; on batches with
+    // many exact zeros the warp ran 3 lanes wide).
+    int mv = D + 1;
+    unsigned unc = 0;
+    unsigned skip = 0;
+#pragma unroll
+    for (int j = 0; j <= D; j++) if (S.n[j] >= 0 && S.n[j] == from) skip |= 1u << j;
+#pragma unroll 1
     for (int j = 0; j <= D; j++) {
-      if (S.n[j] >= 0 && S.n[j] == from) continue;
-      if (orient_replaced<D, true>(S, j, p, st) < 0) { mv = j; break; }
+      if (skip >> j & 1u) continue;
+      const int sg = orient_replaced<D, false>(S, j, p, st);
+      if (sg == 2) unc |= 1u << j;
+      else if (sg < 0 && j < mv) mv = j;
     }
-    if (mv < 0) break;
+    unc &= (1u << mv) - 1u;
+    while (unc) {
+      const int j = __ffs((int)unc) - 1;
+      unc &= unc - 1u;
+      double pts[(D + 1) * D];
+#pragma unroll
+      for (int i = 0; i <= D; i++)
+#pragma unroll
+        for (int k = 0; k < D; k++) pts[i * D + k] = (i == j) ? p[k] : S.x[i * D + k];
+      st.exact++;
+      if (orient_exact<D>(pts) < 0) { mv = j; unc = 0; }
+    }
+    if (mv > D) break;
     int nb = S.n[mv];
     if (nb < 0) {
       st.steps += steps; st.outside++;
@@ -790,19 +814,37 @@ __device__ __forceinline__ double dot_exact_trunc(const double *b, const double 
   return same ? h : nextafter(h, 0.0);
 }
 
-template <int D>
+// COMPACT (exact pass): the loop over the D+1 replaced vertices stays rolled -- that pass is bound by instruction
+// fetch, and D+2 unrolled copies of the pivoting LU are most of its code.  Same operations in the same order.
+template <int D, bool COMPACT = false>
 __device__ __forceinline__ double epilogueD_ref(const double *p, const SimplexD<D> &S) {
   const double *pts[D + 1];
 #pragma unroll
   for (int i = 0; i <= D; i++) pts[i] = &S.x[i * D];
-  double whole = volD<D>(pts);
   double b[D + 1];
+  if (COMPACT) {
+    double whole = 1.0;
+#pragma unroll 1
+    for (int i = -1; i <= D; i++) {
+      const double *q[D + 1];
 #pragma unroll
-  for (int i = 0; i <= D; i++) {
-    const double *q[D + 1];
+      for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
+      const double v = volD<D>(q);
+      if (i < 0) whole = v;
+      else {
 #pragma unroll
-    for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
-    b[i] = volD<D>(q) / whole;
+        for (int j = 0; j <= D; j++) if (j == i) b[j] = v / whole;
+      }
+    }
+  } else {
+    double whole = volD<D>(pts);
+#pragma unroll
+    for (int i = 0; i <= D; i++) {
+      const double *q[D + 1];
+#pragma unroll
+      for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
+      b[i] = volD<D>(q) / whole;
+    }
   }
   return dot_exact_trunc<D + 1>(b, S.f);
 }

@@ -15,9 +15,11 @@
 #if defined(__CUDACC__)
 #define DLI_HD __host__ __device__
 #define DLI_HDI __host__ __device__ __forceinline__
+#define DLI_HD_NOINLINE __host__ __device__ __noinline__
 #else
 #define DLI_HD
 #define DLI_HDI inline
+#define DLI_HD_NOINLINE __attribute__((noinline))
 #endif
 
 #include <cstring>
@@ -257,6 +259,23 @@ DLI_HDI I256 i256_mul_i64(const I256 &a, long long b) {  // no overflow by const
   }
   return (na != nb) ? i256_neg(r) : r;
 }
+DLI_HDI I256 i256_mul_i128(__int128 a, __int128 b) {   // |a|, |b| < 2^126
+  const bool neg = (a < 0) != (b < 0);
+  const unsigned __int128 ua = a < 0 ? (unsigned __int128)0 - (unsigned __int128)a : (unsigned __int128)a;
+  const unsigned __int128 ub = b < 0 ? (unsigned __int128)0 - (unsigned __int128)b : (unsigned __int128)b;
+  const unsigned long long a0 = (unsigned long long)ua, a1 = (unsigned long long)(ua >> 64);
+  const unsigned long long b0 = (unsigned long long)ub, b1 = (unsigned long long)(ub >> 64);
+  const unsigned __int128 p00 = (unsigned __int128)a0 * b0, p01 = (unsigned __int128)a0 * b1,
+                          p10 = (unsigned __int128)a1 * b0, p11 = (unsigned __int128)a1 * b1;
+  I256 r;
+  r.w[0] = (unsigned long long)p00;
+  const unsigned __int128 mid = (p00 >> 64) + (unsigned long long)p01 + (unsigned long long)p10;
+  r.w[1] = (unsigned long long)mid;
+  const unsigned __int128 hi = (mid >> 64) + (p01 >> 64) + (p10 >> 64) + (unsigned long long)p11;
+  r.w[2] = (unsigned long long)hi;
+  r.w[3] = (unsigned long long)((hi >> 64) + (p11 >> 64));
+  return neg ? i256_neg(r) : r;
+}
 DLI_HDI int i256_sign(const I256 &a) {
   if (a.w[3] >> 63) return -1;
   return (a.w[0] | a.w[1] | a.w[2] | a.w[3]) ? 1 : 0;
@@ -286,10 +305,13 @@ DLI_HDI I256 i256_det3(const long long *m, int ld) {
   return r;
 }
 // exact sign of det[p_i - p_D]; false = the coordinates do not fit the fixed-point budget (caller falls back)
+// (loops deliberately NOT unrolled: the exact pass is bound by instruction fetch -- its hot code must stay inside the
+// 32 KB L1.5 instruction cache -- not by the few hundred integer operations of one evaluation)
 template <int D>
 DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
   static_assert(D == 3 || D == 4, "integer path is written for D = 3, 4");
   int gexp = 1 << 30, top = -(1 << 30);
+#pragma unroll 1
   for (int i = 0; i < (D + 1) * D; i++) {
     const long long b = dli_double_bits(pts[i]);
     const int e = (int)((b >> 52) & 0x7ff);
@@ -304,6 +326,7 @@ DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
   if (top < gexp) { sign = 0; return true; }      // all coordinates zero
   if (top - gexp > 60) return false;
   long long X[(D + 1) * D];
+#pragma unroll 1
   for (int i = 0; i < (D + 1) * D; i++) {
     const long long b = dli_double_bits(pts[i]);
     const int e = (int)((b >> 52) & 0x7ff);
@@ -314,22 +337,23 @@ DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
     X[i] = b < 0 ? -v : v;
   }
   long long M[D * D];
+#pragma unroll 1
   for (int i = 0; i < D; i++)
+#pragma unroll
     for (int j = 0; j < D; j++) M[i * D + j] = X[i * D + j] - X[D * D + j];
   if (D == 3) {
     sign = i256_sign(i256_det3(M, 3));
   } else {
+    // Laplace expansion by the first two rows: six products of complementary 2 x 2 minors (|minor| < 2^125)
     I256 acc;
     acc.w[0] = acc.w[1] = acc.w[2] = acc.w[3] = 0;
-    for (int k = 0; k < 4; k++) {                 // Laplace expansion along row 0
-      long long sub[9];
-      for (int i = 1; i < 4; i++) {
-        int c = 0;
-        for (int j = 0; j < 4; j++)
-          if (j != k) sub[(i - 1) * 3 + c++] = M[i * 4 + j];
-      }
-      I256 t = i256_mul_i64(i256_det3(sub, 3), M[k]);
-      acc = i256_add(acc, (k & 1) ? i256_neg(t) : t);
+    const int ci[6] = {0, 0, 0, 1, 1, 2}, cj[6] = {1, 2, 3, 2, 3, 3}, ck[6] = {2, 1, 1, 0, 0, 0}, cl[6] = {3, 3, 2, 3, 2, 1};
+#pragma unroll 1
+    for (int t = 0; t < 6; t++) {
+      const __int128 top = i128_minor2(M[ci[t]], M[cj[t]], M[4 + ci[t]], M[4 + cj[t]]);
+      const __int128 bot = i128_minor2(M[8 + ck[t]], M[8 + cl[t]], M[12 + ck[t]], M[12 + cl[t]]);
+      const I256 pr = i256_mul_i128(top, bot);
+      acc = i256_add(acc, ((ci[t] + cj[t]) & 1) ? pr : i256_neg(pr));   // sign (-1)^(i + j + 1)
     }
     sign = i256_sign(acc);
   }
@@ -338,12 +362,18 @@ DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
 
 // merge-free exact accumulation: products are generated one at a time and added with grow_ze.
 // Cost O(n^2) two_sums in the worst case; n <= 96 (D=3) / 960 (D=4); it only runs when the filter fails.
+// (kept out of line: it is large -- 8 KB of local memory in 4D -- and rare; inlined, it bloated the exact-pass kernels
+// to 8.7k instructions / 168 registers and the pass stalled on instruction fetch)
+template <int D>
+DLI_HD_NOINLINE int orient_exact_expansion(const double *pts);
 template <int D>
 DLI_HD inline int orient_exact(const double *pts) {
-  {
-    int s;
-    if (orient_exact_int<D>(pts, s)) return s;
-  }
+  int s;
+  if (orient_exact_int<D>(pts, s)) return s;
+  return orient_exact_expansion<D>(pts);
+}
+template <int D>
+DLI_HD_NOINLINE int orient_exact_expansion(const double *pts) {
   double e[ExactCap<D>::value];
   int n = 0;
   // iterate over the rows r left out (the Laplace expansion along the ones column) and over all

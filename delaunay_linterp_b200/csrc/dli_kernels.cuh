@@ -661,7 +661,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
       y = __longlong_as_double(0x7ff8000000000000LL);
       if (status == DLI_STATUS_OUTSIDE_NAN) s = -1;
     } else {
-      y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
+      y = (EPI == 0) ? epilogueD_ref<D, true>(p, S) : epilogueD_fast<D>(p, S);
     }
     if (ys) ys[i] = y;
     if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + s) : -1;
