@@ -10,6 +10,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--cfg", default="3,4a,4b,5")
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--opts", default="{}")
+ap.add_argument("--opts-list", default="", help="JSON list of option dicts: the 4a/4b mesh is built once and measured with each")
 a = ap.parse_args()
 OPTS = json.loads(a.opts)
 BALG = {2: 108, 3: 176, 4: 260}
@@ -49,8 +50,10 @@ for cfg in a.cfg.split(","):
     elif cfg in ("4a", "4b"):
         dim = 3 if cfg == "4a" else 4
         t0 = time.time(); pts, f, sv, sn = helpers.random_mesh(dim, 200000, 1003 if dim == 3 else 1004); tb = time.time() - t0
-        t0 = time.time(); m = dl.Mesh(pts, f, sv, sn, **OPTS); tf = time.time() - t0
-        report("4 %dD 200k" % dim, m, dim, 20000000, 0.1, 0.9, 2004 if dim == 3 else 2005, dict(build_s=round(tb, 2), flatten_s=round(tf, 3)))
+        for o in (json.loads(a.opts_list) if a.opts_list else [OPTS]):
+            t0 = time.time(); m = dl.Mesh(pts, f, sv, sn, **o); tf = time.time() - t0
+            report("4 %dD 200k" % dim, m, dim, 20000000, 0.1, 0.9, 2004 if dim == 3 else 2005, dict(build_s=round(tb, 2), flatten_s=round(tf, 3), opts=o))
+            del m
     elif cfg == "5":
         pts = np.random.default_rng(1005).random((16000000, 2))
         t0 = time.time(); t = dl.DelaunayInterp2(); t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False); tb = time.time() - t0
