@@ -740,7 +740,7 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
     e = grow_buffer(m->d_hull, 0, sizeof(int4) * (size_t)cap);
     if (e == cudaSuccess) m->cap_h = cap;
   }
-  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed: ") + cudaGetErrorString(e));
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
   // ---- upload + rebuild the derived records of the listed simplices (one scratch buffer, one upload)
   const int64_t nnew = nv_total - nv0;
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -751,7 +751,7 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
   if (total > m->upd_cap) {
     cudaFree(m->d_upd); m->d_upd = nullptr; m->upd_cap = 0;
     e = cudaMalloc(&m->d_upd, total * 2);
-    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: scratch allocation failed: ") + cudaGetErrorString(e));
+    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: scratch allocation failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
     m->upd_cap = total * 2;
   }
   std::vector<unsigned char> stage(total, 0);
@@ -864,8 +864,14 @@ MeshDView viewD(const dli_mesh *m) {
   return v;
 }
 
-constexpr int64_t kChunk = 1ll << 30;      // queries per launch pair (int32 indices in the straggler queue)
-constexpr int64_t kQueueCap = 1ll << 22;   // straggler queue entries (16 MiB); overflow = the full pass re-runs the batch
+constexpr int64_t kChunk = 1ll << 28;      // queries per launch pair (int32 indices in the straggler queue)
+// Straggler queue entries per launch pair: one per query of the chunk (4 B each, from the stream-ordered pool), so the
+// queue cannot overflow.  It used to hold 4M entries with "overflow = the exact pass re-runs the whole chunk": a 50M-query
+// batch with 17 % of its queries outside the hull fell off that cliff (26 ms instead of 7).
+#ifndef DLI_X_QCAP
+#define DLI_X_QCAP kChunk
+#endif
+constexpr int64_t kQueueCap = DLI_X_QCAP;
 
 struct Launch {
   const dli_mesh *m;

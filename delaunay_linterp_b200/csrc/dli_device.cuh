@@ -334,6 +334,12 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
   uint8_t status = DLI_STATUS_OK;
   int from = -1;
   unsigned int steps = 0;
+  // A projected point that still tests strictly outside its own hull edge (by an ulp: the projection is an inexact
+  // construction) is projected on the same line again and usually lands on itself: from then on every round repeats
+  // the previous one exactly (same point, same edge, same start face), so the remaining rounds up to the cap are
+  // skipped -- the result is the one the capped loop returns.
+  bool stuck = false;
+  int prev_h = -1;
   for (int proj = 0;; proj++) {
     int exit_h = -1;
     bool found = false;
@@ -369,13 +375,16 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
       return DLI_STATUS_OUTSIDE_NAN;
     }
     status = DLI_STATUS_OUTSIDE_PROJECTED;
-    if (proj >= kMaxProjections) break;  // accept the hull face (ulp-level extrapolation)
+    if (proj >= kMaxProjections || stuck) break;  // accept the hull face (ulp-level extrapolation)
     int h = canonical_visible_hull_edge(m, px, py, exit_h, st);
     int4 r = __ldg(m.hull + h);
     Face2 F = load_face(m, r.x);
     int vs[3] = {F.v0, F.v1, F.v2};
     double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
+    const double opx = px, opy = py;
     project_on_line(P.x, P.y, Q.x, Q.y, px, py);
+    stuck = (h == prev_h && px == opx && py == opy);
+    prev_h = h;
     f = r.x;
     from = -1;
   }

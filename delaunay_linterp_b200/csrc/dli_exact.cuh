@@ -87,6 +87,9 @@ DLI_HDI int expansion_sign(const double *e, int n) {
 
 // exact sign of (ax-cx)(by-cy) - (ay-cy)(bx-cx): the six surviving products of raw coordinates,
 // each split exactly with two_prod, summed exactly.
+template <int D>
+DLI_HD inline bool orient_exact_int(const double *pts, int &sign);   // fixed-point integer path, defined below
+
 DLI_HD inline int orient2d_exact(double ax, double ay, double bx, double by, double cx, double cy) {
   // Common case first (Shewchuk's adaptive stage B): when the four coordinate differences are exact -- always for
   // points on a lattice, and for most near-degenerate inputs, where the operands are close -- the determinant is the
@@ -105,6 +108,12 @@ DLI_HD inline int orient2d_exact(double ax, double ay, double bx, double by, dou
       grow(e, n, l0); grow(e, n, -r0); grow(e, n, l1); grow(e, n, -r1);
       return expansion_sign(e, n);
     }
+  }
+  {  // coordinates on a common fixed-point grid: one 128-bit 2 x 2 determinant (e.g. a point projected on a hull
+    // edge line tested against that edge: differences are not exact, the filter cannot decide)
+    const double pts[6] = {ax, ay, bx, by, cx, cy};
+    int s;
+    if (orient_exact_int<2>(pts, s)) return s;
   }
   double e[12];
   int n = 0;
@@ -309,7 +318,7 @@ DLI_HDI I256 i256_det3(const long long *m, int ld) {
 // 32 KB L1.5 instruction cache -- not by the few hundred integer operations of one evaluation)
 template <int D>
 DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
-  static_assert(D == 3 || D == 4, "integer path is written for D = 3, 4");
+  static_assert(D >= 2 && D <= 4, "integer path is written for D = 2, 3, 4");
   int gexp = 1 << 30, top = -(1 << 30);
 #pragma unroll 1
   for (int i = 0; i < (D + 1) * D; i++) {
@@ -341,7 +350,10 @@ DLI_HD inline bool orient_exact_int(const double *pts, int &sign) {
   for (int i = 0; i < D; i++)
 #pragma unroll
     for (int j = 0; j < D; j++) M[i * D + j] = X[i * D + j] - X[D * D + j];
-  if (D == 3) {
+  if (D == 2) {
+    const __int128 d2 = i128_minor2(M[0], M[1], M[2], M[3]);
+    sign = d2 > 0 ? 1 : (d2 < 0 ? -1 : 0);
+  } else if (D == 3) {
     sign = i256_sign(i256_det3(M, 3));
   } else {
     // Laplace expansion by the first two rows: six products of complementary 2 x 2 minors (|minor| < 2^125)

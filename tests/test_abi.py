@@ -84,3 +84,22 @@ def test_host_predicate_on_lattice_points_fixed_point_path():
         want = np.array([pyoracle.orient(p.tolist()) for p in pts], dtype=np.int8)
         assert np.array_equal(sign, want)
         assert (want == 0).sum() >= 100 and (want != 0).sum() >= 100
+
+
+def test_host_predicate_2d_projected_points():
+    """a point projected on the line of a segment (inexact construction) tested against that segment: the filter
+    cannot decide, the differences are not exact -> fixed-point integer path of the 2D exact predicate."""
+    import delaunay_linterp_b200 as dl
+    from oracle import pyoracle
+    rng = np.random.default_rng(9)
+    P, Q, X = rng.random((3000, 2)), rng.random((3000, 2)), rng.random((3000, 2)) * 1.2 - 0.1
+    d = Q - P
+    t = ((X - P) * d).sum(1) / (d * d).sum(1)
+    R = P + t[:, None] * d                                   # on the line PQ up to rounding
+    pts = np.stack([P, Q, R], axis=1)
+    pts[:200, 2] = 0.5 * (P[:200] + Q[:200])                 # midpoints: often exactly collinear
+    pts[200:300, 0, 0] = 1e-40                               # out of the fixed-point budget: expansion path
+    sign = dl.debug_orient(pts, on_device=False)
+    want = np.array([pyoracle.orient(p.tolist()) for p in pts], dtype=np.int8)
+    assert np.array_equal(sign, want)
+    assert (want == 0).sum() > 20 and (want > 0).sum() > 500 and (want < 0).sum() > 500

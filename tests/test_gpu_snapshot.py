@@ -25,6 +25,11 @@ def test_save_load_roundtrip(gpu, tmp_path, dim, opts):
         g0, g1 = m.gradient(q), r.gradient(q)
         assert np.array_equal(np.isnan(g0), np.isnan(g1)) and np.array_equal(g0[np.isfinite(g0)], g1[np.isfinite(g1)])
     assert r.stats()["slow_simplices"] == m.stats()["slow_simplices"]
+    if dim == 2:
+        a, b = m.line_segments(), r.line_segments()       # plot data works on a replica (hull size travels in the header)
+        assert all(np.array_equal(u, v) for u, v in zip(a, b))
+        # a replica has no host connectivity: it cannot be patched, the caller re-creates it
+        assert r.update(np.zeros((0, 2)), [], r.n_simplices, [], np.zeros((0, 3)), np.zeros((0, 3))) is False
     with pytest.raises(dl.DliError):
         r.simplices()          # replicas carry no host connectivity
 
