@@ -973,9 +973,10 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
   }
   int64_t cap = std::min(n, kQueueCap);
   int32_t *queue = nullptr;
-  CU(cudaMallocAsync(&queue, sizeof(int32_t) * (size_t)cap + 16, st));
-  unsigned int *qcount = reinterpret_cast<unsigned int *>(queue + cap);
-  // (queue + cap) is 4-byte aligned, which is all an unsigned int needs
+  // [cap] query indices, [cap] faces the fast pass stopped in, then the counter
+  CU(cudaMallocAsync(&queue, sizeof(int32_t) * 2 * (size_t)cap + 16, st));
+  unsigned int *qcount = reinterpret_cast<unsigned int *>(queue + 2 * cap);
+  // (queue + 2 * cap is 4-byte aligned, which is all an unsigned int needs)
   Launch L;
   L.m = m; L.st = st; L.queue = queue; L.qcount = qcount; L.qcap = (unsigned int)cap; L.stats = m->d_stats;
   if (m->collect_stats) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, st));

@@ -124,7 +124,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
       }
       if (give_up) {
         unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = f; }   // exact pass resumes here
         active = false;
       }
     }
@@ -475,7 +475,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
       }
       if (give_up) {
         unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = CELL ? __ldg(m.slot_face + f) : f; }
         active = false;
       }
     }
@@ -508,7 +508,9 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
       if (status_out) status_out[i] = DLI_STATUS_STEP_LIMIT;
       continue;
     }
-    int f = hint2(m, px, py);
+    // resume the walk in the face where the fast pass stopped (hull exit, step cap, uncertain sign): the walk up to
+    // there is not repeated.  direct mode (no queue): start from the hint.
+    int f = direct ? hint2(m, px, py) : queue[(size_t)queue_cap + k];
     if (OUT == 1) {
       double2 g;
       uint8_t status = gradient2_full(m, px, py, f, g, st);
@@ -621,7 +623,7 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
       }
       if (give_up) {
         unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = s; }
         active = false;
       }
     }
@@ -653,7 +655,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
       if (status_out) status_out[i] = DLI_STATUS_STEP_LIMIT;
       continue;
     }
-    int s = hintD<D>(m, p);
+    int s = direct ? hintD<D>(m, p) : queue[(size_t)queue_cap + k];   // resume where the fast pass stopped
     SimplexD<D> S;
     uint8_t status = locateD_full<D>(m, p, s, S, st);
     double y;
@@ -1125,7 +1127,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
       }
       if (give_up) {
         unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) queue[slot] = (int32_t)qi;
+        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = s; }
         active = false;
       }
     }
