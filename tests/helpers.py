@@ -64,3 +64,31 @@ def lattice_predicate_inputs(d, seed=4):
     tiny[:, 0, 0] = 1e-30
     neg = -lat[:100] * 3.0 + 1.0
     return np.concatenate([lat, tiny, neg])
+
+
+def regular_grid_mesh_2d(n, lo=0.0, hi=5.0):
+    """config 1 scaled up, vectorised: n x n grid on [lo, hi]^2, every cell split by the (x1,y0)-(x0,y1) diagonal."""
+    g = np.linspace(lo, hi, n)
+    X, Y = np.meshgrid(g, g, indexing="ij")
+    coords = np.stack([X.ravel(), Y.ravel()], 1)
+    I, J = np.meshgrid(np.arange(n - 1), np.arange(n - 1), indexing="ij")
+    a = (I * n + J).ravel(); b = a + n; c = a + 1; d = a + n + 1
+    tri = np.concatenate([np.stack([a, b, c], 1), np.stack([b, d, c], 1)]).astype(np.int32)
+    return coords, cobb_douglas(coords + 0.5), tri
+
+
+def kuhn_grid_mesh(dim, n):
+    """regular grid on [0,1]^dim, every cell split into dim! Kuhn simplices (vectorised)."""
+    import itertools
+    g = np.arange(n, dtype=np.float64) / (n - 1)
+    grid = np.stack(np.meshgrid(*([g] * dim), indexing="ij"), -1).reshape(-1, dim)
+    cells = np.stack(np.meshgrid(*([np.arange(n - 1)] * dim), indexing="ij"), -1).reshape(-1, dim)
+    simp = []
+    for perm in itertools.permutations(range(dim)):
+        cur = cells.copy()
+        verts = [np.ravel_multi_index(cur.T, (n,) * dim)]
+        for ax in perm:
+            cur[:, ax] += 1
+            verts.append(np.ravel_multi_index(cur.T, (n,) * dim))
+        simp.append(np.stack(verts, 1))
+    return grid, 1.0 + cobb_douglas(grid + 0.5), np.concatenate(simp).astype(np.int32)

@@ -211,3 +211,43 @@ def test_cfg5_one_shard_full_size_properties(gpu):
     yo, so, sto = OracleMesh(c, f, sv, sn).interp(xq[:n1].cpu().numpy(), mode=1, nthreads=8)
     assert np.max(np.abs(ys[:n1].cpu().numpy() - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
     assert np.mean(s[:n1].cpu().numpy() == so) > 0.99999
+
+
+@pytest.mark.parametrize("dim", [2, 3, 4])
+def test_degenerate_lattice_batches(gpu, dim):
+    """The README example scaled up: lattice queries on a regular-grid mesh, every query exactly on a vertex, edge or
+    facet (the filter can certify nothing: the whole batch takes the exact pass) -- statuses, containment and values
+    against the oracle on a subsample, finiteness and engine agreement on the whole batch."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    rng = np.random.default_rng(70 + dim)
+    if dim == 2:
+        n = 1000
+        c, f, sv = helpers.regular_grid_mesh_2d(n)
+        nq = 8_000_000
+        q = rng.integers(0, 4 * (n - 1) + 1, (nq, 2)) * (5.0 / (4 * (n - 1)))
+    else:
+        n = 40 if dim == 3 else 12
+        c, f, sv = helpers.kuhn_grid_mesh(dim, n)
+        nq = 2_000_000 if dim == 3 else 1_000_000
+        q = rng.integers(0, 4 * (n - 1) + 1, (nq, dim)) / (4.0 * (n - 1))
+    m = dl.Mesh(c, f, sv, None)
+    xq = torch.tensor(q, device="cuda")
+    m.collect_stats(True)
+    ys, s, st = m.interp(xq, return_simplex=True, return_status=True)
+    torch.cuda.synchronize()
+    stats = m.stats()
+    m.collect_stats(False)
+    assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
+    assert stats["straggler_queries"] > 0.5 * nq and stats["exact_fallbacks"] > 0.5 * nq     # really the exact pass
+    m2 = dl.Mesh(c, f, sv, None, epilogue=1)                                                   # reference-order engine
+    y2 = m2.interp(xq)
+    assert float(((ys - y2).abs() / y2.abs().clamp_min(1e-300)).max().item()) <= REL_TOL
+    sub = rng.choice(nq, 100_000, replace=False)
+    om = OracleMesh(c, f, sv, None)
+    yo, so, sto = om.interp(q[sub], mode=1, nthreads=8)
+    assert np.array_equal(st[sub].cpu().numpy(), sto)
+    contains, _ = om.classify(q[sub], s[sub].cpu().numpy())
+    assert contains.all()                                  # a closed simplex containing the query (any incident one)
+    yg = ys[sub].cpu().numpy()
+    assert np.max(np.abs(yg - yo) / np.maximum(np.abs(yo), 1e-300)) <= REL_TOL
