@@ -5,7 +5,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <mutex>
+#include <new>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -163,6 +165,13 @@ extern "C" void dli_options_init(dli_options *o) {
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
+
+// "no exception ever crosses the ABI" (include/dli.h): entry points that allocate host memory run inside this guard
+#define DLI_GUARD_BEGIN try {
+#define DLI_GUARD_END(who)                                                                                   \
+  } catch (const std::bad_alloc &) { return fail(DLI_ERR_NOMEM, who ": out of host memory");                 \
+  } catch (const std::exception &e) { return fail(DLI_ERR_ARG, std::string(who ": ") + e.what());            \
+  } catch (...) { return fail(DLI_ERR_ARG, who ": unknown exception"); }
 
 extern "C" int dli_device_count(void) {
   int n = 0;
@@ -494,6 +503,7 @@ static void hull_table2(int64_t nv, int64_t ns, const std::vector<int32_t> &sv, 
 
 extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const double *f, int64_t ns,
                                const int32_t *sv_in, const int32_t *sn_in, const dli_options *opt, dli_mesh **out) {
+  DLI_GUARD_BEGIN
   if (!out) return fail(DLI_ERR_ARG, "dli_mesh_create: out is NULL");
   *out = nullptr;
   if (dim < 2 || dim > 4) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_create: dim must be 2, 3 or 4");
@@ -598,6 +608,7 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
   if (rc != DLI_OK) { mesh_free(m); return rc; }
   *out = m;
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_create")
 }
 
 extern "C" int dli_mesh_set_values(dli_mesh *m, const double *f) {
@@ -625,6 +636,7 @@ static cudaError_t grow_buffer(T *&p, size_t keep_bytes, size_t new_bytes) {
 extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_coords, const double *new_f,
                                int64_t n_fchg, const int32_t *fchg_ids, const double *fchg_vals, int64_t ns_total,
                                int64_t n_dirty, const int32_t *dirty_ids, const int32_t *dirty_sv, const int32_t *dirty_sn) {
+  DLI_GUARD_BEGIN
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_update: NULL mesh");
   const int64_t nv0 = m->nv, ns0 = m->ns;
   if (nv_total < nv0 || ns_total < ns0 || n_fchg < 0 || n_dirty < 0 || nv_total > 0x7fffffff)
@@ -804,6 +816,7 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
   }
   m->n_updates++;
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_update")
 }
 
 extern "C" void dli_mesh_destroy(dli_mesh *m) { mesh_free(m); }
@@ -818,11 +831,13 @@ extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
                    (m->cellmode ? (int64_t)sizeof(int32_t) * (m->nslots + m->grid.g[1] + 1) : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
+  DLI_GUARD_BEGIN
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_get_simplices: NULL mesh");
   if (m->h_sv.empty() && m->ns > 0) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_get_simplices: mesh was created from a header (no host copy)");
   if (sv) memcpy(sv, m->h_sv.data(), sizeof(int32_t) * m->h_sv.size());
   if (sn) memcpy(sn, m->h_sn.data(), sizeof(int32_t) * m->h_sn.size());
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_get_simplices")
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1162,6 +1177,7 @@ extern "C" int64_t dli_mesh_num_edges(const dli_mesh *m) {
 
 extern "C" int dli_mesh_line_segments(const dli_mesh *m, double *segments, int32_t *concave, double *min_coords,
                                       double *max_coords) {
+  DLI_GUARD_BEGIN
   if (!m) return fail(DLI_ERR_ARG, "dli_mesh_line_segments: NULL mesh");
   if (m->dim != 2) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_line_segments: 2D meshes only (as is_edge_concave)");
   DeviceGuard guard(m->device);
@@ -1215,6 +1231,7 @@ extern "C" int dli_mesh_line_segments(const dli_mesh *m, double *segments, int32
   cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_seg); cudaFree(d_cc); cudaFree(d_tmp);
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_line_segments: ") + cudaGetErrorString(e));
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_line_segments")
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1265,6 +1282,7 @@ extern "C" int64_t dli_simplex_error_count(const dli_mesh *m) {
 
 extern "C" int dli_simplex_error_prepare(const dli_mesh *mc, double *centroids, int32_t *item_simplex,
                                          int32_t *item_vertices) {
+  DLI_GUARD_BEGIN
   dli_mesh *m = const_cast<dli_mesh *>(mc);
   if (!m || !centroids) return fail(DLI_ERR_ARG, "dli_simplex_error_prepare: NULL argument");
   int rc = ensure_items(m);
@@ -1287,9 +1305,11 @@ extern "C" int dli_simplex_error_prepare(const dli_mesh *mc, double *centroids, 
   cudaFree(d_c);
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_simplex_error_prepare: ") + cudaGetErrorString(e));
   return DLI_OK;
+  DLI_GUARD_END("dli_simplex_error_prepare")
 }
 
 extern "C" int dli_simplex_error_finish(const dli_mesh *mc, int64_t n, const double *phi, double *err) {
+  DLI_GUARD_BEGIN
   dli_mesh *m = const_cast<dli_mesh *>(mc);
   if (!m || (n > 0 && (!phi || !err))) return fail(DLI_ERR_ARG, "dli_simplex_error_finish: NULL argument");
   int rc = ensure_items(m);
@@ -1315,6 +1335,7 @@ extern "C" int dli_simplex_error_finish(const dli_mesh *mc, int64_t n, const dou
   cudaFree(d_err);
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_simplex_error_finish: ") + cudaGetErrorString(e));
   return DLI_OK;
+  DLI_GUARD_END("dli_simplex_error_finish")
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1442,6 +1463,7 @@ extern "C" int dli_mesh_set_grid_params(dli_mesh *m, const double *in) {
 static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '1'};
 
 extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
+  DLI_GUARD_BEGIN
   if (!m || !path) return fail(DLI_ERR_ARG, "dli_mesh_save: NULL argument");
   FILE *fp = fopen(path, "wb");
   if (!fp) return fail(DLI_ERR_ARG, std::string("dli_mesh_save: cannot open ") + path);
@@ -1468,9 +1490,11 @@ extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
   if (rc != DLI_OK) return rc;
   if (!ok) return fail(DLI_ERR_ARG, std::string("dli_mesh_save: write failed: ") + path);
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_save")
 }
 
 extern "C" int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh **out) {
+  DLI_GUARD_BEGIN
   if (!path || !out) return fail(DLI_ERR_ARG, "dli_mesh_load: NULL argument");
   *out = nullptr;
   FILE *fp = fopen(path, "rb");
@@ -1502,6 +1526,7 @@ extern "C" int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh 
   if (rc != DLI_OK) { mesh_free(m); return rc; }
   *out = m;
   return DLI_OK;
+  DLI_GUARD_END("dli_mesh_load")
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -12,6 +12,7 @@
 #include <queue>
 #include <unordered_map>
 #include <unordered_set>
+#include <new>
 #include <vector>
 
 #include "../../include/dli_error_math.h"
@@ -477,6 +478,12 @@ struct dli_di2 {
   }
 };
 
+
+// "no exception ever crosses the ABI" (include/dli.h): host-side entry points that allocate run inside this guard
+#define DLI_GUARD_BEGIN try {
+#define DLI_GUARD_END                                   \
+  } catch (const std::bad_alloc &) { return DLI_ERR_NOMEM; \
+  } catch (...) { return DLI_ERR_ARG; }
 extern "C" {
 
 dli_di2 *dli_di2_create(dli_fn fn, void *user) {
@@ -491,12 +498,15 @@ void dli_di2_destroy(dli_di2 *d) {
   delete d;
 }
 int32_t dli_di2_insert(dli_di2 *d, double x, double y, double f) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   if (!(std::isfinite(x) && std::isfinite(y))) return DLI_ERR_ARG;
   return d->insert(x, y, f);
+  DLI_GUARD_END
 }
 
 int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f, int spatial_sort, int use_gpu) {
+  DLI_GUARD_BEGIN
   if (!d || n < 0 || (n > 0 && (!xy || !f))) return DLI_ERR_ARG;
   d->need_full = true;
   std::vector<int64_t> order((size_t)n);
@@ -551,6 +561,7 @@ int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f
   if (rc != DLI_OK) return rc;
   for (int64_t i = 0; i < ni; i++) d->push(err[i], phi[i], cent[2 * i], cent[2 * i + 1], handle[item_simplex[i]]);
   return DLI_OK;
+  DLI_GUARD_END
 }
 
 int dli_di2_get_largest_error_tuple(dli_di2 *d, double *err, double *f, double *xy) {
@@ -564,6 +575,7 @@ int dli_di2_get_largest_error_tuple(dli_di2 *d, double *err, double *f, double *
   return DLI_OK;
 }
 int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, double *xy) {
+  DLI_GUARD_BEGIN
   if (!d || !d->fn) return DLI_ERR_ARG;
   d->prune();
   if (d->pq.empty()) return DLI_ERR_ARG;
@@ -573,6 +585,7 @@ int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, doubl
   if (xy) { xy[0] = e.x; xy[1] = e.y; }
   d->insert(e.x, e.y, e.f);
   return DLI_OK;
+  DLI_GUARD_END
 }
 // k-at-a-time adaptive refinement.  Sequential semantics are kept wherever the k insertions do not
 // interact: tuples are taken in queue order; a tuple whose face shares a vertex with a face already taken in this
@@ -583,6 +596,7 @@ int dli_di2_insert_largest_error_point(dli_di2 *d, double *err, double *f, doubl
 // k_error_finish runs on the device; a round holds a few items per inserted point, so it is evaluated on the host).
 int64_t dli_di2_refine(dli_di2 *d, int64_t k, double rel_threshold, dli_fn_batch fnb, void *user_b, double *err_out, double *f_out,
                        double *xy_out) {
+  DLI_GUARD_BEGIN
   if (!d || k < 0 || (!d->fn && !fnb)) return DLI_ERR_ARG;
   double top_err = -1.0;
   HostMesh2 &hm = d->hm;
@@ -649,9 +663,11 @@ int64_t dli_di2_refine(dli_di2 *d, int64_t k, double rel_threshold, dli_fn_batch
     d->push(dli_simplex_error<2>(item_nv[(size_t)i], &w[9 * (size_t)i], phi[(size_t)i]), phi[(size_t)i], cent[2 * (size_t)i],
             cent[2 * (size_t)i + 1], item_face[(size_t)i]);
   return done;
+  DLI_GUARD_END
 }
 int64_t dli_di2_error_queue_size(dli_di2 *d) { return d ? d->live : 0; }
 int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   std::vector<QEntry> all;
   auto copy = d->pq;
@@ -665,6 +681,7 @@ int dli_di2_get_error_queue(dli_di2 *d, double *err, double *f, double *xy) {
     if (xy) { xy[2 * i] = all[i].x; xy[2 * i + 1] = all[i].y; }
   }
   return DLI_OK;
+  DLI_GUARD_END
 }
 
 int64_t dli_di2_num_vertices(const dli_di2 *d) { return d ? (int64_t)d->hm.X.size() : 0; }
@@ -672,12 +689,14 @@ int64_t dli_di2_num_faces(const dli_di2 *d) { return d ? d->hm.n_finite : 0; }
 int dli_di2_dimension(const dli_di2 *d) { return d ? d->hm.dim : -1; }
 
 int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, int32_t *nbr) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   const HostMesh2 &hm = d->hm;
   int64_t nv = (int64_t)hm.X.size();
   if (f) memcpy(f, hm.F.data(), sizeof(double) * (size_t)nv);
   const_cast<dli_di2 *>(d)->flatten(coords, tri, nbr, nullptr);   // (renumbers only after a non-compact insertion)
   return DLI_OK;
+  DLI_GUARD_END
 }
 
 int dli_di2_set_options(dli_di2 *d, const dli_options *opt) {
@@ -743,17 +762,21 @@ void dli_di2_sync_counts(const dli_di2 *d, int64_t *n_full, int64_t *n_increment
 
 int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
                    void *stream) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   int rc = di2_refresh(d);
   if (rc != DLI_OK) return rc;
   return dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);
+  DLI_GUARD_END
 }
 int dli_di2_gradient(dli_di2 *d, int64_t n, const double *xs, double *grads, int32_t *simplex_out, uint8_t *status_out,
                      void *stream) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   int rc = di2_refresh(d);
   if (rc != DLI_OK) return rc;
   return dli_gradient(d->mesh, n, xs, grads, simplex_out, status_out, stream);
+  DLI_GUARD_END
 }
 const dli_mesh *dli_di2_device_mesh(dli_di2 *d) {
   if (!d) return nullptr;
@@ -763,6 +786,7 @@ const dli_mesh *dli_di2_device_mesh(dli_di2 *d) {
 
 // get_line_segments with concavity flags and min / max (src/delaunay_2_interp.h:842-862, :766-803), batched on the GPU
 int64_t dli_di2_line_segments(dli_di2 *d, double *segments, int32_t *concave, double *min_coords, double *max_coords) {
+  DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
   int rc = di2_refresh(d);
   if (rc != DLI_OK) return rc;
@@ -773,6 +797,7 @@ int64_t dli_di2_line_segments(dli_di2 *d, double *segments, int32_t *concave, do
     if (rc != DLI_OK) return rc;
   }
   return ne;
+  DLI_GUARD_END
 }
 
 int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz) {
@@ -782,6 +807,7 @@ int64_t dli_di2_get_all_vertices(const dli_di2 *d, double *xyz) {
   return nv;
 }
 int64_t dli_di2_get_line_segments(const dli_di2 *d, double *seg) {
+  DLI_GUARD_BEGIN
   if (!d) return 0;
   const HostMesh2 &hm = d->hm;
   int64_t ne = 0;
@@ -800,6 +826,7 @@ int64_t dli_di2_get_line_segments(const dli_di2 *d, double *seg) {
     }
   }
   return ne;
+  DLI_GUARD_END
 }
 
 }  // extern "C"
