@@ -961,7 +961,7 @@ void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
     k_interpD_fast<D, STATS, EPI><<<(unsigned)((warps + wpb - 1) / wpb), tpb, 0, L.st>>>(v, n, per_warp, xs, ys, so, sto, L.queue,
                                                                                         L.qcount, L.qcap, L.stats);
   L.mark(1);
-  k_interpD_full<D, STATS, EPI><<<148 * 3, 128, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
+  k_interpD_full<D, STATS, EPI><<<148 * DLI_X_FULLD_BLOCKS, 128, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
   L.mark(2);
   L.launches += 2;
 }

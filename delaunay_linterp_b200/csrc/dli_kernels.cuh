@@ -631,8 +631,11 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
   if (STATS) flush_stats(stats, st);
 }
 
+#ifndef DLI_X_FULLD_BLOCKS
+#define DLI_X_FULLD_BLOCKS 5   // measured on all-degenerate batches: 3 / 4 / 5 / 6 / 8 CTAs per SM -> 8.4 / 7.9 / 7.5 / 7.8 / 9.1 ms (4D)
+#endif
 template <int D, bool STATS, int EPI>
-__global__ void __launch_bounds__(128, 3)
+__global__ void __launch_bounds__(128, DLI_X_FULLD_BLOCKS)
 k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ ys,
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
