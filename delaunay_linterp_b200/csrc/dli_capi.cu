@@ -289,7 +289,9 @@ int build_hint_grid(dli_mesh *m, const double *coords) {
       if (x > hi[k]) hi[k] = x;
     }
   float cps = m->opt.hint_cells_per_simplex;
-  if (!(cps > 0.f)) cps = (d == 2) ? 2.0f : (d == 3 ? 4.0f : 8.0f);  // measured optima
+  // measured optima; cell-indexed records (3.1b) have no hint table to keep small: 2 / 3 / 4 / 6 cells per
+  // face give 30.0 / 31.4 / 32.3 / 33.3 Gq/s on cfg5 for 6.7 / 8.9 / 11.1 / 15.6 GB
+  if (!(cps > 0.f)) cps = (d == 2) ? (m->cellmode ? 4.0f : 2.0f) : (d == 3 ? 4.0f : 8.0f);
   double target = std::max(1.0, (double)m->ns * cps);
   int g = (int)std::ceil(std::pow(target, 1.0 / d));
   g = std::max(1, std::min(g, d == 2 ? 16384 : (d == 3 ? 1024 : 128)));

@@ -66,7 +66,7 @@ typedef struct dli_mesh dli_mesh; /* opaque: owns the device structure-of-arrays
 typedef struct dli_options {
   int32_t struct_size;            /* sizeof(dli_options); lets the struct grow compatibly */
   int32_t device;                 /* CUDA device ordinal, -1 = current device */
-  float hint_cells_per_simplex;   /* start-hint grid resolution; <= 0 = default (2D: 2, 3D: 4, 4D: 8) */
+  float hint_cells_per_simplex;   /* start-hint grid resolution; <= 0 = default (2D: 2, or 4 with cell-indexed records; 3D: 4, 4D: 8) */
   int32_t max_walk_steps;         /* <= 0 = default (n_simplices + 16) */
   int32_t reserved0;              /* must be 0 (was: device-side query binning; measured not to pay) */
   int32_t epilogue;               /* DLI_EPILOGUE_*: 0 = AUTO (default): 2D meshes with < 2^21-1 faces use the 64-byte

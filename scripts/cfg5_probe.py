@@ -46,7 +46,7 @@ for cps in [float(v) for v in a.cps.split(",")]:
     print(json.dumps(dict(opts=OPTS, stragglers=st["straggler_queries"], cps=cps, order="random", ms=round(ms, 3), gqps=round(a.nq / ms / 1e6, 2), steps=round(st["walk_steps"] / st["queries"], 3),
                           mesh_MB=round(m.device_bytes / 1e6), flatten_s=round(tf, 2))), flush=True)
     if cps == 2.0:
-        for B in [int(v) for v in a.tiles.split(",")]:
+        for B in [int(v) for v in a.tiles.split(",") if v]:
             tile = (xq[:, 0] * B).long().clamp_(0, B - 1) + B * (xq[:, 1] * B).long().clamp_(0, B - 1)
             perm = torch.argsort(tile); del tile
             xs = xq[perm].contiguous(); del perm
