@@ -1,6 +1,7 @@
 // dli_capi.cu -- the C ABI (include/dli.h): flattener, hint-grid build, batched interp / locate
 // dispatch (device-pointer and host-pointer paths), error evaluator, replication support.
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cstdio>
 #include <cstdlib>
@@ -9,6 +10,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -61,6 +63,34 @@ struct HostPipe {
   int32_t *s[kSlots] = {nullptr, nullptr, nullptr};
   uint8_t *t[kSlots] = {nullptr, nullptr, nullptr};
 };
+// Pageable host buffers (numpy arrays, std::vector): a cudaMemcpyAsync from pageable memory is staged by the driver
+// through one thread at 6-10 GB/s.  Buffers that are not page-locked therefore go through slots with their own pinned
+// staging memory, one worker thread per slot: every worker copies a chunk in, runs it on its stream, copies the
+// results out, so the host copies of several chunks proceed in parallel and overlap the DMA of the others.
+constexpr int kMaxStage = 16;
+constexpr int64_t kStageChunk = 1ll << 19;        // queries per staged chunk at most (8 MB of 2D queries)
+constexpr int64_t kStageMinChunk = 1ll << 16;     // ... and at least (medium batches are cut so that every worker gets two)
+constexpr int64_t kStageMinQueries = 1ll << 18;   // smaller batches: the driver's own pageable path is as fast
+struct StageSlot {
+  cudaStream_t st = nullptr;
+  double *dx = nullptr, *dy = nullptr, *hx = nullptr, *hy = nullptr;
+  int32_t *ds = nullptr, *hs = nullptr;
+  uint8_t *dt = nullptr, *ht = nullptr;
+};
+struct StagePipe {
+  int nslots = 0;
+  StageSlot slot[kMaxStage];
+};
+static void stage_free(StagePipe &P) {
+  for (int i = 0; i < kMaxStage; i++) {
+    StageSlot &S = P.slot[i];
+    if (S.st) { cudaStreamSynchronize(S.st); cudaStreamDestroy(S.st); }
+    cudaFree(S.dx); cudaFree(S.dy); cudaFree(S.ds); cudaFree(S.dt);
+    cudaFreeHost(S.hx); cudaFreeHost(S.hy); cudaFreeHost(S.hs); cudaFreeHost(S.ht);
+    S = StageSlot();
+  }
+  P.nslots = 0;
+}
 static void pipe_free(HostPipe &P) {
   for (int i = 0; i < HostPipe::kSlots; i++) {
     if (P.st[i]) { cudaStreamSynchronize(P.st[i]); cudaStreamDestroy(P.st[i]); }
@@ -121,6 +151,7 @@ struct dli_mesh {
   // host-pointer path staging ring (created on first use)
   mutable std::mutex pipe_mu;
   mutable HostPipe pipe;
+  mutable StagePipe stage;
 };
 
 // 2D meshes with at least this many faces (512 MB of walk records, 4 x L2) use cell-indexed walk records
@@ -145,6 +176,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_upd);
   cudaFree(m->d_stats);
   pipe_free(m->pipe);
+  stage_free(m->stage);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
   delete m;
 }
@@ -996,7 +1028,6 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
   // (queue + 2 * cap is 4-byte aligned, which is all an unsigned int needs)
   Launch L;
   L.m = m; L.st = st; L.queue = queue; L.qcount = qcount; L.qcap = (unsigned int)cap; L.stats = m->d_stats;
-  if (m->collect_stats) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, st));
   const int d = m->dim;
   for (int64_t off = 0; off < n; off += kChunk) {
     int64_t cn = std::min(kChunk, n - off);
@@ -1029,6 +1060,92 @@ bool is_device_ptr(const void *p, bool *known) {
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+static bool is_pageable(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+static int stage_threads() {
+  static const int t = [] {
+    int v = 0;
+    if (const char *e = getenv("DLI_HOST_COPY_THREADS")) v = atoi(e);
+    if (v <= 0) v = std::min(8, (int)std::thread::hardware_concurrency() / 2);
+    return std::max(1, std::min(kMaxStage, v));
+  }();
+  return t;
+}
+// pageable host buffers: see StagePipe.  Called with m->pipe_mu held.
+int run_host_staged(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto, int *launches,
+                    int out) {
+  const int d = m->dim, yw = out == 1 ? 2 : 1;
+  StagePipe &P = m->stage;
+  // statistics / per-launch timing are accumulated per call: keep those calls on one worker
+  int T = (m->collect_stats || m->collect_timing) ? 1 : stage_threads();
+  int64_t chunk = (n + 2 * T - 1) / (2 * T);
+  chunk = std::min<int64_t>(kStageChunk, std::max<int64_t>(kStageMinChunk, (chunk + 4095) & ~(int64_t)4095));
+  T = (int)std::min<int64_t>(T, (n + chunk - 1) / chunk);
+  const int64_t cap = kStageChunk;       // slot buffers are sized for the largest chunk
+  for (int i = 0; i < T; i++) {          // slots are created on first use and kept
+    StageSlot &S = P.slot[i];
+    cudaError_t e = cudaSuccess;
+    if (!S.st) e = cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking);
+    if (e == cudaSuccess && !S.dx) e = cudaMalloc(&S.dx, sizeof(double) * (size_t)cap * d);
+    if (e == cudaSuccess && !S.hx) e = cudaMallocHost(&S.hx, sizeof(double) * (size_t)cap * d);
+    if (e == cudaSuccess && ys && !S.dy) e = cudaMalloc(&S.dy, sizeof(double) * (size_t)cap * 2);   // room for gradients
+    if (e == cudaSuccess && ys && !S.hy) e = cudaMallocHost(&S.hy, sizeof(double) * (size_t)cap * 2);
+    if (e == cudaSuccess && so && !S.ds) e = cudaMalloc(&S.ds, sizeof(int32_t) * (size_t)cap);
+    if (e == cudaSuccess && so && !S.hs) e = cudaMallocHost(&S.hs, sizeof(int32_t) * (size_t)cap);
+    if (e == cudaSuccess && sto && !S.dt) e = cudaMalloc(&S.dt, (size_t)cap);
+    if (e == cudaSuccess && sto && !S.ht) e = cudaMallocHost(&S.ht, (size_t)cap);
+    if (e != cudaSuccess) {
+      stage_free(P);
+      return fail(DLI_ERR_CUDA, std::string("dli_interp: staging allocation failed: ") + cudaGetErrorString(e));
+    }
+    P.nslots = std::max(P.nslots, i + 1);
+  }
+  std::atomic<int64_t> next{0};
+  std::atomic<int> rc_all{DLI_OK}, launch_all{0};
+  std::mutex err_mu;
+  std::string err_msg;
+  auto work = [&](int w) {
+    StageSlot &S = P.slot[w];
+    int rc = DLI_OK, nl = 0;
+    if (cudaSetDevice(m->device) != cudaSuccess) rc = fail(DLI_ERR_CUDA, "dli_interp: cannot select device");
+    while (rc == DLI_OK && rc_all.load(std::memory_order_relaxed) == DLI_OK) {
+      const int64_t off = next.fetch_add(1) * chunk;
+      if (off >= n) break;
+      const int64_t cn = std::min(chunk, n - off);
+      memcpy(S.hx, xs + off * d, sizeof(double) * (size_t)cn * d);
+      cudaError_t e = cudaMemcpyAsync(S.dx, S.hx, sizeof(double) * (size_t)cn * d, cudaMemcpyHostToDevice, S.st);
+      if (e != cudaSuccess) { rc = fail(DLI_ERR_CUDA, std::string("H2D copy failed: ") + cudaGetErrorString(e)); break; }
+      rc = run_device(m, cn, S.dx, ys ? S.dy : nullptr, so ? S.ds : nullptr, sto ? S.dt : nullptr, S.st, &nl, out);
+      if (rc != DLI_OK) break;
+      if (ys) e = cudaMemcpyAsync(S.hy, S.dy, sizeof(double) * (size_t)cn * yw, cudaMemcpyDeviceToHost, S.st);
+      if (e == cudaSuccess && so) e = cudaMemcpyAsync(S.hs, S.ds, sizeof(int32_t) * (size_t)cn, cudaMemcpyDeviceToHost, S.st);
+      if (e == cudaSuccess && sto) e = cudaMemcpyAsync(S.ht, S.dt, (size_t)cn, cudaMemcpyDeviceToHost, S.st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(S.st);
+      if (e != cudaSuccess) { rc = fail(DLI_ERR_CUDA, std::string("dli_interp: ") + cudaGetErrorString(e)); break; }
+      if (ys) memcpy(ys + off * yw, S.hy, sizeof(double) * (size_t)cn * yw);
+      if (so) memcpy(so + off, S.hs, sizeof(int32_t) * (size_t)cn);
+      if (sto) memcpy(sto + off, S.ht, (size_t)cn);
+    }
+    launch_all.fetch_add(nl);
+    if (rc != DLI_OK) {
+      std::lock_guard<std::mutex> lk(err_mu);
+      if (rc_all.load() == DLI_OK) { rc_all.store(rc); err_msg = g_err; }
+    }
+  };
+  std::vector<std::thread> pool;
+  try {
+    for (int w = 1; w < T; w++) pool.emplace_back(work, w);
+  } catch (...) {}                       // fewer helpers than planned: the remaining workers take all chunks
+  work(0);
+  for (std::thread &t : pool) t.join();
+  if (launches) *launches += launch_all.load();
+  return rc_all.load() == DLI_OK ? DLI_OK : fail(rc_all.load(), err_msg);
+}
+
 // host-pointer path: chunked H2D / compute / D2H pipeline over a ring of device slots.  The ring (streams +
 // staging buffers + straggler queues) lives in the mesh and is created once: a call costs no cudaMalloc /
 // cudaFree / stream creation.  H2D of chunk k+1, the kernels of chunk k and the D2H of chunk k-1 run on
@@ -1038,6 +1155,8 @@ int run_host(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t
   if (n == 0) return DLI_OK;
   const int d = m->dim;
   std::lock_guard<std::mutex> lk(m->pipe_mu);  // one host-path call at a time per mesh
+  if (n >= kStageMinQueries && (is_pageable(xs) || is_pageable(ys) || is_pageable(so) || is_pageable(sto)))
+    return run_host_staged(m, n, xs, ys, so, sto, launches, out);
   HostPipe &P = m->pipe;
   const int64_t chunk = kHostChunk;
   if (!P.ready) {
@@ -1100,6 +1219,10 @@ int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, in
     return fail(DLI_ERR_ARG, std::string(who) + ": misaligned device pointer");
   int launches = 0;
   int rc;
+  if (m->collect_stats) {     // counters cover the whole call, however many chunks the host paths cut it into
+    if (dev) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, (cudaStream_t)stream));
+    else { CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS)); CU(cudaDeviceSynchronize()); }
+  }
   if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches, out);
   else rc = run_host(m, n, xs, ys, so, sto, &launches, out);
   m->last.kernel_launches = launches;

@@ -13,7 +13,11 @@
  *   - query / result pointers may be HOST or DEVICE pointers (detected with
  *     cudaPointerGetAttributes).  With device pointers the call only enqueues work on `stream`
  *     and returns; with host pointers it runs a chunked H2D / compute / D2H pipeline and returns
- *     when the results are in the host buffers.
+ *     when the results are in the host buffers.  Page-locked host buffers (cudaMallocHost /
+ *     cudaHostRegister) are copied by DMA directly and run at the PCIe rate; pageable buffers
+ *     (malloc, std::vector, numpy) of >= 2^18 queries are staged through the library's own pinned
+ *     buffers by up to 8 worker threads (environment variable DLI_HOST_COPY_THREADS overrides the
+ *     default of half the host threads) -- about 4 x the driver's own pageable path.
  *   - per-query conditions are reported in status_out, never as an error return.
  *   - a mesh handle is immutable apart from dli_mesh_set_values() and dli_mesh_update(), which must
  *     not run while queries on the mesh are in flight; interp/locate calls on the same mesh may be

@@ -95,6 +95,35 @@ def test_device_pointer_path_matches_host_path(gpu):
     assert np.array_equal(ys_h, ys_d.cpu().numpy(), equal_nan=True)
 
 
+@pytest.mark.parametrize("dim", [2, 3])
+def test_pageable_host_buffers_take_the_staged_path(gpu, dim):
+    """numpy arrays are pageable memory: batches of >= 2^18 queries go through the pinned staging slots with one
+    worker thread per slot (several chunks, ragged last chunk, queries outside the hull included); every output must
+    equal the device-pointer path bit for bit, for interp, simplex, status and (2D) gradient."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(dim, 5000 if dim == 2 else 2000, 23)
+    n = (1 << 19) * 3 + 12345
+    q = np.random.default_rng(24).random((n, dim)) * 1.04 - 0.02
+    m = dl.Mesh(pts, f, sv, sn)
+    xq = torch.from_numpy(q).cuda()
+    y_d, s_d, t_d = m.interp(xq, return_simplex=True, return_status=True)
+    y_h, s_h, t_h = m.interp(q, return_simplex=True, return_status=True)
+    assert np.array_equal(y_h, y_d.cpu().numpy(), equal_nan=True)
+    assert np.array_equal(s_h, s_d.cpu().numpy()) and np.array_equal(t_h, t_d.cpu().numpy())
+    assert np.array_equal(m.interp(q), y_h, equal_nan=True)          # values only (no simplex / status staging)
+    if dim == 2:
+        assert np.array_equal(m.gradient(q), m.gradient(xq).cpu().numpy(), equal_nan=True)
+    # statistics calls stay on one worker and still count every query
+    # statistics cover the whole call, however many chunks it is cut into
+    m.collect_stats(True)
+    k = (1 << 19) + 7
+    _, t_k = m.interp(q[:k], return_status=True)
+    st = m.stats()
+    assert st["queries"] == k and st["outside"] == int(((t_k == 1) | (t_k == 2)).sum())
+    m.collect_stats(False)
+
+
 def test_closed_form_epilogue_within_tolerance(gpu):
     import delaunay_linterp_b200 as dl
     pts, f, sv, sn = helpers.random_mesh(2, 20000, 31)
