@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DLI_LIB") or os.path.join(_HERE, "libdli.so")  # DLI_LIB: developer override (kernel experiments)
 
-DLI_MAX_DIM = 6
+DLI_MAX_DIM = 4
 DLI_MESH_HEADER_WORDS = 16
 
 STATUS_OK, STATUS_OUTSIDE_PROJECTED, STATUS_OUTSIDE_NAN, STATUS_STEP_LIMIT, STATUS_NO_MESH = 0, 1, 2, 3, 4
@@ -34,7 +34,8 @@ class Options(C.Structure):
         ("queries_per_warp", C.c_int32),
         ("packed_faces", C.c_int32),
         ("prefetch_ring", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("outside_nan", C.c_int32),
+        ("reserved", C.c_int32 * 5),
     ]
 
 
@@ -122,6 +123,26 @@ HOST_SYMBOLS = [
     ("dli_di2_get_all_vertices", C.c_int64, [_vp, _vp]),
     ("dli_di2_get_line_segments", C.c_int64, [_vp, _vp]),
     ("dli_di2_line_segments", C.c_int64, [_vp, _vp, _vp, _vp, _vp]),
+    ("dli_dd_create", _vp, [C.c_int, DLI_FN, _vp]),
+    ("dli_dd_destroy", None, [_vp]),
+    ("dli_dd_dimension", C.c_int, [_vp]),
+    ("dli_dd_current_dimension", C.c_int, [_vp]),
+    ("dli_dd_num_vertices", C.c_int64, [_vp]),
+    ("dli_dd_num_simplices", C.c_int64, [_vp]),
+    ("dli_dd_insert", C.c_int32, [_vp, _vp, C.c_double]),
+    ("dli_dd_insert_many", C.c_int, [_vp, C.c_int64, _vp, _vp, C.c_int, C.c_int]),
+    ("dli_dd_insert_largest_error_point", C.c_int, [_vp, _dp, _dp, _vp]),
+    ("dli_dd_get_largest_error_tuple", C.c_int, [_vp, _dp, _dp, _vp]),
+    ("dli_dd_error_queue_size", C.c_int64, [_vp]),
+    ("dli_dd_get_error_queue", C.c_int64, [_vp, C.c_int64, _vp, _vp, _vp]),
+    ("dli_dd_export", C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    ("dli_dd_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_dd_device_mesh", _vp, [_vp]),
+    ("dli_dd_sync_count", C.c_int64, [_vp]),
+    ("dli_dd_set_options", C.c_int, [_vp, C.POINTER(Options)]),
+    ("dli_dd_get_all_vertices", C.c_int64, [_vp, _vp]),
+    ("dli_dd_get_line_segments", C.c_int64, [_vp, _vp, _vp, _vp]),
+    ("dli_dd_validate", C.c_int, [_vp, C.c_int]),
 ]
 
 _lib = None

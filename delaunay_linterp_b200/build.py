@@ -12,8 +12,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdli.so")
-SOURCES = ["dli_capi.cu", "dli_hostmesh.cpp"]
-HEADERS = ["dli_exact.cuh", "dli_device.cuh", "dli_kernels.cuh", "../../include/dli.h", "../../include/dli_host.h",
+SOURCES = ["dli_capi.cu", "dli_hostmesh.cpp", "dli_hostmesh_d.cpp"]
+HEADERS = ["dli_exact.cuh", "dli_device.cuh", "dli_kernels.cuh", "dli_refmath.h", "dli_host_small.h", "../../include/dli.h", "../../include/dli_host.h",
            "../../include/dli_error_math.h"]
 
 NVCC_FLAGS = [

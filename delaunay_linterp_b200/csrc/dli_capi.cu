@@ -197,6 +197,7 @@ extern "C" void dli_options_init(dli_options *o) {
   o->queries_per_warp = 0;
   o->packed_faces = 0;
   o->prefetch_ring = 0;
+  o->outside_nan = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -904,6 +905,7 @@ Mesh2View view2(const dli_mesh *m) {
   v.gx = m->grid.g[0]; v.gy = m->grid.g[1];
   v.ns = (int)m->ns; v.nh = m->nh;
   v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
+  v.outside_nan = m->opt.outside_nan;
   return v;
 }
 MeshDView viewD(const dli_mesh *m) {
@@ -1017,7 +1019,8 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
                cudaStream_t st, int *launches, int out = 0) {
   if (n == 0) return DLI_OK;
   if (m->ns == 0) {
-    k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out == 1 ? 2 * n : n, ys, nullptr, nullptr);
+    const int64_t cnt = out == 1 ? 2 * n : n;   // one thread per element: gradients are two doubles per query
+    k_fill_nomesh<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(cnt, ys, nullptr, nullptr);
     if (so || sto) k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, nullptr, so, sto);
     CU(cudaGetLastError());
     if (launches) *launches += 1;

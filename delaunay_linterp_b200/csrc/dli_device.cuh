@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include "dli_exact.cuh"
+#include "dli_refmath.h"
 #include "../../include/dli.h"
 
 namespace dli {
@@ -43,6 +44,7 @@ struct Mesh2View {
   int ns, nh;
   int max_steps;   // hard cap on simplices visited per query
   int fast_steps;  // fast-path cap; longer walks are re-run by the straggler/exact pass
+  int outside_nan; // != 0: queries outside the hull report DLI_STATUS_OUTSIDE_NAN instead of being projected
 };
 
 // dD (D = 3, 4): vertex record VS doubles {x_0..x_{D-1}, f, pad}; simplex record SS ints
@@ -105,33 +107,10 @@ struct StatsAcc {  // per-thread accumulators, flushed by the kernels when stats
 // 2D epilogue (reference operation order)
 // ---------------------------------------------------------------------------------------------
 
-// Eigen partial-pivot LU determinant of [[a, b], [c, d]]
-__device__ __forceinline__ double lu_det2(double a, double b, double c, double d) {
-  double s = 1.0;
-  if (fabs(c) > fabs(a)) {
-    double t = a; a = c; c = t;
-    t = b; b = d; d = t;
-    s = -1.0;
-  }
-  double l = (a != 0.0) ? c / a : 0.0;
-  double u = d - l * b;
-  return s * (a * u);
-}
-// signed area: column j = P_{j+1} - P_0 (src/delaunay_2_interp.h:202-207), det / 2!
-__device__ __forceinline__ double vol2(double ax, double ay, double bx, double by, double cx, double cy) {
-  return lu_det2(bx - ax, cx - ax, by - ay, cy - ay) * 0.5;
-}
+// reference operation order (dli_refmath.h: lu_det2 / vol2 / epilogue2_ref_xy, shared with the host side of small batches)
 __device__ __forceinline__ double epilogue2_ref(double px, double py, const double4 &A, const double4 &B,
                                                  const double4 &C) {
-  double whole = vol2(A.x, A.y, B.x, B.y, C.x, C.y);
-  double b0 = vol2(px, py, B.x, B.y, C.x, C.y) / whole;
-  double b1 = vol2(A.x, A.y, px, py, C.x, C.y) / whole;
-  double b2 = vol2(A.x, A.y, B.x, B.y, px, py) / whole;
-  double sum = 0.0;
-  sum = sum + b0 * A.z;
-  sum = sum + b1 * B.z;
-  sum = sum + b2 * C.z;
-  return sum;
+  return epilogue2_ref_xy(px, py, A.x, A.y, A.z, B.x, B.y, B.z, C.x, C.y, C.z);
 }
 // closed form (option epilogue = 1): one reciprocal, cross products
 __device__ __forceinline__ double epilogue2_fast(double px, double py, const double4 &A, const double4 &B,
@@ -144,33 +123,7 @@ __device__ __forceinline__ double epilogue2_fast(double px, double py, const dou
   return (w0 * A.z + w1 * B.z + w2 * C.z) * r;
 }
 
-// CGAL Cartesian Line_2(P,Q) + projection in plain doubles
-__device__ inline void project_on_line(double Px, double Py, double Qx, double Qy, double &px, double &py) {
-  double a, b, c;
-  if (Py == Qy) {
-    a = 0.0;
-    if (Qx > Px) { b = 1.0; c = -Py; }
-    else if (Qx == Px) { b = 0.0; c = 0.0; }
-    else { b = -1.0; c = Py; }
-  } else if (Qx == Px) {
-    b = 0.0;
-    if (Qy > Py) { a = -1.0; c = Px; }
-    else { a = 1.0; c = -Px; }
-  } else {
-    a = Py - Qy;
-    b = Qx - Px;
-    c = -Px * a - Py * b;
-  }
-  double x, y;
-  if (a == 0.0) { x = px; y = -c / b; }
-  else if (b == 0.0) { x = -c / a; y = py; }
-  else {
-    double a2 = a * a, b2 = b * b, d = a2 + b2;
-    x = (b2 * px - a * b * py - a * c) / d;
-    y = (-a * b * px + a2 * py - b * c) / d;
-  }
-  px = x; py = y;
-}
+// (project_on_line, hull_edge_score: dli_refmath.h)
 
 __device__ __forceinline__ int hint2(const Mesh2View &m, double x, double y) {
   int i = (int)((x - m.ox) * m.icx);
@@ -288,11 +241,6 @@ __device__ __forceinline__ bool locate2_fast(const Mesh2View &m, double px, doub
 // infinite face CGAL's walk ended in".  Farthest-line-first guarantees progress: after a projection p sits on the
 // line of its edge within rounding and that edge may still test strictly visible by an ulp; a fixed preference for
 // it would re-project p on the same line until the round cap.
-__device__ __forceinline__ double hull_edge_score(double Px, double Py, double Qx, double Qy, double px, double py) {
-  const double dx = Qx - Px, dy = Qy - Py;
-  const double det = dx * (py - Py) - dy * (px - Px);
-  return (det * det) / (dx * dx + dy * dy);
-}
 __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px, double py, int h0,
                                                   StatsAcc &st) {
   int best = h0;
@@ -709,153 +657,11 @@ __device__ inline uint8_t locateD_full(const MeshDView &m, const double *p, int 
   return DLI_STATUS_OK;
 }
 
-// Eigen PartialPivLU determinant (unblocked), n = D, matrix row-major in registers (destroyed)
-template <int D>
-__device__ __forceinline__ double lu_det(double *a) {
-  double sgn = 1.0;
-#pragma unroll
-  for (int c = 0; c < D; c++) {
-    int piv = c;
-    double best = fabs(a[c * D + c]);
-#pragma unroll
-    for (int r = c + 1; r < D; r++) {
-      double v = fabs(a[r * D + c]);
-      if (v > best) { best = v; piv = r; }
-    }
-    // swap rows c and piv (piv is dynamic: select-based swap keeps everything in registers)
-#pragma unroll
-    for (int r = c + 1; r < D; r++) {
-      if (r == piv) {
-#pragma unroll
-        for (int j = 0; j < D; j++) { double t = a[c * D + j]; a[c * D + j] = a[r * D + j]; a[r * D + j] = t; }
-      }
-    }
-    if (piv != c) sgn = -sgn;
-    double pv = a[c * D + c];
-#pragma unroll
-    for (int r = c + 1; r < D; r++) {
-      double l = (pv != 0.0) ? a[r * D + c] / pv : a[r * D + c];
-      a[r * D + c] = l;
-#pragma unroll
-      for (int j = c + 1; j < D; j++) a[r * D + j] = a[r * D + j] - l * a[c * D + j];
-    }
-  }
-  double prod = a[0];
-#pragma unroll
-  for (int i = 1; i < D; i++) prod = prod * a[i * D + i];
-  return sgn * prod;
-}
+// (lu_det, volD, dot_exact_trunc, epilogueD_ref_xf: dli_refmath.h)
 
-// signed volume; column j = pts[j+1] - pts[0]; exact difference rounded toward zero (Gmpq
-// subtraction + mpq_get_d, src/delaunay_d_interp.h:608-613), det / D!
-template <int D>
-__device__ __forceinline__ double volD(const double *const *pts) {
-  double a[D * D];
-#pragma unroll
-  for (int j = 0; j < D; j++)
-#pragma unroll
-    for (int i = 0; i < D; i++) a[i * D + j] = __dsub_rz(pts[j + 1][i], pts[0][i]);
-  constexpr double fact = (D == 2 ? 2.0 : D == 3 ? 6.0 : D == 4 ? 24.0 : 120.0);
-  return lu_det<D>(a) / fact;
-}
-
-// exact sum of products truncated toward zero (Gmpq accumulation + mpq_get_d, :998-1004): slow, exact path
-template <int K>
-__device__ __noinline__ double dot_exact_trunc_slow(const double *b, const double *f) {
-  double e[2 * K + 1], t[2 * K + 2];
-  int n = 0;
-  for (int i = 0; i < K; i++) {
-    double p, q;
-    two_prod(b[i], f[i], p, q);
-    grow_ze(e, n, q);
-    grow_ze(e, n, p);
-  }
-  double A = 0.0;
-  for (int i = n - 1; i >= 0; i--) A += e[i];
-  if (!isfinite(A)) return A;
-  for (int it = 0; it < 8; it++) {
-    int tn = n;
-    for (int i = 0; i < n; i++) t[i] = e[i];
-    grow_ze(t, tn, -A);
-    int sd = expansion_sign(t, tn);
-    int sa = (A > 0.0) - (A < 0.0);
-    if (sd == 0) break;
-    if (sa != 0 && sd == -sa) { A = nextafter(A, 0.0); continue; }
-    double up = nextafter(A, sd > 0 ? (double)INFINITY : -(double)INFINITY);
-    tn = n;
-    for (int i = 0; i < n; i++) t[i] = e[i];
-    grow_ze(t, tn, -up);
-    int su = expansion_sign(t, tn);
-    if (su == 0 || su == sd) { A = up; if (su == 0) break; continue; }
-    break;
-  }
-  return A;
-}
-
-// Same value, register-only fast path: compensated (double-double) accumulation gives the total as h + l
-// with |l| <= ulp(h)/2 up to an error far below |l|; the truncation toward zero is then h when l has the
-// sign of h (or is an exact zero), else the neighbour of h towards zero.  When l is too small to trust its
-// sign (relative to the accumulated rounding bound) the exact path decides.
-template <int K>
-__device__ __forceinline__ double dot_exact_trunc(const double *b, const double *f) {
-  double s, lo = 0.0, pabs, q;
-  two_prod(b[0], f[0], s, q);
-  lo = q;
-  pabs = fabs(s);
-  bool all_exact = (q == 0.0);
-#pragma unroll
-  for (int i = 1; i < K; i++) {
-    double p, qq, sn, e;
-    two_prod(b[i], f[i], p, qq);
-    two_sum(s, p, sn, e);
-    s = sn;
-    lo += e + qq;
-    pabs += fabs(p);
-    all_exact = all_exact && (e == 0.0) && (qq == 0.0);
-  }
-  if (all_exact) return s;  // every operation was exact: s is the exact total
-  double h, l;
-  two_sum(s, lo, h, l);  // (|lo| <= |s| is not guaranteed under cancellation, so not fast_two_sum)
-  if (!isfinite(h)) return h;
-  // rounding of `lo` itself is bounded by ~K^2 2^-106 sum|p_i|; demand a wide margin
-  if (!(fabs(l) > 8.673617379884035e-19 * 1.1102230246251565e-16 * 1048576.0 * pabs)) return dot_exact_trunc_slow<K>(b, f);
-  bool same = (l > 0.0) == (h > 0.0);
-  return same ? h : nextafter(h, 0.0);
-}
-
-// COMPACT (exact pass): the loop over the D+1 replaced vertices stays rolled -- that pass is bound by instruction
-// fetch, and D+2 unrolled copies of the pivoting LU are most of its code.  Same operations in the same order.
 template <int D, bool COMPACT = false>
 __device__ __forceinline__ double epilogueD_ref(const double *p, const SimplexD<D> &S) {
-  const double *pts[D + 1];
-#pragma unroll
-  for (int i = 0; i <= D; i++) pts[i] = &S.x[i * D];
-  double b[D + 1];
-  if (COMPACT) {
-    double whole = 1.0;
-#pragma unroll 1
-    for (int i = -1; i <= D; i++) {
-      const double *q[D + 1];
-#pragma unroll
-      for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
-      const double v = volD<D>(q);
-      if (i < 0) whole = v;
-      else {
-#pragma unroll
-        for (int j = 0; j <= D; j++) if (j == i) b[j] = v / whole;
-      }
-    }
-  } else {
-    double whole = volD<D>(pts);
-#pragma unroll
-    for (int i = 0; i <= D; i++) {
-      const double *q[D + 1];
-#pragma unroll
-      for (int j = 0; j <= D; j++) q[j] = (j == i) ? p : pts[j];
-      b[i] = volD<D>(q) / whole;
-    }
-  }
-  return dot_exact_trunc<D + 1>(b, S.f);
+  return epilogueD_ref_xf<D, COMPACT>(p, S.x, S.f);
 }
 
 // closed form (option epilogue = 1): one LU solve of [P1-P0 .. PD-P0] lam = p - P0

@@ -520,15 +520,15 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
       continue;
     }
     double4 A, B, C;
-    uint8_t status = locate2_full(m, px, py, f, A, B, C, st);
+    uint8_t status = m.outside_nan ? locate2_full<false>(m, px, py, f, A, B, C, st) : locate2_full(m, px, py, f, A, B, C, st);
     double y;
-    if (status == DLI_STATUS_STEP_LIMIT) {
+    if (status == DLI_STATUS_STEP_LIMIT || status == DLI_STATUS_OUTSIDE_NAN) {
       y = __longlong_as_double(0x7ff8000000000000LL);
     } else {
       y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
     }
     if (ys) ys[i] = y;
-    if (simplex_out) simplex_out[i] = __ldg(m.orig + f);
+    if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN) ? -1 : __ldg(m.orig + f);
     if (status_out) status_out[i] = status;
   }
   if (STATS) {

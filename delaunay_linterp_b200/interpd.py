@@ -5,28 +5,15 @@ Same method names and conventions (points are lists of floats, ErrorTuple -> (er
 hull returns NaN, :1005-1008), plus batched interp(ndarray (n, d)) -> ndarray (n,) on the GPU.
 
 Host side: the reference builds on the patched CGAL Delaunay_d (modified_cgal/Delaunay_d.h), which is unavailable;
-here the d-dimensional triangulation is maintained by Qhull in incremental mode (scipy.spatial.Delaunay(incremental=True)),
-which stays on the host like the reference's CGAL.  Per-insertion error tuples (a handful of simplices) are computed on
-the host with the closed form of include/dli_error_math.h; rebuild_error_queue() evaluates the whole mesh on the GPU.
+the d-dimensional triangulation and the adaptive queue are native (csrc/dli_hostmesh_d.cpp behind the `dli_dd_*` C ABI
+of include/dli_host.h -- the same object the C++ drop-in header include/delaunay_d_interp.h wraps).
 """
-import heapq
-import itertools
+import ctypes as C
 
 import numpy as np
 
-from .mesh import Mesh, _is_torch_tensor
-
-
-def _simplex_error(w, phi):
-    """closed form of compute_simplex_error (src/delaunay_d_interp.h:1078-1093): w (np, d+1) lifted vertices."""
-    fbar = w[:, -1].mean()
-    u = (w[1:] - w[0]).T                       # (d+1, np-1)
-    q, _ = np.linalg.qr(u)
-    ez = np.zeros(w.shape[1])
-    ez[-1] = 1.0
-    r = ez - q @ (q.T @ ez)
-    r = r - q @ (q.T @ r)
-    return float((phi - fbar) ** 2 * (r @ r))
+from ._capi import DLI_FN, DliError, check, lib
+from .mesh import _is_torch_tensor, _make_options
 
 
 class Delaunay_incremental_interp_d:
@@ -34,192 +21,145 @@ class Delaunay_incremental_interp_d:
         if not 2 <= n_dims <= 4:
             raise ValueError("n_dims must be 2, 3 or 4")
         self.N = int(n_dims)
-        self.fn = fn
-        self._options = options
-        self._pts = []          # inserted points (lists)
-        self._f = []
-        self._index = {}        # point tuple -> vertex id
-        self._tri = None        # scipy Delaunay once d+1 affinely independent points exist
-        self._incremental = False
-        self._mesh = None       # device copy, rebuilt lazily
-        self._keys = {}         # frozenset(vertex ids) of current simplices -> live entry count holder
-        self._heap = []         # (-err, seq, f, x tuple, simplex key)
-        self._seq = 0
+        self.fn = fn                                  # read-only attribute of the reference binding (:366)
+        if fn is not None:
+            def _tramp(n, x, _user):
+                return float(fn([x[i] for i in range(n)]))   # callback receives a list (src/delaunay_d_python.cpp:233-241)
+            self._cb = DLI_FN(_tramp)
+        else:
+            self._cb = C.cast(None, DLI_FN)
+        self._h = C.c_void_p(lib().dli_dd_create(self.N, self._cb, None))
+        if not self._h:
+            raise ValueError("dli_dd_create failed")
+        if options:
+            opt = _make_options(**options)
+            check(lib().dli_dd_set_options(self._h, C.byref(opt)))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().dli_dd_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    @property
+    def triang(self):
+        """the reference exposes its CGAL Delaunay_d here (:365); this object plays both roles"""
+        return self
 
     def get_dimension(self):
         return self.N
+
+    def dimension(self):
+        return self.N
+
+    def current_dimension(self):
+        return lib().dli_dd_current_dimension(self._h)
+
+    def number_of_vertices(self):
+        return lib().dli_dd_num_vertices(self._h)
+
+    def number_of_simplices(self):
+        return lib().dli_dd_num_simplices(self._h)
 
     # ---- construction (host)
     def _point(self, x):
         if len(x) != self.N:
             raise TypeError("a point is a list of %d floats" % self.N)
-        return tuple(float(v) for v in x)
+        return (C.c_double * self.N)(*[float(v) for v in x])
 
     def insert(self, x, f):
-        p = self._point(x)
-        self._mesh = None
-        if p in self._index:                      # existing point: value overwritten
-            self._f[self._index[p]] = float(f)
-            return
-        self._index[p] = len(self._pts)
-        self._pts.append(p)
-        self._f.append(float(f))
-        if self._tri is not None and self._incremental:
-            self._tri.add_points(np.array([p]))
-        elif len(self._pts) >= self.N + 1:
-            self._try_start()
-        if self._tri is not None and self.fn is not None:
-            self._update_queue()
+        v = lib().dli_dd_insert(self._h, self._point(x), float(f))
+        if v < 0:
+            raise DliError(v, "insert: bad point")
+        return None
 
-    def _try_start(self):
-        """Qhull's incremental mode cannot start from cospherical / too few sites; until it can, the (small)
-        triangulation is rebuilt from scratch on every insertion (default options, which include Qz)."""
-        from scipy.spatial import Delaunay
-        from scipy.spatial import QhullError
-        pts = np.array(self._pts)
-        try:
-            self._tri = Delaunay(pts, incremental=True)
-            self._incremental = True
-            return
-        except QhullError:
-            pass
-        try:
-            self._tri = Delaunay(pts)
-            self._incremental = False
-        except QhullError:
-            self._tri = None                      # fewer than d+1 affinely independent points so far
+    def insert_many(self, xs, fs, spatial_sort=True, use_gpu=True):
+        xs = np.ascontiguousarray(xs, dtype=np.float64).reshape(-1, self.N)
+        fs = np.ascontiguousarray(fs, dtype=np.float64).reshape(-1)
+        assert xs.shape[0] == fs.shape[0]
+        check(lib().dli_dd_insert_many(self._h, xs.shape[0], xs.ctypes.data, fs.ctypes.data, int(spatial_sort),
+                                       int(use_gpu)))
 
-    def _current(self):
-        sv = self._tri.simplices.astype(np.int32)
-        sn = self._tri.neighbors.astype(np.int32)
-        return sv, sn
+    def validate(self, check_delaunay=True):
+        """0 when the triangulation is structurally valid (and Delaunay); test hook (dli_dd_validate)."""
+        return lib().dli_dd_validate(self._h, int(check_delaunay))
 
-    def _items_of(self, simplex, neighbors):
-        """vertex subsets that get an error tuple for this simplex: itself + every subset (size >= 2) of each hull facet
-        (src/delaunay_d_interp.h:810-848); duplicates across simplices are kept, as in the reference."""
-        k = self.N + 1
-        items = [tuple(int(v) for v in simplex)]
-        for j in range(k):
-            if neighbors[j] < 0:
-                facet = [int(simplex[i]) for i in range(k) if i != j]
-                for size in range(2, len(facet) + 1):
-                    items.extend(itertools.combinations(facet, size))
-        return items
+    def get_largest_error_tuple(self):
+        e, f, x = C.c_double(), C.c_double(), (C.c_double * self.N)()
+        rc = lib().dli_dd_get_largest_error_tuple(self._h, C.byref(e), C.byref(f), x)
+        assert rc == 0, "empty queue or no callback"          # the reference asserts (:1029-1030)
+        return (e.value, f.value, list(x))
 
-    def _push_simplex(self, key, simplex, neighbors):
-        pts = np.array(self._pts)
-        fv = np.array(self._f)
-        n = 0
-        for verts in self._items_of(simplex, neighbors):
-            v = list(verts)
-            c = pts[v].sum(axis=0) / len(v)
-            phi = float(self.fn([float(t) for t in c]))
-            w = np.c_[pts[v], fv[v]]
-            heapq.heappush(self._heap, (-_simplex_error(w, phi), self._seq, phi, tuple(c.tolist()), key))
-            self._seq += 1
-            n += 1
-        self._keys[key] = n
+    def insert_largest_error_point(self):
+        e, f, x = C.c_double(), C.c_double(), (C.c_double * self.N)()
+        rc = lib().dli_dd_insert_largest_error_point(self._h, C.byref(e), C.byref(f), x)
+        if rc != 0:
+            raise AssertionError("insert_largest_error_point: empty queue or no callback")
+        return (e.value, f.value, list(x))
 
-    def _update_queue(self):
-        sv, sn = self._current()
-        new = {}
-        for s in range(len(sv)):
-            new[frozenset(int(v) for v in sv[s])] = s
-        for key in [k for k in self._keys if k not in new]:
-            del self._keys[key]                   # entries become stale (lazy deletion)
-        for key, s in new.items():
-            if key not in self._keys:
-                self._push_simplex(key, sv[s], sn[s])
+    def get_error_queue(self):
+        cap = lib().dli_dd_error_queue_size(self._h)
+        err, f, xs = np.empty(max(cap, 1)), np.empty(max(cap, 1)), np.empty((max(cap, 1), self.N))
+        n = lib().dli_dd_get_error_queue(self._h, cap, err.ctypes.data, f.ctypes.data, xs.ctypes.data)
+        if n < 0:
+            raise DliError(n, "get_error_queue")
+        return [(float(err[i]), float(f[i]), xs[i].tolist()) for i in range(n)]
 
     def rebuild_error_queue(self):
         """recompute every tuple of the current triangulation in one batch on the GPU (dli_simplex_error_*)."""
-        assert self.fn is not None and self._tri is not None
-        m = self._device_mesh()
-        cent, item_simplex, item_verts = m.simplex_error_items()
-        phi = np.array([float(self.fn(c.tolist())) for c in cent])
-        err = m.simplex_error(phi)
-        csv, _ = m.simplices()
-        self._heap, self._keys = [], {}
-        for i in range(len(err)):
-            key = frozenset(int(v) for v in csv[item_simplex[i]])
-            self._keys[key] = self._keys.get(key, 0) + 1
-            self._heap.append((-float(err[i]), self._seq, float(phi[i]), tuple(cent[i].tolist()), key))
-            self._seq += 1
-        heapq.heapify(self._heap)
+        assert self.fn is not None
+        check(lib().dli_dd_insert_many(self._h, 0, None, None, 0, 1))
 
-    def _prune(self):
-        while self._heap and self._heap[0][4] not in self._keys:
-            heapq.heappop(self._heap)
-
-    def get_largest_error_tuple(self):
-        self._prune()
-        assert self.fn is not None and self._heap, "empty queue or no callback"
-        e = self._heap[0]
-        return (-e[0], e[2], list(e[3]))
-
-    def insert_largest_error_point(self):
-        t = self.get_largest_error_tuple()
-        self.insert(t[2], t[1])
-        return t
-
-    def get_error_queue(self):
-        live = [e for e in self._heap if e[4] in self._keys]
-        live.sort()
-        return [(-e[0], e[2], list(e[3])) for e in live]
-
-    # ---- the hot path (GPU)
-    def _device_mesh(self):
-        if self._mesh is None:
-            if self._tri is None:
-                sv = np.zeros((0, self.N + 1), np.int32)
-                pts = np.array(self._pts, dtype=np.float64).reshape(-1, self.N)
-                self._mesh = Mesh(pts, np.array(self._f, dtype=np.float64), sv, None, **self._options)
-            else:
-                sv, sn = self._current()
-                self._mesh = Mesh(np.array(self._pts), np.array(self._f), sv, sn, **self._options)
-        return self._mesh
-
+    # ---- the hot path (GPU; one point at a time is answered on the host, see include/dli_host.h)
     def interp(self, x, return_status=False):
         """interp([x...]) -> float (NaN outside the hull) or interp(ndarray (n, d) / torch CUDA tensor) -> array."""
-        m = self._device_mesh()
         if _is_torch_tensor(x):
-            return m.interp(x, return_status=return_status)
+            import torch
+            xs = x.contiguous().view(-1, self.N)
+            ys = torch.empty(xs.shape[0], dtype=torch.float64, device=xs.device)
+            st = torch.empty(xs.shape[0], dtype=torch.uint8, device=xs.device) if return_status else None
+            check(lib().dli_dd_interp(self._h, xs.shape[0], xs.data_ptr(), ys.data_ptr(), None,
+                                      st.data_ptr() if st is not None else None,
+                                      torch.cuda.current_stream(xs.device).cuda_stream))
+            return (ys, st) if return_status else ys
         scalar = isinstance(x, (list, tuple)) and len(x) == self.N and not isinstance(x[0], (list, tuple, np.ndarray))
         xs = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, self.N)
-        ys, st = m.interp(xs, return_status=True)
+        n = xs.shape[0]
+        ys = np.empty(n, np.float64)
+        st = np.empty(n, np.uint8)
+        check(lib().dli_dd_interp(self._h, n, xs.ctypes.data, ys.ctypes.data, None, st.ctypes.data, None))
         if scalar:
             return float(ys[0])
         return (ys, st) if return_status else ys
 
     # ---- plot data
     def get_all_vertices(self):
-        return [list(p) + [f] for p, f in zip(self._pts, self._f)]
+        nv = lib().dli_dd_get_all_vertices(self._h, None)
+        out = np.empty((max(nv, 1), self.N + 1))
+        lib().dli_dd_get_all_vertices(self._h, out.ctypes.data)
+        return out[:nv].tolist()
 
     def get_line_segments(self):
         """(all_segments, min_coords, max_coords) as the reference returns it (src/delaunay_d_interp.h:1115-1142): the
         segments of a simplex are its consecutive vertex pairs (i, i+1 mod N+1) (:1103-1112), every pair once, flag 1."""
         n1 = self.N + 1
-        lo, hi = [float(np.finfo(np.float64).max)] * n1, [-float(np.finfo(np.float64).max)] * n1
-        if self._tri is None:
-            return [], lo, hi
-        sv, _ = self._current()
-        edges = set()
-        for s in sv:
-            for i in range(n1):
-                a, b = int(s[i]), int(s[(i + 1) % n1])
-                edges.add((min(a, b), max(a, b)))
-        out = []
-        for a, b in sorted(edges):
-            pa, pb = list(self._pts[a]) + [self._f[a]], list(self._pts[b]) + [self._f[b]]
-            out.append((pa, pb, 1))
-            for p in (pa, pb):
-                lo = [min(u, v) for u, v in zip(lo, p)]
-                hi = [max(u, v) for u, v in zip(hi, p)]
-        return out, lo, hi
+        ne = lib().dli_dd_get_line_segments(self._h, None, None, None)
+        if ne < 0:
+            raise DliError(ne, "get_line_segments")
+        seg = np.empty((max(ne, 1), 2, n1))
+        lo, hi = np.empty(n1), np.empty(n1)
+        lib().dli_dd_get_line_segments(self._h, seg.ctypes.data, lo.ctypes.data, hi.ctypes.data)
+        return [(seg[i, 0].tolist(), seg[i, 1].tolist(), 1) for i in range(ne)], lo.tolist(), hi.tolist()
 
     def export(self):
-        sv, sn = self._current() if self._tri is not None else (np.zeros((0, self.N + 1), np.int32),) * 2
-        return np.array(self._pts), np.array(self._f), sv, sn
+        nv, ns, k = self.number_of_vertices(), self.number_of_simplices(), self.N + 1
+        pts, f = np.empty((nv, self.N)), np.empty(nv)
+        sv, sn = np.empty((ns, k), np.int32), np.empty((ns, k), np.int32)
+        check(lib().dli_dd_export(self._h, pts.ctypes.data if nv else None, f.ctypes.data if nv else None,
+                                  sv.ctypes.data if ns else None, sn.ctypes.data if ns else None))
+        return pts, f, sv, sn
 
 
 def get_lifted_point(x):

@@ -34,8 +34,8 @@
 extern "C" {
 #endif
 
-#define DLI_VERSION 1
-#define DLI_MAX_DIM 6
+#define DLI_VERSION 2
+#define DLI_MAX_DIM 4 /* dimensions 2, 3 and 4 are supported */
 
 /* error returns */
 #define DLI_OK 0
@@ -89,7 +89,11 @@ typedef struct dli_options {
                                      addressed by its hint cell, no hint read; for tests) */
   int32_t prefetch_ring;          /* 2D walk-record fast pass: 0 = per-warp cp.async prefetch ring for queries and start
                                      hints (default), -1 = plain loads */
-  int32_t reserved[6];
+  int32_t outside_nan;            /* 2D: 0 = queries outside the hull are projected on the hull (Delaunay_incremental_interp_2,
+                                     src/delaunay_2_interp.h:530-545; default), 1 = they report DLI_STATUS_OUTSIDE_NAN with a
+                                     quiet NaN like the dD class (src/delaunay_d_interp.h:1005-1008; what
+                                     Delaunay_incremental_interp_d(2) needs).  dD meshes always report NaN. */
+  int32_t reserved[5];
 } dli_options;
 
 /* fills *opt with the defaults */

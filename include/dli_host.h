@@ -1,7 +1,7 @@
 /*
  * dli_host.h -- C ABI of the host-side objects that stand where the reference keeps CGAL:
- * an incremental 2D Delaunay triangulation with vertex values and the adaptive-insertion
- * error queue, feeding the GPU engine (include/dli.h) through the flattener.
+ * incremental Delaunay triangulations (2D: dli_di2, d dimensions: dli_dd) with vertex values and the
+ * adaptive-insertion error queue, feeding the GPU engine (include/dli.h) through the flattener.
  *
  * The reference builds on CGAL::Delaunay_triangulation_2 (src/delaunay_2_interp.h:66-95), which is
  * not available here (no CGAL in the image), so construction is native: Bowyer-Watson insertion with
@@ -98,6 +98,72 @@ int64_t dli_di2_get_line_segments(const dli_di2 *d, double *segments);
    edge (:766-803) and the min / max of (x, y, f); evaluated on the GPU (dli_mesh_line_segments).  Returns ne (call
    with NULL arrays first), or a negative error. */
 int64_t dli_di2_line_segments(dli_di2 *d, double *segments, int32_t *concave, double *min_coords, double *max_coords);
+
+/*
+ * dli_dd mirrors class Delaunay_incremental_interp_d (src/delaunay_d_interp.h:753-1142) for n_dims = 2, 3, 4.
+ * The reference builds on its patched CGAL Delaunay_d (modified_cgal/Delaunay_d.h over modified_cgal/Convex_hull_d.h:
+ * lower hull of the lifted points, Gmpq coordinates, history DAG); here the triangulation is native: Bowyer-Watson
+ * insertion directly in d dimensions with an infinite vertex, exact orientation and in-sphere predicates (fp64 filter,
+ * then floating-point expansions), vertex -> value stored with the vertex (m_pointMap :757).
+ *   ctor(int) / ctor(int, fn)        :772-781   -> dli_dd_create
+ *   get_dimension                    :783       -> dli_dd_dimension
+ *   insert / insert_point            :933-956   -> dli_dd_insert (dirty set = simplices created / removed, the
+ *                                                  "modified simplices" of modified_cgal/Convex_hull_d.h:1172-1178)
+ *   interp / interp_point            :982-1010  -> dli_dd_interp (batched, on the GPU; NaN outside the hull)
+ *   insert_largest_error_point       :1028-1034 -> dli_dd_insert_largest_error_point
+ *   get_largest_error_tuple          :1036-1038 -> dli_dd_get_largest_error_tuple
+ *   get_error_queue                  :1040-1043 -> dli_dd_get_error_queue
+ *   get_all_vertices                 :1097-1101 -> dli_dd_get_all_vertices
+ *   get_line_segments                :1103-1141 -> dli_dd_get_line_segments
+ *   set_simplex_info / add_error_of_boundary_subsimplices / clear_simplex_info :832-916 (host, per inserted star)
+ */
+typedef struct dli_dd dli_dd;
+
+/* n_dims in 2 .. DLI_MAX_DIM (NULL otherwise); fn may be NULL: no error queue is kept (:772-775) */
+dli_dd *dli_dd_create(int n_dims, dli_fn fn, void *user);
+void dli_dd_destroy(dli_dd *d);
+int dli_dd_dimension(const dli_dd *d);
+/* affine dimension of the points inserted so far (Delaunay_d::current_dimension): -1 none, n_dims once simplices exist */
+int dli_dd_current_dimension(const dli_dd *d);
+int64_t dli_dd_num_vertices(const dli_dd *d);
+int64_t dli_dd_num_simplices(const dli_dd *d); /* finite simplices */
+
+/* insert(x [n_dims], f): a duplicate point only overwrites its value.  Returns the vertex id or a negative error. */
+int32_t dli_dd_insert(dli_dd *d, const double *x, double f);
+/* bulk insertion; spatial_sort != 0 inserts in a biased randomised order along a Morton curve (same triangulation for
+   points in general position, much faster).  With a callback the error queue is rebuilt afterwards (batched on the GPU
+   through dli_simplex_error_* when use_gpu != 0). */
+int dli_dd_insert_many(dli_dd *d, int64_t n, const double *xs, const double *f, int spatial_sort, int use_gpu);
+
+/* DLI_ERR_ARG if the queue is empty or there is no callback (the reference asserts, :1029-1030) */
+int dli_dd_insert_largest_error_point(dli_dd *d, double *err, double *f, double *x /* [n_dims] */);
+int dli_dd_get_largest_error_tuple(dli_dd *d, double *err, double *f, double *x /* [n_dims] */);
+int64_t dli_dd_error_queue_size(dli_dd *d);
+/* up to cap live tuples ordered by decreasing error; xs [cap][n_dims]; returns the number written (or a negative error) */
+int64_t dli_dd_get_error_queue(dli_dd *d, int64_t cap, double *err, double *f, double *xs);
+
+/* flattened triangulation: coords [nv][n_dims], f [nv], sv [ns][n_dims + 1] (positively oriented), sn [ns][n_dims + 1]
+   (k-th entry opposite vertex k, -1 = hull); any may be NULL */
+int dli_dd_export(const dli_dd *d, double *coords, double *f, int32_t *sv, int32_t *sn);
+
+/* batched interp.  The device mesh is re-created lazily after insertions.  Host or device pointers as dli_interp;
+   queries outside the hull (or before n_dims + 1 affinely independent points exist) get a quiet NaN (:1005-1008) and
+   DLI_STATUS_OUTSIDE_NAN / DLI_STATUS_NO_MESH.  Small batches of host pointers (one point at a time, as the reference's
+   own loops call it) are answered on the host by an exact walk on the triangulation -- no GPU call; see dli_host_small.h. */
+int dli_dd_interp(dli_dd *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
+                  void *stream);
+const dli_mesh *dli_dd_device_mesh(dli_dd *d);
+int64_t dli_dd_sync_count(const dli_dd *d); /* how often the device mesh was (re-)created */
+int dli_dd_set_options(dli_dd *d, const dli_options *opt);
+
+/* plot data: vertices as (x..., f) rows [nv][n_dims + 1]; count query with NULL */
+int64_t dli_dd_get_all_vertices(const dli_dd *d, double *out);
+/* get_line_segments (:1103-1141): the consecutive vertex pairs (i, i + 1 mod n_dims + 1) of every simplex, each
+   unordered pair once, as segments [ne][2][n_dims + 1]; min / max over the end points [n_dims + 1] (DBL_MAX / -DBL_MAX
+   without segments).  Returns ne (call with NULL arrays first) or a negative error. */
+int64_t dli_dd_get_line_segments(const dli_dd *d, double *segments, double *min_coords, double *max_coords);
+/* test hook: 0 when the triangulation is structurally valid (and Delaunay, with check_delaunay != 0) */
+int dli_dd_validate(const dli_dd *d, int check_delaunay);
 
 #ifdef __cplusplus
 }
