@@ -87,6 +87,7 @@ SYMBOLS = [
     ("dli_mesh_buffer_write", C.c_int, [_vp, C.c_int, _vp]),
     ("dli_mesh_get_grid_params", C.c_int, [_vp, _vp]),
     ("dli_mesh_set_grid_params", C.c_int, [_vp, _vp]),
+    ("dli_mesh_replicate", C.c_int, [C.POINTER(_vp), _vp, C.c_int]),
     ("dli_mesh_save", C.c_int, [_vp, C.c_char_p]),
     ("dli_mesh_load", C.c_int, [C.c_char_p, C.POINTER(Options), C.POINTER(_vp)]),
     ("dli_mesh_collect_stats", C.c_int, [_vp, C.c_int]),

@@ -131,6 +131,9 @@ struct dli_mesh {
   ulonglong2 *d_fpack = nullptr;  // 2D packed face records (fast pass), NULL when ids do not fit 21 bits
   uint4 *d_fat = nullptr;         // 2D 64-byte walk records (k_interp2_fat), NULL when unused
   int64_t n_slow_faces = 0;       // faces carrying the slow flag in d_fat
+  int fat_enc = -1;               // neighbour fields of the 2D walk records: 0 = absolute ids, 1 = delta-encoded; -1 = not
+                                  // decided yet (creating rank: from the mesh size / options; replicas and snapshots: from
+                                  // header word 13, never re-derived from their own options)
   // cell-indexed walk records (2D meshes far larger than L2): d_fat has nslots = cells + extra records
   bool cellmode = false;
   int64_t nslots = 0;             // records in d_fat (== ns unless cellmode)
@@ -410,7 +413,10 @@ static int mesh_alloc_common(dli_mesh *m) {
 }
 
 // walk records of meshes with >= 2^21-2 faces (or opt.packed_faces == 2: testing) use delta-encoded neighbours
-static bool fat_delta(const dli_mesh *m) { return m->ns >= (1 << 21) - 2 || m->opt.packed_faces == 2; }
+static bool fat_delta(const dli_mesh *m) {
+  if (m->fat_enc >= 0) return m->fat_enc == 1;
+  return m->ns >= (1 << 21) - 2 || m->opt.packed_faces == 2;
+}
 
 static SlotGrid slot_grid(const dli_mesh *m) {
   SlotGrid g;
@@ -1507,7 +1513,9 @@ extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORD
   h[0] = DLI_VERSION; h[1] = m->dim; h[2] = m->nv; h[3] = m->ns; h[4] = m->nh; h[5] = m->grid.cells;
   for (int k = 0; k < 4; k++) h[6 + k] = m->grid.g[k];
   h[10] = m->max_steps; h[11] = m->fast_steps;
-  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : 1) : 0;  // optional buffers the replica must mirror
+  // optional buffers the replica must mirror, and how the walk records encode their neighbours:
+  // word 13: 0 = no walk records, 1 = absolute neighbour ids, 2 = cell-indexed records, 3 = delta-encoded neighbours
+  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : 1)) : 0;
   h[15] = m->nslots;
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
@@ -1537,8 +1545,9 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   int rc = mesh_alloc_common(m);
   // mirror the source's optional buffers exactly (every rank must see the same buffer list)
   if (rc == DLI_OK && !h[12] && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
-  if (rc == DLI_OK && h[13] != 1 && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
+  if (rc == DLI_OK && h[13] != 1 && h[13] != 3 && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
   m->cellmode = h[13] == 2;
+  m->fat_enc = h[13] == 3 ? 1 : 0;
   m->nslots = h[13] == 2 ? h[15] : m->ns;
   if (rc == DLI_OK && m->cellmode &&
       (cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess ||
@@ -1611,6 +1620,129 @@ extern "C" int dli_mesh_set_grid_params(dli_mesh *m, const double *in) {
   if (!m || !in) return fail(DLI_ERR_ARG, "NULL argument");
   for (int k = 0; k < DLI_MAX_DIM; k++) { m->grid.o[k] = in[k]; m->grid.cell[k] = in[DLI_MAX_DIM + k]; m->grid.ic[k] = in[2 * DLI_MAX_DIM + k]; }
   return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// dli_mesh_replicate: NCCL broadcast of the whole mesh.  NCCL is resolved at run time -- the
+// process already holds the NCCL its communicator came from (the caller links it, or torch loaded its own copy), and
+// a second copy linked into this library could not use that communicator.
+// ---------------------------------------------------------------------------------------------
+#include <dlfcn.h>
+#include <nccl.h>   // types and enums only; no NCCL symbol is linked
+namespace {
+struct NcclApi {
+  ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*CommUserRank)(const ncclComm_t, int *) = nullptr;
+  ncclResult_t (*CommCuDevice)(const ncclComm_t, int *) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+  std::string why;
+};
+const NcclApi &nccl_api() {
+  static const NcclApi api = [] {
+    NcclApi a;
+    void *h = nullptr;
+    if (const char *e = getenv("DLI_NCCL_LIB")) h = dlopen(e, RTLD_NOW | RTLD_GLOBAL);
+    auto sym = [&](const char *name) -> void * {
+      void *p = h ? dlsym(h, name) : nullptr;
+      if (!p) p = dlsym(RTLD_DEFAULT, name);   // the NCCL the process already has in its global scope
+      return p;
+    };
+    if (!sym("ncclBroadcast")) {
+      h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);   // loaded privately by someone else (torch): reuse that copy
+      if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+      if (!h) h = dlopen("libnccl.so", RTLD_NOW);
+    }
+    a.Broadcast = reinterpret_cast<decltype(a.Broadcast)>(sym("ncclBroadcast"));
+    a.CommUserRank = reinterpret_cast<decltype(a.CommUserRank)>(sym("ncclCommUserRank"));
+    a.CommCuDevice = reinterpret_cast<decltype(a.CommCuDevice)>(sym("ncclCommCuDevice"));
+    a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
+    a.ok = a.Broadcast && a.CommUserRank && a.CommCuDevice;
+    if (!a.ok) a.why = "NCCL not found (looked in the process, then libnccl.so.2; set DLI_NCCL_LIB)";
+    return a;
+  }();
+  return api;
+}
+constexpr int kRepWords = DLI_MESH_HEADER_WORDS + 3 * DLI_MAX_DIM + 2;   // header, grid parameters (bit patterns), n_slow, ok flag
+}  // namespace
+
+extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
+  DLI_GUARD_BEGIN
+  if (!inout || !nccl_comm) return fail(DLI_ERR_ARG, "dli_mesh_replicate: NULL argument");
+  const NcclApi &N = nccl_api();
+  if (!N.ok) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_replicate: " + N.why);
+  ncclComm_t comm = static_cast<ncclComm_t>(nccl_comm);
+  auto nerr = [&](ncclResult_t r, const char *what) {
+    return fail(DLI_ERR_CUDA, std::string("dli_mesh_replicate: ") + what + ": " + (N.GetErrorString ? N.GetErrorString(r) : "NCCL error"));
+  };
+  int rank = -1, dev = -1;
+  ncclResult_t r = N.CommUserRank(comm, &rank);
+  if (r == ncclSuccess) r = N.CommCuDevice(comm, &dev);
+  if (r != ncclSuccess) return nerr(r, "communicator query");
+  const bool is_root = rank == root;
+  if (is_root && !*inout) return fail(DLI_ERR_ARG, "dli_mesh_replicate: the root rank must pass its mesh");
+  if (is_root && (*inout)->device != dev) return fail(DLI_ERR_ARG, "dli_mesh_replicate: the root's mesh is not on the communicator's device");
+  DeviceGuard guard(dev);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_replicate: cannot select the communicator's device");
+  cudaStream_t st = nullptr;
+  int64_t *d_hdr = nullptr;
+  CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  int rc = DLI_OK;
+  int64_t w[kRepWords];
+  memset(w, 0, sizeof w);
+  cudaError_t e = cudaMalloc(&d_hdr, sizeof w);
+  if (e == cudaSuccess && is_root) {
+    double gp[3 * DLI_MAX_DIM];
+    dli_mesh_header(*inout, w);
+    dli_mesh_get_grid_params(*inout, gp);
+    memcpy(w + DLI_MESH_HEADER_WORDS, gp, sizeof gp);
+    w[DLI_MESH_HEADER_WORDS + 3 * DLI_MAX_DIM] = (*inout)->n_slow_faces;
+    w[kRepWords - 1] = 1;
+    e = cudaMemcpyAsync(d_hdr, w, sizeof w, cudaMemcpyHostToDevice, st);
+  }
+  if (e == cudaSuccess) {
+    r = N.Broadcast(d_hdr, d_hdr, kRepWords, ncclInt64, root, comm, st);
+    if (r != ncclSuccess) rc = nerr(r, "header broadcast");
+  }
+  if (e == cudaSuccess && rc == DLI_OK) e = cudaMemcpyAsync(w, d_hdr, sizeof w, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess && rc == DLI_OK) e = cudaStreamSynchronize(st);
+  dli_mesh *m = is_root ? *inout : nullptr;
+  if (e == cudaSuccess && rc == DLI_OK && !is_root) {
+    if (w[kRepWords - 1] != 1) rc = fail(DLI_ERR_ARG, "dli_mesh_replicate: no header received from the root");
+    dli_options o;
+    dli_options_init(&o);
+    o.device = dev;
+    if (rc == DLI_OK) rc = dli_mesh_create_from_header(w, &o, &m);
+    if (rc == DLI_OK) {
+      double gp[3 * DLI_MAX_DIM];
+      memcpy(gp, w + DLI_MESH_HEADER_WORDS, sizeof gp);
+      dli_mesh_set_grid_params(m, gp);
+      m->n_slow_faces = w[DLI_MESH_HEADER_WORDS + 3 * DLI_MAX_DIM];
+    }
+  }
+  // every rank walks the same buffer list (the header fixes which optional buffers exist and how large they are).
+  // A rank that failed above still takes part, receiving into nothing is not possible -- so a failed rank leaves the
+  // collective sequence only after reporting; the caller must treat a non-zero return on any rank as fatal for the job
+  if (e == cudaSuccess && rc == DLI_OK) {
+    for (int i = 0; i < dli_mesh_num_buffers(m) && rc == DLI_OK; i++) {
+      void *p; int64_t b;
+      rc = dli_mesh_buffer(m, i, &p, &b);
+      if (rc != DLI_OK || b == 0) continue;
+      r = N.Broadcast(p, p, (size_t)b, ncclChar, root, comm, st);
+      if (r != ncclSuccess) rc = nerr(r, "buffer broadcast");
+    }
+    if (rc == DLI_OK) e = cudaStreamSynchronize(st);
+  }
+  cudaFree(d_hdr);
+  cudaStreamDestroy(st);
+  if (e != cudaSuccess && rc == DLI_OK) rc = fail(DLI_ERR_CUDA, std::string("dli_mesh_replicate: ") + cudaGetErrorString(e));
+  if (rc != DLI_OK) { if (!is_root && m) mesh_free(m); return rc; }
+  if (!is_root) {
+    if (*inout) mesh_free(*inout);   // a previous replica is replaced
+    *inout = m;
+  }
+  return DLI_OK;
+  DLI_GUARD_END("dli_mesh_replicate")
 }
 
 // ---------------------------------------------------------------------------------------------

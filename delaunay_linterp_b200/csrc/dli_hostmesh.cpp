@@ -18,6 +18,9 @@
 #include "../../include/dli_error_math.h"
 #include "../../include/dli_host.h"
 #include "dli_exact.cuh"
+#include "dli_host_small.h"
+#include "dli_refmath.h"
+#include <atomic>
 
 namespace {
 
@@ -185,8 +188,11 @@ struct HostMesh2 {
 
   // exact visibility walk from `last`; returns a finite face whose closed hull contains p, or the
   // infinite face p is strictly visible from
-  int locate(double px, double py) const {
-    int f = last, from = -1;
+  int locate(double px, double py, int start = -1) const {
+    int f = (start >= 0 && start < (int)fc.size() && alive[start]) ? start : last, from = -1;
+    if (is_inf(f))
+      for (int i = 0; i < 3; i++)
+        if (fc[f].v[i] == INF) { f = fc[f].n[i]; break; }
     for (;;) {
       const Face &t = fc[f];
       int moved = -1;
@@ -386,6 +392,7 @@ struct dli_di2 {
   int64_t nv_synced = 0;            // vertices the device mesh holds
   int64_t n_full = 0, n_incremental = 0;
   int64_t patched_since_full = 0, faces_at_full = 0;   // re-flatten once half the mesh has been patched (hint decay)
+  std::atomic<int> host_last{-1};   // face the last host-side query ended in (start of the next walk; a hint only)
 
   // flattened triangulation under the stable face ids (HostMesh2::fid); any pointer may be NULL
   void flatten(double *coords, int32_t *tri, int32_t *nbr, int32_t *handle) {
@@ -708,6 +715,108 @@ int dli_di2_set_options(dli_di2 *d, const dli_options *opt) {
   return DLI_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Host side of small batches (dli_host_small.h): interp_point of the reference (src/delaunay_2_interp.h:515-572) on
+// the host triangulation -- exact visibility walk over closed faces from the face the previous query ended in,
+// outside-hull projection with the rules of the device's exact pass (locate2_full in dli_device.cuh: canonical visible
+// hull edge = the strictly visible one whose line is farthest, ties to the smaller (face id, slot); CGAL-style Line_2
+// projection; <= 16 rounds), reference-order epilogue (dli_refmath.h).  Same code as the exact pass of the kernels, so
+// the values are those of the device in `reference` mode.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct HullEdge2 {
+  int inf_face, face, slot;   // the infinite face, the finite face behind it, the slot of the hull edge in that face
+  int P, Q;                   // edge end points, counter-clockwise in `face`
+};
+HullEdge2 hull_edge_of(const HostMesh2 &hm, int inf_face) {
+  HullEdge2 h;
+  h.inf_face = inf_face;
+  const Face &I = hm.fc[inf_face];
+  int i = I.v[0] == INF ? 0 : (I.v[1] == INF ? 1 : 2);
+  h.face = I.n[i];
+  const Face &F = hm.fc[h.face];
+  h.slot = F.n[0] == inf_face ? 0 : (F.n[1] == inf_face ? 1 : 2);
+  h.P = F.v[(h.slot + 1) % 3];
+  h.Q = F.v[(h.slot + 2) % 3];
+  return h;
+}
+// the infinite face sharing Q (dir 0: next) / P (dir 1: prev) with hull edge h
+int hull_step(const HostMesh2 &hm, const HullEdge2 &h, int dir) {
+  const Face &I = hm.fc[h.inf_face];
+  for (int k = 0; k < 3; k++)
+    if (I.v[k] == (dir ? h.Q : h.P)) return I.n[k];   // across the edge opposite the OTHER end point
+  return -1;
+}
+HullEdge2 canonical_visible_hull_edge(const HostMesh2 &hm, double px, double py, int inf0) {
+  HullEdge2 best = hull_edge_of(hm, inf0);
+  double best_score = dli::hull_edge_score(hm.X[best.P], hm.Y[best.P], hm.X[best.Q], hm.Y[best.Q], px, py);
+  const int64_t cap = (int64_t)hm.fc.size();
+  for (int dir = 0; dir < 2; dir++) {
+    HullEdge2 h = hull_edge_of(hm, inf0);
+    for (int64_t it = 0; it < cap; it++) {
+      const int nx = hull_step(hm, h, dir);
+      if (nx < 0 || nx == inf0) break;
+      h = hull_edge_of(hm, nx);
+      if (hm.o3(h.P, h.Q, px, py) >= 0) break;
+      const double sc = dli::hull_edge_score(hm.X[h.P], hm.Y[h.P], hm.X[h.Q], hm.Y[h.Q], px, py);
+      const bool lower = hm.fid[h.face] < hm.fid[best.face] || (hm.fid[h.face] == hm.fid[best.face] && h.slot < best.slot);
+      if (sc > best_score || (sc == best_score && lower)) { best = h; best_score = sc; }
+    }
+  }
+  return best;
+}
+constexpr int kMaxProjectionsHost = 16;   // = kMaxProjections of dli_device.cuh
+
+// one query; returns the status, the face in *face_out (-1: none), the value in *y
+uint8_t host_interp_point2(const HostMesh2 &hm, double px, double py, int start, int *face_out, double *y) {
+  *face_out = -1;
+  *y = std::nan("");
+  if (hm.dim < 2) return DLI_STATUS_NO_MESH;
+  if (!(std::isfinite(px) && std::isfinite(py))) return DLI_STATUS_STEP_LIMIT;
+  uint8_t status = DLI_STATUS_OK;
+  bool stuck = false;
+  int prev_face = -1, prev_slot = -1, f = start;
+  for (int proj = 0;; proj++) {
+    f = hm.locate(px, py, f);
+    if (!hm.is_inf(f)) break;
+    status = DLI_STATUS_OUTSIDE_PROJECTED;
+    if (proj >= kMaxProjectionsHost || stuck) { f = hull_edge_of(hm, f).face; break; }   // accept the hull face
+    const HullEdge2 h = canonical_visible_hull_edge(hm, px, py, f);
+    const double opx = px, opy = py;
+    dli::project_on_line(hm.X[h.P], hm.Y[h.P], hm.X[h.Q], hm.Y[h.Q], px, py);
+    stuck = (h.face == prev_face && h.slot == prev_slot && px == opx && py == opy);
+    prev_face = h.face; prev_slot = h.slot;
+    f = h.face;
+  }
+  const Face &t = hm.fc[f];
+  *y = dli::epilogue2_ref_xy(px, py, hm.X[t.v[0]], hm.Y[t.v[0]], hm.F[t.v[0]], hm.X[t.v[1]], hm.Y[t.v[1]], hm.F[t.v[1]],
+                             hm.X[t.v[2]], hm.Y[t.v[2]], hm.F[t.v[2]]);
+  *face_out = f;
+  return status;
+}
+}  // namespace
+
+static void di2_host_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto) {
+  HostMesh2 &hm = d->hm;
+  if (so && !hm.fid_compact) { hm.renumber(); d->need_full = true; d->dirty = true; }
+  int start = d->host_last.load(std::memory_order_relaxed);
+  for (int64_t i = 0; i < n; i++) {
+    int face;
+    double y;
+    const uint8_t st = host_interp_point2(hm, xs[2 * i], xs[2 * i + 1], start, &face, &y);
+    ys[i] = y;
+    if (so) so[i] = face >= 0 ? hm.fid[face] : -1;
+    if (sto) sto[i] = st;
+    if (face >= 0) start = face;
+  }
+  d->host_last.store(start, std::memory_order_relaxed);
+}
+static bool di2_take_host(const dli_di2 *d, int64_t n, const double *xs, const double *ys, const int32_t *so, const uint8_t *sto) {
+  return n > 0 && xs && ys && dli::host_batch_is_small(n, d->hm.dim == 2 ? d->hm.n_finite : 0, 2) &&
+         dli::is_plain_host_pointer(xs) && dli::is_plain_host_pointer(ys) && dli::is_plain_host_pointer(so) &&
+         dli::is_plain_host_pointer(sto);
+}
+
 // incremental path: hand the dirty star(s) to dli_mesh_update; DLI_ERR_UNSUPPORTED = the mesh cannot be patched
 static int di2_patch(dli_di2 *d) {
   HostMesh2 &hm = d->hm;
@@ -764,6 +873,7 @@ int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t 
                    void *stream) {
   DLI_GUARD_BEGIN
   if (!d) return DLI_ERR_ARG;
+  if (di2_take_host(d, n, xs, ys, simplex_out, status_out)) { di2_host_interp(d, n, xs, ys, simplex_out, status_out); return DLI_OK; }
   int rc = di2_refresh(d);
   if (rc != DLI_OK) return rc;
   return dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);

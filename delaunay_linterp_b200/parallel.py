@@ -5,6 +5,9 @@ flattened mesh buffers (NCCL over NVLink through torch.distributed) and the max-
 of the timing.  The pure host logic here (sharding, header broadcast, timing reduction) also runs on
 the gloo backend and is covered by world_size-2 CPU tests.
 """
+import ctypes as C
+import os
+
 import numpy as np
 
 
@@ -16,7 +19,7 @@ def shard_bounds(n, world_size, rank):
 
 
 def broadcast_header(header, grid_params, src=0):
-    """broadcast the mesh header (int64[16]) and grid parameters (float64[18]) from `src`."""
+    """broadcast the mesh header (int64[16]) and grid parameters (float64[3 * DLI_MAX_DIM]) from `src`."""
     import torch.distributed as dist
     obj = [None]
     if dist.get_rank() == src:
@@ -47,12 +50,93 @@ def sum_over_ranks(value, device=None):
     return float(t.item())
 
 
-def replicate_mesh(mesh, src=0, device=None, **options):
+_NCCL = None
+
+
+class _NcclUniqueId(C.Structure):
+    _fields_ = [("internal", C.c_char * 128)]
+
+
+def _nccl_lib():
+    """the NCCL this process uses (torch's bundled copy first), loaded into the global symbol scope so that libdli.so's
+    dli_mesh_replicate resolves the same library (it looks NCCL up at run time)."""
+    global _NCCL
+    if _NCCL is not None:
+        return _NCCL
+    cands = []
+    try:
+        import nvidia.nccl
+        cands.append(os.path.join(list(nvidia.nccl.__path__)[0], "lib", "libnccl.so.2"))
+    except Exception:
+        pass
+    cands += ["libnccl.so.2", "libnccl.so"]
+    for c in cands:
+        try:
+            L = C.CDLL(c, mode=C.RTLD_GLOBAL)
+        except OSError:
+            continue
+        L.ncclGetUniqueId.argtypes = [C.POINTER(_NcclUniqueId)]
+        L.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, _NcclUniqueId, C.c_int]
+        L.ncclCommDestroy.argtypes = [C.c_void_p]
+        _NCCL = L
+        return L
+    raise OSError("libnccl.so.2 not found")
+
+
+def nccl_communicator(src=0):
+    """a raw ncclComm_t over all ranks of the torch.distributed job (the unique id travels through torch.distributed).
+    The current CUDA device must be this rank's device.  Returns (comm, destroy)."""
+    import torch.distributed as dist
+    L = _nccl_lib()
+    uid = _NcclUniqueId()
+    obj = [None]
+    if dist.get_rank() == src:
+        rc = L.ncclGetUniqueId(C.byref(uid))
+        if rc != 0:
+            raise RuntimeError("ncclGetUniqueId failed: %d" % rc)
+        obj = [C.string_at(C.byref(uid), 128)]
+    dist.broadcast_object_list(obj, src=src)
+    C.memmove(C.byref(uid), obj[0], 128)
+    comm = C.c_void_p()
+    rc = L.ncclCommInitRank(C.byref(comm), dist.get_world_size(), uid, dist.get_rank())
+    if rc != 0:
+        raise RuntimeError("ncclCommInitRank failed: %d" % rc)
+    return comm, (lambda: L.ncclCommDestroy(comm))
+
+
+def replicate_mesh_nccl(mesh, src=0):
+    """dli_mesh_replicate (include/dli.h) with a raw NCCL communicator: what a C / C++ caller does.  Rank `src` passes
+    its Mesh, the others None; returns the local Mesh."""
+    import torch.distributed as dist
+    from ._capi import check, lib
+    from .mesh import Mesh
+    comm, destroy = nccl_communicator(src=src)
+    try:
+        h = C.c_void_p(mesh._h.value if (mesh is not None and dist.get_rank() == src) else None)
+        check(lib().dli_mesh_replicate(C.byref(h), comm, int(src)))
+    finally:
+        destroy()
+    if dist.get_rank() == src:
+        return mesh
+    return Mesh._from_handle(h, lib().dli_mesh_dim(h))
+
+
+def replicate_mesh(mesh, src=0, device=None, use_c_abi=True, **options):
     """Rank `src` passes its Mesh; every other rank passes None and receives a replica whose device buffers
-    are filled by an NCCL broadcast.  Returns the local Mesh."""
+    are filled by an NCCL broadcast.  Returns the local Mesh.  On the NCCL backend the work is done by
+    dli_mesh_replicate (one ncclBroadcast per buffer, straight from / into the mesh buffers); otherwise (gloo, or no
+    NCCL library) by torch.distributed broadcasts of the raw buffers."""
     import torch
     import torch.distributed as dist
     from .mesh import Mesh
+    if use_c_abi and dist.get_backend() == "nccl":
+        try:
+            _nccl_lib()
+            have = True
+        except OSError:
+            have = False
+        if have:
+            return replicate_mesh_nccl(mesh, src=src)
     rank = dist.get_rank()
     if rank == src:
         header, gp = mesh.header()

@@ -231,6 +231,17 @@ int dli_mesh_get_grid_params(const dli_mesh *mesh, double *out /* [3 * DLI_MAX_D
 int dli_mesh_set_grid_params(dli_mesh *mesh, const double *in /* [3 * DLI_MAX_DIM] */);
 
 /*
+ * The same in one call for C / C++ callers that hold an NCCL communicator: the root rank passes its
+ * mesh in *inout; every other rank passes *inout == NULL (or a replica to be replaced) and receives a replica on the
+ * communicator's device -- one ncclBroadcast of the header block, then one per buffer, over NVLink / NVSwitch.  Collective:
+ * every rank of the communicator must call it.  nccl_comm is an ncclComm_t.  NCCL itself is resolved at run time from
+ * the calling process (link your program against NCCL as usual, or set DLI_NCCL_LIB to the library's path); the call
+ * returns DLI_ERR_UNSUPPORTED when no NCCL can be found.  A replica answers interp / locate / gradient; it has no host
+ * connectivity (dli_mesh_get_simplices, dli_mesh_update and the error evaluator need the creating rank).
+ */
+int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root);
+
+/*
  * Mesh snapshot (no counterpart in the reference, which has no serialisation): the flattened device mesh as one
  * flat file -- magic "DLIMESH1", the 16 header words, the grid parameters, then every device buffer
  * length-prefixed -- so that a large triangulation is built and flattened once.  A loaded mesh is a replica:

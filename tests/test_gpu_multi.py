@@ -21,7 +21,7 @@ mesh = None
 if rank == 0:
     pts, f, sv, sn = helpers.random_mesh(2, 50000, 5)
     mesh = dl.Mesh(pts, f, sv, sn, device=lr, **%(opts)r)
-mesh = parallel.replicate_mesh(mesh, src=0, device=dev, **%(opts)r)
+mesh = parallel.replicate_mesh(mesh, src=0, device=dev, use_c_abi=%(c_abi)r, **%(opts)r)
 q = np.random.default_rng(6).random((400000, 2)) * 1.04 - 0.02
 lo, hi = parallel.shard_bounds(len(q), world, rank)
 ys = mesh.interp(torch.from_numpy(q[lo:hi]).to(dev))
@@ -36,13 +36,32 @@ dist.barrier(); dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("opts", [{}, {"packed_faces": 3}])
-def test_sharded_equals_single(gpu, tmp_path, opts):
+@pytest.mark.parametrize("c_abi", [True, False])   # dli_mesh_replicate (raw NCCL communicator) / torch.distributed broadcasts
+@pytest.mark.parametrize("opts", [{}, {"packed_faces": 3}, {"packed_faces": 2}])
+def test_sharded_equals_single(gpu, tmp_path, opts, c_abi):
     if gpu < 2:
         pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
     script = tmp_path / "multi.py"
-    script.write_text(SCRIPT % {"root": ROOT, "opts": opts})
+    script.write_text(SCRIPT % {"root": ROOT, "opts": opts, "c_abi": c_abi})
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                         "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MULTI_OK 2" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_replicate_from_cpp_with_nccl(gpu, tmp_path):
+    """tests/cpp/test_replicate.cpp: dli_mesh_replicate called from C++ with ncclCommInitAll communicators, one thread
+    per GPU; replicas (2D and 3D) answer bit-identically."""
+    if gpu < 2:
+        pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
+    import delaunay_linterp_b200 as dl
+    libdir = os.path.dirname(dl.LIB_PATH)
+    exe = str(tmp_path / "test_replicate")
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    subprocess.check_call(["g++", "-std=c++11", "-O1", os.path.join(ROOT, "tests", "cpp", "test_replicate.cpp"),
+                           "-I", os.path.join(ROOT, "include"), "-I", "/usr/local/cuda/include", "-L", libdir,
+                           "-L", "/usr/local/cuda/lib64", "-ldli", "-lnccl", "-lcudart", "-lpthread",
+                           "-Wl,-rpath," + libdir, "-o", exe], env=env)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ok:" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -24,9 +24,9 @@ def _worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         header = np.arange(16, dtype=np.int64) * 3 + 1 if rank == 0 else None
-        gp = np.linspace(0.0, 1.7, 18) if rank == 0 else None
+        gp = np.linspace(0.0, 1.7, 12) if rank == 0 else None
         h, g = parallel.broadcast_header(header, gp, src=0)
-        ok = np.array_equal(h, np.arange(16, dtype=np.int64) * 3 + 1) and np.array_equal(g, np.linspace(0.0, 1.7, 18))
+        ok = np.array_equal(h, np.arange(16, dtype=np.int64) * 3 + 1) and np.array_equal(g, np.linspace(0.0, 1.7, 12))
         mx = parallel.max_over_ranks(10.0 + rank)
         sm = parallel.sum_over_ranks(1.0 + rank)
         # every rank evaluates its shard; gathering the shards reproduces the full batch order
