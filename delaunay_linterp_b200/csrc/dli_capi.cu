@@ -1750,7 +1750,7 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
 // (length-prefixed).  The same bytes the replication path broadcasts; a loaded mesh is a replica
 // (no host copy of the connectivity: dli_mesh_get_simplices / the error evaluator are unavailable).
 // ---------------------------------------------------------------------------------------------
-static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '1'};
+static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '2'};
 
 extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
   DLI_GUARD_BEGIN

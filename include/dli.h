@@ -243,7 +243,7 @@ int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root);
 
 /*
  * Mesh snapshot (no counterpart in the reference, which has no serialisation): the flattened device mesh as one
- * flat file -- magic "DLIMESH1", the 16 header words, the grid parameters, then every device buffer
+ * flat file -- magic "DLIMESH2", the 16 header words, the grid parameters, then every device buffer
  * length-prefixed -- so that a large triangulation is built and flattened once.  A loaded mesh is a replica:
  * interp / locate / gradient work, dli_mesh_get_simplices and the error evaluator need the creating process.
  */

@@ -114,3 +114,29 @@ def test_interp2_class_gradient_on_gpu(gpu):
     gq, sq = a.gradient(q, return_status=True)
     go, _, so = OracleMesh(c, f, t, nb).gradient(q)
     assert np.array_equal(sq, so) and np.array_equal(gq[so != 2], go[so != 2])
+
+
+def test_reference_module_names_resolve():
+    """`import _delaunay_2_python` / `import _delaunay_d_python` (delaunay_2.py:22, delaunay_d_test.py:4) and the
+    reference's own test1() body (delaunay_d_test.py:34-44) without the plotting"""
+    import _delaunay_2_python as _delaunay2
+    import _delaunay_d_python as _delaunayd
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
+    triang = _delaunayd.Delaunay_incremental_interp_d(2, fn)
+    for x in [[0.01, 0.01], [0.01, 3.0], [3.0, 0.01], [3.0, 3.0]]:
+        triang.insert(x, fn(x))
+    for _ in range(50):
+        triang.insert_largest_error_point()
+    segs, lo, hi = triang.get_line_segments()
+    assert len(triang.get_all_vertices()) == 54 and len(segs) > 54 and lo[0] == 0.01 and hi[1] == 3.0
+    assert triang.fn is fn and triang.triang.dimension() == 2
+    assert abs(triang.interp([1.0, 2.0]) - fn([1.0, 2.0])) < 0.05
+    assert math.isnan(triang.interp([5.0, 5.0]))
+    t2 = _delaunay2.DelaunayInterp2(fn)
+    for x in [[0.01, 0.01], [0.01, 3.0], [3.0, 0.01], [3.0, 3.0]]:
+        t2.insert(x, fn(x))
+    for _ in range(50):
+        t2.insert_largest_error_point()
+    # one point at a time is answered on the host: no GPU needed; outside the hull is projected (2D class)
+    assert abs(t2.interp([1.0, 2.0]) - fn([1.0, 2.0])) < 0.05
+    assert t2.interp([5.0, 2.0]) == t2.interp([3.0, 2.0])
