@@ -215,6 +215,233 @@ def run_reference(args, rank, world):
     return 0
 
 
+# ---------------------------------------------------------------------------------------------
+# The other BASELINE configs: bounded legs after the cfg2 headline, reported under "extras"
+# ---------------------------------------------------------------------------------------------
+B_ALG_DIM = {2: 108, 3: 176, 4: 260}
+ALPHA = np.array([0.3, 0.6, 0.2, 0.1])  # f(x) = prod x_i^alpha_i (src/delaunay_2_test.cpp:32-50)
+CFG5_CHUNK = 1_000_000                  # cfg5 queries are generated in chunks keyed by their global index: the stream is
+                                        # the same whatever the number of GPUs
+
+
+def f_prod(x):
+    return np.prod(np.power(x, ALPHA[: x.shape[1]]), axis=1)
+
+
+def morton_sort_rows(q, bits=10):
+    """rows of q ordered along a Z-curve (so that the oracle's walk-from-previous-result mode is fast)"""
+    lo, hi = q.min(0), q.max(0)
+    g = np.minimum(((q - lo) / np.maximum(hi - lo, 1e-300) * (1 << bits)).astype(np.int64), (1 << bits) - 1)
+    key = np.zeros(len(q), np.int64)
+    for b in range(bits):
+        for c in range(q.shape[1]):
+            key |= ((g[:, c] >> b) & 1) << (b * q.shape[1] + c)
+    return q[np.argsort(key, kind="stable")]
+
+
+def timed_leg(mesh, xq, ys, steps, warmup, dev, dist, world, total_queries_per_step, dim, peak):
+    """device-resident timing of one config: CUDA events around `steps` calls (max over ranks), per-launch kernel times
+    from the library, roofline of the fast-pass kernel"""
+    import torch
+    from delaunay_linterp_b200 import parallel
+    for _ in range(max(warmup, 3)):
+        mesh.interp(xq, out=ys)
+    mesh.collect_stats(False, timing=True)
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        mesh.interp(xq, out=ys)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    ms = parallel.max_over_ranks(e0.elapsed_time(e1), device=dev) / steps
+    st = mesh.stats()
+    mesh.collect_stats(False, timing=False)
+    nl = max(1, st["fast_kernel_launches"])
+    fast_ms = st["fast_kernel_ms"] / nl
+    q_per_launch = xq.shape[0] * steps / nl
+    b_alg = B_ALG_DIM[dim]
+    achieved = b_alg * q_per_launch / (fast_ms * 1e-3) / 1e9 if fast_ms > 0 else 0.0
+    out = {
+        "value": total_queries_per_step / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps,
+        "queries_per_step": int(total_queries_per_step), "queries_per_gpu": int(xq.shape[0]),
+        "mesh_simplices": int(mesh.n_simplices), "mesh_device_MB": mesh.device_bytes / 1e6,
+        "gpu_launches": int(st["kernel_launches"] * steps),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "algorithmic_bytes_per_query": b_alg, "avg_launch_ms": fast_ms, "queries_per_launch": q_per_launch,
+                     "straggler_pass_ms_per_step": st["full_kernel_ms"] / steps, "traffic": None},
+    }
+    return out
+
+
+def walk_stats(mesh, xq):
+    import torch
+    n1 = min(xq.shape[0], 4_000_000)
+    mesh.collect_stats(True)
+    mesh.interp(xq[:n1])
+    torch.cuda.synchronize()
+    st = mesh.stats()
+    mesh.collect_stats(False)
+    return {"walk_steps_per_query": st["walk_steps"] / max(1, st["queries"]), "max_walk_steps": st["max_walk_steps"],
+            "straggler_fraction": st["straggler_queries"] / max(1, st["queries"]), "slow_simplices": st["slow_simplices"]}
+
+
+def oracle_check(mesh, host_mesh, q):
+    """GPU vs the CPU oracle on a sample (sorted along a Z-curve: the oracle then walks from its previous result)"""
+    from oracle.oracle import OracleMesh
+    q = morton_sort_rows(q)
+    yo, so, sto = OracleMesh(*host_mesh).interp(q, mode=1, nthreads=min(8, os.cpu_count() or 1))
+    yg, stg = mesh.interp(q, return_status=True)
+    ok = sto == 0
+    rel = float(np.max(np.abs(yg[ok] - yo[ok]) / np.maximum(np.abs(yo[ok]), 1e-300))) if ok.any() else 0.0
+    return {"max_rel_diff_gpu_vs_oracle_on_sample": rel, "sample": int(len(q)), "status_equal": bool(np.array_equal(stg, sto)),
+            "nan_equal": bool(np.array_equal(np.isnan(yg), np.isnan(yo)))}
+
+
+def extras_single_gpu(args, dev, peak):
+    """cfg3, cfg4-3D, cfg4-4D on one GPU (N = 1 only)"""
+    import torch
+    import delaunay_linterp_b200 as dl
+    out = {}
+    steps = max(3, min(args.steps, 10))
+
+    def queries(n, dim, lo, hi, seed):
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed)
+        return torch.rand(n, dim, dtype=torch.float64, device=dev, generator=g) * (hi - lo) + lo
+
+    # ---- cfg3: 2D adaptive, 100k points placed by insert_largest_error_point; 50M queries + one full error evaluation
+    try:
+        fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6   # noqa: E731
+        t0 = time.perf_counter()
+        t = dl.DelaunayInterp2(fn)
+        for p in ([0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]):
+            t.insert(p, fn(p))
+        n_adapt = args.cfg3_vertices - 4
+        for _ in range(n_adapt):
+            t.insert_largest_error_point()
+        t_build = time.perf_counter() - t0
+        hm = t.export()
+        mesh = dl.Mesh(*hm, device=dev.index)
+        nq = args.cfg3_queries
+        xq, ys = queries(nq, 2, 0.01, 5.0, 2003), torch.empty(nq, dtype=torch.float64, device=dev)
+        leg = timed_leg(mesh, xq, ys, steps, args.warmup, dev, None, 1, nq, 2, peak)
+        leg.update(walk_stats(mesh, xq))
+        # batched per-simplex error evaluation over every face + hull edge (k_error_prepare / k_error_finish)
+        t0 = time.perf_counter()
+        cent, isx, iv = mesh.simplex_error_items()
+        t_prep = time.perf_counter() - t0
+        phi = f_cobb_douglas(cent)
+        t0 = time.perf_counter()
+        err = mesh.simplex_error(phi)
+        t_fin = time.perf_counter() - t0
+        leg["error_eval"] = {"items": int(len(err)), "prepare_ms": t_prep * 1e3, "finish_ms": t_fin * 1e3,
+                             "algorithmic_bytes_per_item": 116, "max_err": float(err.max()),
+                             "note": "host wall time of the two C-ABI calls incl. item table build and copies"}
+        leg["workload"] = ("cfg3: 2D adaptive, %d points placed by insert_largest_error_point on [0.01,5]^2, %dM unsorted "
+                           "queries (seed 2003) + one batched error evaluation" % (args.cfg3_vertices, nq // 1_000_000))
+        leg["mesh_build_s"] = t_build
+        leg.update(oracle_check(mesh, hm, np.random.default_rng(2003).random((200_000, 2)) * 4.99 + 0.01))
+        out["cfg3"] = leg
+        del mesh, xq, ys, t
+    except Exception as e:  # noqa: BLE001
+        out["cfg3"] = {"error": "%s: %s" % (type(e).__name__, e)}
+    torch.cuda.empty_cache()
+
+    # ---- cfg4: dD via delaunay_d_interp, 200k random vertices, 20M queries inside the hull
+    for dim, seed_m, seed_q, key in ((3, 1003, 2004, "cfg4_3d"), (4, 1004, 2005, "cfg4_4d")):
+        try:
+            t0 = time.perf_counter()
+            pts = np.random.default_rng(seed_m).random((args.cfg4_vertices, dim))
+            t = dl.Delaunay_incremental_interp_d(dim)
+            t.insert_many(pts, f_prod(pts), spatial_sort=True, use_gpu=False)   # native dD triangulation (host)
+            t_build = time.perf_counter() - t0
+            hm = t.export()
+            mesh = dl.Mesh(*hm, device=dev.index)
+            nq = args.cfg4_queries
+            xq, ys = queries(nq, dim, 0.1, 0.9, seed_q), torch.empty(nq, dtype=torch.float64, device=dev)
+            leg = timed_leg(mesh, xq, ys, steps, args.warmup, dev, None, 1, nq, dim, peak)
+            leg.update(walk_stats(mesh, xq))
+            leg["workload"] = ("cfg4: %dD, %d uniform-random vertices (seed %d) through the native dD triangulation, %dM queries "
+                               "in U[0.1,0.9)^%d (seed %d)" % (dim, args.cfg4_vertices, seed_m, nq // 1_000_000, dim, seed_q))
+            leg["mesh_build_s"] = t_build
+            leg["nan_fraction"] = float(torch.isnan(ys).double().mean().item())
+            leg.update(oracle_check(mesh, hm, np.random.default_rng(seed_q).random((100_000, dim)) * 0.8 + 0.1))
+            out[key] = leg
+            del mesh, xq, ys, t
+        except Exception as e:  # noqa: BLE001
+            out[key] = {"error": "%s: %s" % (type(e).__name__, e)}
+        torch.cuda.empty_cache()
+    return out
+
+
+def cfg5_queries(lo_chunk, hi_chunk, dev):
+    """queries [lo_chunk * CFG5_CHUNK, hi_chunk * CFG5_CHUNK) of the cfg5 stream: chunk c is Philox(seed 2006 + c)"""
+    import torch
+    xq = torch.empty(((hi_chunk - lo_chunk) * CFG5_CHUNK, 2), dtype=torch.float64, device=dev)
+    g = torch.Generator(device=dev)
+    for c in range(lo_chunk, hi_chunk):
+        g.manual_seed(2006 + c)
+        v = xq[(c - lo_chunk) * CFG5_CHUNK:(c - lo_chunk + 1) * CFG5_CHUNK]
+        v.uniform_(0.0, 1.0, generator=g)
+    xq.mul_(0.96).add_(0.02)
+    return xq
+
+
+def extras_cfg5(args, rank, world, local_rank, dev, dist, peak):
+    """cfg5 as BASELINE states it: 16M-vertex 2D mesh replicated per GPU, the SAME 1B queries split across the ranks
+    (strong scaling); checksum = wrap-around int64 sum of the result bit patterns (order-independent, so equal across N
+    iff every result is bit-identical)"""
+    import torch
+    import delaunay_linterp_b200 as dl
+    from delaunay_linterp_b200 import parallel
+    t0 = time.perf_counter()
+    mesh, hm = None, None
+    t_tri = 0.0
+    if rank == 0:
+        pts = np.random.default_rng(1005).random((args.cfg5_vertices, 2))
+        t = dl.DelaunayInterp2()
+        t.insert_many(pts, f_cobb_douglas(pts), spatial_sort=True, use_gpu=False)
+        hm = t.export()
+        del t, pts
+        t_tri = time.perf_counter() - t0
+        mesh = dl.Mesh(*hm, device=local_rank)
+    t_build = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    if world > 1:
+        mesh = parallel.replicate_mesh(mesh, src=0, device=dev)
+    t_repl = time.perf_counter() - t0
+    n_chunks = args.cfg5_queries // CFG5_CHUNK
+    lo, hi = parallel.shard_bounds(n_chunks, world, rank)
+    xq = cfg5_queries(lo, hi, dev)
+    ys = torch.empty(xq.shape[0], dtype=torch.float64, device=dev)
+    steps = max(3, min(args.steps, 5))
+    leg = timed_leg(mesh, xq, ys, steps, args.warmup, dev, dist, world, n_chunks * CFG5_CHUNK, 2, peak)
+    chk = ys.view(torch.int64).sum()      # int64 wrap-around sum
+    nan = torch.isnan(ys).sum()
+    if dist is not None:
+        dist.all_reduce(chk)
+        dist.all_reduce(nan)
+    leg.update(walk_stats(mesh, xq))
+    leg["value_per_gpu"] = leg["value"] / world
+    leg["scaling"] = "strong"
+    leg["checksum_int64_bits"] = int(chk.item())
+    leg["nan"] = int(nan.item())
+    leg["workload"] = ("cfg5: 16M-vertex 2D mesh (seed 1005) replicated per GPU, the same %dM queries in U[0.02,0.98)^2 (chunk c = "
+                       "Philox seed 2006+c, %d queries per chunk) split across %d GPU(s)" % (n_chunks * CFG5_CHUNK // 1_000_000, CFG5_CHUNK, world))
+    leg["triangulate_s"], leg["flatten_s"], leg["replicate_s"] = t_tri, t_build - t_tri, t_repl
+    if rank == 0 and hm is not None:
+        leg.update(oracle_check(mesh, hm, np.random.default_rng(2006).random((200_000, 2)) * 0.96 + 0.02))
+    del xq, ys, mesh
+    torch.cuda.empty_cache()
+    return leg
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import delaunay_linterp_b200 as dl
@@ -325,13 +552,31 @@ def run_ours(args, rank, world, local_rank):
                          "hull-adjacent face, one query per call, 1 thread); host has %d cores" % (len(q), os.cpu_count() or 1),
                "max_rel_diff_gpu_vs_oracle_on_sample": rel}
 
+    # ---- the other BASELINE configs (bounded legs; cfg3 / cfg4 at N = 1 only, cfg5 strong-scaled at every N)
+    extras = {}
+    if not args.no_extras:
+        del xq, ys, hx, hy, hx_np, hy_np
+        mesh_n_simplices, mesh_device_bytes = int(mesh.n_simplices), mesh.device_bytes
+        del mesh
+        torch.cuda.empty_cache()
+        t0 = time.perf_counter()
+        if world == 1:
+            extras.update(extras_single_gpu(args, dev, peak))
+        try:
+            extras["cfg5"] = extras_cfg5(args, rank, world, local_rank, dev, dist, peak)
+        except Exception as e:  # noqa: BLE001
+            extras["cfg5"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        extras["wall_s"] = time.perf_counter() - t0
+    else:
+        mesh_n_simplices, mesh_device_bytes = int(mesh.n_simplices), mesh.device_bytes
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(nq), "queries_per_gpu": nq, "mesh_vertices": NV,
-                       "mesh_simplices": int(mesh.n_simplices), "mesh_device_MB": mesh.device_bytes / 1e6,
+                       "mesh_simplices": mesh_n_simplices, "mesh_device_MB": mesh_device_bytes / 1e6,
                        "l2_policy": "inputs larger than L2 (1.6 GB of queries + 0.8 GB of results streamed per step)",
                        "epilogue": "auto: affine form f0 + g.(p - p0) on 64-byte walk records where its a-priori error bound is <= 1e-13 relative, reference operation order on the other faces and in the exact pass", "parallelism": "replicated mesh, query shards, no collective",
                        "mesh_build_s": t_build, "mesh_replicate_s": t_repl, "checksum": checksum,
@@ -342,6 +587,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": roofline,
             "cpu_baseline": cpu,
+            "extras": extras,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -358,6 +604,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--queries", type=int, default=NQ, help="queries per GPU per step (default: the cfg2 100M)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg3 / cfg4 / cfg5 legs (extras)")
+    ap.add_argument("--cfg3-vertices", type=int, default=100_000)
+    ap.add_argument("--cfg3-queries", type=int, default=50_000_000)
+    ap.add_argument("--cfg4-vertices", type=int, default=200_000)
+    ap.add_argument("--cfg4-queries", type=int, default=20_000_000)
+    ap.add_argument("--cfg5-vertices", type=int, default=16_000_000)
+    ap.add_argument("--cfg5-queries", type=int, default=1_000_000_000, help="total over all GPUs (multiple of 8M)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -925,13 +925,11 @@ MeshDView viewD(const dli_mesh *m) {
 }
 
 constexpr int64_t kChunk = 1ll << 28;      // queries per launch pair (int32 indices in the straggler queue)
-// Straggler queue entries per launch pair: one per query of the chunk (4 B each, from the stream-ordered pool), so the
-// queue cannot overflow.  It used to hold 4M entries with "overflow = the exact pass re-runs the whole chunk": a 50M-query
-// batch with 17 % of its queries outside the hull fell off that cliff (26 ms instead of 7).
-#ifndef DLI_X_QCAP
-#define DLI_X_QCAP kChunk
-#endif
-constexpr int64_t kQueueCap = DLI_X_QCAP;
+// Straggler queue entries per launch pair: 1/16 of the launch (at least 2^16), 8 B each from the stream-ordered pool --
+// 50 MB for a 100M-query launch (it used to be one entry per query: 0.8 GB).  Queries that do not fit are marked in
+// their result slot and found again by the exact pass (enqueue_straggler in dli_kernels.cuh): an overflow costs one
+// scan of the results, not a re-run of the batch.
+static int64_t queue_capacity(int64_t n) { return std::min<int64_t>(n, std::max<int64_t>(1 << 16, n / 16)); }
 
 struct Launch {
   const dli_mesh *m;
@@ -1032,7 +1030,7 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     if (launches) *launches += 1;
     return DLI_OK;
   }
-  int64_t cap = std::min(n, kQueueCap);
+  const int64_t cap = queue_capacity(std::min(n, kChunk));
   int32_t *queue = nullptr;
   // [cap] query indices, [cap] faces the fast pass stopped in, then the counter
   CU(cudaMallocAsync(&queue, sizeof(int32_t) * 2 * (size_t)cap + 16, st));

@@ -38,6 +38,29 @@ __device__ __forceinline__ void flush_stats(unsigned long long *g, const StatsAc
   }
 }
 
+// Straggler queue of the fast passes.  The queue holds a fraction of the launch (run_device); a query that does not
+// fit is marked instead -- a reserved NaN bit pattern in its result slot (the simplex slot for dli_locate) -- and the
+// exact pass, when the counter shows an overflow, also scans the results for marks and serves those queries from their
+// start hint.  Every query is written by the fast pass (value, queue slot or mark) before the exact pass starts, and a
+// stale slot that happens to hold the mark is merely answered twice, so this is exact; the scan (8 B per query) only
+// runs on batches where more than 1/16 of the queries need the exact pass.
+constexpr long long kOverflowBits = 0x7ff8d11d11d11d11LL;
+constexpr int kOverflowSimplex = (int)0x80000001;
+template <int OUT>
+__device__ __forceinline__ void enqueue_straggler(int32_t *__restrict__ queue, unsigned int *__restrict__ queue_count,
+                                                  unsigned int queue_cap, int64_t qi, int where, double *__restrict__ ys,
+                                                  int32_t *__restrict__ simplex_out) {
+  const unsigned int slot = atomicAdd(queue_count, 1u);
+  if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = where; }   // exact pass resumes there
+  else if (ys) ys[OUT == 1 ? 2 * qi : qi] = __longlong_as_double(kOverflowBits);
+  else if (simplex_out) simplex_out[qi] = kOverflowSimplex;
+}
+template <int OUT>
+__device__ __forceinline__ bool is_overflow_mark(const double *__restrict__ ys, const int32_t *__restrict__ simplex_out, int64_t i) {
+  if (ys) return __double_as_longlong(ys[OUT == 1 ? 2 * i : i]) == kOverflowBits;
+  return simplex_out && simplex_out[i] == kOverflowSimplex;
+}
+
 // ---------------------------------------------------------------------------------------------
 // 2D interp
 // ---------------------------------------------------------------------------------------------
@@ -123,8 +146,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
         }
       }
       if (give_up) {
-        unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = f; }   // exact pass resumes here
+        enqueue_straggler<OUT>(queue, queue_count, queue_cap, qi, f, ys, simplex_out);
         active = false;
       }
     }
@@ -474,8 +496,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
         }
       }
       if (give_up) {
-        unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = CELL ? __ldg(m.slot_face + f) : f; }
+        enqueue_straggler<OUT>(queue, queue_count, queue_cap, qi, CELL ? __ldg(m.slot_face + f) : f, ys, simplex_out);
         active = false;
       }
     }
@@ -493,12 +514,16 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
                unsigned int queue_cap, int64_t n /* batch size: processed directly if the queue overflowed */,
                unsigned long long *__restrict__ stats) {
-  int64_t cnt = (int64_t)*queue_count;
-  const bool direct = cnt > (int64_t)queue_cap;
-  if (direct) cnt = n;
+  const int64_t total = (int64_t)*queue_count;
+  const bool overflow = total > (int64_t)queue_cap;
+  const int64_t cnt = overflow ? (int64_t)queue_cap : total;
   StatsAcc st;
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
-    int64_t i = direct ? k : (int64_t)queue[k];
+  // k < cnt: queue entries; k >= cnt (overflow only): scan of the batch for marked queries
+  const int64_t span = overflow ? cnt + n : cnt;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < span; k += (int64_t)gridDim.x * blockDim.x) {
+    const bool queued = k < cnt;
+    const int64_t i = queued ? (int64_t)queue[k] : k - cnt;
+    if (!queued && !is_overflow_mark<OUT>(ys, simplex_out, i)) continue;
     double2 q = xs[i];
     double px = q.x, py = q.y;
     if (!(isfinite(px) && isfinite(py))) {  // NaN / Inf coordinates: no face can be certified, report instead of walking
@@ -509,8 +534,8 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
       continue;
     }
     // resume the walk in the face where the fast pass stopped (hull exit, step cap, uncertain sign): the walk up to
-    // there is not repeated.  direct mode (no queue): start from the hint.
-    int f = direct ? hint2(m, px, py) : queue[(size_t)queue_cap + k];
+    // there is not repeated.  Marked queries (queue overflow) start from the hint.
+    int f = queued ? queue[(size_t)queue_cap + k] : hint2(m, px, py);
     if (OUT == 1) {
       double2 g;
       uint8_t status = gradient2_full(m, px, py, f, g, st);
@@ -528,12 +553,12 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
       y = (EPI == 0) ? epilogue2_ref(px, py, A, B, C) : epilogue2_fast(px, py, A, B, C);
     }
     if (ys) ys[i] = y;
-    if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN) ? -1 : __ldg(m.orig + f);
+    if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN || status == DLI_STATUS_STEP_LIMIT) ? -1 : __ldg(m.orig + f);
     if (status_out) status_out[i] = status;
   }
   if (STATS) {
     flush_stats(stats, st);
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
   }
 }
 
@@ -622,8 +647,7 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
         give_up = true;
       }
       if (give_up) {
-        unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = s; }
+        enqueue_straggler<0>(queue, queue_count, queue_cap, qi, s, ys, simplex_out);
         active = false;
       }
     }
@@ -640,12 +664,15 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
                unsigned int queue_cap, int64_t n, unsigned long long *__restrict__ stats) {
-  int64_t cnt = (int64_t)*queue_count;
-  const bool direct = cnt > (int64_t)queue_cap;
-  if (direct) cnt = n;
+  const int64_t total = (int64_t)*queue_count;
+  const bool overflow = total > (int64_t)queue_cap;
+  const int64_t cnt = overflow ? (int64_t)queue_cap : total;
   StatsAcc st;
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < cnt; k += (int64_t)gridDim.x * blockDim.x) {
-    int64_t i = direct ? k : (int64_t)queue[k];
+  const int64_t span = overflow ? cnt + n : cnt;   // queue entries, then (overflow only) a scan for marked queries
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < span; k += (int64_t)gridDim.x * blockDim.x) {
+    const bool queued = k < cnt;
+    const int64_t i = queued ? (int64_t)queue[k] : k - cnt;
+    if (!queued && !is_overflow_mark<0>(ys, simplex_out, i)) continue;
     double p[D];
 #pragma unroll
     for (int a = 0; a < D; a++) p[a] = xs[i * D + a];
@@ -658,13 +685,13 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
       if (status_out) status_out[i] = DLI_STATUS_STEP_LIMIT;
       continue;
     }
-    int s = direct ? hintD<D>(m, p) : queue[(size_t)queue_cap + k];   // resume where the fast pass stopped
+    int s = queued ? queue[(size_t)queue_cap + k] : hintD<D>(m, p);   // resume where the fast pass stopped
     SimplexD<D> S;
     uint8_t status = locateD_full<D>(m, p, s, S, st);
     double y;
     if (status != DLI_STATUS_OK) {
       y = __longlong_as_double(0x7ff8000000000000LL);
-      if (status == DLI_STATUS_OUTSIDE_NAN) s = -1;
+      s = -1;
     } else {
       y = (EPI == 0) ? epilogueD_ref<D, true>(p, S) : epilogueD_fast<D>(p, S);
     }
@@ -674,7 +701,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
   }
   if (STATS) {
     flush_stats(stats, st);
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)cnt);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
   }
 }
 
@@ -1129,8 +1156,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
         }
       }
       if (give_up) {
-        unsigned int slot = atomicAdd(queue_count, 1u);
-        if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = s; }
+        enqueue_straggler<0>(queue, queue_count, queue_cap, qi, s, ys, simplex_out);
         active = false;
       }
     }

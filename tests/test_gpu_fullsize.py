@@ -241,7 +241,7 @@ def test_degenerate_lattice_batches(gpu, dim):
     m.collect_stats(False)
     assert int(st.max().item()) == 0 and bool(torch.isfinite(ys).all())
     assert stats["straggler_queries"] > 0.5 * nq and stats["exact_fallbacks"] > 0.5 * nq     # really the exact pass
-    m2 = dl.Mesh(c, f, sv, None, epilogue=1)                                                   # reference-order engine
+    m2 = dl.Mesh(c, f, sv, None, epilogue="reference")                                         # reference-order engine
     y2 = m2.interp(xq)
     assert float(((ys - y2).abs() / y2.abs().clamp_min(1e-300)).max().item()) <= REL_TOL
     sub = rng.choice(nq, 100_000, replace=False)

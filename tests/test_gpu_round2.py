@@ -1,0 +1,227 @@
+"""GPU tests added in round 2: bounded straggler queue (overflow marks), outside_nan, empty-mesh gradient, a third
+opinion (scipy LinearNDInterpolator) for 2D / 3D / 4D, concurrent calls on one mesh, k-at-a-time refinement followed by
+the device mesh, the native dD class on the GPU in every dimension."""
+import math
+import threading
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle.oracle import OracleMesh
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-12
+
+
+def _rel(a, b):
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+
+
+@pytest.mark.parametrize("dim,nv", [(2, 20000), (3, 5000), (4, 1200)])
+@pytest.mark.parametrize("via", ["host", "device"])
+def test_straggler_queue_overflow_marks(gpu, dim, nv, via):
+    """more than 1/16 of the batch needs the exact pass (queries far outside the hull, queries on vertices): the queue
+    overflows, the rest is marked in the result slots and found again by the exact pass -- results as without overflow"""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(dim, nv, 70 + dim)
+    rng = np.random.default_rng(71)
+    nq = 1 << 20
+    q = rng.random((nq, dim)) * 2.0 - 0.5                      # ~ 1 - 2^-dim of the queries are outside the hull
+    q[: nq // 8] = pts[rng.integers(0, nv, nq // 8)]           # exactly on vertices: the filter cannot certify them
+    m = dl.Mesh(pts, f, sv, sn)
+    m.collect_stats(True)
+    if via == "device":
+        ys, s, st = m.interp(torch.from_numpy(q).cuda(), return_simplex=True, return_status=True)
+        ys, s, st = ys.cpu().numpy(), s.cpu().numpy(), st.cpu().numpy()
+    else:
+        ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+    stats = m.stats()
+    assert stats["straggler_queries"] > nq // 4                # far beyond the queue capacity (nq / 16)
+    yo, so, sto = OracleMesh(pts, f, sv, sn).interp(helpers_sorted(q), mode=1, nthreads=8)
+    order = helpers_order(q)
+    assert np.array_equal(st[order], sto)
+    ok = sto != 2
+    assert _rel(ys[order][ok], yo[ok]) <= REL_TOL and np.array_equal(np.isnan(ys[order]), np.isnan(yo))
+    assert (s[order][sto == 2] == -1).all()
+    # dli_locate (no value array: the mark goes into the simplex slot)
+    s2, st2 = m.locate(q, return_status=True)
+    assert np.array_equal(st2, st) and np.array_equal(s2 >= 0, s >= 0)
+    if dim == 2:
+        g, sg = m.gradient(q, return_status=True)
+        assert np.isnan(g[sg == 2]).all() and np.isfinite(g[sg != 2]).all()
+
+
+def helpers_order(q, bits=8):
+    lo, hi = q.min(0), q.max(0)
+    g = np.minimum(((q - lo) / (hi - lo) * (1 << bits)).astype(np.int64), (1 << bits) - 1)
+    key = np.zeros(len(q), np.int64)
+    for b in range(bits):
+        for c in range(q.shape[1]):
+            key |= ((g[:, c] >> b) & 1) << (b * q.shape[1] + c)
+    return np.argsort(key, kind="stable")
+
+
+def helpers_sorted(q):
+    return q[helpers_order(q)]
+
+
+def test_outside_nan_option_2d(gpu):
+    """Delaunay_incremental_interp_d(2) answers NaN outside the hull (src/delaunay_d_interp.h:1005-1008); the 2D engine
+    projects by default (src/delaunay_2_interp.h:530-545)"""
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 5000, 81)
+    q = np.random.default_rng(82).random((200000, 2)) * 1.4 - 0.2
+    y0, s0, st0 = dl.Mesh(pts, f, sv, sn).interp(q, return_simplex=True, return_status=True)
+    y1, s1, st1 = dl.Mesh(pts, f, sv, sn, outside_nan=1).interp(q, return_simplex=True, return_status=True)
+    out = st0 == dl.STATUS_OUTSIDE_PROJECTED
+    assert out.sum() > 50000 and (st1[out] == dl.STATUS_OUTSIDE_NAN).all() and np.isnan(y1[out]).all() and (s1[out] == -1).all()
+    assert np.array_equal(y0[~out], y1[~out]) and np.array_equal(st0[~out], st1[~out]) and np.array_equal(s0[~out], s1[~out])
+    # the dD class in two dimensions, batch large enough for the GPU
+    t = dl.Delaunay_incremental_interp_d(2)
+    t.insert_many(pts, f, use_gpu=False)
+    yd, std = t.interp(q, return_status=True)
+    assert np.array_equal(np.isnan(yd), out) and (std[out] == dl.STATUS_OUTSIDE_NAN).all()
+    assert _rel(yd[~out], y0[~out]) <= REL_TOL
+
+
+def test_empty_mesh_gradient_is_all_nan(gpu):
+    """the no-mesh fill must cover 2 n doubles for gradients"""
+    import torch
+    import delaunay_linterp_b200 as dl
+    m = dl.Mesh(np.array([[0.0, 0.0], [1.0, 1.0]]), np.zeros(2), np.zeros((0, 3), np.int32))
+    q = np.random.default_rng(1).random((5000, 2))
+    g, st = m.gradient(q, return_status=True)
+    assert np.isnan(g).all() and (st == dl.STATUS_NO_MESH).all()
+    gd = torch.full((5000, 2), 7.0, dtype=torch.float64, device="cuda")
+    dl.lib().dli_gradient(m._h, 5000, torch.from_numpy(q).cuda().data_ptr(), gd.data_ptr(), None, None, None)
+    torch.cuda.synchronize()
+    assert bool(torch.isnan(gd).all())
+    a = dl.DelaunayInterp2()
+    a.insert([0.0, 0.0], 1.0)
+    assert np.isnan(a.gradient(q)).all()
+
+
+@pytest.mark.parametrize("dim,nv", [(2, 20000), (3, 6000), (4, 1500)])
+def test_third_opinion_scipy_linear_nd_interpolator(gpu, dim, nv):
+    """an implementation that shares no code with this repo or its oracle (Qhull + scipy's own barycentric
+    transform arithmetic).  Well-shaped simplices only: scipy's affine transforms lose digits on slivers."""
+    from scipy.interpolate import LinearNDInterpolator
+    from scipy.spatial import Delaunay
+    import delaunay_linterp_b200 as dl
+    rng = np.random.default_rng(90 + dim)
+    pts = rng.random((nv, dim))
+    f = 1.0 + helpers.cobb_douglas(pts)
+    tri = Delaunay(pts)
+    q = rng.random((200000, dim)) * 0.9 + 0.05
+    want = LinearNDInterpolator(tri, f)(q)
+    t = dl.Delaunay_incremental_interp_d(dim)             # native triangulation + GPU engine
+    t.insert_many(pts, f, use_gpu=False)
+    got = t.interp(q)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    # condition of the containing simplex: skip the worst 0.1 % (slivers)
+    s = tri.find_simplex(q)
+    T = tri.transform[s, :dim]
+    cond = np.linalg.norm(T.reshape(len(q), -1), axis=1)
+    keep = (~np.isnan(want)) & (cond <= np.quantile(cond, 0.999))
+    assert _rel(got[keep], want[keep]) <= 1e-11
+
+
+def test_concurrent_calls_on_one_mesh(gpu):
+    """include/dli.h: interp / locate calls on the same mesh may be issued concurrently from several host threads and
+    streams.  4 threads x (device-pointer calls on own streams + host-pointer calls), results bit-identical."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 50000, 95)
+    m = dl.Mesh(pts, f, sv, sn)
+    rng = np.random.default_rng(96)
+    qs = [rng.random((300000, 2)) * 1.1 - 0.05 for _ in range(4)]
+    want = [m.interp(q) for q in qs]
+    errors = []
+
+    def work(i):
+        try:
+            torch.cuda.set_device(0)
+            stream = torch.cuda.Stream()
+            xq = torch.from_numpy(qs[i]).cuda()
+            for rep in range(8):
+                with torch.cuda.stream(stream):
+                    yd = m.interp(xq, stream=stream.cuda_stream)
+                stream.synchronize()
+                if not np.array_equal(yd.cpu().numpy(), want[i]):
+                    errors.append("device path, thread %d rep %d" % (i, rep))
+                if not np.array_equal(m.interp(qs[i]), want[i]):
+                    errors.append("host path, thread %d rep %d" % (i, rep))
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errors, errors[:3]
+
+
+def test_refine_rounds_keep_the_device_mesh_in_step(gpu):
+    """k-at-a-time refinement (dli_di2_refine) + incremental device update; after every round the
+    device mesh answers like the oracle on the exported triangulation, and the patch path (not a re-flatten) ran"""
+    import delaunay_linterp_b200 as dl
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6   # noqa: E731
+    fnb = lambda xs: helpers.cobb_douglas(xs)   # noqa: E731
+    t = dl.DelaunayInterp2(fn)
+    for p in ([0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]):
+        t.insert(p, fn(p))
+    for _ in range(500):
+        t.insert_largest_error_point()
+    q = np.random.default_rng(97).random((100000, 2)) * 5.2 - 0.1
+    t.interp(q)
+    full0, inc0 = t.sync_counts()
+    total = 0
+    for rnd in range(12):
+        total += len(t.insert_largest_error_points(64, fn_batch=fnb))
+        ys, st = t.interp(q, return_status=True)
+        c, f, tri, nb = t.export()
+        yo, so, sto = OracleMesh(c, f, tri, nb).interp(helpers_sorted(q), mode=1, nthreads=8)
+        o = helpers_order(q)
+        assert np.array_equal(st[o], sto) and _rel(ys[o], yo) <= REL_TOL
+    full1, inc1 = t.sync_counts()
+    assert total > 200 and inc1 - inc0 >= 10 and full1 - full0 <= 2
+    # the GPU evaluator over the whole refined mesh == the queue the rounds left behind (nothing stale, nothing missing)
+    m = dl.Mesh(c, f, tri, nb)
+    cent, isx, iv = m.simplex_error_items()
+    err = np.sort(m.simplex_error(fnb(cent)))
+    have = np.sort(np.array([e[0] for e in t.get_error_queue()]))
+    assert len(err) == len(have) and np.allclose(err, have, rtol=1e-9, atol=1e-18)
+
+
+@pytest.mark.parametrize("dim", [2, 3, 4])
+def test_native_dd_class_on_gpu(gpu, dim):
+    """Delaunay_incremental_interp_d on the native triangulation: adaptive loop on the host, batched interp on the GPU,
+    per-point interp on the host -- same values; GPU-rebuilt queue == per-insert host queue"""
+    import delaunay_linterp_b200 as dl
+    a = np.array([0.3, 0.6, 0.2, 0.1])[:dim]
+    fn = lambda x: float(np.prod(np.power(x, a)))   # noqa: E731
+    t = dl.Delaunay_incremental_interp_d(dim, fn)
+    for c in range(1 << dim):
+        p = [2.0 if (c >> k) & 1 else 0.01 for k in range(dim)]
+        t.insert(p, fn(p))
+    for _ in range(150):
+        t.insert_largest_error_point()
+    assert t.validate() == 0
+    q = np.random.default_rng(98).random((50000, dim)) * 2.2 - 0.1
+    ys, st = t.interp(q, return_status=True)
+    pts, f, sv, sn = t.export()
+    o = helpers_order(q)
+    yo, so, sto = OracleMesh(pts, f, sv, sn).interp(q[o], mode=1, nthreads=8)
+    assert np.array_equal(st[o], np.where(sto == 1, 2, sto)) or np.array_equal(st[o], sto)
+    ok = sto == 0
+    assert _rel(ys[o][ok], yo[ok]) <= REL_TOL and np.isnan(ys[o][~ok]).all()
+    one = np.array([t.interp(p.tolist()) for p in q[:300]])
+    assert np.array_equal(np.isnan(one), np.isnan(ys[:300])) and _rel(one[~np.isnan(one)], ys[:300][~np.isnan(one)]) <= REL_TOL
+    before = np.sort([e[0] for e in t.get_error_queue()])
+    t.rebuild_error_queue()
+    after = np.sort([e[0] for e in t.get_error_queue()])
+    assert len(before) == len(after) and np.allclose(before, after, rtol=1e-8, atol=1e-18)
+    assert math.isnan(t.interp([9.0] * dim))
