@@ -89,7 +89,14 @@ static int run(double lo, const char *want_regular, const char *want_adaptive, b
   adaptive_triang.interp_batch(xs.data(), true_f.size(), ada_b.data());
   double sse1 = 0, sse2 = 0;
   for (size_t i = 0; i < true_f.size(); i++) {
-    CHECK(std::fabs(reg[i] - reg_b[i]) <= 1e-12 * std::fabs(reg[i]) && std::fabs(ada[i] - ada_b[i]) <= 1e-12 * std::fabs(ada[i]));
+    // (1e-14 absolute = a few ulps of the data scale max|f| = 4.3: a query exactly on a vertex / edge where f vanishes,
+    // e.g. the corner (0, 5) with lo = 0, is answered from whichever incident face the walk reaches first -- exactly 0
+    // from one face, 0 * f_i + 1e-17 * f_j from another)
+    const double tol_abs = 1e-14;
+    if (!(std::fabs(reg[i] - reg_b[i]) <= 1e-12 * std::fabs(reg[i]) + tol_abs && std::fabs(ada[i] - ada_b[i]) <= 1e-12 * std::fabs(ada[i]) + tol_abs))
+      printf("query %zu (%.17g, %.17g): regular host %.17g batch %.17g | adaptive host %.17g batch %.17g | status %d\n", i,
+             xs[2 * i], xs[2 * i + 1], reg[i], reg_b[i], ada[i], ada_b[i], (int)st[i]);
+    CHECK(std::fabs(reg[i] - reg_b[i]) <= 1e-12 * std::fabs(reg[i]) + tol_abs && std::fabs(ada[i] - ada_b[i]) <= 1e-12 * std::fabs(ada[i]) + tol_abs);
     CHECK(st[i] == DLI_STATUS_OK);
     sse1 += (true_f[i] - reg[i]) * (true_f[i] - reg[i]);
     sse2 += (true_f[i] - ada[i]) * (true_f[i] - ada[i]);
@@ -104,7 +111,7 @@ static int run(double lo, const char *want_regular, const char *want_adaptive, b
     for (size_t i = 0; i < true_f.size(); i++) same += ada[i] == ada_b[i];
     // (queries exactly on an edge may be answered from either incident face: equal within rounding, not bit for bit)
     CHECK(same + 40 >= true_f.size());
-    for (size_t i = 0; i < true_f.size(); i++) CHECK(std::fabs(ada[i] - ada_b[i]) <= 4e-16 * std::fabs(ada[i]));
+    for (size_t i = 0; i < true_f.size(); i++) CHECK(std::fabs(ada[i] - ada_b[i]) <= 4e-16 * std::fabs(ada[i]) + 1e-14);
     CHECK(dli_di2_set_options(adaptive_triang.handle(), nullptr) == DLI_OK);
   }
   char b1[64], b2[64];

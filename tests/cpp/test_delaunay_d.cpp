@@ -99,6 +99,9 @@ static int run(int N, bool host_only) {
   vector<vector<double>> qp;
   grid_points(N, interp_grid, qp);
   vector<double> true_f, reg, ada, xs;
+  // (one untimed call first: on a GPU box the library's first CUDA runtime query -- "is this a device pointer?" -- creates
+  // the CUDA context, a one-time ~40 ms that is not part of the per-call cost)
+  (void)triang.interp(qp[0].begin(), qp[0].end());
   auto t0 = std::chrono::steady_clock::now();
   for (auto &x : qp) {
     true_f.push_back(fn(N, x.data()));
