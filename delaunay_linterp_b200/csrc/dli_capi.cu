@@ -151,6 +151,7 @@ struct dli_mesh {
   bool collect_stats = false;   // counters (atomics in the kernels)
   bool collect_timing = false;  // CUDA events around the interp kernels
   unsigned long long *d_stats = nullptr;
+  float *h_straggler_frac = nullptr;   // mapped pinned word written by the exact passes: straggler fraction of the last launch
   mutable dli_stats last{};
   mutable std::mutex ev_mu;
   mutable std::vector<cudaEvent_t> ev;  // triples (before fast, after fast, after full)
@@ -164,7 +165,12 @@ struct dli_mesh {
 constexpr int64_t kCellModeFaces = 8ll << 20;
 
 // bytes per walk record (2D: 64, 3D: 128, 4D: 192)
-static int fat_record_bytes(int dim) { return dim == 2 ? 64 : (dim == 3 ? FatD<3>::BYTES : FatD<4>::BYTES); }
+// 4D walk records: one packed 128-byte record per simplex (FatD<4, true>) unless the mesh has too many simplices for the
+// 24-bit neighbour fields or opt.packed_faces == 5 asks for the split layout (tests); replicas / snapshots follow header word 13
+static bool fat_pack4(const dli_mesh *m);
+static int fat_record_bytes(const dli_mesh *m) {
+  return m->dim == 2 ? 64 : (m->dim == 3 ? FatD<3>::BYTES : (fat_pack4(m) ? FatD<4, true>::BYTES : FatD<4>::BYTES));
+}
 
 static void mesh_free(dli_mesh *m) {
   if (!m) return;
@@ -181,6 +187,7 @@ static void mesh_free(dli_mesh *m) {
   cudaFree(m->d_item_verts);
   cudaFree(m->d_upd);
   cudaFree(m->d_stats);
+  if (m->h_straggler_frac) cudaFreeHost(m->h_straggler_frac);
   pipe_free(m->pipe);
   stage_free(m->stage);
   for (cudaEvent_t e : m->ev) cudaEventDestroy(e);
@@ -399,10 +406,13 @@ static int mesh_alloc_common(dli_mesh *m) {
   if (m->opt.epilogue == DLI_EPILOGUE_AUTO && m->opt.packed_faces >= 0 && m->ns > 0) {
     // 2D meshes whose records are far larger than L2 get cell-indexed records (allocated once the hint grid exists)
     m->cellmode = d == 2 && (m->opt.packed_faces == 3 || (m->opt.packed_faces == 0 && m->ns >= kCellModeFaces));
-    if (!m->cellmode) CU(cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(d) * (size_t)m->ns));
+    if (!m->cellmode) CU(cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m) * (size_t)m->ns));
   }
   CU(cudaMalloc(&m->d_stats, sizeof(unsigned long long) * ST_WORDS));
   CU(cudaMemset(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS));
+  // (a failed allocation only loses the hint: the queue then keeps its default size)
+  if (cudaHostAlloc(&m->h_straggler_frac, sizeof(float), cudaHostAllocMapped) == cudaSuccess) *m->h_straggler_frac = 0.f;
+  else { cudaGetLastError(); m->h_straggler_frac = nullptr; }
   // keep stream-ordered allocations cached between calls
   cudaMemPool_t pool;
   if (cudaDeviceGetDefaultMemPool(&pool, m->device) == cudaSuccess) {
@@ -412,6 +422,11 @@ static int mesh_alloc_common(dli_mesh *m) {
   return DLI_OK;
 }
 
+static bool fat_pack4(const dli_mesh *m) {
+  if (m->dim != 4) return false;
+  if (m->fat_enc >= 0) return m->fat_enc == 4;
+  return m->ns < (1 << 24) - 1 && m->opt.packed_faces != 5;
+}
 // walk records of meshes with >= 2^21-2 faces (or opt.packed_faces == 2: testing) use delta-encoded neighbours
 static bool fat_delta(const dli_mesh *m) {
   if (m->fat_enc >= 0) return m->fat_enc == 1;
@@ -502,6 +517,8 @@ static int build_fat_records(dli_mesh *m) {
                                                reinterpret_cast<const double4 *>(m->d_vrec), m->d_fat, d_cnt);
   } else if (m->dim == 3) {
     k_build_fatD<3><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
+  } else if (fat_pack4(m)) {
+    k_build_fatD<4, true><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
   } else {
     k_build_fatD<4><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
   }
@@ -871,7 +888,7 @@ extern "C" int64_t dli_mesh_device_bytes(const dli_mesh *m) {
   if (!m) return 0;
   return (int64_t)(sizeof(double) * m->nv * m->vs + sizeof(int32_t) * m->ns * m->ss + sizeof(int4) * m->nh +
                    sizeof(int32_t) * m->grid.cells + sizeof(int32_t) * m->ns + (m->d_fpack ? sizeof(ulonglong2) * m->ns : 0) +
-                   (m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->nslots : 0) +
+                   (m->d_fat ? (int64_t)fat_record_bytes(m) * m->nslots : 0) +
                    (m->cellmode ? (int64_t)sizeof(int32_t) * (m->nslots + m->grid.g[1] + 1) : 0));
 }
 extern "C" int dli_mesh_get_simplices(const dli_mesh *m, int32_t *sv, int32_t *sn) {
@@ -912,15 +929,17 @@ Mesh2View view2(const dli_mesh *m) {
   v.ns = (int)m->ns; v.nh = m->nh;
   v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   v.outside_nan = m->opt.outside_nan;
+  v.straggler_frac = m->h_straggler_frac;
   return v;
 }
 MeshDView viewD(const dli_mesh *m) {
   MeshDView v;
   v.vrec = m->d_vrec; v.srec = m->d_srec; v.hint = m->d_hint; v.orig = m->d_orig;
   v.fat = m->d_fat;
-  v.epi = (m->d_fat && m->dim == 4) ? m->d_fat + (size_t)m->ns * FatD<4>::CHUNKS : nullptr;
+  v.epi = (m->d_fat && m->dim == 4 && !fat_pack4(m)) ? m->d_fat + (size_t)m->ns * FatD<4>::CHUNKS : nullptr;
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
+  v.straggler_frac = m->h_straggler_frac;
   return v;
 }
 
@@ -929,7 +948,17 @@ constexpr int64_t kChunk = 1ll << 28;      // queries per launch pair (int32 ind
 // 50 MB for a 100M-query launch (it used to be one entry per query: 0.8 GB).  Queries that do not fit are marked in
 // their result slot and found again by the exact pass (enqueue_straggler in dli_kernels.cuh): an overflow costs one
 // scan of the results, not a re-run of the batch.
-static int64_t queue_capacity(int64_t n) { return std::min<int64_t>(n, std::max<int64_t>(1 << 16, n / 16)); }
+// The exact pass reports the straggler fraction of its launch through a mapped host word (no copy, no synchronisation;
+// a stale or concurrent value is only a worse hint): a mesh whose batches keep sending more than 1/16 of their queries
+// to the exact pass (lattice queries on a regular grid: 30-60 %) gets a queue that holds them from its second call on.
+static int64_t queue_capacity(const dli_mesh *m, int64_t n) {
+  double frac = 1.0 / 16;
+  if (m->h_straggler_frac) {
+    const float seen = *(volatile float *)m->h_straggler_frac;
+    if (seen > 0.05f && seen <= 1.0f) frac = std::min(1.0, 1.25 * (double)seen + 0.01);
+  }
+  return std::min<int64_t>(n, std::max<int64_t>(1 << 16, (int64_t)(frac * (double)n)));
+}
 
 struct Launch {
   const dli_mesh *m;
@@ -993,7 +1022,24 @@ void launchD(Launch &L, int64_t n, const double *xs, double *ys, int32_t *so, ui
   L.mark(0);
   if (EPI == 0 && L.m->d_fat) {
     const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
-    if (L.m->opt.prefetch_ring >= 0)
+    const bool ring = L.m->opt.prefetch_ring >= 0;
+    if constexpr (D == 4) {
+      if (fat_pack4(L.m)) {
+        using FP = FatD<4, true>;
+        if (ring)
+          k_interpD_fat<4, STATS, true, true><<<grid, tpb, (size_t)wpb * (FP::SMEM_PER_WARP + RingD<4>::BYTES), L.st>>>(
+              v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+        else
+          k_interpD_fat<4, STATS, false, true><<<grid, tpb, (size_t)wpb * FP::SMEM_PER_WARP, L.st>>>(
+              v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
+        L.mark(1);
+        k_interpD_full<D, STATS, EPI><<<148 * DLI_X_FULLD_BLOCKS, 128, 0, L.st>>>(v, xs, ys, so, sto, L.queue, L.qcount, L.qcap, n, L.stats);
+        L.mark(2);
+        L.launches += 2;
+        return;
+      }
+    }
+    if (ring)
       k_interpD_fat<D, STATS, true><<<grid, tpb, (size_t)wpb * (FatD<D>::SMEM_PER_WARP + RingD<D>::BYTES), L.st>>>(
           v, n, per_warp, xs, ys, so, sto, L.queue, L.qcount, L.qcap, L.stats);
     else
@@ -1030,7 +1076,7 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     if (launches) *launches += 1;
     return DLI_OK;
   }
-  const int64_t cap = queue_capacity(std::min(n, kChunk));
+  const int64_t cap = queue_capacity(m, std::min(n, kChunk));
   int32_t *queue = nullptr;
   // [cap] query indices, [cap] faces the fast pass stopped in, then the counter
   CU(cudaMallocAsync(&queue, sizeof(int32_t) * 2 * (size_t)cap + 16, st));
@@ -1512,8 +1558,9 @@ extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORD
   for (int k = 0; k < 4; k++) h[6 + k] = m->grid.g[k];
   h[10] = m->max_steps; h[11] = m->fast_steps;
   // optional buffers the replica must mirror, and how the walk records encode their neighbours:
-  // word 13: 0 = no walk records, 1 = absolute neighbour ids, 2 = cell-indexed records, 3 = delta-encoded neighbours
-  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : 1)) : 0;
+  // word 13: 0 = no walk records, 1 = absolute neighbour ids (4D: split records), 2 = cell-indexed records,
+  // 3 = delta-encoded neighbours, 4 = 4D packed one-line records
+  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : (fat_pack4(m) ? 4 : 1))) : 0;
   h[15] = m->nslots;
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
@@ -1543,9 +1590,10 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   int rc = mesh_alloc_common(m);
   // mirror the source's optional buffers exactly (every rank must see the same buffer list)
   if (rc == DLI_OK && !h[12] && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
-  if (rc == DLI_OK && h[13] != 1 && h[13] != 3 && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
+  // (mesh_alloc_common sized d_fat from this side's options: drop it and allocate for the source's layout below)
+  if (rc == DLI_OK && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
   m->cellmode = h[13] == 2;
-  m->fat_enc = h[13] == 3 ? 1 : 0;
+  m->fat_enc = h[13] == 3 ? 1 : (h[13] == 4 ? 4 : 0);
   m->nslots = h[13] == 2 ? h[15] : m->ns;
   if (rc == DLI_OK && m->cellmode &&
       (cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess ||
@@ -1554,7 +1602,7 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   if (rc == DLI_OK && h[12] && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "packed face allocation failed");
   if (rc == DLI_OK && h[13] && !m->d_fat &&
-      cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m->dim) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess)
+      cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "walk record allocation failed");
   m->max_steps = (int)h[10];
   m->fast_steps = (int)h[11];
@@ -1577,7 +1625,7 @@ extern "C" int dli_mesh_buffer(const dli_mesh *m, int index, void **ptr, int64_t
     case 2: *ptr = m->d_hull; *bytes = m->d_hull ? (int64_t)sizeof(int4) * std::max<int32_t>(m->nh, 1) : 0; break;
     case 3: *ptr = m->d_hint; *bytes = (int64_t)sizeof(int32_t) * m->grid.cells; break;
     case 4: *ptr = m->d_fpack; *bytes = m->d_fpack ? (int64_t)sizeof(ulonglong2) * m->ns : 0; break;
-    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)fat_record_bytes(m->dim) * m->nslots : 0; break;
+    case 5: *ptr = m->d_fat; *bytes = m->d_fat ? (int64_t)fat_record_bytes(m) * m->nslots : 0; break;
     case 6: *ptr = m->d_orig; *bytes = (int64_t)sizeof(int32_t) * std::max<int64_t>(m->ns, 1); break;
     case 7: *ptr = m->d_slot_face; *bytes = m->cellmode ? (int64_t)sizeof(int32_t) * m->nslots : 0; break;
     case 8: *ptr = m->d_rowstart; *bytes = m->cellmode ? (int64_t)sizeof(int) * (m->grid.g[1] + 1) : 0; break;

@@ -45,6 +45,7 @@ struct Mesh2View {
   int max_steps;   // hard cap on simplices visited per query
   int fast_steps;  // fast-path cap; longer walks are re-run by the straggler/exact pass
   int outside_nan; // != 0: queries outside the hull report DLI_STATUS_OUTSIDE_NAN instead of being projected
+  float *straggler_frac;  // mapped pinned host word: the exact pass reports the straggler fraction of its launch (queue sizing)
 };
 
 // dD (D = 3, 4): vertex record VS doubles {x_0..x_{D-1}, f, pad}; simplex record SS ints
@@ -66,6 +67,7 @@ struct MeshDView {
   int ns;
   int max_steps;
   int fast_steps;
+  float *straggler_frac;  // as Mesh2View::straggler_frac
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -83,13 +85,24 @@ struct MeshDView {
 // half an fp32 ulp) is covered by the filter constant kFatKD, so a certified barycentric sign is the sign of the exact
 // orientation predicate on the fp64 mesh.
 // ---------------------------------------------------------------------------------------------
-template <int D>
+// D = 4, PACK = true (the default for 4D meshes with < 2^24 - 1 simplices): the whole simplex in ONE 128-byte line, so a
+//        query touches one line per walk step and none for the interpolant (the split layout reads a second, random
+//        line per query for 40 useful bytes: 450 B per query moved against 260 B algorithmic, profiles/r01_k_interpD_fat4_split_ncu.txt):
+//        c0 p0x p0y | c1 p0z p0w | c2 f0 gx | c3 gy gz | c4 gw, W0 | c5 W1 W2 | c6 W3 W4 | c7 neighbours
+//        W0..W4 = 320 bits: row i of G in bits [80 i, 80 i + 80) as BLOCK FLOATING POINT -- four 18-bit mantissas
+//        (q + 2^17, |q| < 2^17) and one 8-bit exponent (e + 128): G_ik ~ q_ik 2^e_i with e_i chosen from the row
+//        maximum, so every entry is within 2^-16 of the ROW MAXIMUM (checked per entry at build time, together with the
+//        error of computing G itself; else the slow flag).  The step's bound is relative to the row maximum anyway
+//        (kFatKD * max|G_i| * |d|_1), so block scaling loses nothing but 7 bits of band: kFatKP = 2^-15.
+//        c7 = five 24-bit neighbour ids (0xffffff = hull) + 8 flag bits (bit 0 = slow).
+template <int D, bool PACK = false>
 struct FatD {
+  static_assert(!PACK || D == 4, "packed walk records exist for D = 4 only");
   static constexpr int CHUNKS = 8;                        // walk record size in 16-byte chunks (one 128-byte line)
   static constexpr int LOADED = 8;                        // chunks actually staged
   static constexpr int LPR = 8;                           // lanes cooperating on one record
   static constexpr int SSTRIDE = 9;                       // shared-memory record stride in chunks (odd: conflict-free)
-  static constexpr bool SPLIT = (D == 4);                 // affine interpolant in a separate record array
+  static constexpr bool SPLIT = (D == 4) && !PACK;        // affine interpolant in a separate record array
   static constexpr int EPI_CHUNKS = SPLIT ? 4 : 0;        // interpolant record stride in chunks (64 B)
   static constexpr int EPI_LOADED = SPLIT ? 3 : 0;
   static constexpr int ESTRIDE = 5;                       // per-lane shared slot: 3 interpolant chunks + d[4] (conflict-free)
@@ -97,6 +110,16 @@ struct FatD {
   static constexpr int SMEM_PER_WARP = 32 * SSTRIDE * 16 + (SPLIT ? 32 * ESTRIDE * 16 : 0);
 };
 constexpr double kFatKD = 2.384185791015625e-07;  // 2^-22 = 4 fp32 unit roundoffs
+constexpr double kFatKP = 3.0517578125e-05;       // 2^-15 = twice the block-floating-point entry error 2^-16 (packed 4D records)
+constexpr unsigned kPackNb24 = 0xFFFFFFu;         // packed 4D records: 24-bit neighbour field, all ones = hull
+// field [OFF, OFF + LEN) of the 320-bit string W[0..4] (compile-time position: one or two shifts)
+template <int OFF, int LEN>
+__host__ __device__ __forceinline__ unsigned pack_field(const unsigned long long (&W)[5]) {
+  constexpr int w = OFF / 64, b = OFF % 64;
+  unsigned long long v = W[w] >> b;
+  if constexpr (b + LEN > 64) v |= W[w + 1] << (64 - b);
+  return (unsigned)v & ((1u << LEN) - 1u);
+}
 
 struct StatsAcc {  // per-thread accumulators, flushed by the kernels when stats are enabled
   unsigned long long steps = 0, exact = 0, outside = 0;
@@ -299,17 +322,32 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
       B = load_vert(m, F.v1);
       C = load_vert(m, F.v2);
       int nbs[3] = {F.n0, F.n1, F.n2};
-      int mv = -1;
+      // The decision "first strictly negative edge in the order 0, 1, 2", taken in two convergent stages (as
+      // locateD_full does): the fp64 filter on all three edges, branch-free; then the exact predicate on the uncertain
+      // edges below the first certainly-negative one, lowest first, through ONE call site -- lanes resolve their k-th
+      // uncertain edge together whatever its index (with the predicate inlined per edge, a warp of on-edge queries
+      // ran 13 lanes wide: profiles/r02_k_interp2_full_lattice_before_ncu.txt).
+      int mv = 3;
+      unsigned unc = 0;
 #pragma unroll
       for (int j = 0; j < 3; j++) {
         if (nbs[j] >= 0 && nbs[j] == from) continue;
         const double4 &X = (j == 0) ? B : (j == 1 ? C : A);
         const double4 &Y = (j == 0) ? C : (j == 1 ? A : B);
-        int s = orient2d_filtered(X.x, X.y, Y.x, Y.y, px, py);
-        if (s == 2) { st.exact++; s = orient2d_exact(X.x, X.y, Y.x, Y.y, px, py); }
-        if (s < 0) { mv = j; break; }
+        const int s = orient2d_filtered(X.x, X.y, Y.x, Y.y, px, py);
+        if (s == 2) unc |= 1u << j;
+        else if (s < 0 && j < mv) mv = j;
       }
-      if (mv < 0) { found = true; break; }
+      unc &= (1u << mv) - 1u;
+      while (unc) {
+        const int j = __ffs((int)unc) - 1;
+        unc &= unc - 1u;
+        const double Xx = (j == 0) ? B.x : (j == 1 ? C.x : A.x), Xy = (j == 0) ? B.y : (j == 1 ? C.y : A.y);
+        const double Yx = (j == 0) ? C.x : (j == 1 ? A.x : B.x), Yy = (j == 0) ? C.y : (j == 1 ? A.y : B.y);
+        st.exact++;
+        if (orient2d_exact(Xx, Xy, Yx, Yy, px, py) < 0) { mv = j; unc = 0; }
+      }
+      if (mv > 2) { found = true; break; }
       int nb = nbs[mv];
       if (nb < 0) { exit_h = ~nb; break; }
       from = f;

@@ -474,7 +474,14 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
           if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
           else { from = f; f = nb; }
         } else {
-          bool pos = ((o0 > e0) | c0) & ((o1 > e1) | c1) & ((o2 > e2) | c2);
+          // closed face: o >= e certifies "not negative".  e carries a factor 2 of slack over the rounding analysis, so
+          // o == e > 0 is still strictly positive; o == e == 0 happens only when both products of the edge's cross
+          // product are exact zeros (an axis-aligned edge through vertex 0 with the query's coordinate equal to the
+          // vertex's: fp32(A) = 0 iff A = 0, p - p0 = 0 iff p = p0; barring underflow), i.e. the query is exactly ON
+          // that edge -- CGAL's EDGE / VERTEX locate types, which the reference answers from the face at hand.
+          // Gradient queries (OUT = 1) keep the strict test: on an edge / vertex they need gradient2_full's averaging.
+          bool pos = OUT == 1 ? (((o0 > e0) | c0) & ((o1 > e1) | c1) & ((o2 > e2) | c2))
+                              : (((o0 >= e0) | c0) & ((o1 >= e1) | c1) & ((o2 >= e2) | c2));
           if (pos) {
             if (ys) {
               const double f0 = __hiloint2double((int)V[1], (int)V[0]);
@@ -556,6 +563,7 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
     if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN || status == DLI_STATUS_STEP_LIMIT) ? -1 : __ldg(m.orig + f);
     if (status_out) status_out[i] = status;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0) *m.straggler_frac = (float)total / (float)n;
   if (STATS) {
     flush_stats(stats, st);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
@@ -699,6 +707,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
     if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + s) : -1;
     if (status_out) status_out[i] = status;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0) *m.straggler_frac = (float)total / (float)n;
   if (STATS) {
     flush_stats(stats, st);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
@@ -775,7 +784,7 @@ struct DetDD<1> {
 // bound below accounts for it).  The slow flag is set when an entry of the fp32 G is not within 1.5 fp32
 // ulps-of-the-row-maximum of the exact value, or when the a-priori error bound of the affine interpolant exceeds
 // 1e-13 * min|f_i| (see k_build_fat2): k_interpD_full handles those simplices in the reference's operation order.
-template <int D>
+template <int D, bool PACK = false>
 __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, const double *__restrict__ vrec, int vs,
                              uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -835,11 +844,40 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
     dG[i] = eps * fabs(G[i]) + edd * (P[i] + fabs(G[i]) * PW) / aW;
     g32[i] = (float)G[i];
   }
+  unsigned long long W[5] = {0ull, 0ull, 0ull, 0ull, 0ull};   // PACK: block-floating-point G (FatD<4, true>)
+  if constexpr (PACK) {
+    for (int i = 0; i < D; i++) {
+      double gmax = 0.0;
+      for (int k = 0; k < D; k++) gmax = fmax(gmax, fabs(G[i * D + k]));
+      bool ok = gmax > 0.0 && gmax < 1e300;
+      int e = ok ? ilogb(gmax) - 16 : 0;                      // gmax / 2^e in [2^16, 2^17)
+      if (e < -128 || e > 127) { ok = false; e = 0; }
+      double dmax = 0.0, dec[D];
+      unsigned __int128 row = 0;   // 80 bits: four 18-bit mantissas (q + 2^17), then the exponent byte (e + 128)
+      for (int k = 0; k < D; k++) {
+        double q = ok ? rint(ldexp(G[i * D + k], -e)) : 0.0;
+        q = fmin(131071.0, fmax(-131071.0, q));
+        dec[k] = ldexp(q, e);
+        dmax = fmax(dmax, fabs(dec[k]));
+        row |= (unsigned __int128)(unsigned long long)((long long)q + 131072ll) << (18 * k);
+      }
+      row |= (unsigned __int128)(unsigned long long)(e + 128) << 72;
+      // every decoded entry within 2^-16 of the decoded row maximum, the error of computing G included
+      for (int k = 0; k < D; k++) ok = ok && (fabs(dec[k] - G[i * D + k]) + dG[i * D + k] <= 1.52587890625e-05 * dmax);
+      slow |= !ok;
+      // row i occupies bits [80 i, 80 i + 80) of W: byte-aligned, so bytes never straddle a 64-bit word
+      for (int t = 0; t < 10; t++) {
+        const int pos = 80 * i + 8 * t;
+        W[pos / 64] |= (unsigned long long)((unsigned)(row >> (8 * t)) & 0xffu) << (pos % 64);
+      }
+    }
+  } else {
   for (int i = 0; i < D; i++) {
     double gmax = 0.0;
     for (int k = 0; k < D; k++) gmax = fmax(gmax, fabs((double)g32[i * D + k]));
     slow |= !(gmax > 0.0 && gmax < 1e300);
     for (int k = 0; k < D; k++) slow |= !(fabs((double)g32[i * D + k] - G[i * D + k]) + dG[i * D + k] <= 1.5 * u * gmax);
+  }
   }
   // affine interpolant (gradient accumulated in double-double) and its a-priori error bound over the simplex
   double g[D], E_eval = (D + 2) * eps * fabs(f[0]);
@@ -880,7 +918,7 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
     return make_uint4(__float_as_uint(a), __float_as_uint(b), __float_as_uint(c), __float_as_uint(d));
   };
   const double flags = __longlong_as_double(slow ? 1ll : 0ll);
-  uint4 *o = fat + (size_t)s * FatD<D>::CHUNKS;
+  uint4 *o = fat + (size_t)s * FatD<D, PACK>::CHUNKS;
   if constexpr (D == 3) {
     o[0] = d2(x0[0], x0[1]);
     o[1] = d2(x0[2], f[0]);
@@ -890,6 +928,20 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
     o[5] = f4(g32[4], g32[5], g32[6], g32[7]);
     o[6] = f4(g32[8], 0.f, 0.f, 0.f);
     o[7] = make_uint4((unsigned)nb[0], (unsigned)nb[1], (unsigned)nb[2], (unsigned)nb[3]);
+  } else if constexpr (PACK) {
+    auto n24 = [&](int j) -> unsigned { return nb[j] < 0 ? kPackNb24 : (unsigned)nb[j]; };   // (ns < 2^24 - 1: checked by the host)
+    o[0] = d2(x0[0], x0[1]);
+    o[1] = d2(x0[2], x0[3]);
+    o[2] = d2(f[0], g[0]);
+    o[3] = d2(g[1], g[2]);
+    uint4 c4 = d2(g[3], 0.0);
+    c4.z = (unsigned)W[0]; c4.w = (unsigned)(W[0] >> 32);
+    o[4] = c4;
+    o[5] = make_uint4((unsigned)W[1], (unsigned)(W[1] >> 32), (unsigned)W[2], (unsigned)(W[2] >> 32));
+    o[6] = make_uint4((unsigned)W[3], (unsigned)(W[3] >> 32), (unsigned)W[4], (unsigned)(W[4] >> 32));
+    // 128-bit little-endian string: n_j in bits [24 j, 24 j + 24), flags in bits [120, 128)
+    const unsigned a0 = n24(0), a1 = n24(1), a2 = n24(2), a3 = n24(3), a4 = n24(4);
+    o[7] = make_uint4(a0 | (a1 << 24), (a1 >> 8) | (a2 << 16), (a2 >> 16) | (a3 << 8), a4 | ((slow ? 1u : 0u) << 24));
   } else {
     const unsigned fl = slow ? 1u : 0u;
     o[0] = d2(x0[0], x0[1]);
@@ -922,12 +974,12 @@ struct RingD {
   static constexpr int QBYTES = 96 * D * 8, HBYTES = 64 * 4;
   static constexpr int BYTES = QBYTES + HBYTES;
 };
-template <int D, bool STATS, bool RING = false>
+template <int D, bool STATS, bool RING = false, bool PACK = false>
 __global__ void __launch_bounds__(128)
 k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
-  using F = FatD<D>;
+  using F = FatD<D, PACK>;
   constexpr unsigned FULL = 0xffffffffu;
   extern __shared__ __align__(16) unsigned char stage_smem[];
   const int lane = threadIdx.x & 31;
@@ -1062,6 +1114,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
       steps++;
       double x0[D], f0, g[D];
       float G[D * D];
+      double rowscale[D];   // PACK: 2^e_i of the block-floating-point rows (unused otherwise)
       int nb[D + 1];
       unsigned long long flags;
       {
@@ -1076,6 +1129,29 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
           G[4] = __uint_as_float(c5.x); G[5] = __uint_as_float(c5.y); G[6] = __uint_as_float(c5.z); G[7] = __uint_as_float(c5.w);
           G[8] = __uint_as_float(c6.x);
           nb[0] = (int)c7.x; nb[1] = (int)c7.y; nb[2] = (int)c7.z; nb[3] = (int)c7.w;
+        } else if constexpr (PACK) {
+          const uint4 c0 = mine[0], c1 = mine[1], c2 = mine[2], c3 = mine[3], c4 = mine[4], c5 = mine[5], c6 = mine[6], c7 = mine[7];
+          x0[0] = lo(c0); x0[1] = hi(c0); x0[2] = lo(c1); x0[3] = hi(c1);
+          f0 = lo(c2); g[0] = hi(c2); g[1] = lo(c3); g[2] = hi(c3); g[3] = lo(c4);
+          const unsigned long long W[5] = {((unsigned long long)c4.w << 32) | c4.z, ((unsigned long long)c5.y << 32) | c5.x,
+                                           ((unsigned long long)c5.w << 32) | c5.z, ((unsigned long long)c6.y << 32) | c6.x,
+                                           ((unsigned long long)c6.w << 32) | c6.z};
+          // mantissas as exact small integers in fp32 (magic-number conversion: 2^23 + field, minus 2^23 + 2^17)
+          auto mant = [](unsigned fld) { return __uint_as_float(0x4B000000u | fld) - 8519680.0f; };
+          G[0] = mant(pack_field<0, 18>(W));    G[1] = mant(pack_field<18, 18>(W));   G[2] = mant(pack_field<36, 18>(W));   G[3] = mant(pack_field<54, 18>(W));
+          G[4] = mant(pack_field<80, 18>(W));   G[5] = mant(pack_field<98, 18>(W));   G[6] = mant(pack_field<116, 18>(W));  G[7] = mant(pack_field<134, 18>(W));
+          G[8] = mant(pack_field<160, 18>(W));  G[9] = mant(pack_field<178, 18>(W));  G[10] = mant(pack_field<196, 18>(W)); G[11] = mant(pack_field<214, 18>(W));
+          G[12] = mant(pack_field<240, 18>(W)); G[13] = mant(pack_field<258, 18>(W)); G[14] = mant(pack_field<276, 18>(W)); G[15] = mant(pack_field<294, 18>(W));
+          // row scales 2^e as doubles (exponent byte e + 128 -> biased fp64 exponent e + 1023)
+          rowscale[0] = __hiloint2double((int)((pack_field<72, 8>(W) + 895u) << 20), 0);
+          rowscale[1] = __hiloint2double((int)((pack_field<152, 8>(W) + 895u) << 20), 0);
+          rowscale[2] = __hiloint2double((int)((pack_field<232, 8>(W) + 895u) << 20), 0);
+          rowscale[3] = __hiloint2double((int)((pack_field<312, 8>(W) + 895u) << 20), 0);
+          const unsigned a0 = c7.x & kPackNb24, a1 = (c7.x >> 24) | ((c7.y & 0xffffu) << 8), a2 = (c7.y >> 16) | ((c7.z & 0xffu) << 16),
+                         a3 = c7.z >> 8, a4 = c7.w & kPackNb24;
+          nb[0] = a0 == kPackNb24 ? -1 : (int)a0; nb[1] = a1 == kPackNb24 ? -1 : (int)a1; nb[2] = a2 == kPackNb24 ? -1 : (int)a2;
+          nb[3] = a3 == kPackNb24 ? -1 : (int)a3; nb[4] = a4 == kPackNb24 ? -1 : (int)a4;
+          flags = c7.w >> 24;
         } else {
           uint4 c0 = mine[0], c1 = mine[1], c6 = mine[6], c7 = mine[7];
           x0[0] = lo(c0); x0[1] = hi(c0); x0[2] = lo(c1); x0[3] = hi(c1);
@@ -1104,8 +1180,13 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
         float gm = 0.f;
 #pragma unroll
         for (int k = 0; k < D; k++) { acc = fma((double)G[i * D + k], d[k], acc); gm = fmaxf(gm, fabsf(G[i * D + k])); }
+        if constexpr (PACK) {   // block floating point: exact power-of-two scaling of the row
+          acc *= rowscale[i];
+          e[i + 1] = (kFatKP * ((double)gm * rowscale[i])) * d1;
+        } else {
+          e[i + 1] = (kFatKD * (double)gm) * d1;
+        }
         b[i + 1] = acc;
-        e[i + 1] = (kFatKD * (double)gm) * d1;
         sb += acc;
         se += e[i + 1];
       }

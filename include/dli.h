@@ -86,7 +86,10 @@ typedef struct dli_options {
                                      -1 = never, 2 = walk records with delta-encoded neighbours even on small meshes
                                      (the encoding large meshes get; for tests), 3 = cell-indexed walk records even on
                                      small meshes (the layout meshes with >= 8M faces get: a query's start record is
-                                     addressed by its hint cell, no hint read; for tests) */
+                                     addressed by its hint cell, no hint read; for tests);
+                                     4D: 0 = one packed 128-byte walk record per simplex (block-floating-point barycentric
+                                     gradients, 24-bit neighbour ids; default below 2^24 - 1 simplices), 5 = the split layout
+                                     larger meshes get (128-byte geometry record + 64-byte interpolant record; for tests) */
   int32_t prefetch_ring;          /* 2D walk-record fast pass: 0 = per-warp cp.async prefetch ring for queries and start
                                      hints (default), -1 = plain loads */
   int32_t outside_nan;            /* 2D: 0 = queries outside the hull are projected on the hull (Delaunay_incremental_interp_2,

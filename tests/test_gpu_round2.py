@@ -225,3 +225,46 @@ def test_native_dd_class_on_gpu(gpu, dim):
     after = np.sort([e[0] for e in t.get_error_queue()])
     assert len(before) == len(after) and np.allclose(before, after, rtol=1e-8, atol=1e-18)
     assert math.isnan(t.interp([9.0] * dim))
+
+
+def test_4d_packed_records_equal_split_records(gpu):
+    """4D walk records: the packed one-line layout (block-floating-point barycentric gradients, default) answers like the
+    split layout (fp32 gradients + separate interpolant record; packed_faces=5) -- same statuses, same simplex for
+    every query both fast passes certify, bit-identical values on the same simplex (same fp64 interpolant, same
+    operation order) -- and like the oracle; the wider filter band of the packed mantissas only sends a few more
+    queries to the exact pass."""
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(4, 3000, 81)
+    rng = np.random.default_rng(82)
+    q = rng.random((200000, 4)) * 1.04 - 0.02
+    q[:200] = pts[:200]
+    res = {}
+    for name, opt in (("packed", {}), ("split", {"packed_faces": 5})):
+        m = dl.Mesh(pts, f, sv, sn, **opt)
+        m.collect_stats(True)
+        ys, s, st = m.interp(q, return_simplex=True, return_status=True)
+        res[name] = (ys, s, st, m.stats())
+    (y1, s1, t1, st1), (y2, s2, t2, st2) = res["packed"], res["split"]
+    assert np.array_equal(t1, t2)
+    same = s1 == s2
+    assert same.mean() > 0.999
+    # the same fp64 interpolant in the same operation order -> the same bits, except for the queries only ONE layout's
+    # filter could not certify (the exact pass evaluates those in the reference's operation order)
+    bits = (y1[same] == y2[same]) | (np.isnan(y1[same]) & np.isnan(y2[same]))
+    assert bits.mean() > 0.99
+    fin = same & np.isfinite(y2)
+    assert np.array_equal(np.isnan(y1), np.isnan(y2)) and _rel(y1[fin], y2[fin]) <= REL_TOL
+    assert st1["straggler_queries"] < 0.02 * len(q) + st2["straggler_queries"]
+    om = OracleMesh(pts, f, sv, sn)
+    yo, so, sto = om.interp(q, mode=1, nthreads=8)
+    assert np.array_equal(t1, sto)
+    ok = sto == 0
+    cg, _ = om.classify(q, s1)
+    assert cg[ok].all()
+    assert _rel(y1[ok], yo[ok]) <= REL_TOL
+    # coordinates at another scale: row exponents far from 0
+    for scale in (1e-30, 3e25):
+        m = dl.Mesh(pts * scale, f, sv, sn)
+        ys, st = m.interp(q * scale, return_status=True)
+        agree = (st == sto) & ok      # (a scale that is not a power of two re-rounds the coordinates)
+        assert np.mean(st == sto) > 0.9999 and _rel(ys[agree], yo[agree]) <= 1e-10
