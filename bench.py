@@ -126,6 +126,66 @@ class ClockSampler:
         return out
 
 
+def bind_from_nvidia_smi_topo(local_rank):
+    """sysfs shows numa_node = -1 (VMs): take the GPU's "CPU Affinity" column of `nvidia-smi topo -m` instead."""
+    import re
+    import subprocess
+    try:
+        txt = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+        for line in txt.splitlines():
+            cols = [c.strip() for c in re.sub(r"\x1b\[[0-9;]*m", "", line).split("\t") if c.strip()]
+            if not cols or cols[0] != "GPU%d" % local_rank:
+                continue
+            for tok in cols[1:]:
+                if re.fullmatch(r"\d+(-\d+)?(,\d+(-\d+)?)*", tok) and ("-" in tok or "," in tok):
+                    cpus = set()
+                    for part in tok.split(","):
+                        a, _, b = part.partition("-")
+                        cpus.update(range(int(a), int(b or a) + 1))
+                    cpus &= os.sched_getaffinity(0)
+                    if not cpus:
+                        return "numa_node=-1; nvidia-smi topo affinity %s has no allowed cpus" % tok
+                    if cpus == os.sched_getaffinity(0):
+                        return "numa_node=-1; nvidia-smi topo affinity %s = every allowed cpu (single node)" % tok
+                    os.sched_setaffinity(0, cpus)
+                    return "numa_node=-1; bound to nvidia-smi topo affinity %s (%d cpus)" % (tok, len(cpus))
+            return "numa_node=-1; no CPU affinity column for GPU%d" % local_rank
+        return "numa_node=-1; GPU%d not in nvidia-smi topo" % local_rank
+    except Exception as e:  # noqa: BLE001
+        return "numa_node=-1; nvidia-smi topo unavailable (%s)" % type(e).__name__
+
+
+def raw_copy_bound(dev, hx, hy, xq, ys, steps, barrier, max_over_ranks, world, chunk_q=1 << 22):
+    """What the host <-> device DMA path alone delivers for one step's bytes: 16 B per query pinned -> device and
+    8 B per query device -> pinned, both directions at once on two streams, in the 4M-query chunks the engine's ring
+    uses, on every rank concurrently.  No kernel runs.  This is the ceiling of the end-to-end leg on this box."""
+    import torch
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    n = xq.shape[0]
+
+    def once():
+        for off in range(0, n, chunk_q):
+            end = min(n, off + chunk_q)
+            with torch.cuda.stream(s_in):
+                xq[off:end].copy_(hx[off:end], non_blocking=True)
+            with torch.cuda.stream(s_out):
+                hy[off:end].copy_(ys[off:end], non_blocking=True)
+
+    once()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        once()
+    torch.cuda.synchronize(dev)
+    dt = max_over_ranks(time.perf_counter() - t0, device=dev)
+    return {"value": world * n * steps / dt, "unit": UNIT, "ms_per_step": dt / steps * 1e3,
+            "aggregate_GBps": world * n * 24 * steps / dt / 1e9,
+            "note": "raw cudaMemcpyAsync of the step's 16 B/query in + 8 B/query out (pinned buffers, both directions "
+                    "concurrently, %dM-query chunks, all ranks at once, no kernel): the DMA ceiling of the e2e leg. "
+                    "24 B/query (fp64 in, fp64 out) is the floor of this leg; narrowing below the reference's fp64 is "
+                    "not an option" % (chunk_q >> 20)}
+
+
 def bind_to_gpu_numa_node(local_rank):
     """Pin this rank to the CPUs of the NUMA node its GPU hangs off, BEFORE the pinned staging buffers are allocated
     (first touch places them on that node): with 8 ranks on one host the end-to-end leg is bound by host memory and
@@ -137,7 +197,7 @@ def bind_to_gpu_numa_node(local_rank):
         with open("/sys/bus/pci/devices/%s/numa_node" % bus) as fh:
             node = int(fh.read().strip())
         if node < 0:
-            return "numa_node=-1 (not exposed)"
+            return bind_from_nvidia_smi_topo(local_rank)
         with open("/sys/devices/system/node/node%d/cpulist" % node) as fh:
             cpus = set()
             for part in fh.read().strip().split(","):
@@ -199,15 +259,23 @@ def run_reference(args, rank, world):
         om.interp(q, mode=0, nthreads=ncores)
     dt = time.perf_counter() - t0
     val = len(q) * args.steps / dt
+    # the reference itself is single-threaded: also time one thread on a slice, so the ratio can be read both ways
+    q1 = q[: max(2000, len(q) // (4 * ncores))]
+    t0 = time.perf_counter()
+    om.interp(q1, mode=0, nthreads=1)
+    val_1thread = len(q1) / (time.perf_counter() - t0)
     sample = ("%d of the %dM cfg2 queries per step (un-hinted exact-predicate walk from a fixed hull-adjacent "
               "face + reference-order epilogue, one query at a time per thread)" % (len(q), NQ // 1_000_000))
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(NQ), "sample_queries_per_step": len(q),
-                   "note": "reference (CGAL 4.2/Eigen/Boost) is not buildable here; CPU oracle port of its path"},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": ncores, "kind": "port", "sample": sample},
+        "config": {"workload": workload_name(NQ)},
+        "sample_queries_per_step": len(q), "threads": ncores, "value_1_thread": val_1thread,
+        "note": "reference (CGAL 4.2/Eigen/Boost) is not buildable here; CPU oracle port of its path, on all host threads "
+                "(the reference is single-threaded: value_1_thread is the like-for-like rate)",
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": ncores, "kind": "port", "sample": sample,
+                         "value_1_thread": val_1thread},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -519,6 +587,11 @@ def run_ours(args, rank, world, local_rank):
     e2e_val = world * nq * args.steps / e2e_s
     clocks = sampler.stop()   # sampled across the device-resident and the end-to-end timed regions
     e2e_ok = bool(np.array_equal(hy_np[:1000000], ys[:1000000].cpu().numpy()))
+    try:
+        raw_bound = raw_copy_bound(dev, hx, hy, xq, ys, max(2, min(args.steps, 5)), barrier, parallel.max_over_ranks, world)
+        raw_bound["e2e_fraction_of_bound"] = e2e_val / raw_bound["value"]
+    except Exception as e:  # noqa: BLE001
+        raw_bound = {"error": "%s: %s" % (type(e).__name__, e)}
 
     # ---- roofline of the dominant kernel
     peak, peak_src = load_peak()
@@ -583,7 +656,8 @@ def run_ours(args, rank, world, local_rank):
                        "host_numa_binding": numa},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": nq * 16, "d2h_bytes_per_step": nq * 8,
-                    "ms_per_step": e2e_s / args.steps * 1e3, "matches_device_path": e2e_ok},
+                    "ms_per_step": e2e_s / args.steps * 1e3, "matches_device_path": e2e_ok,
+                    "raw_copy_bound": raw_bound},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": roofline,
             "cpu_baseline": cpu,

@@ -927,6 +927,7 @@ Mesh2View view2(const dli_mesh *m) {
   v.icx = m->grid.ic[0]; v.icy = m->grid.ic[1];
   v.gx = m->grid.g[0]; v.gy = m->grid.g[1];
   v.ns = (int)m->ns; v.nh = m->nh;
+  v.nv = (int)m->nv; v.nslots = m->nslots;
   v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   v.outside_nan = m->opt.outside_nan;
   v.straggler_frac = m->h_straggler_frac;
@@ -939,6 +940,7 @@ MeshDView viewD(const dli_mesh *m) {
   v.epi = (m->d_fat && m->dim == 4 && !fat_pack4(m)) ? m->d_fat + (size_t)m->ns * FatD<4>::CHUNKS : nullptr;
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
+  v.nv = (int)m->nv; v.cells = m->grid.cells;
   v.straggler_frac = m->h_straggler_frac;
   return v;
 }

@@ -14,6 +14,31 @@
 
 namespace dli {
 
+// -DDLI_BOUNDS_CHECK: every index the kernels form into a mesh buffer is checked on the device (printf + trap, so the
+// next CUDA call fails loudly).  compute-sanitizer is not available on the build pool; scripts/bounds_check.sh builds
+// this variant and runs the small parity tests against it.  Off (the shipped build): the macro is the bare index.
+#ifdef DLI_BOUNDS_CHECK
+__device__ __noinline__ void dli_bounds_fail(long long i, long long n, int line) {
+  printf("DLI_BOUNDS_CHECK: index %lld outside [0, %lld) at dli source line %d\n", i, n, line);
+  __trap();
+}
+#define DLI_IDX(i, n) (((long long)(i) < 0 || (long long)(i) >= (long long)(n)) ? (::dli::dli_bounds_fail((long long)(i), (long long)(n), __LINE__), (i)) : (i))
+#else
+#define DLI_IDX(i, n) (i)
+#endif
+
+// DRAM fetch size of scattered record loads.  On B200 a global load that misses L2 brings in the whole 128-byte line
+// whatever it asked for (measured: 126.7 B of DRAM traffic per random 16 / 32 / 64-byte request, profiles/
+// r02_dram_granularity_ncu.txt; cudaLimitMaxL2FetchGranularity changes nothing).  The PTX prefetch-size qualifier
+// .L2::64B is what limits the fetch to the 64-byte half line (63.7 B per request in the same probe), so every gather of
+// a record of <= 64 B (2D walk records, canonical face / vertex records, start hints) carries it: on meshes larger than
+// L2 that halves the bytes a walk step moves.  -DDLI_X_NO_L2_64B: experiment knob, the plain loads.
+#ifdef DLI_X_NO_L2_64B
+#define DLI_L2_64B ""
+#else
+#define DLI_L2_64B ".L2::64B"
+#endif
+
 constexpr int kMaxProjections = 16;  // 2D outside-hull project/re-locate rounds before accepting the hull face
 
 // ---------------------------------------------------------------------------------------------
@@ -42,6 +67,8 @@ struct Mesh2View {
   double ox, oy, icx, icy;  // hint grid origin and 1/cell size
   int gx, gy;
   int ns, nh;
+  int nv;          // vertices; nslots: records in `fat` (== ns unless cell-indexed)  [index checks of DLI_BOUNDS_CHECK builds]
+  long long nslots;
   int max_steps;   // hard cap on simplices visited per query
   int fast_steps;  // fast-path cap; longer walks are re-run by the straggler/exact pass
   int outside_nan; // != 0: queries outside the hull report DLI_STATUS_OUTSIDE_NAN instead of being projected
@@ -65,6 +92,8 @@ struct MeshDView {
   double o[DLI_MAX_DIM], ic[DLI_MAX_DIM];
   int g[DLI_MAX_DIM];
   int ns;
+  int nv;            // vertices, hint cells  [index checks of DLI_BOUNDS_CHECK builds]
+  long long cells;
   int max_steps;
   int fast_steps;
   float *straggler_frac;  // as Mesh2View::straggler_frac
@@ -148,12 +177,18 @@ __device__ __forceinline__ double epilogue2_fast(double px, double py, const dou
 
 // (project_on_line, hull_edge_score: dli_refmath.h)
 
+// a start hint: 4 bytes from a table that is usually much larger than L2 -- fetch 64 bytes for it, not 128
+__device__ __forceinline__ int ldg_hint(const int32_t *p) {
+  int v;
+  asm volatile("ld.global.nc" DLI_L2_64B ".b32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
 __device__ __forceinline__ int hint2(const Mesh2View &m, double x, double y) {
   int i = (int)((x - m.ox) * m.icx);
   int j = (int)((y - m.oy) * m.icy);
   i = max(0, min(m.gx - 1, i));
   j = max(0, min(m.gy - 1, j));
-  return __ldg(m.hint + (size_t)j * m.gx + i);
+  return ldg_hint(m.hint + DLI_IDX((size_t)j * m.gx + i, (size_t)m.gx * m.gy));
 }
 
 // hint-grid cell index of a point (the start slot of cell-indexed walk records)
@@ -162,7 +197,7 @@ __device__ __forceinline__ int cell2(const Mesh2View &m, double x, double y) {
   int j = (int)((y - m.oy) * m.icy);
   i = max(0, min(m.gx - 1, i));
   j = max(0, min(m.gy - 1, j));
-  return __ldg(m.rowstart + j) + i;
+  return __ldg(m.rowstart + DLI_IDX(j, m.gy + 1)) + i;
 }
 
 struct Face2 {
@@ -172,15 +207,15 @@ struct Face2 {
 __device__ __forceinline__ Face2 load_face(const Mesh2View &m, int f) {
   Face2 r;
   int p0, p1;
-  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+  asm volatile("ld.global.nc" DLI_L2_64B ".v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r.v0), "=r"(r.v1), "=r"(r.v2), "=r"(r.n0), "=r"(r.n1), "=r"(r.n2), "=r"(p0), "=r"(p1)
-               : "l"(m.frec + 2 * (size_t)f));
+               : "l"(m.frec + 2 * (size_t)DLI_IDX(f, m.ns)));
   return r;
 }
 constexpr unsigned kPackMask = 0x1FFFFFu;
 __device__ __forceinline__ Face2 load_face_packed(const Mesh2View &m, int f) {
   unsigned long long w0, w1;
-  asm volatile("ld.global.nc.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(m.fpack + f));
+  asm volatile("ld.global.nc" DLI_L2_64B ".v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(m.fpack + DLI_IDX(f, m.ns)));
   Face2 r;
   r.v0 = (int)(w0 & kPackMask); r.v1 = (int)((w0 >> 21) & kPackMask); r.v2 = (int)(w0 >> 42);
   int n0 = (int)(w1 & kPackMask), n1 = (int)((w1 >> 21) & kPackMask), n2 = (int)(w1 >> 42);
@@ -191,7 +226,7 @@ __device__ __forceinline__ Face2 load_face_packed(const Mesh2View &m, int f) {
 }
 __device__ __forceinline__ double4 load_vert(const Mesh2View &m, int v) {
   double4 r;
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(m.vrec + v));
+  asm volatile("ld.global.nc" DLI_L2_64B ".v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(m.vrec + DLI_IDX(v, m.nv)));
   return r;
 }
 
@@ -213,7 +248,7 @@ constexpr unsigned kFatFar = 0x1FFFFEu;  // DELTA encoding: neighbour index diff
 constexpr int kFatBias = 1 << 20;        // DELTA encoding: field = neighbour - face + kFatBias
 constexpr double kFatK = 1.1920928955078125e-07;  // 2^-23: twice the fp32 unit roundoff 2^-24
 
-#define DLI_LDG256 "ld.global.nc.v8.b32"
+#define DLI_LDG256 "ld.global.nc" DLI_L2_64B ".v8.b32"
 __device__ __forceinline__ void ldg256(unsigned (&r)[8], const void *p) {
   asm volatile(DLI_LDG256 " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
@@ -269,7 +304,7 @@ __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px,
   int best = h0;
   double best_score;
   {
-    int4 r = __ldg(m.hull + h0);
+    int4 r = __ldg(m.hull + DLI_IDX(h0, m.nh));
     Face2 F = load_face(m, r.x);
     int vs[3] = {F.v0, F.v1, F.v2};
     double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
@@ -278,10 +313,10 @@ __device__ inline int canonical_visible_hull_edge(const Mesh2View &m, double px,
   for (int dir = 0; dir < 2; dir++) {
     int h = h0;
     for (int it = 0; it < m.nh; it++) {
-      int4 hr = __ldg(m.hull + h);
+      int4 hr = __ldg(m.hull + DLI_IDX(h, m.nh));
       h = dir ? hr.w : hr.z;
       if (h < 0 || h == h0) break;
-      int4 r = __ldg(m.hull + h);
+      int4 r = __ldg(m.hull + DLI_IDX(h, m.nh));
       Face2 F = load_face(m, r.x);
       int vs[3] = {F.v0, F.v1, F.v2};
       double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
@@ -363,7 +398,7 @@ __device__ inline uint8_t locate2_full(const Mesh2View &m, double &px, double &p
     status = DLI_STATUS_OUTSIDE_PROJECTED;
     if (proj >= kMaxProjections || stuck) break;  // accept the hull face (ulp-level extrapolation)
     int h = canonical_visible_hull_edge(m, px, py, exit_h, st);
-    int4 r = __ldg(m.hull + h);
+    int4 r = __ldg(m.hull + DLI_IDX(h, m.nh));
     Face2 F = load_face(m, r.x);
     int vs[3] = {F.v0, F.v1, F.v2};
     double4 P = load_vert(m, vs[(r.y + 1) % 3]), Q = load_vert(m, vs[(r.y + 2) % 3]);
@@ -408,7 +443,7 @@ __device__ __forceinline__ int face_nb(const Face2 &F, int j) { return j == 0 ? 
 // its clockwise-most face (the convention is part of the ABI contract, include/dli.h).
 __device__ inline double2 vertex_avg_gradient2(const Mesh2View &m, int f0, int v) {
   // clockwise sweep: find the start face
-  int start = f0, best_id = __ldg(m.orig + f0), f = f0;
+  int start = f0, best_id = __ldg(m.orig + DLI_IDX(f0, m.ns)), f = f0;
   bool open = false;
   for (int it = 0; it < m.max_steps; it++) {
     Face2 F = load_face(m, f);
@@ -416,7 +451,7 @@ __device__ inline double2 vertex_avg_gradient2(const Mesh2View &m, int f0, int v
     if (nb < 0) { open = true; start = f; break; }
     if (nb == f0) break;
     f = nb;
-    int id = __ldg(m.orig + f);
+    int id = __ldg(m.orig + DLI_IDX(f, m.ns));
     if (id < best_id) { best_id = id; start = f; }
   }
   // counter-clockwise sum from `start`
@@ -486,7 +521,7 @@ __device__ __forceinline__ int hintD(const MeshDView &m, const double *p) {
     i = max(0, min(m.g[a] - 1, i));
     idx = idx * m.g[a] + i;
   }
-  return __ldg(m.hint + idx);
+  return ldg_hint(m.hint + DLI_IDX(idx, m.cells));
 }
 
 template <int D>
@@ -499,7 +534,7 @@ struct SimplexD {
 template <int D>
 __device__ __forceinline__ void load_simplex_ids(const MeshDView &m, int s, SimplexD<D> &S) {
   constexpr int SS = RecD<D>::SS;
-  const int4 *r = reinterpret_cast<const int4 *>(m.srec + (size_t)s * SS);
+  const int4 *r = reinterpret_cast<const int4 *>(m.srec + (size_t)DLI_IDX(s, m.ns) * SS);
   int tmp[SS];
 #pragma unroll
   for (int i = 0; i < SS / 4; i++) {
@@ -516,7 +551,7 @@ __device__ __forceinline__ void load_simplex_verts(const MeshDView &m, SimplexD<
   constexpr int VS = RecD<D>::VS;
 #pragma unroll
   for (int i = 0; i <= D; i++) {
-    const double2 *r = reinterpret_cast<const double2 *>(m.vrec + (size_t)S.v[i] * VS);
+    const double2 *r = reinterpret_cast<const double2 *>(m.vrec + (size_t)DLI_IDX(S.v[i], m.nv) * VS);
     double tmp[VS];
 #pragma unroll
     for (int k = 0; k < VS / 2; k++) {

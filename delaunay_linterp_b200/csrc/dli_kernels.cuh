@@ -51,7 +51,7 @@ __device__ __forceinline__ void enqueue_straggler(int32_t *__restrict__ queue, u
                                                   unsigned int queue_cap, int64_t qi, int where, double *__restrict__ ys,
                                                   int32_t *__restrict__ simplex_out) {
   const unsigned int slot = atomicAdd(queue_count, 1u);
-  if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[queue_cap + slot] = where; }   // exact pass resumes there
+  if (slot < queue_cap) { queue[slot] = (int32_t)qi; queue[(size_t)queue_cap + slot] = where; }   // exact pass resumes there
   else if (ys) ys[OUT == 1 ? 2 * qi : qi] = __longlong_as_double(kOverflowBits);
   else if (simplex_out) simplex_out[qi] = kOverflowSimplex;
 }
@@ -137,7 +137,7 @@ k_interp2_fast(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__
               __stcs(ys + qi, y);
             }
           }
-          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + f));
+          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(f, m.ns)));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
           if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
           active = false;
@@ -375,9 +375,9 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
       int ci = (int)((q.x - m.ox) * m.icx), cj = (int)((q.y - m.oy) * m.icy);
       ci = max(0, min(m.gx - 1, ci));
       cj = max(0, min(m.gy - 1, cj));
-      asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(
+      asm volatile("cp.async.ca.shared.global.L2::cache_hint" DLI_L2_64B " [%0], [%1], 4, %2;" ::"r"(
                        (unsigned)__cvta_generic_to_shared(ringh + (j & (kRingSlots - 1)))),
-                   "l"(m.hint + ((size_t)cj * m.gx + ci)), "l"(pol_last)
+                   "l"(m.hint + DLI_IDX((size_t)cj * m.gx + ci, (size_t)m.gx * m.gy)), "l"(pol_last)
                    : "memory");
     }
   };
@@ -435,8 +435,8 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
     const int fp = __shfl_xor_sync(FULL, fs, 1);
     const int fe = odd ? fp : fs, fo = odd ? fs : fp;
     unsigned R1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, R2[8] = {0, 0, 0, 0, 0, 0, 0, 0}, X[8];
-    if (fe >= 0) ldg256(R1, rec + (size_t)fe * 64);
-    if (fo >= 0) ldg256(R2, rec + (size_t)fo * 64);
+    if (fe >= 0) ldg256(R1, rec + (size_t)DLI_IDX(fe, m.nslots) * 64);
+    if (fo >= 0) ldg256(R2, rec + (size_t)DLI_IDX(fo, m.nslots) * 64);
 #pragma unroll
     for (int i = 0; i < 8; i++) X[i] = __shfl_xor_sync(FULL, odd ? R1[i] : R2[i], 1);
     if (active) {
@@ -469,7 +469,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
           if (DELTA) {
             const unsigned kc = neg0 ? k0 : (neg1 ? k1 : k2);
             if (kc == kFatFar)  // neighbour too far away in index space for the 21-bit field: canonical record
-              nb = CELL ? -1 : __ldg(reinterpret_cast<const int *>(m.frec) + 8 * (size_t)f + 3 + (neg0 ? 0 : (neg1 ? 1 : 2)));
+              nb = CELL ? -1 : __ldg(reinterpret_cast<const int *>(m.frec) + 8 * (size_t)DLI_IDX(f, m.ns) + 3 + (neg0 ? 0 : (neg1 ? 1 : 2)));
           }
           if (nb < 0 || (int)steps >= m.fast_steps) give_up = true;  // hull exit / straggler
           else { from = f; f = nb; }
@@ -491,8 +491,8 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
               else __stcs(ys + qi, f0 + fma(gx, dx, gy * dy));
             }
             if (simplex_out) {
-              const int face = CELL ? __ldg(m.slot_face + f) : f;
-              __stcs(simplex_out + qi, __ldg(m.orig + face));
+              const int face = CELL ? __ldg(m.slot_face + DLI_IDX(f, m.nslots)) : f;
+              __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(face, m.ns)));
             }
             if (status_out) status_out[qi] = DLI_STATUS_OK;
             if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
@@ -503,7 +503,7 @@ k_interp2_fat(Mesh2View m, int64_t n, int per_warp, const double2 *__restrict__ 
         }
       }
       if (give_up) {
-        enqueue_straggler<OUT>(queue, queue_count, queue_cap, qi, CELL ? __ldg(m.slot_face + f) : f, ys, simplex_out);
+        enqueue_straggler<OUT>(queue, queue_count, queue_cap, qi, CELL ? __ldg(m.slot_face + DLI_IDX(f, m.nslots)) : f, ys, simplex_out);
         active = false;
       }
     }
@@ -647,7 +647,7 @@ k_interpD_fast(MeshDView m, int64_t n, int per_warp, const double *__restrict__ 
           double y = (EPI == 0) ? epilogueD_ref<D>(p, S) : epilogueD_fast<D>(p, S);
           __stcs(ys + qi, y);
         }
-        if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + s));
+        if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(s, m.ns)));
         if (status_out) status_out[qi] = DLI_STATUS_OK;
         if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
         active = false;
@@ -704,7 +704,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
       y = (EPI == 0) ? epilogueD_ref<D, true>(p, S) : epilogueD_fast<D>(p, S);
     }
     if (ys) ys[i] = y;
-    if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + s) : -1;
+    if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + DLI_IDX(s, m.ns)) : -1;
     if (status_out) status_out[i] = status;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0) *m.straggler_frac = (float)total / (float)n;
@@ -974,8 +974,14 @@ struct RingD {
   static constexpr int QBYTES = 96 * D * 8, HBYTES = 64 * 4;
   static constexpr int BYTES = QBYTES + HBYTES;
 };
+// min CTAs per SM of the packed 4D walk-record kernel: ptxas's own choice is 107 registers = 4 CTAs, and ncu showed the
+// kernel latency-bound there (DRAM 61 % busy, profiles/r02_k_interpD_fat4_packed_4cta_ncu.txt); measured on cfg4-4D with
+// 1 / 6 / 7 / 8: 14.6 / 16.3 / 12.5 / 11.1 Gq/s (80 registers at 6; 72 and 64 spill into the staging loop)
+#ifndef DLI_X_FATD4_BLOCKS
+#define DLI_X_FATD4_BLOCKS 6
+#endif
 template <int D, bool STATS, bool RING = false, bool PACK = false>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, (D == 4 && PACK) ? DLI_X_FATD4_BLOCKS : 1)
 k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
@@ -1086,14 +1092,14 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
       const int fr = __shfl_sync(FULL, fs, r);
       if (fr >= 0 && csub < F::LOADED)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + (unsigned)(r * F::SSTRIDE * 16)),
-                     "l"(m.fat + (size_t)fr * F::CHUNKS + csub)
+                     "l"(m.fat + (size_t)DLI_IDX(fr, m.ns) * F::CHUNKS + csub)
                      : "memory");
     }
     if (F::SPLIT && pqi >= 0) {
-      const uint4 *er = m.epi + (size_t)ps * F::EPI_CHUNKS;
+      const uint4 *er = m.epi + (size_t)DLI_IDX(ps, m.ns) * F::EPI_CHUNKS;
 #pragma unroll
       for (int c = 0; c < F::EPI_LOADED; c++)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(edst + (unsigned)(c * 16)), "l"(er + c) : "memory");
+        asm volatile("cp.async.cg.shared.global" DLI_L2_64B " [%0], [%1], 16;" ::"r"(edst + (unsigned)(c * 16)), "l"(er + c) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -1228,7 +1234,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
               __stcs(ys + qi, f0 + y);
             }
           }
-          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + s));
+          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(s, m.ns)));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
           if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
           active = false;

@@ -8,10 +8,12 @@
 //   insert_point(Point const&, double)          :455-493   same
 //   insert_largest_error_point() -> ErrorTuple  :498-504   same (asserts on empty queue / no callback like :499-500)
 //   get_largest_error_tuple()                   :506-508   same
-//   interp(IterT, IterT) / interp_point(Point)  :510-572   same result; evaluated through the GPU engine (n = 1)
+//   interp(IterT, IterT) / interp_point(Point)  :510-572   same result; one point at a time is answered on the host (exact walk on the
+//                                                          native triangulation from the previous result, reference-order epilogue:
+//                                                          no GPU call, ~0.3 us per call); batches go through the GPU engine
 //   get_error_queue()                           :743-746   same (ordered by decreasing error)
 //   get_all_vertices() / get_line_segments()    :806-862   same data, plain arrays
-//   gradient(Point)                             :608-642   not yet provided (SURVEY.md 8(f) "next" #1)
+//   gradient(Point)                             :608-642   same (FACE / EDGE / VERTEX averaging, NaN outside the hull); gradient_batch for n queries
 //   public data m_pTriang / m_err_pqueue / m_face_to_pqueue_handles are CGAL/Boost typed in the reference and have
 //   no counterpart here (neither library is available); m_fn is kept.
 // New:

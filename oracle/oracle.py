@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "_ref", "libdli_oracle.so")
+_LIB_PATH = os.path.join(_HERE, "_port", "libdli_oracle.so")
 
 OK, OUTSIDE_PROJECTED, OUTSIDE_NAN, STEP_LIMIT, NO_MESH, ON_EDGE, ON_VERTEX = 0, 1, 2, 3, 4, 5, 6
 
