@@ -347,6 +347,22 @@ def timed_leg(mesh, xq, ys, steps, warmup, dev, dist, world, total_queries_per_s
     return out
 
 
+def random_access_model(leg, hint_access):
+    """Secondary roofline for meshes far larger than L2: the walk kernels are bound by the RATE of random DRAM accesses
+    (profiles/r02_random_access_peak.json), one per walk step plus one for the start hint unless the start record is
+    addressed by the hint cell itself (2D cell-indexed records, dD start copies).  A model (every access counted as a
+    miss), reported next to the contract's byte roofline, not instead of it."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_random_access_peak.json")) as fh:
+            peak = float(json.load(fh)["line_fetches_per_s"])
+        acc = leg["walk_steps_per_query"] + (1.0 if hint_access else 0.0)
+        rate = acc * leg["roofline"]["queries_per_launch"] / (leg["roofline"]["avg_launch_ms"] * 1e-3)
+        return {"bound": "dram random-access rate (model: every walk step a miss)", "accesses_per_query": acc,
+                "achieved": rate, "peak": peak, "unit": "line fetches/s", "frac": rate / peak}
+    except Exception as e:  # noqa: BLE001
+        return {"error": "%s: %s" % (type(e).__name__, e)}
+
+
 def walk_stats(mesh, xq):
     import torch
     n1 = min(xq.shape[0], 4_000_000)
@@ -435,6 +451,8 @@ def extras_single_gpu(args, dev, peak):
             xq, ys = queries(nq, dim, 0.1, 0.9, seed_q), torch.empty(nq, dtype=torch.float64, device=dev)
             leg = timed_leg(mesh, xq, ys, steps, args.warmup, dev, None, 1, nq, dim, peak)
             leg.update(walk_stats(mesh, xq))
+            if dim == 4:   # 1.4 GB of records + 7 GB of start copies: every access a DRAM miss; start copies: no hint access
+                leg["roofline"]["random_access"] = random_access_model(leg, hint_access=False)
             leg["workload"] = ("cfg4: %dD, %d uniform-random vertices (seed %d) through the native dD triangulation, %dM queries "
                                "in U[0.1,0.9)^%d (seed %d)" % (dim, args.cfg4_vertices, seed_m, nq // 1_000_000, dim, seed_q))
             leg["mesh_build_s"] = t_build
@@ -496,6 +514,7 @@ def extras_cfg5(args, rank, world, local_rank, dev, dist, peak):
         dist.all_reduce(chk)
         dist.all_reduce(nan)
     leg.update(walk_stats(mesh, xq))
+    leg["roofline"]["random_access"] = random_access_model(leg, hint_access=False)   # cell-indexed records: no hint access
     leg["value_per_gpu"] = leg["value"] / world
     leg["scaling"] = "strong"
     leg["checksum_int64_bits"] = int(chk.item())

@@ -35,7 +35,8 @@ class Options(C.Structure):
         ("packed_faces", C.c_int32),
         ("prefetch_ring", C.c_int32),
         ("outside_nan", C.c_int32),
-        ("reserved", C.c_int32 * 5),
+        ("start_records", C.c_int32),
+        ("reserved", C.c_int32 * 4),
     ]
 
 

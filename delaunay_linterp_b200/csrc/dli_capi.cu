@@ -134,6 +134,8 @@ struct dli_mesh {
   int fat_enc = -1;               // neighbour fields of the 2D walk records: 0 = absolute ids, 1 = delta-encoded; -1 = not
                                   // decided yet (creating rank: from the mesh size / options; replicas and snapshots: from
                                   // header word 13, never re-derived from their own options)
+  // dD start copies (MeshDView::start_copies): d_fat has nslots = ns + cells records
+  bool startcopy = false;
   // cell-indexed walk records (2D meshes far larger than L2): d_fat has nslots = cells + extra records
   bool cellmode = false;
   int64_t nslots = 0;             // records in d_fat (== ns unless cellmode)
@@ -208,6 +210,7 @@ extern "C" void dli_options_init(dli_options *o) {
   o->packed_faces = 0;
   o->prefetch_ring = 0;
   o->outside_nan = 0;
+  o->start_records = 0;
 }
 
 extern "C" const char *dli_last_error(void) { return g_err.c_str(); }
@@ -427,6 +430,16 @@ static bool fat_pack4(const dli_mesh *m) {
   if (m->fat_enc >= 0) return m->fat_enc == 4;
   return m->ns < (1 << 24) - 1 && m->opt.packed_faces != 5;
 }
+// start copies on the creating rank (replicas / snapshots: header word 13): 4D packed records by default while the
+// copies stay below 24 GB, 3D on request (its hint table and most of its records are L2-resident: no gain there)
+constexpr int64_t kStartCopyMaxBytes = 24ll << 30;
+static bool want_startcopy(const dli_mesh *m) {
+  if (m->dim < 3 || !m->d_fat || m->ns == 0 || m->opt.start_records < 0) return false;
+  if (m->dim == 4 && !fat_pack4(m)) return false;
+  if ((m->ns + m->grid.cells) >= 0x7fffff00ll) return false;
+  if (m->opt.start_records > 0) return true;
+  return m->dim == 4 && m->grid.cells * (int64_t)FatD<4, true>::BYTES <= kStartCopyMaxBytes;
+}
 // walk records of meshes with >= 2^21-2 faces (or opt.packed_faces == 2: testing) use delta-encoded neighbours
 static bool fat_delta(const dli_mesh *m) {
   if (m->fat_enc >= 0) return m->fat_enc == 1;
@@ -509,6 +522,18 @@ static int build_fat_records(dli_mesh *m) {
     return DLI_OK;
   }
   if (!m->d_fat) return DLI_OK;
+  if (!m->startcopy && m->fat_enc < 0 && want_startcopy(m)) {   // creating rank, first build: room for the copies
+    uint4 *big = nullptr;
+    const size_t bytes = (size_t)fat_record_bytes(m) * (size_t)(m->ns + m->grid.cells);
+    if (cudaMalloc(&big, bytes) == cudaSuccess) {
+      cudaFree(m->d_fat);
+      m->d_fat = big;
+      m->startcopy = true;
+      m->nslots = m->ns + m->grid.cells;
+    } else {
+      cudaGetLastError();   // not enough memory for the copies: the mesh works without them
+    }
+  }
   unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
   CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
   if (m->dim == 2) {
@@ -523,6 +548,12 @@ static int build_fat_records(dli_mesh *m) {
     k_build_fatD<4><<<(unsigned)((m->ns + 127) / 128), 128>>>((int)m->ns, m->d_srec, m->ss, m->d_vrec, m->vs, m->d_fat, d_cnt);
   }
   CU(cudaGetLastError());
+  if (m->startcopy) {
+    const int chunks = fat_record_bytes(m) / 16;
+    const long long work = (long long)m->grid.cells * chunks;
+    k_start_copies<<<(unsigned)((work + 255) / 256), 256>>>((long long)m->grid.cells, (int)m->ns, chunks, m->d_hint, m->d_fat);
+    CU(cudaGetLastError());
+  }
   unsigned int cnt = 0;
   CU(cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost));
   CU(cudaMemset(d_cnt, 0, sizeof(unsigned int)));
@@ -941,6 +972,8 @@ MeshDView viewD(const dli_mesh *m) {
   for (int k = 0; k < DLI_MAX_DIM; k++) { v.o[k] = m->grid.o[k]; v.ic[k] = m->grid.ic[k]; v.g[k] = m->grid.g[k]; }
   v.ns = (int)m->ns; v.max_steps = m->max_steps; v.fast_steps = m->fast_steps;
   v.nv = (int)m->nv; v.cells = m->grid.cells;
+  v.start_copies = m->startcopy ? 1 : 0;
+  v.nrec = m->startcopy ? m->ns + m->grid.cells : m->ns;
   v.straggler_frac = m->h_straggler_frac;
   return v;
 }
@@ -1561,8 +1594,9 @@ extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORD
   h[10] = m->max_steps; h[11] = m->fast_steps;
   // optional buffers the replica must mirror, and how the walk records encode their neighbours:
   // word 13: 0 = no walk records, 1 = absolute neighbour ids (4D: split records), 2 = cell-indexed records,
-  // 3 = delta-encoded neighbours, 4 = 4D packed one-line records
-  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : (fat_pack4(m) ? 4 : 1))) : 0;
+  // 3 = delta-encoded neighbours, 4 = 4D packed one-line records, 5 = 4 + start copies, 6 = 1 + start copies (dD);
+  // word 15 = records in the walk-record buffer
+  h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : (fat_pack4(m) ? (m->startcopy ? 5 : 4) : (m->startcopy ? 6 : 1)))) : 0;
   h[15] = m->nslots;
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
@@ -1595,8 +1629,10 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   // (mesh_alloc_common sized d_fat from this side's options: drop it and allocate for the source's layout below)
   if (rc == DLI_OK && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
   m->cellmode = h[13] == 2;
-  m->fat_enc = h[13] == 3 ? 1 : (h[13] == 4 ? 4 : 0);
-  m->nslots = h[13] == 2 ? h[15] : m->ns;
+  m->fat_enc = h[13] == 3 ? 1 : ((h[13] == 4 || h[13] == 5) ? 4 : 0);
+  m->startcopy = h[13] == 5 || h[13] == 6;
+  m->nslots = (h[13] == 2 || m->startcopy) ? h[15] : m->ns;
+  if (m->startcopy && m->nslots != m->ns + m->grid.cells) rc = fail(DLI_ERR_ARG, "header: start-copy record count does not match ns + cells");
   if (rc == DLI_OK && m->cellmode &&
       (cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess ||
        cudaMalloc(&m->d_rowstart, sizeof(int) * ((size_t)m->grid.g[1] + 1)) != cudaSuccess))
@@ -1861,6 +1897,21 @@ extern "C" int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh 
     rc = dli_mesh_buffer_write(m, i, host.data());
   }
   fclose(fp);
+  if (rc == DLI_OK && m->ns > 0) {   // a damaged file must not become out-of-range device reads: check every index once
+    DeviceGuard guard(m->device);
+    unsigned int *d_bad = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
+    unsigned int bad = 0;
+    const long long span = std::max<long long>(std::max<long long>(m->ns, m->grid.cells), m->nh);
+    cudaError_t e = cudaMemset(d_bad, 0, sizeof(unsigned int));
+    if (e == cudaSuccess) {
+      k_validate_ids<<<(unsigned)((span + 255) / 256), 256>>>(m->ns, m->nv, m->nh, m->dim, m->ss, m->d_srec, m->grid.cells, m->d_hint,
+                                                            m->dim == 2 ? m->d_hull : nullptr, d_bad);
+      e = cudaMemcpy(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost);
+    }
+    if (e == cudaSuccess) e = cudaMemset(d_bad, 0, sizeof(unsigned int));
+    if (e != cudaSuccess) rc = fail(DLI_ERR_CUDA, std::string("dli_mesh_load: validation failed: ") + cudaGetErrorString(e));
+    else if (bad) rc = fail(DLI_ERR_ARG, "dli_mesh_load: snapshot holds out-of-range indices (damaged file)");
+  }
   if (rc != DLI_OK) { mesh_free(m); return rc; }
   *out = m;
   return DLI_OK;

@@ -28,15 +28,17 @@ __device__ __noinline__ void dli_bounds_fail(long long i, long long n, int line)
 #endif
 
 // DRAM fetch size of scattered record loads.  On B200 a global load that misses L2 brings in the whole 128-byte line
-// whatever it asked for (measured: 126.7 B of DRAM traffic per random 16 / 32 / 64-byte request, profiles/
-// r02_dram_granularity_ncu.txt; cudaLimitMaxL2FetchGranularity changes nothing).  The PTX prefetch-size qualifier
-// .L2::64B is what limits the fetch to the 64-byte half line (63.7 B per request in the same probe), so every gather of
-// a record of <= 64 B (2D walk records, canonical face / vertex records, start hints) carries it: on meshes larger than
-// L2 that halves the bytes a walk step moves.  -DDLI_X_NO_L2_64B: experiment knob, the plain loads.
-#ifdef DLI_X_NO_L2_64B
-#define DLI_L2_64B ""
-#else
+// whatever it asked for (126.7 B of DRAM traffic per random 16 / 32 / 64-byte request, profiles/r02_dram_granularity_ncu.txt;
+// cudaLimitMaxL2FetchGranularity changes nothing); the PTX prefetch-size qualifier .L2::64B limits the fetch to the
+// 64-byte half line (63.7 B per request).  MEASURED AND NOT USED: with the qualifier on every record gather and hint
+// load, cfg5 moves 41 % fewer DRAM bytes (12.8 vs 21.7 GB per 125M queries) in the SAME time (3.87 vs 3.90 ms) -- the
+// walk kernels are bound by the rate of random DRAM accesses (~47 G line fetches/s in the probe, whatever their size),
+// not by bytes -- and cfg2 gets 4 % slower (52.4 vs 54.4 Gq/s: the other half of a fetched line is often the next
+// face of the walk, Morton order).  -DDLI_X_L2_64B turns it on (scripts/build_variants.py) for experiments.
+#ifdef DLI_X_L2_64B
 #define DLI_L2_64B ".L2::64B"
+#else
+#define DLI_L2_64B ""
 #endif
 
 constexpr int kMaxProjections = 16;  // 2D outside-hull project/re-locate rounds before accepting the hull face
@@ -94,6 +96,13 @@ struct MeshDView {
   int ns;
   int nv;            // vertices, hint cells  [index checks of DLI_BOUNDS_CHECK builds]
   long long cells;
+  // start copies (4D packed records by default): `fat` holds ns canonical records followed by one COPY of the record of
+  // hint[c] per hint cell c, so a query's first record is fat[ns + cell(p)] -- one DRAM access instead of two dependent
+  // ones (the 4-byte hint, then the record it names).  The walk-record kernels run at the DRAM random-access rate on
+  // meshes larger than L2 (~47 G line fetches/s on B200, whatever their size: profiles/r02_dram_granularity_ncu.txt),
+  // so what counts is accesses per query.  A record index >= ns is a copy; its simplex is hint[index - ns].
+  int start_copies;
+  long long nrec;    // records in `fat`: ns, or ns + cells with start copies
   int max_steps;
   int fast_steps;
   float *straggler_frac;  // as Mesh2View::straggler_frac
@@ -177,7 +186,7 @@ __device__ __forceinline__ double epilogue2_fast(double px, double py, const dou
 
 // (project_on_line, hull_edge_score: dli_refmath.h)
 
-// a start hint: 4 bytes from a table that is usually much larger than L2 -- fetch 64 bytes for it, not 128
+// a start hint (one 4-byte entry of the hint grid)
 __device__ __forceinline__ int ldg_hint(const int32_t *p) {
   int v;
   asm volatile("ld.global.nc" DLI_L2_64B ".b32 %0, [%1];" : "=r"(v) : "l"(p));
@@ -522,6 +531,24 @@ __device__ __forceinline__ int hintD(const MeshDView &m, const double *p) {
     idx = idx * m.g[a] + i;
   }
   return ldg_hint(m.hint + DLI_IDX(idx, m.cells));
+}
+
+// first record of a query's walk: the hinted simplex, or (start copies) the copy of its record that lives in the hint cell
+template <int D>
+__device__ __forceinline__ int startD(const MeshDView &m, const double *p) {
+  size_t idx = 0;
+#pragma unroll
+  for (int a = D - 1; a >= 0; a--) {
+    int i = (int)((p[a] - m.o[a]) * m.ic[a]);
+    i = max(0, min(m.g[a] - 1, i));
+    idx = idx * m.g[a] + i;
+  }
+  if (m.start_copies) return m.ns + (int)idx;
+  return ldg_hint(m.hint + DLI_IDX(idx, m.cells));
+}
+// simplex of a record index
+__device__ __forceinline__ int record_simplex(const MeshDView &m, int r) {
+  return r >= m.ns ? ldg_hint(m.hint + DLI_IDX(r - m.ns, m.cells)) : r;
 }
 
 template <int D>

@@ -515,6 +515,9 @@ int32_t dli_di2_insert(dli_di2 *d, double x, double y, double f) {
 int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f, int spatial_sort, int use_gpu) {
   DLI_GUARD_BEGIN
   if (!d || n < 0 || (n > 0 && (!xy || !f))) return DLI_ERR_ARG;
+  // every coordinate is checked BEFORE the first insertion: a rejected call leaves the triangulation and its queue untouched
+  for (int64_t i = 0; i < 2 * n; i++)
+    if (!std::isfinite(xy[i])) return DLI_ERR_ARG;
   d->need_full = true;
   std::vector<int64_t> order((size_t)n);
   for (int64_t i = 0; i < n; i++) order[i] = i;
@@ -532,7 +535,6 @@ int dli_di2_insert_many(dli_di2 *d, int64_t n, const double *xy, const double *f
   d->fn = nullptr;  // build the triangulation first, then the queue in one batch
   for (int64_t k = 0; k < n; k++) {
     int64_t i = order[k];
-    if (!(std::isfinite(xy[2 * i]) && std::isfinite(xy[2 * i + 1]))) { d->fn = fn; return DLI_ERR_ARG; }
     d->insert(xy[2 * i], xy[2 * i + 1], f[i]);
   }
   d->fn = fn;

@@ -960,6 +960,15 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
   }
 }
 
+// start copies: record ns + c = a copy of the record of hint[c], 16-byte chunk per thread (MeshDView::start_copies)
+__global__ void k_start_copies(long long cells, int ns, int chunks, const int32_t *__restrict__ hint, uint4 *__restrict__ fat) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= cells * chunks) return;
+  const long long c = t / chunks;
+  const int k = (int)(t % chunks);
+  fat[((size_t)ns + (size_t)c) * chunks + k] = fat[(size_t)hint[c] * chunks + k];
+}
+
 // dD fast pass on walk records.  Lane state machine as k_interpD_fast; per iteration the warp stages the 32 records
 // of this step into shared memory with coalesced cp.async (FatD<D>::LPR lanes x 16 B per record, one or two
 // 128-byte lines per record instead of D+2 scattered gathers), then every lane reads its own record with LDS.128.
@@ -1039,9 +1048,9 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
     double q0[D], q1[D];
     load_q(0, q0); load_q(1, q1); load_q(2, hq);
     store_q(0, q0); store_q(1, q1); store_q(2, hq);
-    ringh[lane] = hintD<D>(m, q0);
-    ringh[32 + lane] = hintD<D>(m, q1);
-    hh = hintD<D>(m, hq);
+    ringh[lane] = startD<D>(m, q0);
+    ringh[32 + lane] = startD<D>(m, q1);
+    hh = startD<D>(m, hq);
     load_q(3, hq);
     __syncwarp();
   }
@@ -1054,7 +1063,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
         // (all ring reads of block blk - 1 were consumed by the previous iterations' arithmetic)
         ringh[((blk + 1) & 1) * 32 + lane] = hh;                 // hints of block blk + 1
         store_q(b3 == 0 ? 2 : b3 - 1, hq);                       // queries of block blk + 2  ((blk + 2) % 3 == (b3 + 2) % 3)
-        hh = hintD<D>(m, hq);                                    // hint of block blk + 2: in flight until the next transition
+        hh = startD<D>(m, hq);                                    // hint of block blk + 2: in flight until the next transition
         load_q(blk + 3, hq);                                     // queries of block blk + 3: likewise
         __syncwarp();
       }
@@ -1073,7 +1082,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
         } else {
 #pragma unroll
           for (int k = 0; k < D; k++) p[k] = __ldcs(xs + idx * D + k);
-          s = hintD<D>(m, p);
+          s = startD<D>(m, p);
         }
         qi = idx;
         from = -1;
@@ -1092,7 +1101,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
       const int fr = __shfl_sync(FULL, fs, r);
       if (fr >= 0 && csub < F::LOADED)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + (unsigned)(r * F::SSTRIDE * 16)),
-                     "l"(m.fat + (size_t)DLI_IDX(fr, m.ns) * F::CHUNKS + csub)
+                     "l"(m.fat + (size_t)DLI_IDX(fr, m.nrec) * F::CHUNKS + csub)
                      : "memory");
     }
     if (F::SPLIT && pqi >= 0) {
@@ -1234,7 +1243,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
               __stcs(ys + qi, f0 + y);
             }
           }
-          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(s, m.ns)));
+          if (simplex_out) __stcs(simplex_out + qi, __ldg(m.orig + DLI_IDX(record_simplex(m, s), m.ns)));
           if (status_out) status_out[qi] = DLI_STATUS_OK;
           if (STATS) { st.steps += steps; st.max_steps = max(st.max_steps, steps); }
           active = false;
@@ -1243,7 +1252,7 @@ k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ x
         }
       }
       if (give_up) {
-        enqueue_straggler<0>(queue, queue_count, queue_cap, qi, s, ys, simplex_out);
+        enqueue_straggler<0>(queue, queue_count, queue_cap, qi, record_simplex(m, s), ys, simplex_out);
         active = false;
       }
     }
@@ -1551,6 +1560,30 @@ __global__ void k_error_finish(int64_t n, const int32_t *__restrict__ item_verts
     np++;
   }
   err[i] = dli_simplex_error<D>(np, w, phi[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Snapshot validation (dli_mesh_load): every index of the canonical records and of the hint grid in range.  The walk
+// records are derived data; their neighbour fields are checked against the same limits where they are absolute ids.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_validate_ids(long long ns, long long nv, long long nh, int dim, int ss, const int32_t *__restrict__ srec,
+                               long long cells, const int32_t *__restrict__ hint, const int4 *__restrict__ hull,
+                               unsigned int *__restrict__ bad) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool wrong = false;
+  if (t < ns) {
+    for (int k = 0; k <= dim; k++) {
+      const int v = srec[t * ss + k], nb = srec[t * ss + dim + 1 + k];
+      wrong |= v < 0 || v >= nv;
+      wrong |= nb >= ns || (dim == 2 ? nb < -nh : nb < -1);      // 2D: ~hull edge index; dD: -1
+    }
+  }
+  if (t < cells) wrong |= hint[t] < 0 || hint[t] >= ns;
+  if (hull && t < nh) {
+    const int4 h = hull[t];
+    wrong |= h.x < 0 || h.x >= ns || h.y < 0 || h.y > 2 || h.z < -1 || h.z >= nh || h.w < -1 || h.w >= nh;
+  }
+  if (wrong) atomicAdd(bad, 1u);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -17,7 +17,7 @@ def _is_torch_tensor(x):
 
 
 def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, epilogue=0,
-                  threads_per_block=0, queries_per_warp=0, packed_faces=0, prefetch_ring=0, outside_nan=0):
+                  threads_per_block=0, queries_per_warp=0, packed_faces=0, prefetch_ring=0, outside_nan=0, start_records=0):
     o = Options()
     lib().dli_options_init(C.byref(o))
     o.device = int(device)
@@ -29,6 +29,7 @@ def _make_options(device=-1, hint_cells_per_simplex=0.0, max_walk_steps=0, epilo
     o.packed_faces = int(packed_faces)
     o.prefetch_ring = int(prefetch_ring)
     o.outside_nan = int(outside_nan)
+    o.start_records = int(start_records)
     return o
 
 

@@ -96,7 +96,11 @@ typedef struct dli_options {
                                      src/delaunay_2_interp.h:530-545; default), 1 = they report DLI_STATUS_OUTSIDE_NAN with a
                                      quiet NaN like the dD class (src/delaunay_d_interp.h:1005-1008; what
                                      Delaunay_incremental_interp_d(2) needs).  dD meshes always report NaN. */
-  int32_t reserved[5];
+  int32_t start_records;          /* dD walk records: 0 = default: 4D meshes on packed records keep, behind the records, one COPY of the
+                                     hinted simplex's record per hint cell, so that a query starts with ONE memory access
+                                     (the record in its cell) instead of two dependent ones (hint, then record) -- costs
+                                     128 B per hint cell (auto only while that stays below 24 GB); -1 = never; 1 = also in 3D (tests) */
+  int32_t reserved[4];
 } dli_options;
 
 /* fills *opt with the defaults */

@@ -244,7 +244,7 @@ def test_degenerate_lattice_batches(gpu, dim):
     # axis-aligned edges through vertex 0 of a walk record itself (closed-face test o >= e with both products exact
     # zeros); the ones on cell diagonals (18.75 %) need the exact predicate.  dD: every on-facet query takes the exact pass.
     need = 0.15 if dim == 2 else 0.5
-    assert stats["straggler_queries"] > need * nq and stats["exact_fallbacks"] > need * nq    # really the exact pass
+    assert stats["straggler_queries"] > need * nq and stats["exact_fallbacks"] > 0.6 * need * nq    # really the exact pass
     m2 = dl.Mesh(c, f, sv, None, epilogue="reference")                                         # reference-order engine
     y2 = m2.interp(xq)
     assert float(((ys - y2).abs() / y2.abs().clamp_min(1e-300)).max().item()) <= REL_TOL

@@ -268,3 +268,38 @@ def test_4d_packed_records_equal_split_records(gpu):
         ys, st = m.interp(q * scale, return_status=True)
         agree = (st == sto) & ok      # (a scale that is not a power of two re-rounds the coordinates)
         assert np.mean(st == sto) > 0.9999 and _rel(ys[agree], yo[agree]) <= 1e-10
+
+
+@pytest.mark.parametrize("dim,nv", [(3, 6000), (4, 2500)])
+def test_start_copies_equal_hinted_start(gpu, dim, nv):
+    """dD start copies (a copy of the hinted simplex's record in every hint cell: the first record of a walk costs one
+    memory access instead of hint + record; default in 4D): the same walks, so the same simplices, statuses and bits as
+    with the hint table -- except where the second step's facet test against the facet the walk came through is
+    uncertain (a copy does not know its own id), which only moves that query to the exact pass."""
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(dim, nv, 90 + dim)
+    rng = np.random.default_rng(91)
+    q = rng.random((300000, dim)) * 1.04 - 0.02
+    q[:300] = pts[:300]
+    on = dl.Mesh(pts, f, sv, sn, start_records=1)
+    off = dl.Mesh(pts, f, sv, sn, start_records=-1)
+    assert on.device_bytes > off.device_bytes
+    y1, s1, t1 = on.interp(q, return_simplex=True, return_status=True)
+    y0, s0, t0 = off.interp(q, return_simplex=True, return_status=True)
+    assert np.array_equal(t1, t0)
+    same = s1 == s0
+    assert same.mean() > 0.999
+    bits = (y1[same] == y0[same]) | (np.isnan(y1[same]) & np.isnan(y0[same]))
+    assert bits.mean() > 0.999
+    om = OracleMesh(pts, f, sv, sn)
+    yo, so, sto = om.interp(q, mode=1, nthreads=8)
+    ok = sto == 0
+    assert np.array_equal(t1, sto) and _rel(y1[ok], yo[ok]) <= REL_TOL
+    cg, _ = om.classify(q, s1)
+    assert cg[ok].all()
+    # locate and new values go through the copies too
+    s2, t2 = on.locate(q, return_status=True)
+    assert np.array_equal(t2, t1) and np.array_equal(s2 >= 0, s1 >= 0)
+    on.set_values(2.0 * f + 1.0)
+    y3 = on.interp(q)
+    assert _rel(y3[ok], 2.0 * yo[ok] + 1.0) <= 1e-11

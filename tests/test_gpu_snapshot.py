@@ -7,7 +7,8 @@ import helpers
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("dim,opts", [(2, {}), (2, {"epilogue": "reference"}), (2, {"packed_faces": 2}), (2, {"packed_faces": 3}), (3, {}), (4, {})])
+@pytest.mark.parametrize("dim,opts", [(2, {}), (2, {"epilogue": "reference"}), (2, {"packed_faces": 2}), (2, {"packed_faces": 3}), (3, {}), (4, {}),
+                                      (3, {"start_records": 1}), (4, {"start_records": -1}), (4, {"packed_faces": 5})])
 def test_save_load_roundtrip(gpu, tmp_path, dim, opts):
     import delaunay_linterp_b200 as dl
     pts, f, sv, sn = helpers.random_mesh(dim, 3000 if dim < 4 else 600, 40 + dim)
