@@ -133,7 +133,7 @@ def bind_from_nvidia_smi_topo(local_rank):
     try:
         txt = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
         for line in txt.splitlines():
-            cols = [c.strip() for c in re.sub(r"\x1b\[[0-9;]*m", "", line).split("\t") if c.strip()]
+            cols = re.sub(r"\x1b\[[0-9;]*m", "", line).split()
             if not cols or cols[0] != "GPU%d" % local_rank:
                 continue
             for tok in cols[1:]:
