@@ -118,6 +118,7 @@ struct dli_mesh {
   std::vector<int32_t> h_inv;
   std::vector<double> h_xy;
   int64_t cap_v = 0, cap_s = 0;
+  int64_t cap_fat = 0;               // dD: walk records d_fat has room for (>= cap_s; the start copies leave room behind ns)
   int32_t cap_h = 0;
   int64_t n_updates = 0;
   unsigned char *d_upd = nullptr;   // grow-only device scratch of dli_mesh_update
@@ -675,9 +676,9 @@ extern "C" int dli_mesh_create(int dim, int64_t nv, const double *coords, const 
       }
     }
     for (auto &h : hull) h.x = inv[(size_t)h.x];
-    if (d == 2 && ns > 0 && ns < (1 << 21) - 2) {   // what dli_mesh_update needs later
+    if ((d == 2 && ns > 0 && ns < (1 << 21) - 2) || (d > 2 && ns > 0)) {   // what dli_mesh_update needs later
       m->h_inv = inv;
-      m->h_xy.assign(coords, coords + (size_t)nv * 2);
+      m->h_xy.assign(coords, coords + (size_t)nv * d);
     }
     cudaError_t e = cudaMemcpy(m->d_vrec, vrec.data(), sizeof(double) * vrec.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(m->d_srec, srec.data(), sizeof(int32_t) * srec.size(), cudaMemcpyHostToDevice);
@@ -725,6 +726,168 @@ static cudaError_t grow_buffer(T *&p, size_t keep_bytes, size_t new_bytes) {
   return cudaSuccess;
 }
 
+// dD (3D, 4D packed records) form of dli_mesh_update: same contract, no hull table, no packed faces.  The start copies
+// (MeshDView::start_copies) are dropped by the first patch -- their region starts at record ns, which moves -- and come
+// back with the next full flatten; the start-hint grid is kept, as in 2D.
+static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coords, const double *new_f, int64_t n_fchg,
+                          const int32_t *fchg_ids, const double *fchg_vals, int64_t ns_total, int64_t n_dirty,
+                          const int32_t *dirty_ids, const int32_t *dirty_sv, const int32_t *dirty_sn) {
+  const int d = m->dim, k = d + 1;
+  const int64_t nv0 = m->nv, ns0 = m->ns;
+  if (ns0 == 0 || m->h_inv.empty() || m->h_sv.empty() || m->h_xy.empty())
+    return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: mesh cannot be patched (replica or empty)");
+  if (d == 4 && m->d_fat && !fat_pack4(m))
+    return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: 4D split walk records cannot be patched");
+  if (d == 4 && ns_total >= (1 << 24) - 1)
+    return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: ids no longer fit the packed records");
+  for (int64_t v = 0; v < nv_total - nv0; v++)
+    for (int c = 0; c < d; c++) {
+      const double x = new_coords[d * v + c], lo = m->grid.o[c], hi = lo + m->grid.cell[c] * m->grid.g[c];
+      if (!(x >= lo && x <= hi)) return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: new vertex outside the start-hint grid");
+    }
+  {
+    int64_t appended = 0;
+    std::vector<uint8_t> seen((size_t)(ns_total - ns0), 0);
+    for (int64_t i = 0; i < n_dirty; i++) {
+      const int32_t id = dirty_ids[i];
+      if (id < 0 || id >= ns_total) return fail(DLI_ERR_MESH, "dli_mesh_update: simplex id out of range");
+      if (id >= ns0) {
+        if (seen[(size_t)(id - ns0)]) return fail(DLI_ERR_MESH, "dli_mesh_update: simplex id listed twice");
+        seen[(size_t)(id - ns0)] = 1;
+        appended++;
+      }
+      for (int j = 0; j < k; j++) {
+        if (dirty_sv[k * i + j] < 0 || dirty_sv[k * i + j] >= nv_total) return fail(DLI_ERR_MESH, "dli_mesh_update: vertex index out of range");
+        if (dirty_sn[k * i + j] >= ns_total) return fail(DLI_ERR_MESH, "dli_mesh_update: neighbour index out of range");
+      }
+    }
+    if (appended != ns_total - ns0) return fail(DLI_ERR_MESH, "dli_mesh_update: every new simplex id must be listed");
+    for (int64_t i = 0; i < n_fchg; i++)
+      if (fchg_ids[i] < 0 || fchg_ids[i] >= nv0) return fail(DLI_ERR_MESH, "dli_mesh_update: value-change vertex out of range");
+  }
+  DeviceGuard guard(m->device);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_update: cannot select device");
+  // ---- orientation-canonical rows (checked first, then applied)
+  auto X = [&](int32_t v, int c) { return v < nv0 ? m->h_xy[(size_t)d * v + c] : new_coords[(size_t)d * (v - nv0) + c]; };
+  std::vector<uint8_t> flip((size_t)n_dirty, 0);
+  for (int64_t i = 0; i < n_dirty; i++) {
+    double pts[(DLI_MAX_DIM + 1) * DLI_MAX_DIM];
+    for (int j = 0; j < k; j++)
+      for (int c = 0; c < d; c++) pts[j * d + c] = X(dirty_sv[k * i + j], c);
+    const int o = orient_host(d, pts);
+    if (o == 0) return fail(DLI_ERR_MESH, "dli_mesh_update: degenerate simplex (zero volume)");
+    flip[(size_t)i] = o < 0;
+  }
+  m->h_xy.insert(m->h_xy.end(), new_coords, new_coords + (size_t)(nv_total - nv0) * d);
+  m->h_sv.resize((size_t)ns_total * k, 0);
+  m->h_sn.resize((size_t)ns_total * k, -1);
+  auto dev_index = [&](int64_t s) -> int32_t { return s < ns0 ? m->h_inv[(size_t)s] : (int32_t)s; };
+  const int ss = m->ss, vs = m->vs;
+  std::vector<int32_t> idx((size_t)n_dirty), rows((size_t)n_dirty * ss, 0);
+  for (int64_t i = 0; i < n_dirty; i++) {
+    const int64_t sid = dirty_ids[i];
+    int32_t v[DLI_MAX_DIM + 1], nb[DLI_MAX_DIM + 1];
+    for (int j = 0; j < k; j++) { v[j] = dirty_sv[k * i + j]; nb[j] = dirty_sn[k * i + j] < 0 ? -1 : dirty_sn[k * i + j]; }
+    if (flip[(size_t)i]) { std::swap(v[0], v[1]); std::swap(nb[0], nb[1]); }
+    idx[(size_t)i] = dev_index(sid);
+    for (int j = 0; j < k; j++) {
+      m->h_sv[(size_t)sid * k + j] = v[j];
+      m->h_sn[(size_t)sid * k + j] = nb[j];
+      rows[(size_t)i * ss + j] = v[j];
+      rows[(size_t)i * ss + k + j] = nb[j] >= 0 ? dev_index(nb[j]) : -1;
+    }
+  }
+  // ---- capacity
+  cudaError_t e = cudaDeviceSynchronize();
+  const size_t rec = m->d_fat ? (size_t)fat_record_bytes(m) : 0;
+  if (m->cap_fat == 0) m->cap_fat = m->startcopy ? m->nslots : m->cap_s;
+  if (m->startcopy) { m->startcopy = false; m->nslots = ns0; }   // (the region behind the records becomes spare capacity)
+  if (e == cudaSuccess && nv_total > m->cap_v) {
+    const int64_t cap = nv_total + nv_total / 2 + 1024;
+    e = grow_buffer(m->d_vrec, sizeof(double) * (size_t)nv0 * vs, sizeof(double) * (size_t)cap * vs);
+    if (e == cudaSuccess) m->cap_v = cap;
+  }
+  if (e == cudaSuccess && ns_total > m->cap_s) {
+    const int64_t cap = ns_total + ns_total / 2 + 1024;
+    e = grow_buffer(m->d_srec, sizeof(int32_t) * (size_t)ns0 * ss, sizeof(int32_t) * (size_t)cap * ss);
+    if (e == cudaSuccess) e = grow_buffer(m->d_orig, sizeof(int32_t) * (size_t)ns0, sizeof(int32_t) * (size_t)cap);
+    if (e == cudaSuccess) m->cap_s = cap;
+  }
+  if (e == cudaSuccess && m->d_fat && ns_total > m->cap_fat) {
+    const int64_t cap = ns_total + ns_total / 2 + 1024;
+    e = grow_buffer(m->d_fat, rec * (size_t)ns0, rec * (size_t)cap);
+    if (e == cudaSuccess) m->cap_fat = cap;
+  }
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
+  // ---- upload (one scratch buffer) + rebuild the walk records of the listed simplices
+  const int64_t nnew = nv_total - nv0;
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t o_idx = 0, o_ids = al(o_idx + sizeof(int32_t) * (size_t)n_dirty), o_rows = al(o_ids + sizeof(int32_t) * (size_t)n_dirty),
+               o_vid = al(o_rows + sizeof(int32_t) * (size_t)ss * (size_t)n_dirty), o_val = al(o_vid + sizeof(int32_t) * (size_t)n_fchg),
+               o_new = al(o_val + sizeof(double) * (size_t)n_fchg), o_cnt = al(o_new + sizeof(double) * (size_t)vs * (size_t)nnew),
+               total = o_cnt + 256;
+  if (total > m->upd_cap) {
+    cudaFree(m->d_upd); m->d_upd = nullptr; m->upd_cap = 0;
+    e = cudaMalloc(&m->d_upd, total * 2);
+    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: scratch allocation failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
+    m->upd_cap = total * 2;
+  }
+  std::vector<unsigned char> stage(total, 0);
+  memcpy(stage.data() + o_idx, idx.data(), sizeof(int32_t) * (size_t)n_dirty);
+  memcpy(stage.data() + o_ids, dirty_ids, sizeof(int32_t) * (size_t)n_dirty);
+  memcpy(stage.data() + o_rows, rows.data(), sizeof(int32_t) * (size_t)ss * (size_t)n_dirty);
+  if (n_fchg > 0) {
+    memcpy(stage.data() + o_vid, fchg_ids, sizeof(int32_t) * (size_t)n_fchg);
+    memcpy(stage.data() + o_val, fchg_vals, sizeof(double) * (size_t)n_fchg);
+  }
+  {
+    double *vr = reinterpret_cast<double *>(stage.data() + o_new);
+    for (int64_t v = 0; v < nnew; v++) {
+      for (int c = 0; c < d; c++) vr[(size_t)vs * v + c] = new_coords[(size_t)d * v + c];
+      vr[(size_t)vs * v + d] = new_f[v];
+    }
+  }
+  unsigned int cnt = 0;
+  e = cudaMemcpy(m->d_upd, stage.data(), total, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && nnew > 0)
+    e = cudaMemcpyAsync(m->d_vrec + (size_t)nv0 * vs, m->d_upd + o_new, sizeof(double) * (size_t)vs * (size_t)nnew, cudaMemcpyDeviceToDevice, 0);
+  if (e == cudaSuccess && n_fchg > 0)
+    k_update_values_d<<<(unsigned)((n_fchg + 127) / 128), 128>>>((int)n_fchg, reinterpret_cast<const int32_t *>(m->d_upd + o_vid),
+                                                                 reinterpret_cast<const double *>(m->d_upd + o_val), m->d_vrec, vs, d);
+  if (e == cudaSuccess && n_dirty > 0) {
+    const unsigned gb = (unsigned)((n_dirty + 127) / 128);
+    const int32_t *d_idx = reinterpret_cast<const int32_t *>(m->d_upd + o_idx);
+    unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_upd + o_cnt);
+    k_update_simplices_d<<<gb, 128>>>((int)n_dirty, d_idx, reinterpret_cast<const int32_t *>(m->d_upd + o_rows), ss,
+                                      reinterpret_cast<const int32_t *>(m->d_upd + o_ids), m->d_srec, m->d_orig);
+    if (m->d_fat) {
+      const unsigned cb = (unsigned)((ns_total + 255) / 256);
+      if (d == 3) {
+        k_build_fatD<3><<<gb, 128>>>((int)ns_total, m->d_srec, ss, m->d_vrec, vs, m->d_fat, d_cnt + 1, d_idx, (int)n_dirty);
+        k_count_slow_d<3, false><<<cb, 256>>>((int)ns_total, m->d_fat, d_cnt);
+      } else {
+        k_build_fatD<4, true><<<gb, 128>>>((int)ns_total, m->d_srec, ss, m->d_vrec, vs, m->d_fat, d_cnt + 1, d_idx, (int)n_dirty);
+        k_count_slow_d<4, true><<<cb, 256>>>((int)ns_total, m->d_fat, d_cnt);
+      }
+    }
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost);
+  }
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
+  m->h_inv.resize((size_t)ns_total);
+  for (int64_t s2 = ns0; s2 < ns_total; s2++) m->h_inv[(size_t)s2] = (int32_t)s2;
+  m->nv = nv_total; m->ns = ns_total; m->nslots = ns_total;
+  if (m->d_fat && n_dirty > 0) m->n_slow_faces = cnt;
+  if (!(m->opt.max_walk_steps > 0)) m->max_steps = (int)std::min<int64_t>(m->ns + 16, 0x7fffffff);
+  {
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (m->items_ready) { cudaFree(m->d_item_verts); m->d_item_verts = nullptr; m->items_ready = false; }
+  }
+  m->n_updates++;
+  return DLI_OK;
+}
+
 extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_coords, const double *new_f,
                                int64_t n_fchg, const int32_t *fchg_ids, const double *fchg_vals, int64_t ns_total,
                                int64_t n_dirty, const int32_t *dirty_ids, const int32_t *dirty_sv, const int32_t *dirty_sn) {
@@ -736,6 +899,8 @@ extern "C" int dli_mesh_update(dli_mesh *m, int64_t nv_total, const double *new_
   if ((nv_total > nv0 && (!new_coords || !new_f)) || (n_fchg > 0 && (!fchg_ids || !fchg_vals)) ||
       (n_dirty > 0 && (!dirty_ids || !dirty_sv || !dirty_sn)))
     return fail(DLI_ERR_ARG, "dli_mesh_update: NULL array");
+  if (m->dim > 2)
+    return mesh_update_dd(m, nv_total, new_coords, new_f, n_fchg, fchg_ids, fchg_vals, ns_total, n_dirty, dirty_ids, dirty_sv, dirty_sn);
   // ---- can this mesh be patched?
   if (m->dim != 2 || m->cellmode || ns0 == 0 || m->h_inv.empty() || m->h_sv.empty())
     return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: mesh cannot be patched (not 2D, replica, empty or cell-indexed records)");

@@ -202,6 +202,20 @@ struct HostMeshD {
   int sphere_sign = 0;     // sign of insphere_raw for a point inside a positively oriented simplex
   uint32_t rng = 0x9e3779b9u;
   std::vector<int> new_sx, removed_sx;   // finite simplices created / removed by the last insertion
+  // Stable compact ids of the finite simplices (what the device mesh and simplex_out use).  An insertion hands the ids of
+  // the finite simplices it removes to the ones it creates and appends the rest, so ids change only inside the cavity
+  // and the id space stays 0 .. n_finite-1 -- unless an insertion removes more finite simplices than it creates (possible
+  // in 3D / 4D: a large cavity with few boundary facets): then fid_compact drops and the next flatten renumbers.
+  std::vector<int32_t> fid, free_fid;
+  int32_t next_fid = 0;
+  bool fid_compact = true;
+  void renumber() {
+    int32_t c = 0;
+    for (size_t s = 0; s < sx.size(); s++) fid[s] = (alive[s] && !is_inf((int)s)) ? c++ : -1;
+    next_fid = c;
+    free_fid.clear();
+    fid_compact = true;
+  }
   // scratch
   std::vector<int> cavity, stack, tested, created;
   std::vector<RidgeEntry> table;
@@ -218,8 +232,9 @@ struct HostMeshD {
   int new_simplex() {
     int id;
     if (!freelist.empty()) { id = freelist.back(); freelist.pop_back(); }
-    else { id = (int)sx.size(); sx.push_back(Sx()); alive.push_back(0); mark.push_back(0); gen.push_back(0); }
+    else { id = (int)sx.size(); sx.push_back(Sx()); alive.push_back(0); mark.push_back(0); gen.push_back(0); fid.push_back(-1); }
     alive[id] = 1;
+    fid[id] = -1;
     return id;
   }
   // orientation of the simplex `s` with the vertex in slot k replaced by the point p (k < 0: nothing replaced)
@@ -377,11 +392,16 @@ struct HostMeshD {
       mark[c] = 0;
       alive[c] = 0;
       gen[c]++;
-      if (!is_inf(c)) { removed_sx.push_back(c); n_finite--; }
+      if (!is_inf(c)) { removed_sx.push_back(c); n_finite--; free_fid.push_back(fid[c]); fid[c] = -1; }
       freelist.push_back(c);
     }
     for (int id : created)
-      if (!is_inf(id)) { new_sx.push_back(id); n_finite++; last = id; }
+      if (!is_inf(id)) {
+        new_sx.push_back(id); n_finite++; last = id;
+        if (free_fid.empty()) fid[id] = next_fid++;
+        else { fid[id] = free_fid.back(); free_fid.pop_back(); }
+      }
+    if (!free_fid.empty()) fid_compact = false;   // fewer created than removed: holes in the id space
   }
 
   // does the point p leave the affine hull of the basis?  (exact: some (k x k) minor of the differences is non-zero,
@@ -434,6 +454,7 @@ struct HostMeshD {
     n_finite = 1;
     last = t0;
     new_sx.push_back(t0);
+    fid[t0] = next_fid++;
   }
 
   // returns the vertex id; *is_new = false when the point already exists (value overwritten).
@@ -529,10 +550,15 @@ struct dli_dd {
   bool dirty = true;
   dli_options opt;
   bool have_opt = false;
-  int64_t n_full = 0;
-  // host side of small batches (dli_host_small.h): compact ids of the finite simplices (lazily), last simplex found
-  std::vector<int32_t> id_cache;
-  bool id_valid = false;
+  int64_t n_full = 0, n_patch = 0;
+  // incremental device update (dli_mesh_update; the reference's dirty list is p_modified_simplices,
+  // modified_cgal/Convex_hull_d.h:1172-1178, consumed at src/delaunay_d_interp.h:939-965): simplices created since the
+  // last sync, vertices whose value was overwritten, vertices the device mesh already holds
+  std::vector<int> pend_new, pend_values;
+  int64_t nv_synced = 0;
+  bool need_full = true;
+  int64_t patched_since_full = 0, simplices_at_full = 0;
+  // host side of small batches (dli_host_small.h): last simplex found
   int host_last = -1;
 
   // the dD class answers NaN outside the hull in every dimension (src/delaunay_d_interp.h:1005-1008); the 2D engine
@@ -604,6 +630,11 @@ struct dli_dd {
     bool is_new;
     const int v = hm.insert(x, f, &is_new, hint);
     dirty = true;
+    if (mesh && !need_full) {
+      pend_new.insert(pend_new.end(), hm.new_sx.begin(), hm.new_sx.end());
+      if (!is_new) pend_values.push_back(v);
+      if (!hm.fid_compact) need_full = true;
+    }
     if (fn && hm.cur_dim == hm.D) {
       for (int r : hm.removed_sx) drop_entries(r);
       if (nent.size() < hm.sx.size()) nent.resize(hm.sx.size(), 0);
@@ -625,10 +656,13 @@ struct dli_dd {
     const int D = hm.D, k = D + 1;
     if (coords) memcpy(coords, hm.X.data(), sizeof(double) * hm.X.size());
     if (hm.cur_dim < D || !(sv || sn || handle)) return;
+    // ids: the stable compact ids when they are compact (callers that own the mesh renumber first), else slot order
     std::vector<int32_t> id(hm.sx.size(), -1);
     int32_t c = 0;
-    for (size_t s = 0; s < hm.sx.size(); s++)
-      if (hm.alive[s] && !hm.is_inf((int)s)) id[s] = c++;
+    if (hm.fid_compact) { id = hm.fid; c = (int32_t)hm.n_finite; }
+    else
+      for (size_t s = 0; s < hm.sx.size(); s++)
+        if (hm.alive[s] && !hm.is_inf((int)s)) id[s] = c++;
     if (handle) handle->assign((size_t)c, -1);
     for (size_t s = 0; s < hm.sx.size(); s++) {
       const int32_t t = id[s];
@@ -647,9 +681,78 @@ struct dli_dd {
   } catch (const std::bad_alloc &) { return DLI_ERR_NOMEM; \
   } catch (...) { return DLI_ERR_ARG; }
 
+// incremental path: the simplices created since the last sync plus the ring around them (their neighbour links changed)
+// and the stars of overwritten vertices go to dli_mesh_update; DLI_ERR_UNSUPPORTED = the mesh cannot be patched
+static int dd_patch(dli_dd *d) {
+  HostMeshD &hm = d->hm;
+  const int D = hm.D, k = D + 1;
+  const int64_t nv = hm.nv(), nv0 = d->nv_synced, nf = hm.n_finite;
+  std::vector<int> dirty;
+  auto add = [&](int s) {
+    if (s < 0 || !hm.alive[s] || hm.fid[s] < 0 || hm.mark[s]) return;
+    hm.mark[s] = 1;
+    dirty.push_back(s);
+  };
+  for (int s : d->pend_new) {
+    if (!hm.alive[s] || hm.fid[s] < 0) continue;   // created and destroyed again before this sync
+    add(s);
+    for (int j = 0; j < k; j++) add(hm.sx[s].n[j]);
+  }
+  std::vector<int32_t> vid;
+  std::vector<double> vval;
+  if (!d->pend_values.empty()) {
+    std::vector<uint8_t> changed((size_t)nv, 0);
+    for (int v : d->pend_values) {
+      if (v < nv0 && !changed[(size_t)v]) { vid.push_back(v); vval.push_back(hm.F[(size_t)v]); }
+      changed[(size_t)v] = 1;
+    }
+    for (int s = 0; s < (int)hm.sx.size(); s++) {     // the interpolants of their stars change
+      if (!hm.alive[s] || hm.fid[s] < 0) continue;
+      bool has = false;
+      for (int j = 0; j < k; j++) has = has || changed[(size_t)hm.sx[s].v[j]];
+      if (has) add(s);
+    }
+  }
+  for (int s : dirty) hm.mark[s] = 0;
+  std::vector<int32_t> ids(dirty.size()), sv(dirty.size() * k), sn(dirty.size() * k);
+  for (size_t i = 0; i < dirty.size(); i++) {
+    const int s = dirty[i];
+    ids[i] = hm.fid[s];
+    for (int j = 0; j < k; j++) {
+      sv[i * k + j] = hm.sx[s].v[j];
+      sn[i * k + j] = hm.fid[hm.sx[s].n[j]];   // -1 across the hull (infinite simplices carry no id)
+    }
+  }
+  std::vector<double> nx((size_t)(nv - nv0) * D + 1), nfv((size_t)(nv - nv0) + 1);
+  for (int64_t v = nv0; v < nv; v++) {
+    for (int c = 0; c < D; c++) nx[(size_t)(v - nv0) * D + c] = hm.X[(size_t)v * D + c];
+    nfv[(size_t)(v - nv0)] = hm.F[(size_t)v];
+  }
+  d->patched_since_full += (int64_t)ids.size();
+  return dli_mesh_update(d->mesh, nv, nx.data(), nfv.data(), (int64_t)vid.size(), vid.data(), vval.data(), nf,
+                         (int64_t)ids.size(), ids.data(), sv.data(), sn.data());
+}
+
 static int dd_refresh(dli_dd *d) {
   if (!d->dirty && d->mesh) return DLI_OK;
+  // the start-hint grid is not patched: once half of the mesh it was built for has been replaced, start over
+  const bool stale_hints = d->patched_since_full > std::max<int64_t>(4096, d->simplices_at_full / 2);
+  if (d->mesh && !d->need_full && !stale_hints && d->hm.fid_compact && d->hm.cur_dim == d->hm.D) {
+    const int rc = dd_patch(d);
+    if (rc == DLI_OK) {
+      d->dirty = false;
+      d->n_patch++;
+      d->pend_new.clear(); d->pend_values.clear();
+      d->nv_synced = d->hm.nv();
+      return DLI_OK;
+    }
+    if (rc != DLI_ERR_UNSUPPORTED) {   // a failed patch may leave the device mesh half-written: drop it
+      dli_mesh_destroy(d->mesh); d->mesh = nullptr;
+      return rc;
+    }
+  }
   if (d->mesh) { dli_mesh_destroy(d->mesh); d->mesh = nullptr; }
+  if (d->hm.cur_dim == d->hm.D && !d->hm.fid_compact) d->hm.renumber();
   const HostMeshD &hm = d->hm;
   const int D = hm.D, k = D + 1;
   const int64_t nv = hm.nv(), ns = hm.cur_dim == D ? hm.n_finite : 0;
@@ -659,7 +762,14 @@ static int dd_refresh(dli_dd *d) {
   d->flatten(coords.data(), ns ? sv.data() : nullptr, ns ? sn.data() : nullptr, nullptr);
   const dli_options o = d->engine_options();
   int rc = dli_mesh_create(D, nv, coords.data(), fv.data(), ns, sv.data(), sn.data(), &o, &d->mesh);
-  if (rc == DLI_OK) { d->dirty = false; d->n_full++; }
+  if (rc == DLI_OK) {
+    d->dirty = false; d->n_full++;
+    d->need_full = false;
+    d->pend_new.clear(); d->pend_values.clear();
+    d->nv_synced = nv;
+    d->patched_since_full = 0;
+    d->simplices_at_full = ns;
+  }
   return rc;
 }
 
@@ -683,13 +793,9 @@ static void dd_host_interp(dli_dd *d, int64_t n, const double *xs, double *ys, i
   const int D = hm.D;
   const double nan = std::nan("");
   const bool have_mesh = hm.cur_dim == D;
-  if (so && have_mesh && !d->id_valid) {
-    d->id_cache.assign(hm.sx.size(), -1);
-    int32_t c = 0;
-    for (size_t s = 0; s < hm.sx.size(); s++)
-      if (hm.alive[s] && !hm.is_inf((int)s)) d->id_cache[s] = c++;
-    d->id_valid = true;
-  }
+  // simplex ids are the stable compact ids the device mesh uses (renumbered here if an insertion left holes: the
+  // device mesh then follows with a full flatten)
+  if (so && have_mesh && !hm.fid_compact) { hm.renumber(); d->need_full = true; d->dirty = true; }
   int start = d->host_last;
   for (int64_t i = 0; i < n; i++) {
     const double *p = xs + i * D;
@@ -706,7 +812,7 @@ static void dd_host_interp(dli_dd *d, int64_t n, const double *xs, double *ys, i
         st = DLI_STATUS_OK;
         start = s;
         y = D == 2 ? dd_epilogue<2>(hm, s, p) : (D == 3 ? dd_epilogue<3>(hm, s, p) : dd_epilogue<4>(hm, s, p));
-        if (so) sid = d->id_cache[(size_t)s];
+        if (so) sid = hm.fid[(size_t)s];
       }
     }
     ys[i] = y;
@@ -743,7 +849,6 @@ int32_t dli_dd_insert(dli_dd *d, const double *x, double f) {
   if (!d || !x) return DLI_ERR_ARG;
   for (int c = 0; c < d->hm.D; c++)
     if (!std::isfinite(x[c])) return DLI_ERR_ARG;
-  d->id_valid = false;
   return d->insert(x, f);
   DLI_GUARD_END
 }
@@ -755,7 +860,7 @@ int dli_dd_insert_many(dli_dd *d, int64_t n, const double *xs, const double *f, 
   const int D = hm.D;
   for (int64_t i = 0; i < n * D; i++)
     if (!std::isfinite(xs[i])) return DLI_ERR_ARG;   // validated before the first insertion: nothing to roll back
-  d->id_valid = false;
+  d->need_full = true;                               // bulk insertion: the device mesh is flattened from scratch
   std::vector<int64_t> order((size_t)n);
   for (int64_t i = 0; i < n; i++) order[(size_t)i] = i;
   if (spatial_sort && n > 1) {
@@ -847,7 +952,6 @@ int dli_dd_insert_largest_error_point(dli_dd *d, double *err, double *f, double 
   if (err) *err = e.err;
   if (f) *f = e.f;
   if (x) for (int c = 0; c < d->hm.D; c++) x[c] = e.x[c];
-  d->id_valid = false;
   d->insert(e.x, e.f, e.s);   // the point is the centroid of a (sub)simplex of e.s: start the walk there
   return DLI_OK;
   DLI_GUARD_END
@@ -887,6 +991,7 @@ int dli_dd_set_options(dli_dd *d, const dli_options *opt) {
   d->have_opt = opt != nullptr;
   if (opt) d->opt = *opt;
   d->dirty = true;
+  d->need_full = true;
   return DLI_OK;
 }
 
@@ -910,6 +1015,10 @@ const dli_mesh *dli_dd_device_mesh(dli_dd *d) {
   return d->mesh;
 }
 int64_t dli_dd_sync_count(const dli_dd *d) { return d ? d->n_full : 0; }
+void dli_dd_sync_counts(const dli_dd *d, int64_t *n_full, int64_t *n_incremental) {
+  if (n_full) *n_full = d ? d->n_full : 0;
+  if (n_incremental) *n_incremental = d ? d->n_patch : 0;
+}
 
 int64_t dli_dd_get_all_vertices(const dli_dd *d, double *out) {
   if (!d) return 0;

@@ -784,11 +784,17 @@ struct DetDD<1> {
 // bound below accounts for it).  The slow flag is set when an entry of the fp32 G is not within 1.5 fp32
 // ulps-of-the-row-maximum of the exact value, or when the a-priori error bound of the affine interpolant exceeds
 // 1e-13 * min|f_i| (see k_build_fat2): k_interpD_full handles those simplices in the reference's operation order.
+// `list` (dli_mesh_update): the device indices of the simplices to (re)build, n of them; NULL = all ns simplices.
+// `epi_base`: first record index of the interpolant array of the split 4D layout (= the number of walk records).
 template <int D, bool PACK = false>
 __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, const double *__restrict__ vrec, int vs,
-                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+                             uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow, const int32_t *__restrict__ list = nullptr,
+                             int n_list = 0) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= ns) return;
+  if (list) {
+    if (s >= n_list) return;
+    s = list[s];
+  } else if (s >= ns) return;
   const double eps = 1.1102230246251565e-16, u = 5.9604644775390625e-08;
   const double edd = 5.048709793414476e-29;  // 2^-94: bound on the accumulated double-double error per unit of permanent
   int v[D + 1], nb[D + 1];
@@ -1417,6 +1423,34 @@ __global__ void k_build_fat2_list(int n, const int32_t *__restrict__ idx, int ol
   if (f < old_ns) was = (fat[4 * (size_t)f + 3].w >> 31) & 1u;   // kFatSlow = bit 63 of the neighbour word
   const int is = make_fat2(vrec[r0.x], vrec[r0.y], vrec[r0.z], nbr, fat + 4 * (size_t)f) ? 1 : 0;
   if (is != was) atomicAdd(n_slow_delta, is - was);
+}
+
+// dD incremental update: canonical simplex records + id map of the listed simplices (rows: ss ints each, already in
+// device indices), new values of existing vertices
+__global__ void k_update_simplices_d(int n, const int32_t *__restrict__ idx, const int32_t *__restrict__ rows, int ss,
+                                     const int32_t *__restrict__ ids, int32_t *__restrict__ srec, int32_t *__restrict__ orig) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = idx[i];
+  for (int k = 0; k < ss; k++) srec[(size_t)s * ss + k] = rows[(size_t)i * ss + k];
+  orig[s] = ids[i];
+}
+__global__ void k_update_values_d(int n, const int32_t *__restrict__ vid, const double *__restrict__ val, double *__restrict__ vrec,
+                                  int vs, int dim) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) vrec[(size_t)vid[i] * vs + dim] = val[i];
+}
+// slow flags of the dD walk records (recounted after a patch: a handful of bytes per simplex)
+template <int D, bool PACK>
+__global__ void k_count_slow_d(int ns, const uint4 *__restrict__ fat, unsigned int *__restrict__ n_slow) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  const uint4 *r = fat + (size_t)s * FatD<D, PACK>::CHUNKS;
+  unsigned fl;
+  if constexpr (D == 3) fl = r[3].z & 1u;          // flags: low word of the second double of chunk 3
+  else if constexpr (PACK) fl = (r[7].w >> 24) & 1u;
+  else fl = r[7].y & 1u;
+  if (fl) atomicAdd(n_slow, 1u);
 }
 
 __global__ void k_fill_nomesh(int64_t n, double *ys, int32_t *simplex_out, uint8_t *status_out) {

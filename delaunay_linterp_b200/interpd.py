@@ -113,8 +113,16 @@ class Delaunay_incremental_interp_d:
         check(lib().dli_dd_insert_many(self._h, 0, None, None, 0, 1))
 
     # ---- the hot path (GPU; one point at a time is answered on the host, see include/dli_host.h)
-    def interp(self, x, return_status=False):
-        """interp([x...]) -> float (NaN outside the hull) or interp(ndarray (n, d) / torch CUDA tensor) -> array."""
+    def sync_counts(self):
+        """(full re-flattens, in-place patches) of the device mesh so far: after insert / insert_largest_error_point the
+        next interp re-sends only the simplices the insertions touched (dli_mesh_update, SURVEY 8(f) #2)."""
+        a, b = C.c_int64(), C.c_int64()
+        lib().dli_dd_sync_counts(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def interp(self, x, return_status=False, return_simplex=False):
+        """interp([x...]) -> float (NaN outside the hull) or interp(ndarray (n, d) / torch CUDA tensor) -> array.
+        return_simplex (numpy form): also the located simplex, in the numbering of export()."""
         if _is_torch_tensor(x):
             import torch
             xs = x.contiguous().view(-1, self.N)
@@ -129,9 +137,13 @@ class Delaunay_incremental_interp_d:
         n = xs.shape[0]
         ys = np.empty(n, np.float64)
         st = np.empty(n, np.uint8)
-        check(lib().dli_dd_interp(self._h, n, xs.ctypes.data, ys.ctypes.data, None, st.ctypes.data, None))
+        sx = np.empty(n, np.int32) if return_simplex else None
+        check(lib().dli_dd_interp(self._h, n, xs.ctypes.data, ys.ctypes.data, sx.ctypes.data if return_simplex else None,
+                                  st.ctypes.data, None))
         if scalar:
             return float(ys[0])
+        if return_simplex:
+            return (ys, sx, st) if return_status else (ys, sx)
         return (ys, st) if return_status else ys
 
     # ---- plot data

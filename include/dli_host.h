@@ -154,6 +154,11 @@ int dli_dd_interp(dli_dd *d, int64_t n, const double *xs, double *ys, int32_t *s
                   void *stream);
 const dli_mesh *dli_dd_device_mesh(dli_dd *d);
 int64_t dli_dd_sync_count(const dli_dd *d); /* how often the device mesh was (re-)created */
+/* (full re-flattens, in-place patches) of the device mesh so far: after insert / insert_largest_error_point the next
+ * interp re-sends only the simplices the insertions created, the ring around them and the stars of overwritten
+ * vertices (dli_mesh_update; the reference's dirty list: modified_cgal/Convex_hull_d.h:1172-1178 consumed at
+ * src/delaunay_d_interp.h:939-965) */
+void dli_dd_sync_counts(const dli_dd *d, int64_t *n_full, int64_t *n_incremental);
 int dli_dd_set_options(dli_dd *d, const dli_options *opt);
 
 /* plot data: vertices as (x..., f) rows [nv][n_dims + 1]; count query with NULL */

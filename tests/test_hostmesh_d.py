@@ -118,3 +118,40 @@ def test_per_point_interp_is_answered_on_the_host():
         # vertices (closed simplices: found, not NaN).  The reference-order arithmetic is not exact there in dD: a
         # determinant with two equal columns is only ~1e-17 after the pivoting LU
         assert all(abs(t.interp(p.tolist()) - v) <= 4e-16 * abs(v) for p, v in zip(co[:20], f[:20]))
+
+
+@pytest.mark.parametrize("d,n", [(2, 120), (3, 120), (4, 70)])
+def test_simplex_ids_are_stable_and_compact_across_insertions(d, n):
+    """what the incremental device update (dli_mesh_update, dD) relies on: an insertion hands the ids of the simplices it
+    removes to the ones it creates and appends the rest -- every simplex that does not contain the new vertex keeps its
+    id -- and simplex_out of the per-point path speaks the same ids"""
+    rng = np.random.default_rng(300 + d)
+    pts = rng.random((n, d))
+    t = dl.Delaunay_incremental_interp_d(d)
+    prev = None
+    stable_steps = 0
+    for i, p in enumerate(pts):
+        t.insert(p.tolist(), float(p.sum()))
+        if t.number_of_simplices() == 0:
+            continue
+        co, f, sv, sn = t.export()
+        assert len(sv) == t.number_of_simplices() and sv.min() >= 0 and sv.max() < len(co)
+        assert sn.max() < len(sv) and sn.min() >= -1
+        vnew = len(co) - 1
+        if prev is not None and len(sv) >= len(prev):
+            old = ~(sv == vnew).any(axis=1)                  # rows without the new vertex existed before ...
+            ids = np.nonzero(old)[0]
+            assert len(ids) == 0 or ids.max() < len(prev)
+            assert np.array_equal(np.sort(sv[ids], axis=1), np.sort(prev[ids], axis=1))   # ... under the same id
+            stable_steps += 1
+        prev = sv
+    assert stable_steps > n // 2 and t.validate() == 0
+    q = pts[:40] * 0.5 + 0.25
+    ys, sx, st = t.interp(q[:8], return_simplex=True, return_status=True)     # 8 queries: answered on the host
+    co, f, sv, sn = t.export()
+    for k in range(8):
+        if st[k] == 0:
+            # barycentric coordinates of the query in the reported simplex are all >= 0
+            A = np.vstack([co[sv[sx[k]]].T, np.ones(d + 1)])
+            lam = np.linalg.solve(A, np.append(q[k], 1.0))
+            assert lam.min() > -1e-9
