@@ -35,6 +35,11 @@ class Delaunay_incremental_interp_d:
             opt = _make_options(**options)
             check(lib().dli_dd_set_options(self._h, C.byref(opt)))
 
+    def set_options(self, **options):
+        """engine options for the device mesh (see Mesh); the next interp re-flattens the mesh from scratch."""
+        opt = _make_options(**options)
+        check(lib().dli_dd_set_options(self._h, C.byref(opt)))
+
     def __del__(self):
         try:
             if getattr(self, "_h", None):

@@ -128,23 +128,26 @@ int dli_mesh_create(int dim, int64_t n_vertices, const double *coords, const dou
 int dli_mesh_set_values(dli_mesh *mesh, const double *f /* [n_vertices], host */);
 
 /*
- * Incremental update after insertions (2D).  Replaces the reference's per-insert bookkeeping: the dirty set of an
- * insertion is the star of the new vertex (insert_and_get_modifications, src/delaunay_2_interp.h:434-448; value
- * overwrite of an existing vertex :446) -- only those simplices are re-sent and re-derived on the device (canonical
+ * Incremental update after insertions (2D, 3D, 4D).  Replaces the reference's per-insert bookkeeping: the dirty set of
+ * an insertion is the star of the new vertex (2D: insert_and_get_modifications, src/delaunay_2_interp.h:434-448, value
+ * overwrite of an existing vertex :446; dD: p_modified_simplices, modified_cgal/Convex_hull_d.h:1172-1178, consumed at
+ * src/delaunay_d_interp.h:939-965) -- only those simplices are re-sent and re-derived on the device (canonical
  * records, packed records, walk records, hull-edge table when the hull changed) instead of flattening the whole mesh.
  *   n_vertices_total   vertices after the update; the (n_vertices_total - old n_vertices) new ones are appended:
- *                      new_coords [.][2], new_f [.]
+ *                      new_coords [.][dim], new_f [.]
  *   n_value_changes    existing vertices whose value changed: value_ids [.], values [.]
  *   n_simplices_total  simplices after the update.  The caller's id space stays compact: a simplex that disappeared
  *                      hands its id to a new one, further new simplices are appended (ids >= old n_simplices)
  *   n_dirty            simplices whose vertex list, neighbour list or vertex values differ from what the mesh holds:
- *                      dirty_ids [.] (each id once), dirty_vertices [.][3] (any orientation), dirty_neighbors [.][3]
- *                      (-1 across the hull).  Every id >= old n_simplices must be listed.
+ *                      dirty_ids [.] (each id once), dirty_vertices [.][dim+1] (any orientation),
+ *                      dirty_neighbors [.][dim+1] (-1 across the hull).  Every id >= old n_simplices must be listed.
  * Start hints are kept (an id that is reused stays in the neighbourhood of its old simplex), so hint quality decays
  * slowly with many updates; re-create the mesh now and then (dli_host.h does, see di2_refresh).
- * Returns DLI_ERR_UNSUPPORTED -- mesh unchanged -- when the mesh cannot be patched and must be re-created: not 2D, a
- * replica or loaded snapshot (no host connectivity), cell-indexed or delta-encoded walk records, ids that no longer
- * fit the packed records, or a new vertex outside the bounding box of the start-hint grid.
+ * Returns DLI_ERR_UNSUPPORTED -- mesh unchanged -- when the mesh cannot be patched and must be re-created: a replica
+ * or loaded snapshot (no host connectivity), cell-indexed or delta-encoded 2D walk records, split 4D walk records, ids
+ * that no longer fit the packed records, or a new vertex outside the bounding box of the start-hint grid.
+ * dD: the start copies of a 4D mesh (dli_options.start_records) are dropped by the first patch and come back with the
+ * next full flatten.
  * No interp / locate call may be in flight on the mesh.
  */
 int dli_mesh_update(dli_mesh *mesh, int64_t n_vertices_total, const double *new_coords, const double *new_f,

