@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -734,6 +735,16 @@ static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coord
                           const int32_t *dirty_ids, const int32_t *dirty_sv, const int32_t *dirty_sn) {
   const int d = m->dim, k = d + 1;
   const int64_t nv0 = m->nv, ns0 = m->ns;
+  static const bool trace = getenv("DLI_TRACE_UPDATE") != nullptr;   // developer aid: phase times on stderr
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto t_begin = now();
+  auto lap = [&](const char *what) {
+    if (!trace) return;
+    cudaDeviceSynchronize();
+    auto t = now();
+    fprintf(stderr, "[dli_mesh_update dD] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_begin).count());
+    t_begin = t;
+  };
   if (ns0 == 0 || m->h_inv.empty() || m->h_sv.empty() || m->h_xy.empty())
     return fail(DLI_ERR_UNSUPPORTED, "dli_mesh_update: mesh cannot be patched (replica or empty)");
   if (d == 4 && m->d_fat && !fat_pack4(m))
@@ -797,6 +808,7 @@ static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coord
       rows[(size_t)i * ss + k + j] = nb[j] >= 0 ? dev_index(nb[j]) : -1;
     }
   }
+  lap("validate + host rows");
   // ---- capacity
   cudaError_t e = cudaDeviceSynchronize();
   const size_t rec = m->d_fat ? (size_t)fat_record_bytes(m) : 0;
@@ -819,6 +831,7 @@ static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coord
     if (e == cudaSuccess) m->cap_fat = cap;
   }
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update: growing the device buffers failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));
+  lap("capacity");
   // ---- upload (one scratch buffer) + rebuild the walk records of the listed simplices
   const int64_t nnew = nv_total - nv0;
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -860,6 +873,7 @@ static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coord
     unsigned int *d_cnt = reinterpret_cast<unsigned int *>(m->d_upd + o_cnt);
     k_update_simplices_d<<<gb, 128>>>((int)n_dirty, d_idx, reinterpret_cast<const int32_t *>(m->d_upd + o_rows), ss,
                                       reinterpret_cast<const int32_t *>(m->d_upd + o_ids), m->d_srec, m->d_orig);
+    lap("upload + canonical records");
     if (m->d_fat) {
       const unsigned cb = (unsigned)((ns_total + 255) / 256);
       if (d == 3) {
@@ -872,6 +886,7 @@ static int mesh_update_dd(dli_mesh *m, int64_t nv_total, const double *new_coord
     }
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpy(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost);
+    lap("walk records + slow recount");
   }
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_mesh_update failed (the mesh is now inconsistent; destroy it): ") + cudaGetErrorString(e));

@@ -428,8 +428,29 @@ struct dli_di2 {
   void drop_face_entries(int face) {
     if (face < (int)nent.size()) { live -= nent[face]; nent[face] = 0; }
   }
+  // Dead entries leave the top; so do entries whose insertion point already IS a vertex: the ROUNDED midpoint of a
+  // hull edge that is not axis-aligned lands an ulp off the hull when it is inserted, the edge survives (on a sliver, or
+  // on the hull face the point was not beyond) and keeps proposing the same point.  The reference re-inserts it -- a
+  // value overwrite that changes nothing -- and returns the same tuple forever (src/delaunay_2_interp.h:498-504); its
+  // README run never meets this (box hull, exactly representable coordinates: every call there adds a vertex, which
+  // this rule leaves untouched).  Here such a tuple is dropped.
+  bool point_exists(double x, double y, int start) const {
+    if (hm.dim < 2) return false;
+    const int f = hm.locate(x, y, start);
+    if (hm.is_inf(f)) return false;
+    for (int i = 0; i < 3; i++)
+      if (hm.X[hm.fc[f].v[i]] == x && hm.Y[hm.fc[f].v[i]] == y) return true;
+    return false;
+  }
   void prune() {
-    while (!pq.empty() && !entry_live(pq.top())) pq.pop();
+    for (;;) {
+      while (!pq.empty() && !entry_live(pq.top())) pq.pop();
+      if (pq.empty() || !point_exists(pq.top().x, pq.top().y, pq.top().face)) return;
+      const int face = pq.top().face;
+      if (face < (int)nent.size() && nent[face] > 0) nent[face]--;
+      live--;
+      pq.pop();
+    }
   }
   // compute_simplex_error for the face and its hull edges (src/delaunay_2_interp.h:476-491)
   void add_face_errors(int face) {

@@ -12,7 +12,10 @@
 // triangulation is accepted (the reference's choice there depends on its hull's facet triangulation).
 #include <algorithm>
 #include <climits>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstdint>
 #include <cstring>
 #include <new>
@@ -583,8 +586,29 @@ struct dli_dd {
   void drop_entries(int s) {
     if (s < (int)nent.size()) { live -= nent[s]; nent[s] = 0; }
   }
+  // does the point already exist as a vertex?  (a closed simplex containing a vertex's position has it as a vertex)
+  bool point_exists(const double *p, int start) {
+    if (hm.cur_dim < hm.D) return false;
+    const int s = hm.locate(p, start);
+    if (hm.is_inf(s)) return false;
+    for (int i = 0; i <= hm.D; i++)
+      if (std::equal(p, p + hm.D, hm.pt(hm.sx[s].v[i]))) return true;
+    return false;
+  }
+  // Dead entries leave the top; so do entries whose insertion point already IS a vertex.  The latter arise when the
+  // ROUNDED centroid of a hull sub-simplex was inserted an ulp off the hull: the sub-simplex survives on a neighbouring
+  // hull facet and keeps proposing the same point.  The reference re-inserts it (a value overwrite that changes
+  // nothing) and returns the same tuple forever (insert_largest_error_point, src/delaunay_d_interp.h:1028-1034; its
+  // demo never meets this: the box hull there has exactly representable face coordinates); here the tuple is dropped.
   void prune() {
-    while (!pq.empty() && !entry_live(pq.top())) pq.pop();
+    for (;;) {
+      while (!pq.empty() && !entry_live(pq.top())) pq.pop();
+      if (pq.empty() || !point_exists(pq.top().x, pq.top().s)) return;
+      const int s = pq.top().s;
+      if (s < (int)nent.size() && nent[s] > 0) nent[s]--;
+      live--;
+      pq.pop();
+    }
   }
   // items of a simplex, in the order of the batched evaluator (include/dli.h, dli_simplex_error_*): the simplex itself,
   // then for every hull facet (ascending slot) its vertex subsets of size >= 2 by ascending bitmask
@@ -622,6 +646,15 @@ struct dli_dd {
         for (int a = 1; a < np; a++) acc += w[a * N + q];
         c[q] = acc / np;
       }
+      // A hull sub-simplex whose ROUNDED centroid was inserted an ulp inside the hull leaves its hull facet in place,
+      // now on a sliver (facet + the new vertex), and the sliver would queue the same item again -- insertion point =
+      // its own vertex, the same tuple on top of the queue forever (the reference shares this livelock: its
+      // insert_largest_error_point re-inserts the rounded doubles, src/delaunay_d_interp.h:1028-1034; its own demo
+      // never meets it because the box hull there has exactly representable face coordinates).  An item whose
+      // insertion point already is a vertex of its simplex carries no information (the interpolant is exact there) and
+      // is not queued.
+      for (int a = 0; a <= D; a++)
+        if (std::equal(c, c + D, hm.pt(hm.sx[s].v[a]))) return;
       const double phi = fn(D, c, user);
       push(simplex_error_any(D, np, w, phi), phi, c, s);
     });
@@ -729,8 +762,13 @@ static int dd_patch(dli_dd *d) {
     nfv[(size_t)(v - nv0)] = hm.F[(size_t)v];
   }
   d->patched_since_full += (int64_t)ids.size();
-  return dli_mesh_update(d->mesh, nv, nx.data(), nfv.data(), (int64_t)vid.size(), vid.data(), vval.data(), nf,
-                         (int64_t)ids.size(), ids.data(), sv.data(), sn.data());
+  static const bool trace = getenv("DLI_TRACE_UPDATE") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  const int rc = dli_mesh_update(d->mesh, nv, nx.data(), nfv.data(), (int64_t)vid.size(), vid.data(), vval.data(), nf,
+                                 (int64_t)ids.size(), ids.data(), sv.data(), sn.data());
+  if (trace) fprintf(stderr, "[dli_dd] dli_mesh_update %.3f ms, %zu dirty, %zu pending\n",
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), ids.size(), d->pend_new.size());
+  return rc;
 }
 
 static int dd_refresh(dli_dd *d) {
@@ -738,7 +776,10 @@ static int dd_refresh(dli_dd *d) {
   // the start-hint grid is not patched: once half of the mesh it was built for has been replaced, start over
   const bool stale_hints = d->patched_since_full > std::max<int64_t>(4096, d->simplices_at_full / 2);
   if (d->mesh && !d->need_full && !stale_hints && d->hm.fid_compact && d->hm.cur_dim == d->hm.D) {
+    static const bool trace = getenv("DLI_TRACE_UPDATE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
     const int rc = dd_patch(d);
+    if (trace) fprintf(stderr, "[dli_dd] dd_patch %.3f ms (rc %d)\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), rc);
     if (rc == DLI_OK) {
       d->dirty = false;
       d->n_patch++;
@@ -1004,9 +1045,15 @@ int dli_dd_interp(dli_dd *d, int64_t n, const double *xs, double *ys, int32_t *s
     dd_host_interp(d, n, xs, ys, simplex_out, status_out);
     return DLI_OK;
   }
+  static const bool trace = getenv("DLI_TRACE_UPDATE") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
   int rc = dd_refresh(d);
   if (rc != DLI_OK) return rc;
-  return dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);
+  const auto t1 = std::chrono::steady_clock::now();
+  rc = dli_interp(d->mesh, n, xs, ys, simplex_out, status_out, stream);
+  if (trace) fprintf(stderr, "[dli_dd] refresh %.3f ms, dli_interp call %.3f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count());
+  return rc;
   DLI_GUARD_END
 }
 const dli_mesh *dli_dd_device_mesh(dli_dd *d) {

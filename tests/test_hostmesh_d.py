@@ -155,3 +155,30 @@ def test_simplex_ids_are_stable_and_compact_across_insertions(d, n):
             A = np.vstack([co[sv[sx[k]]].T, np.ones(d + 1)])
             lam = np.linalg.solve(A, np.append(q[k], 1.0))
             assert lam.min() > -1e-9
+
+
+@pytest.mark.parametrize("d", [2, 3, 4])
+def test_adaptive_insertion_on_a_general_hull_always_adds_a_vertex(d):
+    """On a hull that is not an axis-aligned box the ROUNDED centroid of a hull sub-simplex lands an ulp off the hull
+    when inserted; the sub-simplex survives and proposes the same point again.  The reference then returns the same
+    tuple forever (src/delaunay_d_interp.h:1028-1034, src/delaunay_2_interp.h:498-504: a no-op value overwrite); here a
+    tuple whose point already is a vertex is dropped, so every call refines the mesh.  Both classes."""
+    al = np.array([0.3, 0.6, 0.2, 0.1])[:d]
+    fn = lambda x: float(np.prod(np.asarray(x) ** al))   # noqa: E731
+    pts = np.random.default_rng(3).random((1500, d)) * 4.99 + 0.01
+    fv = np.array([fn(p) for p in pts])
+    classes = [dl.Delaunay_incremental_interp_d(d, fn)]
+    if d == 2:
+        classes.append(dl.DelaunayInterp2(fn))
+    for t in classes:
+        t.insert_many(pts, fv, use_gpu=False)
+        nv = lambda: t.number_of_vertices() if hasattr(t, "number_of_vertices") else t.n_vertices   # noqa: E731
+        seen = set()
+        for r in range(120):
+            n0 = nv()
+            e = t.insert_largest_error_point()
+            assert nv() == n0 + 1, (r, e)
+            assert tuple(e[2]) not in seen
+            seen.add(tuple(e[2]))
+        q = t.get_error_queue()
+        assert all(q[i][0] >= q[i + 1][0] for i in range(len(q) - 1))
