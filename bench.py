@@ -149,8 +149,8 @@ def bind_from_nvidia_smi_topo(local_rank):
                         return "numa_node=-1; nvidia-smi topo affinity %s = every allowed cpu (single node)" % tok
                     os.sched_setaffinity(0, cpus)
                     return "numa_node=-1; bound to nvidia-smi topo affinity %s (%d cpus)" % (tok, len(cpus))
-            return "numa_node=-1; no CPU affinity column for GPU%d" % local_rank
-        return "numa_node=-1; GPU%d not in nvidia-smi topo" % local_rank
+            # (the header row also starts with "GPU0": keep looking)
+        return "numa_node=-1; no CPU affinity for GPU%d in nvidia-smi topo" % local_rank
     except Exception as e:  # noqa: BLE001
         return "numa_node=-1; nvidia-smi topo unavailable (%s)" % type(e).__name__
 
