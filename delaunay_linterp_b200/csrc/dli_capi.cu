@@ -1159,7 +1159,6 @@ MeshDView viewD(const dli_mesh *m) {
 }
 
 constexpr int64_t kChunk = 1ll << 28;      // queries per launch pair (int32 indices in the straggler queue)
-constexpr int64_t kSingleLaunchQueries = 2048;   // batches up to this size take ONE launch (run_device)
 // Straggler queue entries per launch pair: 1/16 of the launch (at least 2^16), 8 B each from the stream-ordered pool --
 // 50 MB for a 100M-query launch (it used to be one entry per query: 0.8 GB).  Queries that do not fit are marked in
 // their result slot and found again by the exact pass (enqueue_straggler in dli_kernels.cuh): an overflow costs one
@@ -1292,35 +1291,11 @@ int run_device(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32
     if (launches) *launches += 1;
     return DLI_OK;
   }
-  // Small batches: ONE launch.  The exact pass serves every query from its start hint (queue == NULL): no queue
-  // allocation, no counter reset, no fast pass -- a call is then one kernel launch instead of five driver calls, which
-  // is what the per-call floor consists of (32 us -> see profiles/r02_latency_by_batch.json).  Values come from the
-  // reference-order epilogue, as for every query of the exact pass.
-  if (n <= kSingleLaunchQueries && !m->collect_stats && !m->collect_timing) {
-    Launch L;
-    L.m = m; L.st = st; L.queue = nullptr; L.qcount = nullptr; L.qcap = 0; L.stats = m->d_stats;
-    const unsigned grid = (unsigned)std::max<int64_t>(1, (n + 127) / 128);
-    const bool cf = m->opt.epilogue == DLI_EPILOGUE_CLOSED_FORM;
-    if (m->dim == 2) {
-      Mesh2View v = view2(m);
-      const double2 *x2 = reinterpret_cast<const double2 *>(xs);
-      if (out == 1) k_interp2_full<false, 0, 1><<<grid, 128, 0, st>>>(v, x2, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-      else if (cf) k_interp2_full<false, 1, 0><<<grid, 128, 0, st>>>(v, x2, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-      else k_interp2_full<false, 0, 0><<<grid, 128, 0, st>>>(v, x2, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-    } else {
-      MeshDView v = viewD(m);
-      if (m->dim == 3) {
-        if (cf) k_interpD_full<3, false, 1><<<grid, 128, 0, st>>>(v, xs, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-        else k_interpD_full<3, false, 0><<<grid, 128, 0, st>>>(v, xs, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-      } else {
-        if (cf) k_interpD_full<4, false, 1><<<grid, 128, 0, st>>>(v, xs, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-        else k_interpD_full<4, false, 0><<<grid, 128, 0, st>>>(v, xs, ys, so, sto, nullptr, nullptr, 0u, n, L.stats);
-      }
-    }
-    CU(cudaGetLastError());
-    if (launches) *launches += 1;
-    return DLI_OK;
-  }
+  // (A single-launch form for small batches -- the exact pass serving every query from its start hint, no queue, no
+  // counter reset -- was measured and dropped: 36 us instead of 42 us per 1024-query call from Python, because the
+  // per-call floor is host-side (ctypes call, pointer queries, stream synchronisation), not the two launches; and it
+  // breaks the batch-partition invariance of the results, since the exact pass evaluates in the reference's operation
+  // order where the fast pass uses the face's affine form.)
   const int64_t cap = queue_capacity(m, std::min(n, kChunk));
   int32_t *queue = nullptr;
   // [cap] query indices, [cap] faces the fast pass stopped in, then the counter

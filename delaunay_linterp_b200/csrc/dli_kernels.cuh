@@ -521,19 +521,16 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
                unsigned int queue_cap, int64_t n /* batch size: processed directly if the queue overflowed */,
                unsigned long long *__restrict__ stats) {
-  // queue == NULL: single-launch form for small batches (run_device): no fast pass ran, every query is served here
-  // from its start hint
-  const bool all = queue == nullptr;
-  const int64_t total = all ? n : (int64_t)*queue_count;
-  const bool overflow = all || total > (int64_t)queue_cap;
-  const int64_t cnt = all ? 0 : (overflow ? (int64_t)queue_cap : total);
+  const int64_t total = (int64_t)*queue_count;
+  const bool overflow = total > (int64_t)queue_cap;
+  const int64_t cnt = overflow ? (int64_t)queue_cap : total;
   StatsAcc st;
   // k < cnt: queue entries; k >= cnt (overflow only): scan of the batch for marked queries
   const int64_t span = overflow ? cnt + n : cnt;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < span; k += (int64_t)gridDim.x * blockDim.x) {
     const bool queued = k < cnt;
     const int64_t i = queued ? (int64_t)queue[k] : k - cnt;
-    if (!queued && !all && !is_overflow_mark<OUT>(ys, simplex_out, i)) continue;
+    if (!queued && !is_overflow_mark<OUT>(ys, simplex_out, i)) continue;
     double2 q = xs[i];
     double px = q.x, py = q.y;
     if (!(isfinite(px) && isfinite(py))) {  // NaN / Inf coordinates: no face can be certified, report instead of walking
@@ -566,7 +563,7 @@ k_interp2_full(Mesh2View m, const double2 *__restrict__ xs, double *__restrict__
     if (simplex_out) simplex_out[i] = (status == DLI_STATUS_OUTSIDE_NAN || status == DLI_STATUS_STEP_LIMIT) ? -1 : __ldg(m.orig + f);
     if (status_out) status_out[i] = status;
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0 && !all) *m.straggler_frac = (float)total / (float)n;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0) *m.straggler_frac = (float)total / (float)n;
   if (STATS) {
     flush_stats(stats, st);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
@@ -675,16 +672,15 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
                int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out,
                const int32_t *__restrict__ queue, const unsigned int *__restrict__ queue_count,
                unsigned int queue_cap, int64_t n, unsigned long long *__restrict__ stats) {
-  const bool all = queue == nullptr;               // single-launch form for small batches, as in k_interp2_full
-  const int64_t total = all ? n : (int64_t)*queue_count;
-  const bool overflow = all || total > (int64_t)queue_cap;
-  const int64_t cnt = all ? 0 : (overflow ? (int64_t)queue_cap : total);
+  const int64_t total = (int64_t)*queue_count;
+  const bool overflow = total > (int64_t)queue_cap;
+  const int64_t cnt = overflow ? (int64_t)queue_cap : total;
   StatsAcc st;
   const int64_t span = overflow ? cnt + n : cnt;   // queue entries, then (overflow only) a scan for marked queries
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < span; k += (int64_t)gridDim.x * blockDim.x) {
     const bool queued = k < cnt;
     const int64_t i = queued ? (int64_t)queue[k] : k - cnt;
-    if (!queued && !all && !is_overflow_mark<0>(ys, simplex_out, i)) continue;
+    if (!queued && !is_overflow_mark<0>(ys, simplex_out, i)) continue;
     double p[D];
 #pragma unroll
     for (int a = 0; a < D; a++) p[a] = xs[i * D + a];
@@ -711,7 +707,7 @@ k_interpD_full(MeshDView m, const double *__restrict__ xs, double *__restrict__ 
     if (simplex_out) simplex_out[i] = s >= 0 ? __ldg(m.orig + DLI_IDX(s, m.ns)) : -1;
     if (status_out) status_out[i] = status;
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0 && !all) *m.straggler_frac = (float)total / (float)n;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && m.straggler_frac && n > 0) *m.straggler_frac = (float)total / (float)n;
   if (STATS) {
     flush_stats(stats, st);
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + ST_HARD, (unsigned long long)total);
