@@ -532,6 +532,7 @@ static int build_fat_records(dli_mesh *m) {
       m->d_fat = big;
       m->startcopy = true;
       m->nslots = m->ns + m->grid.cells;
+      m->cap_fat = m->nslots;
     } else {
       cudaGetLastError();   // not enough memory for the copies: the mesh works without them
     }

@@ -129,9 +129,9 @@ struct MeshDView {
 //        c0 p0x p0y | c1 p0z p0w | c2 f0 gx | c3 gy gz | c4 gw, W0 | c5 W1 W2 | c6 W3 W4 | c7 neighbours
 //        W0..W4 = 320 bits: row i of G in bits [80 i, 80 i + 80) as BLOCK FLOATING POINT -- four 18-bit mantissas
 //        (q + 2^17, |q| < 2^17) and one 8-bit exponent (e + 128): G_ik ~ q_ik 2^e_i with e_i chosen from the row
-//        maximum, so every entry is within 2^-16 of the ROW MAXIMUM (checked per entry at build time, together with the
+//        maximum, so every entry is within 2^-17 of the ROW MAXIMUM (checked per entry at build time, together with the
 //        error of computing G itself; else the slow flag).  The step's bound is relative to the row maximum anyway
-//        (kFatKD * max|G_i| * |d|_1), so block scaling loses nothing but 7 bits of band: kFatKP = 2^-15.
+//        (kFatKD * max|G_i| * |d|_1), so block scaling loses nothing but 6 bits of band: kFatKP = 2^-16.
 //        c7 = five 24-bit neighbour ids (0xffffff = hull) + 8 flag bits (bit 0 = slow).
 template <int D, bool PACK = false>
 struct FatD {
@@ -148,7 +148,7 @@ struct FatD {
   static constexpr int SMEM_PER_WARP = 32 * SSTRIDE * 16 + (SPLIT ? 32 * ESTRIDE * 16 : 0);
 };
 constexpr double kFatKD = 2.384185791015625e-07;  // 2^-22 = 4 fp32 unit roundoffs
-constexpr double kFatKP = 3.0517578125e-05;       // 2^-15 = twice the block-floating-point entry error 2^-16 (packed 4D records)
+constexpr double kFatKP = 1.52587890625e-05;      // 2^-16 = twice the block-floating-point entry error 2^-17 (packed 4D records)
 constexpr unsigned kPackNb24 = 0xFFFFFFu;         // packed 4D records: 24-bit neighbour field, all ones = hull
 // field [OFF, OFF + LEN) of the 320-bit string W[0..4] (compile-time position: one or two shifts)
 template <int OFF, int LEN>

@@ -868,8 +868,9 @@ __global__ void k_build_fatD(int ns, const int32_t *__restrict__ srec, int ss, c
         row |= (unsigned __int128)(unsigned long long)((long long)q + 131072ll) << (18 * k);
       }
       row |= (unsigned __int128)(unsigned long long)(e + 128) << 72;
-      // every decoded entry within 2^-16 of the decoded row maximum, the error of computing G included
-      for (int k = 0; k < D; k++) ok = ok && (fabs(dec[k] - G[i * D + k]) + dG[i * D + k] <= 1.52587890625e-05 * dmax);
+      // every decoded entry within 2^-17 (half a mantissa unit: gmax / 2^e >= 2^16) of the decoded row maximum, the
+      // error of computing G included; the 2^-10 relative allowance covers dmax < gmax by a unit and dG
+      for (int k = 0; k < D; k++) ok = ok && (fabs(dec[k] - G[i * D + k]) + dG[i * D + k] <= 7.63685e-06 * dmax);
       slow |= !ok;
       // row i occupies bits [80 i, 80 i + 80) of W: byte-aligned, so bytes never straddle a 64-bit word
       for (int t = 0; t < 10; t++) {
