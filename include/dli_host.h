@@ -20,6 +20,19 @@
  *   get_line_segments              :842-862   -> dli_di2_get_line_segments
  *   compute_simplex_error + add_error_of_boundary_subsimplices :725-741, :683-699 (host, per inserted star;
  *   the whole-mesh batched form is dli_simplex_error_* in dli.h)
+ *
+ * Threads: a dli_di2 / dli_dd handle is, like the reference's classes, a single-threaded object -- one thread at a
+ * time may call into a given handle (interp included: it may re-flatten or patch the device mesh, and one-point calls
+ * walk the host triangulation from the previous result).  Concurrency belongs one level down: several threads may
+ * call dli_interp / dli_locate / dli_gradient on ONE dli_mesh (dli_di2_device_mesh / dli_dd_device_mesh) at once,
+ * each on its own stream.
+ *
+ * Deviation from the reference, both classes: a queue tuple whose insertion point already is a vertex is dropped when it
+ * reaches the top.  On a hull that is not an axis-aligned box the ROUNDED centroid of a hull sub-simplex is inserted an
+ * ulp off the hull, the sub-simplex survives and proposes the same point again; the reference re-inserts it (a value
+ * overwrite that changes nothing) and returns the same tuple from insert_largest_error_point forever
+ * (src/delaunay_2_interp.h:498-504, src/delaunay_d_interp.h:1028-1034).  Sequences in which every call adds a vertex --
+ * the README's -- are unaffected.
  */
 #ifndef DLI_HOST_H_
 #define DLI_HOST_H_
