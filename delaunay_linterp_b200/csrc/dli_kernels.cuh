@@ -996,8 +996,14 @@ struct RingD {
 #ifndef DLI_X_FATD4_BLOCKS
 #define DLI_X_FATD4_BLOCKS 6
 #endif
+// 3D: 6 CTAs per SM (80 registers) is the measured optimum (round 1: ptxas chose 79 by itself; 7 / 8 CTAs spill and
+// lose).  Pinned here because the round-2 additions (start copies, record index checks) let ptxas drift to 96
+// registers = 5 CTAs, which cost 10 % (32.7 -> 29.5 Gq/s on cfg4-3D, profiles/r02_k_interpD_fat3_ncu.txt).
+#ifndef DLI_X_FATD3_BLOCKS
+#define DLI_X_FATD3_BLOCKS 6
+#endif
 template <int D, bool STATS, bool RING = false, bool PACK = false>
-__global__ void __launch_bounds__(128, (D == 4 && PACK) ? DLI_X_FATD4_BLOCKS : 1)
+__global__ void __launch_bounds__(128, (D == 4 && PACK) ? DLI_X_FATD4_BLOCKS : (D == 3 ? DLI_X_FATD3_BLOCKS : 1))
 k_interpD_fat(MeshDView m, int64_t n, int per_warp, const double *__restrict__ xs, double *__restrict__ ys,
               int32_t *__restrict__ simplex_out, uint8_t *__restrict__ status_out, int32_t *__restrict__ queue,
               unsigned int *__restrict__ queue_count, unsigned int queue_cap, unsigned long long *__restrict__ stats) {
