@@ -12,7 +12,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._capi import DLI_FN, DliError, check, lib
+from ._capi import DLI_FN, DLI_FN_BATCH, DliError, check, lib
 from .mesh import _is_torch_tensor, _make_options
 
 
@@ -110,6 +110,26 @@ class Delaunay_incremental_interp_d:
         n = lib().dli_dd_get_error_queue(self._h, cap, err.ctypes.data, f.ctypes.data, xs.ctypes.data)
         if n < 0:
             raise DliError(n, "get_error_queue")
+        return [(float(err[i]), float(f[i]), xs[i].tolist()) for i in range(n)]
+
+    def insert_largest_error_points(self, k, fn_batch=None, rel_threshold=0.25):
+        """k-at-a-time adaptive refinement (dli_dd_refine): up to k largest-error tuples on simplices that share no
+        vertex are inserted, then the items of all new simplices are evaluated in one batch.  fn_batch(ndarray (n, d))
+        -> ndarray (n,) is called ONCE per round; None: the scalar callback per item.  k = 1 is
+        insert_largest_error_point (with one batched callback instead of hundreds of scalar ones).  Returns the
+        inserted tuples [(err, f, [x...]), ...]."""
+        k = int(k)
+        err, f, xs = np.empty(max(k, 1)), np.empty(max(k, 1)), np.empty((max(k, 1), self.N))
+        if fn_batch is not None:
+            def _tramp(nd, n, x, out, _user):
+                a = np.ctypeslib.as_array(x, shape=(n, nd))
+                np.ctypeslib.as_array(out, shape=(n,))[:] = np.asarray(fn_batch(a.copy()), dtype=np.float64).reshape(n)
+            cb = DLI_FN_BATCH(_tramp)
+        else:
+            cb = C.cast(None, DLI_FN_BATCH)
+        n = lib().dli_dd_refine(self._h, k, float(rel_threshold), cb, None, err.ctypes.data, f.ctypes.data, xs.ctypes.data)
+        if n < 0:
+            raise AssertionError("insert_largest_error_points: no callback")
         return [(float(err[i]), float(f[i]), xs[i].tolist()) for i in range(n)]
 
     def rebuild_error_queue(self):

@@ -23,6 +23,7 @@
 // New:
 //   interp_batch(xs, n, ys, status)   n queries at once; host or device pointers (see dli_interp in dli.h)
 //   insert_many(xs, f, n)             bulk insertion (spatially sorted)
+//   insert_largest_error_points(k, fn_batch)   k-at-a-time refinement with one batched callback per round (dli_dd_refine)
 //
 // Point / ErrorTuple live in namespace delaunay_d and are exported to the global namespace unless the 2D header
 // (which, as in the reference, defines global types of the same names) was included first.
@@ -139,6 +140,19 @@ class Delaunay_incremental_interp_d {
     assert(rc == DLI_OK && "insert_largest_error_point: empty queue or no callback");
     if (rc != DLI_OK) throw std::logic_error("insert_largest_error_point: empty queue or no callback");
     return ErrorTuple(e, f, Point(x));
+  }
+  // k-at-a-time form (new, dli_dd_refine): up to k largest-error tuples on simplices that share no vertex are inserted,
+  // then the items of every simplex created in the round are evaluated with ONE call of fn_batch (nullptr: m_fn per
+  // item).  k = 1 is insert_largest_error_point.
+  std::vector<ErrorTuple> insert_largest_error_points(size_t k, dli_fn_batch fn_batch = nullptr, void *user = nullptr,
+                                                      double rel_threshold = 0.25) {
+    std::vector<double> e(k + 1), f(k + 1), xs((k + 1) * (size_t)N);
+    int64_t n = dli_dd_refine(h_, (int64_t)k, rel_threshold, fn_batch, user, e.data(), f.data(), xs.data());
+    if (n < 0) throw std::logic_error("insert_largest_error_points: no callback");
+    std::vector<ErrorTuple> out;
+    for (int64_t i = 0; i < n; i++)
+      out.push_back(ErrorTuple(e[(size_t)i], f[(size_t)i], Point(std::vector<double>(xs.begin() + i * N, xs.begin() + (i + 1) * N))));
+    return out;
   }
   ErrorTuple get_largest_error_tuple() const {
     double e, f;

@@ -166,6 +166,12 @@ int dli_dd_export(const dli_dd *d, double *coords, double *f, int32_t *sv, int32
 int dli_dd_interp(dli_dd *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
                   void *stream);
 const dli_mesh *dli_dd_device_mesh(dli_dd *d);
+/* k-at-a-time adaptive refinement, the dD form of dli_di2_refine (same rules): up to k tuples on simplices
+ * that share no vertex are inserted, then the items of every simplex created in the round are evaluated with ONE call of
+ * fn_batch (NULL: the scalar callback of dli_dd_create per item).  err / f [k], xs [k][n_dims] receive the inserted
+ * tuples (any may be NULL).  Returns the number of points inserted (0: empty queue), < 0 on error. */
+int64_t dli_dd_refine(dli_dd *d, int64_t k, double rel_threshold, dli_fn_batch fn_batch, void *user, double *err, double *f,
+                      double *xs);
 int64_t dli_dd_sync_count(const dli_dd *d); /* how often the device mesh was (re-)created */
 /* (full re-flattens, in-place patches) of the device mesh so far: after insert / insert_largest_error_point the next
  * interp re-sends only the simplices the insertions created, the ring around them and the stars of overwritten

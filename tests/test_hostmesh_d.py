@@ -182,3 +182,49 @@ def test_adaptive_insertion_on_a_general_hull_always_adds_a_vertex(d):
             seen.add(tuple(e[2]))
         q = t.get_error_queue()
         assert all(q[i][0] >= q[i + 1][0] for i in range(len(q) - 1))
+
+
+@pytest.mark.parametrize("d", [2, 3, 4])
+def test_dd_refine_k_at_a_time(d):
+    """dli_dd_refine: k = 1 reproduces insert_largest_error_point tuple by tuple (same queue afterwards); a batched
+    round inserts several points with ONE callback, leaves a valid Delaunay triangulation and a queue equal to a
+    from-scratch evaluation of every simplex"""
+    al = np.array([0.3, 0.6, 0.2, 0.1])[:d]
+    fn = lambda x: float(np.prod(np.asarray(x) ** al))                 # noqa: E731
+    fnb = lambda a: np.prod(a ** al, axis=1)                            # noqa: E731
+    lo, hi = 0.0, 4.0                                                   # box hull with exactly representable faces
+    corners = np.array(np.meshgrid(*([[lo, hi]] * d), indexing="ij")).reshape(d, -1).T
+    inner = np.random.default_rng(40 + d).random((60, d)) * 3.0 + 0.5
+    pts = np.concatenate([corners, inner])
+    fv = np.array([fn(p) for p in pts])
+
+    def fresh():
+        t = dl.Delaunay_incremental_interp_d(d, fn)
+        for p, v in zip(pts, fv):
+            t.insert(p.tolist(), float(v))
+        return t
+    a, b = fresh(), fresh()
+    for _ in range(15):
+        ta = a.insert_largest_error_point()
+        tb = b.insert_largest_error_points(1, fn_batch=fnb)
+        assert len(tb) == 1 and tb[0][2] == ta[2] and tb[0][0] == ta[0]
+    qa, qb = a.get_error_queue(), b.get_error_queue()
+    assert len(qa) == len(qb) and all(x[0] == y[0] and x[2] == y[2] for x, y in zip(qa, qb))
+    calls = []
+    c = fresh()
+    n0 = c.number_of_vertices()
+
+    def counted(arr):
+        calls.append(len(arr))
+        return fnb(arr)
+    got = c.insert_largest_error_points(8, fn_batch=counted, rel_threshold=0.0)
+    assert 1 <= len(got) <= 8 and c.number_of_vertices() == n0 + len(got) and len(calls) == 1
+    assert c.validate() == 0
+    errs = sorted(e[0] for e in c.get_error_queue())
+    # from-scratch evaluation of the same triangulation: insert the same points into a new object
+    co = np.array(c.get_all_vertices())
+    r = dl.Delaunay_incremental_interp_d(d, fn)
+    for row in co:
+        r.insert(row[:d].tolist(), float(row[d]))
+    ref = sorted(e[0] for e in r.get_error_queue())
+    assert len(errs) == len(ref) and np.allclose(errs, ref, rtol=1e-9, atol=1e-18)
