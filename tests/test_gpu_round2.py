@@ -303,3 +303,39 @@ def test_start_copies_equal_hinted_start(gpu, dim, nv):
     on.set_values(2.0 * f + 1.0)
     y3 = on.interp(q)
     assert _rel(y3[ok], 2.0 * yo[ok] + 1.0) <= 1e-11
+
+
+@pytest.mark.parametrize("d", [3, 4])
+def test_dd_refine_rounds_keep_the_device_mesh_in_step(gpu, d):
+    """dD form of the test above: dli_dd_refine rounds + the dD incremental device update; after every round the device
+    mesh answers like the oracle on the exported triangulation, and the GPU evaluator over the refined mesh equals the
+    queue the rounds left behind"""
+    import delaunay_linterp_b200 as dl
+    al = np.array([0.3, 0.6, 0.2, 0.1])[:d]
+    fn = lambda x: float(np.prod(np.asarray(x) ** al) + 1.0)   # noqa: E731
+    fnb = lambda a: np.prod(a ** al, axis=1) + 1.0              # noqa: E731
+    corners = np.array(np.meshgrid(*([[0.0, 4.0]] * d), indexing="ij")).reshape(d, -1).T
+    pts = np.concatenate([corners, np.random.default_rng(130 + d).random((1500 if d == 3 else 500, d)) * 3.8 + 0.1])
+    t = dl.Delaunay_incremental_interp_d(d, fn)
+    t.insert_many(pts, fnb(pts), use_gpu=False)
+    q = np.random.default_rng(131).random((60000, d)) * 4.2 - 0.1
+    t.interp(q)
+    full0, inc0 = t.sync_counts()
+    total = 0
+    for rnd in range(6):
+        total += len(t.insert_largest_error_points(16, fn_batch=fnb, rel_threshold=0.0))
+        ys, sx, st = t.interp(q, return_simplex=True, return_status=True)
+        c, f, sv, sn = t.export()
+        om = OracleMesh(c, f, sv, sn)
+        yo, so, sto = om.interp(q, mode=1, nthreads=8)
+        ok = sto == 0
+        assert np.array_equal(st, sto) and _rel(ys[ok], yo[ok]) <= REL_TOL
+        cg, _ = om.classify(q, sx)
+        assert cg[ok].all()
+    full1, inc1 = t.sync_counts()
+    assert total >= 20 and inc1 - inc0 >= 1 and (full1 - full0) + (inc1 - inc0) == 6
+    m = dl.Mesh(c, f, sv, sn)
+    cent, isx, iv = m.simplex_error_items()
+    err = np.sort(m.simplex_error(fnb(cent)))
+    have = np.sort(np.array([e[0] for e in t.get_error_queue()]))
+    assert len(err) == len(have) and np.allclose(err, have, rtol=1e-9, atol=1e-18)
