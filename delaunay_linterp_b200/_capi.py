@@ -11,6 +11,7 @@ LIB_PATH = os.environ.get("DLI_LIB") or os.path.join(_HERE, "libdli.so")  # DLI_
 
 DLI_MAX_DIM = 4
 DLI_MESH_HEADER_WORDS = 16
+DLI_NOALLOC_MAX_QUERIES = 1 << 20
 
 STATUS_OK, STATUS_OUTSIDE_PROJECTED, STATUS_OUTSIDE_NAN, STATUS_STEP_LIMIT, STATUS_NO_MESH = 0, 1, 2, 3, 4
 STATUS_ON_EDGE, STATUS_ON_VERTEX = 5, 6
@@ -73,6 +74,7 @@ SYMBOLS = [
     ("dli_mesh_device_bytes", C.c_int64, [_vp]),
     ("dli_mesh_get_simplices", C.c_int, [_vp, _vp, _vp]),
     ("dli_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    ("dli_interp_noalloc", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_locate", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp]),
     ("dli_gradient", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_simplex_error_count", C.c_int64, [_vp]),

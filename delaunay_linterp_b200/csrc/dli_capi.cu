@@ -1553,6 +1553,106 @@ extern "C" int dli_gradient(const dli_mesh *m, int64_t n, const double *xs, doub
   return interp_common(m, n, xs, grads, so, sto, stream, "dli_gradient", 1);
 }
 
+// ---------------------------------------------------------------------------------------------
+// dli_interp_noalloc: batched interp for callers that must not allocate device memory.
+//
+// dli_interp takes its straggler queue (the hand-over list between the fast walk kernel and the exact-arithmetic
+// kernel: two int32 per queued query plus a counter) from the stream-ordered pool on every call.  Some callers
+// cannot have that: a host program that handed all of the GPU's memory to its own pool at start-up and left the
+// driver nothing to give out; a solver inside a section where an allocation may take a driver lock or synchronise
+// the device and stall its other streams; a driver configuration without stream-ordered pools.  For them the queue
+// lives in the array below, part of the library image: every GPU that loads libdli.so holds these 8 MiB + 256 B
+// until the process exits, whether or not the entry point is ever called.
+//
+// g_noalloc_scratch is a device array.  In host code its name stands for a host-side shadow object, not for memory the
+// GPU can use, so the host never passes the name to a kernel: noalloc_scratch() asks the runtime for the array's
+// address on the current device (cudaGetSymbolAddress) once per device and hands that out.
+// ---------------------------------------------------------------------------------------------
+static_assert(DLI_NOALLOC_MAX_QUERIES > 0 && DLI_NOALLOC_MAX_QUERIES <= (1ll << 22), "keep the resident scratch modest");
+constexpr size_t kNoAllocHead = 256;   // the counter has the first 256 bytes to itself
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHead + sizeof(int32_t) * 2 * (size_t)DLI_NOALLOC_MAX_QUERIES];
+
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char *g_noalloc_addr[kNoAllocMaxDevices];   // per device ordinal; nullptr until the set-up below ran
+
+// device `device` must be current
+static int noalloc_scratch(int device, unsigned char **out) {
+  if (device < 0 || device >= kNoAllocMaxDevices)
+    return fail(DLI_ERR_UNSUPPORTED, "dli_interp_noalloc: device ordinal beyond the 64 the address table holds");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_addr[device]) {
+    void *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(DLI_ERR_CUDA, std::string("dli_interp_noalloc: cudaGetSymbolAddress(scratch) failed: ") + cudaGetErrorString(e));
+    }
+    g_noalloc_addr[device] = static_cast<unsigned char *>(p);
+  }
+  *out = g_noalloc_addr[device];
+  return DLI_OK;
+}
+
+extern "C" int dli_interp_noalloc(const dli_mesh *m, int64_t n, const double *xs, double *ys, int32_t *so, uint8_t *sto,
+                                  void *stream) {
+  const char *who = "dli_interp_noalloc";
+  if (!m) return fail(DLI_ERR_ARG, std::string(who) + ": NULL mesh");
+  if (n < 0) return fail(DLI_ERR_ARG, std::string(who) + ": negative n");
+  if (n > DLI_NOALLOC_MAX_QUERIES) {
+    char b[200];
+    snprintf(b, sizeof b, "%s: n = %lld exceeds DLI_NOALLOC_MAX_QUERIES = %lld (the resident scratch holds no more; split the batch or call dli_interp)",
+             who, (long long)n, (long long)DLI_NOALLOC_MAX_QUERIES);
+    return fail(DLI_ERR_ARG, b);
+  }
+  if (n == 0) return DLI_OK;
+  if (!xs || !ys) return fail(DLI_ERR_ARG, std::string(who) + ": xs / ys is NULL");
+  if (m->collect_timing)
+    return fail(DLI_ERR_UNSUPPORTED, std::string(who) + ": per-launch timing creates CUDA events; switch it off (dli_mesh_collect_stats(mesh, 0 or 1))");
+  DeviceGuard guard(m->device);
+  if (!guard.ok) return fail(DLI_ERR_CUDA, std::string(who) + ": cannot select device");
+  const void *ptrs[4] = {xs, ys, so, sto};
+  for (const void *p : ptrs)
+    if (p) {
+      bool known;
+      if (!is_device_ptr(p, &known)) return fail(DLI_ERR_ARG, std::string(who) + ": device pointers only (the host-pointer pipeline of dli_interp owns staging buffers)");
+    }
+  if (m->dim == 2 && ((uintptr_t)xs & 15)) return fail(DLI_ERR_ARG, std::string(who) + ": 2D device arrays of coordinate pairs must be 16-byte aligned");
+  if (((uintptr_t)xs & 7) || ((uintptr_t)ys & 7) || ((uintptr_t)so & 3)) return fail(DLI_ERR_ARG, std::string(who) + ": misaligned device pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  int launches = 0;
+  if (m->ns == 0) {
+    k_fill_nomesh<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, ys, so, sto);
+    CU(cudaGetLastError());
+    launches = 1;
+  } else {
+    unsigned char *scratch = nullptr;
+    const int rc = noalloc_scratch(m->device, &scratch);
+    if (rc != DLI_OK) return rc;
+    Launch L;
+    L.m = m; L.st = st; L.stats = m->d_stats;
+    L.qcount = reinterpret_cast<unsigned int *>(scratch);
+    L.queue = reinterpret_cast<int32_t *>(scratch + kNoAllocHead);
+    L.qcap = (unsigned int)n;   // room for every query of the batch: the queue cannot overflow
+    if (m->collect_stats) CU(cudaMemsetAsync(m->d_stats, 0, sizeof(unsigned long long) * ST_WORDS, st));
+    // the array keeps what the previous call left in it: the counter must start at zero, the slots are written
+    // before they are read
+    CU(cudaMemsetAsync(L.qcount, 0, sizeof(unsigned int), st));
+    if (m->collect_stats) {
+      if (m->opt.epilogue != DLI_EPILOGUE_CLOSED_FORM) launch_any<true, 0>(L, n, xs, ys, so, sto);
+      else launch_any<true, 1>(L, n, xs, ys, so, sto);
+    } else {
+      if (m->opt.epilogue != DLI_EPILOGUE_CLOSED_FORM) launch_any<false, 0>(L, n, xs, ys, so, sto);
+      else launch_any<false, 1>(L, n, xs, ys, so, sto);
+    }
+    CU(cudaGetLastError());
+    launches = L.launches;
+  }
+  m->last.kernel_launches = launches;
+  m->last.queries = n;
+  return DLI_OK;
+}
+
 extern "C" int dli_mesh_collect_stats(dli_mesh *m, int enable) {
   if (!m) return fail(DLI_ERR_ARG, "NULL mesh");
   m->collect_stats = (enable & 1) != 0;

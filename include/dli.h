@@ -181,6 +181,34 @@ int dli_mesh_get_simplices(const dli_mesh *mesh, int32_t *simplex_vertices, int3
 int dli_interp(const dli_mesh *mesh, int64_t n, const double *xs, double *ys, int32_t *simplex_out,
                uint8_t *status_out, void *stream);
 
+/*
+ * dli_interp for callers that cannot allocate device memory.  No counterpart in the reference (it has no GPU
+ * path and no allocation contract); it exists because of how this engine is built: dli_interp draws its straggler
+ * queue -- the hand-over list between the fast walk kernel and the exact-arithmetic kernel -- from the CUDA
+ * stream-ordered pool on every call.  That is a problem for
+ *   - a host program that gave ALL device memory to its own pool at start-up, so the driver has nothing left for us;
+ *   - a loop that may not risk the driver lock or the device-wide synchronisation an allocation can imply while
+ *     its other streams are busy;
+ *   - a driver set-up without stream-ordered memory pools.
+ * This entry point makes no cudaMalloc / cudaMallocAsync / cudaFree call and calls no allocating library.  Its queue
+ * is a fixed array inside libdli.so's device image: 8 MiB + 256 B on EVERY GPU that loads the library, held until
+ * the process exits, used or not.  Same kernels, same arithmetic, same results as dli_interp.
+ *   limit    n <= DLI_NOALLOC_MAX_QUERIES; a larger n returns DLI_ERR_ARG and touches nothing (split the batch)
+ *   pointers DEVICE pointers only (xs, ys, and simplex_out / status_out when given); host pointers return
+ *            DLI_ERR_ARG -- the host pipeline of dli_interp owns staging buffers, which is what this call avoids
+ *   sharing  all calls on one GPU -- any mesh, any stream, any thread -- use the same array.  Two calls whose
+ *            kernels overlap on the GPU race on it and return garbage: keep them on one stream, or order them
+ *            with events.  The array keeps the previous call's contents; the call re-zeroes the one word
+ *            (the queue counter) that has to start at zero, with a cudaMemsetAsync on `stream`.
+ *   set-up   the FIRST call on each device looks up the array's device address (cudaGetSymbolAddress) and keeps
+ *            it; make that first call before you begin any stream capture.
+ *   timing   returns DLI_ERR_UNSUPPORTED while per-launch timing (dli_mesh_collect_stats bit 1) is on, because that
+ *            mode creates CUDA events per call; the counters (bit 0) work.
+ */
+#define DLI_NOALLOC_MAX_QUERIES (1 << 20)
+int dli_interp_noalloc(const dli_mesh *mesh, int64_t n, const double *xs, double *ys, int32_t *simplex_out,
+                       uint8_t *status_out, void *stream);
+
 /* Point location only (CGAL locate as used at src/delaunay_2_interp.h:525, src/delaunay_d_interp.h:990).
    2D queries outside the hull report the hull face behind the canonical visible hull edge. */
 int dli_locate(const dli_mesh *mesh, int64_t n, const double *xs, int32_t *simplex_out, uint8_t *status_out,
