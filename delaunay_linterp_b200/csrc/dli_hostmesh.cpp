@@ -790,8 +790,10 @@ HullEdge2 canonical_visible_hull_edge(const HostMesh2 &hm, double px, double py,
 }
 constexpr int kMaxProjectionsHost = 16;   // = kMaxProjections of dli_device.cuh
 
-// one query; returns the status, the face in *face_out (-1: none), the value in *y
-uint8_t host_interp_point2(const HostMesh2 &hm, double px, double py, int start, int *face_out, double *y) {
+// one query; returns the status, the face in *face_out (-1: none), the value in *y.  outside_nan: the handle's
+// dli_options.outside_nan -- a query outside the hull is not projected, it reports NaN like the device kernels do
+uint8_t host_interp_point2(const HostMesh2 &hm, double px, double py, int start, int *face_out, double *y,
+                           bool outside_nan = false) {
   *face_out = -1;
   *y = std::nan("");
   if (hm.dim < 2) return DLI_STATUS_NO_MESH;
@@ -802,6 +804,7 @@ uint8_t host_interp_point2(const HostMesh2 &hm, double px, double py, int start,
   for (int proj = 0;; proj++) {
     f = hm.locate(px, py, f);
     if (!hm.is_inf(f)) break;
+    if (outside_nan) return DLI_STATUS_OUTSIDE_NAN;   // *y is NaN, *face_out is -1
     status = DLI_STATUS_OUTSIDE_PROJECTED;
     if (proj >= kMaxProjectionsHost || stuck) { f = hull_edge_of(hm, f).face; break; }   // accept the hull face
     const HullEdge2 h = canonical_visible_hull_edge(hm, px, py, f);
@@ -823,10 +826,11 @@ static void di2_host_interp(dli_di2 *d, int64_t n, const double *xs, double *ys,
   HostMesh2 &hm = d->hm;
   if (so && !hm.fid_compact) { hm.renumber(); d->need_full = true; d->dirty = true; }
   int start = d->host_last.load(std::memory_order_relaxed);
+  const bool outside_nan = d->have_opt && d->opt.outside_nan != 0;
   for (int64_t i = 0; i < n; i++) {
     int face;
     double y;
-    const uint8_t st = host_interp_point2(hm, xs[2 * i], xs[2 * i + 1], start, &face, &y);
+    const uint8_t st = host_interp_point2(hm, xs[2 * i], xs[2 * i + 1], start, &face, &y, outside_nan);
     ys[i] = y;
     if (so) so[i] = face >= 0 ? hm.fid[face] : -1;
     if (sto) sto[i] = st;
@@ -835,6 +839,9 @@ static void di2_host_interp(dli_di2 *d, int64_t n, const double *xs, double *ys,
   d->host_last.store(start, std::memory_order_relaxed);
 }
 static bool di2_take_host(const dli_di2 *d, int64_t n, const double *xs, const double *ys, const int32_t *so, const uint8_t *sto) {
+  // the host walk evaluates in the reference's operation order: a handle that asked for the closed-form epilogue
+  // keeps every batch on the device, so that its values do not depend on the batch size
+  if (d->have_opt && d->opt.epilogue == DLI_EPILOGUE_CLOSED_FORM) return false;
   return n > 0 && xs && ys && dli::host_batch_is_small(n, d->hm.dim == 2 ? d->hm.n_finite : 0, 2) &&
          dli::is_plain_host_pointer(xs) && dli::is_plain_host_pointer(ys) && dli::is_plain_host_pointer(so) &&
          dli::is_plain_host_pointer(sto);

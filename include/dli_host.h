@@ -92,7 +92,10 @@ int dli_di2_export(const dli_di2 *d, double *coords, double *f, int32_t *tri, in
 /* batched interp on the GPU; after insertions the device mesh is brought in step lazily: the stars of the inserted
    points are patched in place (dli_mesh_update, ids of export() are stable across insertions), a full re-flatten
    happens after bulk insertion, when more faces changed than exist, or when the mesh cannot be patched.  Host or device pointers as dli_interp.
-   With dimension < 2 every query reports DLI_STATUS_NO_MESH (the reference throws, :546-551). */
+   With dimension < 2 every query reports DLI_STATUS_NO_MESH (the reference throws, :546-551).
+   Very small batches in plain host memory (the reference's one-point-per-call usage) are answered by an exact walk on
+   the host triangulation; that path follows the handle's options: outside_nan = 1 gives NaN / DLI_STATUS_OUTSIDE_NAN
+   outside the hull there too, and a handle set to DLI_EPILOGUE_CLOSED_FORM never takes it. */
 int dli_di2_interp(dli_di2 *d, int64_t n, const double *xs, double *ys, int32_t *simplex_out, uint8_t *status_out,
                    void *stream);
 /* batched gradient on the GPU (dli_gradient): grads [n][2]; NaN outside the hull (:610-611, :618) */

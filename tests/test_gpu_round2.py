@@ -86,6 +86,22 @@ def test_outside_nan_option_2d(gpu):
     assert _rel(yd[~out], y0[~out]) <= REL_TOL
 
 
+def test_small_batches_equal_large_batches_with_outside_nan(gpu):
+    """the host path for small batches follows the handle's options: with outside_nan=1 a one-point call
+    and a 100k-query call agree on status and value for the same queries (NaN outside the hull, not a projection)."""
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 3000, 83)
+    q = np.random.default_rng(84).random((100000, 2)) * 1.4 - 0.2
+    t = dl.DelaunayInterp2(outside_nan=1)
+    t.insert_many(pts, f, use_gpu=False)
+    yb, stb = t.interp(q, return_status=True)                     # device
+    assert (stb == dl.STATUS_OUTSIDE_NAN).sum() > 20000 and not (stb == dl.STATUS_OUTSIDE_PROJECTED).any()
+    for i in range(0, 400):
+        y1, st1 = t.interp(q[i:i + 1], return_status=True)        # host
+        assert st1[0] == stb[i], (i, st1[0], stb[i])
+        assert (np.isnan(y1[0]) and np.isnan(yb[i])) or abs(y1[0] - yb[i]) <= REL_TOL * max(abs(yb[i]), 1e-300)
+
+
 def test_empty_mesh_gradient_is_all_nan(gpu):
     """the no-mesh fill must cover 2 n doubles for gradients"""
     import torch

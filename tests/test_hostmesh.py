@@ -217,3 +217,27 @@ def test_refine_k_at_a_time_batched_callback():
         ys, _, _ = OracleMesh(cm, fm, trim, nbm).interp(q, nthreads=4)
         sse.append(float(np.sum((helpers.cobb_douglas(q) - ys) ** 2)))
     assert sse[0] <= 1.5 * sse[1], sse
+
+
+def test_one_point_host_path_honours_outside_nan():
+    """a handle configured with outside_nan=1 answers NaN / OUTSIDE_NAN for a query outside the hull whatever
+    the batch size -- the one-point host path used to project it (src/delaunay_d_interp.h:1005-1008 is the behaviour the
+    option stands for; src/delaunay_2_interp.h:530-545 the default).  No GPU involved: batches this small stay on the host."""
+    import delaunay_linterp_b200 as dl
+    g = helpers.linspace_ref(0.0, 5.0, 6)
+    pts = np.array([[a, b] for a in g for b in g])
+    outside = np.array([[-1.0, 2.0], [6.0, 7.0], [2.5, -0.5]])
+    inside = np.array([[1.3, 2.2], [5.0, 5.0], [0.0, 2.5]])
+    for nan in (0, 1):
+        t = dl.DelaunayInterp2(outside_nan=nan) if nan else dl.DelaunayInterp2()
+        t.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False)
+        y, s, st = t.interp(outside, return_status=True, return_simplex=True)
+        if nan:
+            assert np.isnan(y).all() and (st == dl.STATUS_OUTSIDE_NAN).all() and (s == -1).all()
+        else:
+            assert np.isfinite(y).all() and (st == dl.STATUS_OUTSIDE_PROJECTED).all() and (s >= 0).all()
+        yi, sti = t.interp(inside, return_status=True)
+        assert (sti == 0).all() and np.allclose(yi, helpers.cobb_douglas(inside), atol=0.5)
+    ya = dl.DelaunayInterp2()
+    ya.insert_many(pts, helpers.cobb_douglas(pts), use_gpu=False)
+    assert np.array_equal(ya.interp(inside), yi)      # inside the hull the option changes nothing
