@@ -685,6 +685,7 @@ def run_ours(args, rank, world, local_rank):
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
+        parallel.shutdown_nccl()
         dist.destroy_process_group()
     return 0
 

@@ -1884,6 +1884,10 @@ extern "C" int dli_mesh_header(const dli_mesh *m, int64_t h[DLI_MESH_HEADER_WORD
   // word 15 = records in the walk-record buffer
   h[12] = m->d_fpack ? 1 : 0; h[13] = m->d_fat ? (m->cellmode ? 2 : ((m->dim == 2 && fat_delta(m)) ? 3 : (fat_pack4(m) ? (m->startcopy ? 5 : 4) : (m->startcopy ? 6 : 1)))) : 0;
   h[15] = m->nslots;
+  // word 12, bits 8-11: the options that change what a query returns (the walk-step cap is word 10).  A replica or a
+  // loaded snapshot must answer like its source, so they travel with the mesh: bit 8 = the field is valid, bit 9 =
+  // outside_nan, bits 10-11 = epilogue.  (Word 14 is free here; the snapshot file keeps its slow-face count there.)
+  h[12] |= (1 << 8) | ((m->opt.outside_nan ? 1 : 0) << 9) | ((int64_t)(m->opt.epilogue & 3) << 10);
   // grid origin / inverse cell: bit patterns of doubles do not fit 16 words for 4D; pack o and ic for
   // up to 2 dims here and the rest in the reserved words -> instead expose them through buffer index
   // (see dli_mesh_buffer): index 0 = 96-byte parameter block.
@@ -1904,6 +1908,10 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   m->dim = (int)h[1]; m->nv = h[2]; m->ns = h[3]; m->nh = (int32_t)h[4];
   if (m->dim < 2 || m->dim > 4) { delete m; return fail(DLI_ERR_UNSUPPORTED, "bad dim in header"); }
   resolve_options(opt, &m->opt);
+  if (h[12] & (1 << 8)) {   // result-affecting options of the source win over this side's (older headers: field absent)
+    m->opt.outside_nan = (int32_t)((h[12] >> 9) & 1);
+    m->opt.epilogue = (int32_t)((h[12] >> 10) & 3);
+  }
   if (m->opt.device >= 0) m->device = m->opt.device;
   else cudaGetDevice(&m->device);
   DeviceGuard guard(m->device);
@@ -1911,7 +1919,7 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
   for (int k = 0; k < 4; k++) m->grid.g[k] = (int)h[6 + k];
   int rc = mesh_alloc_common(m);
   // mirror the source's optional buffers exactly (every rank must see the same buffer list)
-  if (rc == DLI_OK && !h[12] && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
+  if (rc == DLI_OK && !(h[12] & 1) && m->d_fpack) { cudaFree(m->d_fpack); m->d_fpack = nullptr; }
   // (mesh_alloc_common sized d_fat from this side's options: drop it and allocate for the source's layout below)
   if (rc == DLI_OK && m->d_fat) { cudaFree(m->d_fat); m->d_fat = nullptr; }
   m->cellmode = h[13] == 2;
@@ -1923,7 +1931,7 @@ extern "C" int dli_mesh_create_from_header(const int64_t h[DLI_MESH_HEADER_WORDS
       (cudaMalloc(&m->d_slot_face, sizeof(int32_t) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess ||
        cudaMalloc(&m->d_rowstart, sizeof(int) * ((size_t)m->grid.g[1] + 1)) != cudaSuccess))
     rc = fail(DLI_ERR_CUDA, "slot table allocation failed");
-  if (rc == DLI_OK && h[12] && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
+  if (rc == DLI_OK && (h[12] & 1) && !m->d_fpack && cudaMalloc(&m->d_fpack, sizeof(ulonglong2) * (size_t)std::max<int64_t>(m->ns, 1)) != cudaSuccess)
     rc = fail(DLI_ERR_CUDA, "packed face allocation failed");
   if (rc == DLI_OK && h[13] && !m->d_fat &&
       cudaMalloc(&m->d_fat, (size_t)fat_record_bytes(m) * (size_t)std::max<int64_t>(m->nslots, 1)) != cudaSuccess)
@@ -2002,6 +2010,7 @@ extern "C" int dli_mesh_set_grid_params(dli_mesh *m, const double *in) {
 namespace {
 struct NcclApi {
   ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*CommUserRank)(const ncclComm_t, int *) = nullptr;
   ncclResult_t (*CommCuDevice)(const ncclComm_t, int *) = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
@@ -2024,6 +2033,7 @@ const NcclApi &nccl_api() {
       if (!h) h = dlopen("libnccl.so", RTLD_NOW);
     }
     a.Broadcast = reinterpret_cast<decltype(a.Broadcast)>(sym("ncclBroadcast"));
+    a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
     a.CommUserRank = reinterpret_cast<decltype(a.CommUserRank)>(sym("ncclCommUserRank"));
     a.CommCuDevice = reinterpret_cast<decltype(a.CommCuDevice)>(sym("ncclCommCuDevice"));
     a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
@@ -2050,8 +2060,11 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
   if (r == ncclSuccess) r = N.CommCuDevice(comm, &dev);
   if (r != ncclSuccess) return nerr(r, "communicator query");
   const bool is_root = rank == root;
-  if (is_root && !*inout) return fail(DLI_ERR_ARG, "dli_mesh_replicate: the root rank must pass its mesh");
-  if (is_root && (*inout)->device != dev) return fail(DLI_ERR_ARG, "dli_mesh_replicate: the root's mesh is not on the communicator's device");
+  // A root that cannot send its mesh still takes part in the header broadcast, with an empty header (ok word 0): the
+  // other ranks then return an error instead of waiting in ncclBroadcast for ever.
+  const bool root_no_mesh = is_root && !*inout;
+  const bool root_wrong_dev = is_root && *inout && (*inout)->device != dev;
+  const bool root_bad = root_no_mesh || root_wrong_dev;
   DeviceGuard guard(dev);
   if (!guard.ok) return fail(DLI_ERR_CUDA, "dli_mesh_replicate: cannot select the communicator's device");
   cudaStream_t st = nullptr;
@@ -2061,7 +2074,8 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
   int64_t w[kRepWords];
   memset(w, 0, sizeof w);
   cudaError_t e = cudaMalloc(&d_hdr, sizeof w);
-  if (e == cudaSuccess && is_root) {
+  if (e == cudaSuccess && root_bad) e = cudaMemcpyAsync(d_hdr, w, sizeof w, cudaMemcpyHostToDevice, st);   // all zero
+  if (e == cudaSuccess && is_root && !root_bad) {
     double gp[3 * DLI_MAX_DIM];
     dli_mesh_header(*inout, w);
     dli_mesh_get_grid_params(*inout, gp);
@@ -2077,8 +2091,10 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
   if (e == cudaSuccess && rc == DLI_OK) e = cudaMemcpyAsync(w, d_hdr, sizeof w, cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess && rc == DLI_OK) e = cudaStreamSynchronize(st);
   dli_mesh *m = is_root ? *inout : nullptr;
+  if (root_no_mesh) rc = fail(DLI_ERR_ARG, "dli_mesh_replicate: the root rank must pass its mesh");
+  else if (root_wrong_dev) rc = fail(DLI_ERR_ARG, "dli_mesh_replicate: the root's mesh is not on the communicator's device");
   if (e == cudaSuccess && rc == DLI_OK && !is_root) {
-    if (w[kRepWords - 1] != 1) rc = fail(DLI_ERR_ARG, "dli_mesh_replicate: no header received from the root");
+    if (w[kRepWords - 1] != 1) rc = fail(DLI_ERR_ARG, "dli_mesh_replicate: no header received from the root (the root rank reports why)");
     dli_options o;
     dli_options_init(&o);
     o.device = dev;
@@ -2090,9 +2106,24 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
       m->n_slow_faces = w[DLI_MESH_HEADER_WORDS + 3 * DLI_MAX_DIM];
     }
   }
-  // every rank walks the same buffer list (the header fixes which optional buffers exist and how large they are).
-  // A rank that failed above still takes part, receiving into nothing is not possible -- so a failed rank leaves the
-  // collective sequence only after reporting; the caller must treat a non-zero return on any rank as fatal for the job
+  // Agree on success before the buffer broadcasts: a rank that could not build its replica (allocation failure, bad
+  // header) cannot receive, and the others must not wait for it.  One int64 min-reduction; every rank takes part,
+  // failed or not, as long as it got this far with a working stream and scratch word.
+  if (N.AllReduce && d_hdr) {
+    int64_t ok = (e == cudaSuccess && rc == DLI_OK) ? 1 : 0;
+    cudaError_t e2 = cudaMemcpyAsync(d_hdr, &ok, sizeof ok, cudaMemcpyHostToDevice, st);
+    if (e2 == cudaSuccess) {
+      r = N.AllReduce(d_hdr, d_hdr, 1, ncclInt64, ncclMin, comm, st);
+      if (r != ncclSuccess && rc == DLI_OK) rc = nerr(r, "status all-reduce");
+    }
+    int64_t all_ok = 0;
+    if (e2 == cudaSuccess) e2 = cudaMemcpyAsync(&all_ok, d_hdr, sizeof all_ok, cudaMemcpyDeviceToHost, st);
+    if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(st);
+    if (e2 != cudaSuccess && e == cudaSuccess) e = e2;
+    if (e == cudaSuccess && rc == DLI_OK && all_ok != 1)
+      rc = fail(DLI_ERR_CUDA, "dli_mesh_replicate: another rank could not take part (its own return value says why); nothing was broadcast");
+  }
+  // every rank walks the same buffer list (the header fixes which optional buffers exist and how large they are)
   if (e == cudaSuccess && rc == DLI_OK) {
     for (int i = 0; i < dli_mesh_num_buffers(m) && rc == DLI_OK; i++) {
       void *p; int64_t b;

@@ -104,18 +104,37 @@ def nccl_communicator(src=0):
     return comm, (lambda: L.ncclCommDestroy(comm))
 
 
+_COMM = None        # (ncclComm_t, world_size): created once per process, kept until shutdown_nccl()
+
+
+def cached_nccl_communicator():
+    """the raw communicator of this process, created on first use and kept: ncclCommInitRank costs 0.2 - 0.6 s per call and
+    grows with the number of ranks (it was paid on every replicate_mesh call).  Collective on first use."""
+    global _COMM
+    import torch.distributed as dist
+    if _COMM is None or _COMM[1] != dist.get_world_size():
+        comm, _destroy = nccl_communicator(src=0)
+        _COMM = (comm, dist.get_world_size())
+    return _COMM[0]
+
+
+def shutdown_nccl():
+    """destroy the cached communicator (optional; call on every rank before destroy_process_group)."""
+    global _COMM
+    if _COMM is not None:
+        _nccl_lib().ncclCommDestroy(_COMM[0])
+        _COMM = None
+
+
 def replicate_mesh_nccl(mesh, src=0):
     """dli_mesh_replicate (include/dli.h) with a raw NCCL communicator: what a C / C++ caller does.  Rank `src` passes
     its Mesh, the others None; returns the local Mesh."""
     import torch.distributed as dist
     from ._capi import check, lib
     from .mesh import Mesh
-    comm, destroy = nccl_communicator(src=src)
-    try:
-        h = C.c_void_p(mesh._h.value if (mesh is not None and dist.get_rank() == src) else None)
-        check(lib().dli_mesh_replicate(C.byref(h), comm, int(src)))
-    finally:
-        destroy()
+    comm = cached_nccl_communicator()
+    h = C.c_void_p(mesh._h.value if (mesh is not None and dist.get_rank() == src) else None)
+    check(lib().dli_mesh_replicate(C.byref(h), comm, int(src)))
     if dist.get_rank() == src:
         return mesh
     return Mesh._from_handle(h, lib().dli_mesh_dim(h))
@@ -125,17 +144,21 @@ def replicate_mesh(mesh, src=0, device=None, use_c_abi=True, **options):
     """Rank `src` passes its Mesh; every other rank passes None and receives a replica whose device buffers
     are filled by an NCCL broadcast.  Returns the local Mesh.  On the NCCL backend the work is done by
     dli_mesh_replicate (one ncclBroadcast per buffer, straight from / into the mesh buffers); otherwise (gloo, or no
-    NCCL library) by torch.distributed broadcasts of the raw buffers."""
+    NCCL library on ANY rank -- the ranks agree on the path with an all-reduce, a mixed choice would deadlock) by
+    torch.distributed broadcasts of the raw buffers.  Either way the replica answers like the source: the options
+    that change results travel in the header; `options` only chooses the launch shape of the replica."""
     import torch
     import torch.distributed as dist
     from .mesh import Mesh
     if use_c_abi and dist.get_backend() == "nccl":
         try:
             _nccl_lib()
-            have = True
+            have = 1
         except OSError:
-            have = False
-        if have:
+            have = 0
+        flag = torch.tensor([have], dtype=torch.int32, device=device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
             return replicate_mesh_nccl(mesh, src=src)
     rank = dist.get_rank()
     if rank == src:

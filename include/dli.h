@@ -254,7 +254,9 @@ int dli_simplex_error_finish(const dli_mesh *mesh, int64_t n, const double *f_at
 /*
  * Multi-GPU replication support: the mesh is a set of device buffers.  Rank 0 flattens; the other ranks
  * allocate an empty mesh of the same shape from the 16-word header and receive the buffers through any
- * broadcast (NCCL / torch.distributed) on the raw device pointers.
+ * broadcast (NCCL / torch.distributed) on the raw device pointers.  The header carries the options that decide what a
+ * query returns (outside_nan, epilogue, the walk-step cap): a replica, and a mesh loaded from a snapshot, answers
+ * like its source whatever `opt` says about those; `opt` chooses the device and the launch shape.
  */
 #define DLI_MESH_HEADER_WORDS 16
 int dli_mesh_header(const dli_mesh *mesh, int64_t header[DLI_MESH_HEADER_WORDS]);

@@ -52,3 +52,40 @@ def test_load_rejects_garbage(gpu, tmp_path):
     (tmp_path / "trunc.dli").write_bytes(data[: len(data) // 2])
     with pytest.raises(dl.DliError):
         dl.Mesh.load(tmp_path / "trunc.dli")
+
+
+@pytest.mark.parametrize("opts", [{"outside_nan": 1}, {"epilogue": "closed_form"}, {"outside_nan": 1, "epilogue": "reference"},
+                                  {"max_walk_steps": 3}])
+def test_replica_and_snapshot_answer_like_their_source(gpu, tmp_path, opts):
+    """the options that change what a query returns travel in the mesh header, so a replica built with
+    default options (what dli_mesh_replicate does on the receiving ranks) and a snapshot loaded with default options
+    answer like the mesh they came from.  1-GPU form of the replicate path: header -> dli_mesh_create_from_header ->
+    dli_mesh_buffer_read / _write through a device bounce buffer (what parallel.replicate_mesh does between ranks)."""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(2, 3000, 47)
+    q = np.random.default_rng(8).random((80000, 2)) * 1.3 - 0.15
+    m = dl.Mesh(pts, f, sv, sn, **opts)
+    header, gp = m.header()
+    r = dl.Mesh.from_header(header, gp)                      # no options on the receiving side
+    assert len(r.buffers()) == len(m.buffers())
+    for i, ((_, nb), (_, nb_r)) in enumerate(zip(m.buffers(), r.buffers())):
+        assert nb == nb_r, "buffer %d: %d vs %d bytes" % (i, nb, nb_r)
+        if nb == 0:
+            continue
+        buf = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        m.buffer_read(i, buf.data_ptr())
+        r.buffer_write(i, buf.data_ptr())
+    torch.cuda.synchronize()
+    path = tmp_path / "mesh.dli"
+    m.save(path)
+    s = dl.Mesh.load(path)                                   # default options here too
+    y0, s0, t0 = m.interp(q, return_simplex=True, return_status=True)
+    if "outside_nan" in opts:
+        assert (t0 == dl.STATUS_OUTSIDE_NAN).sum() > 5000
+    if "max_walk_steps" in opts:
+        assert (t0 == dl.STATUS_STEP_LIMIT).sum() > 1000
+    for other in (r, s):
+        y1, s1, t1 = other.interp(q, return_simplex=True, return_status=True)
+        assert np.array_equal(t0, t1) and np.array_equal(s0, s1)
+        assert np.array_equal(np.isnan(y0), np.isnan(y1)) and np.array_equal(y0[np.isfinite(y0)], y1[np.isfinite(y1)])
