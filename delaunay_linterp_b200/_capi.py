@@ -143,7 +143,6 @@ HOST_SYMBOLS = [
     ("dli_dd_interp", C.c_int, [_vp, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
     ("dli_dd_device_mesh", _vp, [_vp]),
     ("dli_dd_refine", C.c_int64, [_vp, C.c_int64, C.c_double, DLI_FN_BATCH, _vp, _vp, _vp, _vp]),
-    ("dli_dd_sync_count", C.c_int64, [_vp]),
     ("dli_dd_sync_counts", None, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     ("dli_dd_set_options", C.c_int, [_vp, C.POINTER(Options)]),
     ("dli_dd_get_all_vertices", C.c_int64, [_vp, _vp]),

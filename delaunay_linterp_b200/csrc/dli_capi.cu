@@ -156,7 +156,9 @@ struct dli_mesh {
   bool collect_timing = false;  // CUDA events around the interp kernels
   unsigned long long *d_stats = nullptr;
   float *h_straggler_frac = nullptr;   // mapped pinned word written by the exact passes: straggler fraction of the last launch
-  mutable dli_stats last{};
+  // most recent call's launch / query count; written by concurrent callers of one mesh (dli.h allows them), so atomic:
+  // the reader sees the numbers of SOME recent call, never a torn value
+  mutable std::atomic<int64_t> last_launches{0}, last_queries{0};
   mutable std::mutex ev_mu;
   mutable std::vector<cudaEvent_t> ev;  // triples (before fast, after fast, after full)
   // host-pointer path staging ring (created on first use)
@@ -1529,8 +1531,8 @@ int interp_common(const dli_mesh *m, int64_t n, const double *xs, double *ys, in
   }
   if (dev) rc = run_device(m, n, xs, ys, so, sto, (cudaStream_t)stream, &launches, out);
   else rc = run_host(m, n, xs, ys, so, sto, &launches, out);
-  m->last.kernel_launches = launches;
-  m->last.queries = n;
+  m->last_launches.store(launches, std::memory_order_relaxed);
+  m->last_queries.store(n, std::memory_order_relaxed);
   return rc;
 }
 
@@ -1648,8 +1650,8 @@ extern "C" int dli_interp_noalloc(const dli_mesh *m, int64_t n, const double *xs
     CU(cudaGetLastError());
     launches = L.launches;
   }
-  m->last.kernel_launches = launches;
-  m->last.queries = n;
+  m->last_launches.store(launches, std::memory_order_relaxed);
+  m->last_queries.store(n, std::memory_order_relaxed);
   return DLI_OK;
 }
 
@@ -1670,12 +1672,12 @@ extern "C" int dli_mesh_get_stats(const dli_mesh *m, dli_stats *out) {
   unsigned long long w[ST_WORDS];
   CU(cudaDeviceSynchronize());
   CU(cudaMemcpy(w, m->d_stats, sizeof w, cudaMemcpyDeviceToHost));
-  out->queries = m->last.queries;
+  out->queries = m->last_queries.load(std::memory_order_relaxed);
   out->walk_steps = (int64_t)w[ST_STEPS];
   out->max_walk_steps = (int64_t)w[ST_MAXSTEPS];
   out->exact_fallbacks = (int64_t)w[ST_EXACT];
   out->outside = (int64_t)w[ST_OUTSIDE];
-  out->kernel_launches = m->last.kernel_launches;
+  out->kernel_launches = m->last_launches.load(std::memory_order_relaxed);
   out->straggler_queries = (int64_t)w[ST_HARD];
   out->slow_simplices = m->n_slow_faces;
   out->fast_kernel_launches = 0;

@@ -1144,7 +1144,6 @@ const dli_mesh *dli_dd_device_mesh(dli_dd *d) {
   if (dd_refresh(d) != DLI_OK) return nullptr;
   return d->mesh;
 }
-int64_t dli_dd_sync_count(const dli_dd *d) { return d ? d->n_full : 0; }
 void dli_dd_sync_counts(const dli_dd *d, int64_t *n_full, int64_t *n_incremental) {
   if (n_full) *n_full = d ? d->n_full : 0;
   if (n_incremental) *n_incremental = d ? d->n_patch : 0;

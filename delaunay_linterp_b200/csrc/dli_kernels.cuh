@@ -72,7 +72,8 @@ __device__ __forceinline__ bool is_overflow_mark(const double *__restrict__ ys, 
 // shared memory).  Walk-length variance therefore costs no SIMT efficiency in the step body.
 // Predicates are filter-only here; queries it cannot certify (filter failure, hull exit, long walk)
 // are appended to `queue` for k_interp2_full.  If the queue overflows (`queue_cap`), the counter
-// keeps growing and k_interp2_full re-runs the whole batch (degenerate inputs only).
+// keeps growing, the query's result slot receives a reserved mark instead (kOverflowBits / kOverflowSimplex) and
+// k_interp2_full, seeing count > cap, scans the results for marks and serves those queries from their start hint.
 // OUT = 0: ys[n] receives the interpolated value; OUT = 1 (dli_gradient): ys is a double2 array and receives the
 // gradient of the located face (strictly interior queries only; everything else goes to the exact pass).
 template <bool STATS, int EPI, bool PACKED, int OUT = 0>

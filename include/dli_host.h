@@ -162,7 +162,9 @@ int64_t dli_dd_get_error_queue(dli_dd *d, int64_t cap, double *err, double *f, d
    (k-th entry opposite vertex k, -1 = hull); any may be NULL */
 int dli_dd_export(const dli_dd *d, double *coords, double *f, int32_t *sv, int32_t *sn);
 
-/* batched interp.  The device mesh is re-created lazily after insertions.  Host or device pointers as dli_interp;
+/* batched interp.  After insertions the device mesh is brought in step lazily: patched in place through dli_mesh_update
+   (stable compact simplex ids), re-created when it cannot be patched (dli_dd_sync_counts tells which happened how
+   often).  Host or device pointers as dli_interp;
    queries outside the hull (or before n_dims + 1 affinely independent points exist) get a quiet NaN (:1005-1008) and
    DLI_STATUS_OUTSIDE_NAN / DLI_STATUS_NO_MESH.  Small batches of host pointers (one point at a time, as the reference's
    own loops call it) are answered on the host by an exact walk on the triangulation -- no GPU call; see dli_host_small.h. */
@@ -175,7 +177,6 @@ const dli_mesh *dli_dd_device_mesh(dli_dd *d);
  * tuples (any may be NULL).  Returns the number of points inserted (0: empty queue), < 0 on error. */
 int64_t dli_dd_refine(dli_dd *d, int64_t k, double rel_threshold, dli_fn_batch fn_batch, void *user, double *err, double *f,
                       double *xs);
-int64_t dli_dd_sync_count(const dli_dd *d); /* how often the device mesh was (re-)created */
 /* (full re-flattens, in-place patches) of the device mesh so far: after insert / insert_largest_error_point the next
  * interp re-sends only the simplices the insertions created, the ring around them and the stars of overwritten
  * vertices (dli_mesh_update; the reference's dirty list: modified_cgal/Convex_hull_d.h:1172-1178 consumed at
