@@ -127,6 +127,42 @@ static int run(int N, bool host_only) {
     // regular-grid interpolant does not depend on how each grid square is split only where f is bilinear; accept the
     // published order of magnitude and require the adaptive grid to beat the regular one, as the reference shows
     CHECK(sse1 > 0.5 && sse1 < 5.0);
+    // Tie the dD arithmetic (N + 2 LU determinants of Gmpq differences, src/delaunay_d_interp.h:601-650, 988-1010) to
+    // the 2D class, whose branch the README's two known answers pin (src/delaunay_2_interp.h:515-572): the same points
+    // in general position -- so that the Delaunay triangulation is unique and both classes hold the same triangles --
+    // through both classes, compared query by query.  (The two drop-in headers both define the reference's global names
+    // Point / ErrorTuple and cannot share a translation unit, as in the reference; the 2D class is driven through the
+    // dli_di2_* calls its header forwards to.)
+    Delaunay_incremental_interp_d dd(2);
+    dli_di2 *d2 = dli_di2_create(nullptr, nullptr);
+    CHECK(d2 != nullptr);
+    unsigned long long lcg = 88172645463325252ull;
+    auto rnd = [&lcg]() {
+      lcg = lcg * 6364136223846793005ull + 1442695040888963407ull;
+      return (double)(lcg >> 11) / 9007199254740992.0;
+    };
+    for (int i = 0; i < 400; i++) {
+      array<double, 2> x = {0.01 + 4.99 * rnd(), 0.01 + 4.99 * rnd()};
+      const double f = fn(2, x.data());
+      dd.insert(x.begin(), x.end(), f);
+      CHECK(dli_di2_insert(d2, x[0], x[1], f) >= 0);
+    }
+    int compared = 0;
+    double worst = 0.0;
+    for (int i = 0; i < 2000; i++) {
+      array<double, 2> q = {0.01 + 4.99 * rnd(), 0.01 + 4.99 * rnd()};
+      const double a = dd.interp(q.begin(), q.end());
+      if (std::isnan(a)) continue;                       // outside the hull: the dD class answers NaN, the 2D class projects
+      double b = 0.0;
+      CHECK(dli_di2_interp(d2, 1, q.data(), &b, nullptr, nullptr, nullptr) == 0);
+      const double rel = std::fabs(a - b) / std::fmax(std::fabs(b), 1e-300);
+      if (rel > worst) worst = rel;
+      if (rel > 1e-12) printf("dD(2) vs 2D class: q = (%.17g, %.17g): %.17g vs %.17g\n", q[0], q[1], a, b);
+      compared++;
+    }
+    printf("N=2: dD class vs 2D class on %d queries over 400 random points: max rel diff %.3g\n", compared, worst);
+    dli_di2_destroy(d2);
+    CHECK(compared > 1500 && worst <= 1e-12);
   }
   CHECK(sse2 < sse1);
   // outside the hull: quiet NaN, no exception (:1005-1008)
