@@ -2153,7 +2153,28 @@ extern "C" int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root) {
 // (length-prefixed).  The same bytes the replication path broadcasts; a loaded mesh is a replica
 // (no host copy of the connectivity: dli_mesh_get_simplices / the error evaluator are unavailable).
 // ---------------------------------------------------------------------------------------------
-static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '2'};
+static const char kSnapMagic[8] = {'D', 'L', 'I', 'M', 'E', 'S', 'H', '3'};
+
+// 64-bit checksum of a buffer as stored in the file (four interleaved FNV-1a lanes over 8-byte words, folded, then the
+// tail bytes): the canonical records, the hint grid and the hull table are range-checked on the device after a load
+// (k_validate_ids), but the DERIVED buffers -- walk records in six encodings, packed faces, slot tables -- carry
+// neighbour ids the fast pass follows first and are not decoded again; the checksum is what keeps a damaged file from
+// becoming out-of-range device reads.  It detects damage, not forgery.
+static uint64_t snap_checksum(const void *data, size_t bytes) {
+  const unsigned char *p = static_cast<const unsigned char *>(data);
+  uint64_t h[4] = {0xcbf29ce484222325ull, 0x84222325cbf29ce4ull, 0x9e3779b97f4a7c15ull, 0xc2b2ae3d27d4eb4full};
+  size_t i = 0;
+  for (; i + 32 <= bytes; i += 32)
+    for (int k = 0; k < 4; k++) {
+      uint64_t w;
+      memcpy(&w, p + i + 8 * k, 8);
+      h[k] = (h[k] ^ w) * 0x100000001b3ull;
+    }
+  uint64_t r = bytes;
+  for (int k = 0; k < 4; k++) r = (r ^ h[k]) * 0x100000001b3ull + (r >> 29);
+  for (; i < bytes; i++) r = (r ^ p[i]) * 0x100000001b3ull;
+  return r;
+}
 
 extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
   DLI_GUARD_BEGIN
@@ -2178,6 +2199,8 @@ extern "C" int dli_mesh_save(const dli_mesh *m, const char *path) {
     host.resize((size_t)b);
     rc = dli_mesh_buffer_read(m, i, host.data());
     if (rc == DLI_OK) ok = fwrite(host.data(), 1, (size_t)b, fp) == (size_t)b;
+    const uint64_t sum = snap_checksum(host.data(), (size_t)b);
+    if (rc == DLI_OK && ok) ok = fwrite(&sum, sizeof sum, 1, fp) == 1;
   }
   if (fclose(fp) != 0) ok = false;
   if (rc != DLI_OK) return rc;
@@ -2212,11 +2235,13 @@ extern "C" int dli_mesh_load(const char *path, const dli_options *opt, dli_mesh 
     if (fread(&b, sizeof b, 1, fp) != 1 || b != want) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: truncated or inconsistent snapshot"); break; }
     if (b == 0) continue;
     host.resize((size_t)b);
-    if (fread(host.data(), 1, (size_t)b, fp) != (size_t)b) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: truncated snapshot"); break; }
+    uint64_t sum = 0;
+    if (fread(host.data(), 1, (size_t)b, fp) != (size_t)b || fread(&sum, sizeof sum, 1, fp) != 1) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: truncated snapshot"); break; }
+    if (sum != snap_checksum(host.data(), (size_t)b)) { rc = fail(DLI_ERR_ARG, "dli_mesh_load: checksum mismatch (damaged snapshot)"); break; }
     rc = dli_mesh_buffer_write(m, i, host.data());
   }
   fclose(fp);
-  if (rc == DLI_OK && m->ns > 0) {   // a damaged file must not become out-of-range device reads: check every index once
+  if (rc == DLI_OK && m->ns > 0) {   // second line of defence behind the checksums: canonical records, hints and hull table in range
     DeviceGuard guard(m->device);
     unsigned int *d_bad = reinterpret_cast<unsigned int *>(m->d_stats + ST_WORDS - 1);
     unsigned int bad = 0;

@@ -1605,8 +1605,9 @@ __global__ void k_error_finish(int64_t n, const int32_t *__restrict__ item_verts
 }
 
 // ---------------------------------------------------------------------------------------------
-// Snapshot validation (dli_mesh_load): every index of the canonical records and of the hint grid in range.  The walk
-// records are derived data; their neighbour fields are checked against the same limits where they are absolute ids.
+// Snapshot validation (dli_mesh_load): every index of the canonical records, of the hint grid and of the hull table in
+// range.  The derived buffers (walk records, packed faces, slot tables) are NOT decoded here; the per-buffer checksums
+// of the snapshot file (snap_checksum in dli_capi.cu) are what protects them against a damaged file.
 // ---------------------------------------------------------------------------------------------
 __global__ void k_validate_ids(long long ns, long long nv, long long nh, int dim, int ss, const int32_t *__restrict__ srec,
                                long long cells, const int32_t *__restrict__ hint, const int4 *__restrict__ hull,

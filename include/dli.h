@@ -283,8 +283,10 @@ int dli_mesh_replicate(dli_mesh **inout, void *nccl_comm, int root);
 
 /*
  * Mesh snapshot (no counterpart in the reference, which has no serialisation): the flattened device mesh as one
- * flat file -- magic "DLIMESH2", the 16 header words, the grid parameters, then every device buffer
- * length-prefixed -- so that a large triangulation is built and flattened once.  A loaded mesh is a replica:
+ * flat file -- magic "DLIMESH3", the 16 header words, the grid parameters, then every device buffer
+ * length-prefixed and followed by a 64-bit checksum -- so that a large triangulation is built and flattened once.
+ * dli_mesh_load rejects a file whose checksums do not match (damage anywhere, derived walk records included) and
+ * range-checks the canonical records, hints and hull table on the device.  A loaded mesh is a replica:
  * interp / locate / gradient work, dli_mesh_get_simplices and the error evaluator need the creating process.
  */
 int dli_mesh_save(const dli_mesh *mesh, const char *path);

@@ -52,6 +52,15 @@ def test_load_rejects_garbage(gpu, tmp_path):
     (tmp_path / "trunc.dli").write_bytes(data[: len(data) // 2])
     with pytest.raises(dl.DliError):
         dl.Mesh.load(tmp_path / "trunc.dli")
+    # damage inside the DERIVED buffers (walk records: the neighbour ids the fast pass follows first) is caught
+    # by the per-buffer checksums -- flip one byte at a few places across the file, every copy must be refused
+    assert dl.Mesh.load(good).n_simplices == m.n_simplices
+    for frac in (0.3, 0.55, 0.75, 0.9, 0.98):
+        bad = bytearray(data)
+        bad[int(len(bad) * frac)] ^= 0x40
+        (tmp_path / "flip.dli").write_bytes(bytes(bad))
+        with pytest.raises(dl.DliError):
+            dl.Mesh.load(tmp_path / "flip.dli")
 
 
 @pytest.mark.parametrize("opts", [{"outside_nan": 1}, {"epilogue": "closed_form"}, {"outside_nan": 1, "epilogue": "reference"},
