@@ -666,7 +666,8 @@ def compact_line(line):
     out["config"] = {"workload": c["workload"], "queries_per_gpu": c["queries_per_gpu"], "mesh_vertices": c["mesh_vertices"],
                      "mesh_simplices": c["mesh_simplices"], "mesh_device_MB": _r(c["mesh_device_MB"]), "l2_policy": "inputs>L2",
                      "parallelism": "replicated mesh, query shards, no collective", "mesh_build_s": _r(c["mesh_build_s"]),
-                     "mesh_replicate_s": _r(c["mesh_replicate_s"]), "checksum": c["checksum"]}
+                     "comm_init_s": _r(c.get("comm_init_s")), "mesh_replicate_s": _r(c["mesh_replicate_s"]),
+                     "mesh_replicate_GBps": _r(c.get("mesh_replicate_GBps")), "checksum": c["checksum"]}
     e = line["e2e"]
     rb = e.get("raw_copy_bound") or {}
     out["e2e"] = {"value": e["value"], "unit": e["unit"], "h2d_bytes_per_step": e["h2d_bytes_per_step"],
@@ -711,9 +712,20 @@ def run_ours(args, rank, world, local_rank):
     else:
         mesh = None
     t_build = time.perf_counter() - t0
+    # the raw NCCL communicator dli_mesh_replicate takes is created once per process (0.2 - 0.6 s, grows with N) and
+    # timed on its own: mesh_replicate_s is then the broadcast of the mesh alone
+    t0 = time.perf_counter()
+    if world > 1:
+        try:
+            parallel.cached_nccl_communicator()
+        except Exception:  # noqa: BLE001  (no NCCL library: replicate_mesh falls back to torch broadcasts on every rank)
+            pass
+        torch.cuda.synchronize(dev)
+    t_comm = time.perf_counter() - t0
     t0 = time.perf_counter()
     if world > 1:
         mesh = parallel.replicate_mesh(mesh, src=0, device=dev)
+        torch.cuda.synchronize(dev)
     t_repl = time.perf_counter() - t0
 
     # ---- queries: device-resident (value) and pinned host copies (e2e)
@@ -843,7 +855,9 @@ def run_ours(args, rank, world, local_rank):
                        "mesh_simplices": mesh_n_simplices, "mesh_device_MB": mesh_device_bytes / 1e6,
                        "l2_policy": "inputs larger than L2 (1.6 GB of queries + 0.8 GB of results streamed per step)",
                        "epilogue": "auto: affine form f0 + g.(p - p0) on 64-byte walk records where its a-priori error bound is <= 1e-13 relative, reference operation order on the other faces and in the exact pass", "parallelism": "replicated mesh, query shards, no collective",
-                       "mesh_build_s": t_build, "mesh_replicate_s": t_repl, "checksum": checksum,
+                       "mesh_build_s": t_build, "comm_init_s": t_comm, "mesh_replicate_s": t_repl,
+                       "mesh_replicate_GBps": (mesh_device_bytes / 1e9 / t_repl) if (world > 1 and t_repl > 0) else None,
+                       "checksum": checksum,
                        "host_numa_binding": numa},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": nq * 16, "d2h_bytes_per_step": nq * 8,
