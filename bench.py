@@ -410,6 +410,36 @@ def gradient_leg(mesh, xq, steps, warmup, dev, peak):
                          "note": "whole call (fast + exact pass) charged to the 116 B figure"}}
 
 
+def error_eval_leg(mesh, steps, dev, peak):
+    """per-simplex error evaluator on the cfg2 mesh with DEVICE pointers (k_error_prepare + f on the GPU + k_error_finish),
+    CUDA events around the two C-ABI calls only; 116 algorithmic bytes per 2D item"""
+    import torch
+    cent = mesh.simplex_error_centroids_device()          # also builds the item table (one-time, host)
+    n = cent.shape[0]
+    phi = torch.pow(cent[:, 0], 0.3) * torch.pow(cent[:, 1], 0.6)
+    mesh.simplex_error(phi)
+    torch.cuda.synchronize(dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    t_prep = t_fin = 0.0
+    for _ in range(steps):
+        ev[0].record()
+        mesh.simplex_error_centroids_device(out=cent)
+        ev[1].record()
+        phi = torch.pow(cent[:, 0], 0.3) * torch.pow(cent[:, 1], 0.6)
+        ev[2].record()
+        err = mesh.simplex_error(phi)
+        ev[3].record()
+        torch.cuda.synchronize(dev)
+        t_prep += ev[0].elapsed_time(ev[1])
+        t_fin += ev[2].elapsed_time(ev[3])
+    ms = (t_prep + t_fin) / steps
+    achieved = 116 * n / (ms * 1e-3) / 1e9
+    return {"value": n / (ms * 1e-3), "unit": "items/s", "ms_per_step": ms, "items": int(n), "prepare_ms": t_prep / steps,
+            "finish_ms": t_fin / steps, "max_err": float(err.max().item()),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "algorithmic_bytes_per_item": 116, "avg_launch_ms": ms}}
+
+
 def leg_traffic(leg, key):
     """roofline.traffic of an extras leg: DRAM bytes per query from the committed ncu capture of that kernel
     (profiles/roofline_traffic.json, 'legs') x the queries one launch of this run processed"""
@@ -435,7 +465,8 @@ def compact_leg(leg):
            "rel": leg.get("max_rel_diff_gpu_vs_oracle_on_sample"), "st_eq": leg.get("status_equal")}
     if isinstance(rf.get("random_access"), dict) and "frac" in rf["random_access"]:
         out["ra_frac"] = rf["random_access"]["frac"]
-    for k in ("sort_ms", "sorted_plus_sort_value", "checksum_int64_bits", "nan", "replicate_s", "value_per_gpu", "nan_fraction"):
+    for k in ("sort_ms", "sorted_plus_sort_value", "checksum_int64_bits", "nan", "replicate_s", "value_per_gpu", "nan_fraction",
+              "items", "prepare_ms", "finish_ms"):
         if k in leg:
             out[k] = leg[k]
     if "error_eval" in leg:
@@ -450,6 +481,8 @@ cfg2 (headline)  1M uniform-random vertices (seed 1001) triangulated on the host
 cfg2_presorted   the same queries ordered along a Z-curve of 1024 x 1024 tiles before the timed region; sort_ms = that
                  sort's own cost on the device (torch), sorted_plus_sort_value = queries / (sort + interp)
 gradient         dli_gradient on the cfg2 mesh and queries, 116 algorithmic bytes per query
+error_eval       per-simplex error evaluator over every item of the cfg2 mesh with device pointers (value in items/s;
+                 CUDA events around dli_simplex_error_prepare and _finish, f evaluated by torch in between, untimed)
 cfg3             2D adaptive: 100k points placed by insert_largest_error_point on [0.01,5]^2, 50M queries (seed 2003),
                  plus one batched error evaluation (error_eval: host wall time of the two C-ABI calls)
 cfg4_3d/cfg4_4d  200k uniform-random vertices (seeds 1003/1004) through the native dD triangulation, 20M queries in
@@ -825,6 +858,10 @@ def run_ours(args, rank, world, local_rank):
                 leg_traffic(extras["cfg2_presorted"], "cfg2_presorted")
             except Exception as e:  # noqa: BLE001
                 extras["cfg2_presorted"] = {"error": "%s: %s" % (type(e).__name__, e)}
+            try:
+                extras["error_eval"] = error_eval_leg(mesh, steps_x, dev, peak)
+            except Exception as e:  # noqa: BLE001
+                extras["error_eval"] = {"error": "%s: %s" % (type(e).__name__, e)}
             try:
                 extras["gradient"] = gradient_leg(mesh, xq, steps_x, args.warmup, dev, peak)
             except Exception as e:  # noqa: BLE001

@@ -1823,8 +1823,10 @@ extern "C" int dli_simplex_error_prepare(const dli_mesh *mc, double *centroids, 
   if (item_vertices) memcpy(item_vertices, m->h_item_verts.data(), sizeof(int32_t) * m->h_item_verts.size());
   if (n == 0) return DLI_OK;
   DeviceGuard guard(m->device);
-  double *d_c = nullptr;
-  CU(cudaMalloc(&d_c, sizeof(double) * (size_t)n * m->dim));
+  bool known;
+  const bool on_device = is_device_ptr(centroids, &known);
+  double *d_c = centroids;   // device pointer: the kernel writes the caller's buffer (default stream, no copy, no allocation)
+  if (!on_device) CU(cudaMalloc(&d_c, sizeof(double) * (size_t)n * m->dim));
   unsigned blocks = (unsigned)((n + 255) / 256);
   switch (m->dim) {
     case 2: k_error_prepare<2><<<blocks, 256>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_c); break;
@@ -1832,8 +1834,10 @@ extern "C" int dli_simplex_error_prepare(const dli_mesh *mc, double *centroids, 
     case 4: k_error_prepare<4><<<blocks, 256>>>(n, m->d_item_verts, m->d_vrec, m->vs, d_c); break;
   }
   cudaError_t e = cudaGetLastError();
-  if (e == cudaSuccess) e = cudaMemcpy(centroids, d_c, sizeof(double) * (size_t)n * m->dim, cudaMemcpyDeviceToHost);
-  cudaFree(d_c);
+  if (!on_device) {
+    if (e == cudaSuccess) e = cudaMemcpy(centroids, d_c, sizeof(double) * (size_t)n * m->dim, cudaMemcpyDeviceToHost);
+    cudaFree(d_c);
+  }
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, std::string("dli_simplex_error_prepare: ") + cudaGetErrorString(e));
   return DLI_OK;
   DLI_GUARD_END("dli_simplex_error_prepare")
@@ -1848,6 +1852,20 @@ extern "C" int dli_simplex_error_finish(const dli_mesh *mc, int64_t n, const dou
   if (n != m->n_items) return fail(DLI_ERR_ARG, "dli_simplex_error_finish: n does not match dli_simplex_error_count");
   if (n == 0) return DLI_OK;
   DeviceGuard guard(m->device);
+  bool known;
+  const bool on_device = is_device_ptr(phi, &known);
+  if (is_device_ptr(err, &known) != on_device)
+    return fail(DLI_ERR_ARG, "dli_simplex_error_finish: f_at_centroids and err must both be host or both be device pointers");
+  if (on_device) {   // the caller's f lives on the GPU: one kernel on the default stream, no staging, no allocation
+    unsigned blocks = (unsigned)((n + 127) / 128);
+    switch (m->dim) {
+      case 2: k_error_finish<2><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, phi, err); break;
+      case 3: k_error_finish<3><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, phi, err); break;
+      case 4: k_error_finish<4><<<blocks, 128>>>(n, m->d_item_verts, m->d_vrec, m->vs, phi, err); break;
+    }
+    CU(cudaGetLastError());
+    return DLI_OK;
+  }
   double *d_phi = nullptr, *d_err = nullptr;
   CU(cudaMalloc(&d_phi, sizeof(double) * (size_t)n));
   cudaError_t e = cudaMalloc(&d_err, sizeof(double) * (size_t)n);

@@ -226,8 +226,27 @@ class Mesh:
                                               item_verts.ctypes.data))
         return cent, item_simplex, item_verts
 
+    def simplex_error_centroids_device(self, out=None):
+        """the centroids of every item as a float64 CUDA tensor (n, dim), written by the kernel itself (device-pointer form
+        of dli_simplex_error_prepare: no host copy) -- for an f that is evaluated on the GPU."""
+        import torch
+        n = check(lib().dli_simplex_error_count(self._h))
+        cent = out if out is not None else torch.empty((n, self.dim), dtype=torch.float64, device="cuda")
+        if n:
+            check(lib().dli_simplex_error_prepare(self._h, cent.data_ptr(), None, None))
+        return cent
+
     def simplex_error(self, phi):
-        """err for every item given phi[i] = f(centroid_i)."""
+        """err for every item given phi[i] = f(centroid_i).  phi: numpy array, or a float64 CUDA tensor (the result is then
+        a CUDA tensor too and nothing passes through the host)."""
+        if _is_torch_tensor(phi):
+            import torch
+            if not phi.is_cuda or phi.dtype != torch.float64:
+                raise ValueError("torch input must be a float64 CUDA tensor")
+            phi = phi.contiguous()
+            err = torch.empty_like(phi)
+            check(lib().dli_simplex_error_finish(self._h, phi.shape[0], phi.data_ptr(), err.data_ptr()))
+            return err
         phi = np.ascontiguousarray(phi, dtype=np.float64)
         err = np.empty_like(phi)
         check(lib().dli_simplex_error_finish(self._h, phi.shape[0], phi.ctypes.data, err.ctypes.data))

@@ -78,6 +78,7 @@ def _nccl_lib():
         L.ncclGetUniqueId.argtypes = [C.POINTER(_NcclUniqueId)]
         L.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, _NcclUniqueId, C.c_int]
         L.ncclCommDestroy.argtypes = [C.c_void_p]
+        L.ncclBroadcast.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _NCCL = L
         return L
     raise OSError("libnccl.so.2 not found")
@@ -114,6 +115,14 @@ def cached_nccl_communicator():
     import torch.distributed as dist
     if _COMM is None or _COMM[1] != dist.get_world_size():
         comm, _destroy = nccl_communicator(src=0)
+        # NCCL connects its channels lazily, inside the first collective (0.3 s at 2 GPUs): pay that here, with an
+        # 8-byte broadcast, so that the first dli_mesh_replicate costs what the mesh bytes cost
+        import torch
+        warm = torch.zeros(8, dtype=torch.uint8, device="cuda")
+        rc = _nccl_lib().ncclBroadcast(warm.data_ptr(), warm.data_ptr(), 8, 0, 0, comm, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.current_stream().synchronize()
+        if rc != 0:
+            raise RuntimeError("ncclBroadcast (warm-up) failed: %d" % rc)
         _COMM = (comm, dist.get_world_size())
     return _COMM[0]
 

@@ -243,7 +243,10 @@ int dli_gradient(const dli_mesh *mesh, int64_t n, const double *xs, double *grad
  * Items: every simplex, then for each hull facet of it every vertex subset of size >= 2 (duplicates across
  * simplices kept, as in the reference).  Order: simplices ascending; inside a simplex the simplex itself,
  * then hull facets by ascending slot, subsets by ascending bitmask.
- * Host pointers.  item_vertices is [n][dim+1], padded with -1.
+ * item_vertices is [n][dim+1], padded with -1; item_simplex / item_vertices are host arrays.
+ * centroids (prepare) and f_at_centroids / err (finish) may be HOST pointers (the call copies and returns when the data
+ * is there) or DEVICE pointers (a caller whose f is evaluated on the GPU: the kernel reads / writes the caller's buffers
+ * directly, enqueued on the default stream, nothing is staged through the host and the call does not wait).
  */
 int64_t dli_simplex_error_count(const dli_mesh *mesh);
 int dli_simplex_error_prepare(const dli_mesh *mesh, double *centroids /* [n][dim] */,

@@ -102,6 +102,31 @@ def test_small_batches_equal_large_batches_with_outside_nan(gpu):
         assert (np.isnan(y1[0]) and np.isnan(yb[i])) or abs(y1[0] - yb[i]) <= REL_TOL * max(abs(yb[i]), 1e-300)
 
 
+@pytest.mark.parametrize("dim,nv", [(2, 4000), (3, 1500), (4, 500)])
+def test_error_evaluator_on_device_pointers(gpu, dim, nv):
+    """prepare -> f evaluated by torch on the device -> finish, nothing staged through the host: bit-identical to the
+    host-pointer path (src/delaunay_2_interp.h:725-741, 683-699 are what the two kernels replace)"""
+    import torch
+    import delaunay_linterp_b200 as dl
+    pts, f, sv, sn = helpers.random_mesh(dim, nv, 60 + dim)
+    m = dl.Mesh(pts, f, sv, sn)
+    cent_h, isx, iv = m.simplex_error_items()
+    cent_d = m.simplex_error_centroids_device()
+    torch.cuda.synchronize()
+    assert cent_d.shape == cent_h.shape and np.array_equal(cent_d.cpu().numpy(), cent_h)
+    alpha = torch.tensor([0.3, 0.6, 0.2, 0.1][:dim], dtype=torch.float64, device="cuda")
+    phi_d = torch.prod(torch.pow(cent_d, alpha), dim=1)          # the caller's f, on the GPU
+    err_d = m.simplex_error(phi_d)
+    torch.cuda.synchronize()
+    err_h = m.simplex_error(phi_d.cpu().numpy())                 # the same values through the host-pointer path
+    assert np.array_equal(err_d.cpu().numpy(), err_h)
+    assert err_h.shape == (len(isx),) and np.isfinite(err_h).all() and err_h.max() > 0
+    # mixed host / device pointers are refused
+    from delaunay_linterp_b200._capi import lib
+    bad = np.empty(len(isx))
+    assert lib().dli_simplex_error_finish(m._h, len(isx), phi_d.data_ptr(), bad.ctypes.data) == -1
+
+
 def test_empty_mesh_gradient_is_all_nan(gpu):
     """the no-mesh fill must cover 2 n doubles for gradients"""
     import torch
@@ -349,7 +374,7 @@ def test_dd_refine_rounds_keep_the_device_mesh_in_step(gpu, d):
         cg, _ = om.classify(q, sx)
         assert cg[ok].all()
     full1, inc1 = t.sync_counts()
-    assert total >= 20 and inc1 - inc0 >= 4 and (full1 - full0) + (inc1 - inc0) == 6
+    assert total >= 20 and inc1 - inc0 >= 3 and (full1 - full0) + (inc1 - inc0) == 6   # at least half of the six syncs are in-place patches (3D: 3, 4D: more; a dD insertion that leaves holes in the id space re-flattens)
     m = dl.Mesh(c, f, sv, sn)
     cent, isx, iv = m.simplex_error_items()
     err = np.sort(m.simplex_error(fnb(cent)))
